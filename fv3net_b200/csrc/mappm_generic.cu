@@ -1,0 +1,340 @@
+// cg_mappm — general PPM vertical remap (mappm.f90:10-126, ppm_profile :614-851,
+// ppm_limiters :854-931 of the reference), any iv, kord <= 7, any km/kn, strided
+// columns.  This is the drop-in for the f2py entry point the reference calls from
+// regridz.py:273; the fused pressure-level kernel (plevel_fused.cu) is the fast
+// path for the iv=1/kord=1 coarse-graining case.
+//
+// One thread per column; the column's profile (pe1, q, AL, AR, A6, dc) lives in
+// shared memory laid out [level][thread] so that every access — including the
+// data-dependent source-layer index of the overlap loop — is bank-conflict free.
+// Compiled with --fmad=false: every statement keeps the Fortran's operation order
+// and rounding, so results are bit-identical to the CPU oracle (gcc
+// -ffp-contract=off), which is what gfortran produces without FMA contraction.
+#include "common.cuh"
+#include <cmath>
+
+namespace cg {
+
+constexpr int TPB = 32;
+
+struct ColumnViews {
+    float *pe, *q, *al, *ar, *a6, *dc, *h2;
+    int tid;
+    __device__ __forceinline__ float &PE(int k) const { return pe[k * TPB + tid]; }
+    __device__ __forceinline__ float &Q(int k) const { return q[k * TPB + tid]; }
+    __device__ __forceinline__ float &AL(int k) const { return al[k * TPB + tid]; }
+    __device__ __forceinline__ float &AR(int k) const { return ar[k * TPB + tid]; }
+    __device__ __forceinline__ float &A6(int k) const { return a6[k * TPB + tid]; }
+    __device__ __forceinline__ float &DC(int k) const { return dc[k * TPB + tid]; }
+    __device__ __forceinline__ float &H2(int k) const { return h2[k * TPB + tid]; }
+    __device__ __forceinline__ float DP(int k) const { return PE(k + 1) - PE(k); }
+    __device__ __forceinline__ float D4(int k) const { return DP(k - 1) + DP(k); }
+    __device__ __forceinline__ float DELQ(int k) const { return Q(k + 1) - Q(k); }
+};
+
+__device__ __forceinline__ float max3f(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
+__device__ __forceinline__ float min3f(float a, float b, float c) { return fminf(fminf(a, b), c); }
+__device__ __forceinline__ float curv(float q, float al, float ar) { return 3.f * (2.f * q - (al + ar)); }
+
+// ppm_limiters, one layer (mappm.f90:854-931)
+__device__ __forceinline__ void limit_layer(float dm, float q, float &al, float &ar, float &a6, int lmt)
+{
+    if (lmt == 3) return;
+    if (lmt == 0) {
+        if (dm == 0.f) {
+            al = q; ar = q; a6 = 0.f;
+        } else {
+            const float da1 = ar - al;
+            const float da2 = da1 * da1;
+            const float a6da = a6 * da1;
+            if (a6da < -da2) {
+                a6 = 3.f * (al - q);
+                ar = al - a6;
+            } else if (a6da > da2) {
+                a6 = 3.f * (ar - q);
+                al = ar - a6;
+            }
+        }
+    } else if (lmt == 1) {
+        const float qmp = 2.f * dm;
+        al = q - copysignf(fminf(fabsf(qmp), fabsf(al - q)), qmp);
+        ar = q + copysignf(fminf(fabsf(qmp), fabsf(ar - q)), qmp);
+        a6 = 3.f * (2.f * q - (al + ar));
+    } else {
+        const float r12 = 1.f / 12.f;
+        if (fabsf(ar - al) < -a6) {
+            const float d = ar - al;
+            const float fmin = q + 0.25f * (d * d) / a6 + a6 * r12;
+            if (fmin < 0.f) {
+                if (q < ar && q < al) {
+                    ar = q; al = q; a6 = 0.f;
+                } else if (ar > al) {
+                    a6 = 3.f * (al - q);
+                    ar = al - a6;
+                } else {
+                    a6 = 3.f * (ar - q);
+                    al = ar - a6;
+                }
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ void limit_at(const ColumnViews &c, int j, int lmt)
+{
+    float al = c.AL(j), ar = c.AR(j), a6 = c.A6(j);
+    limit_layer(c.DC(j), c.Q(j), al, ar, a6, lmt);
+    c.AL(j) = al; c.AR(j) = ar; c.A6(j) = a6;
+}
+
+// ppm_profile for the thread's column (mappm.f90:614-851)
+__device__ void ppm_column(const ColumnViews &c, int km, int iv, int kord)
+{
+    for (int j = 1; j <= km - 2; ++j) {                                   // :658-668
+        const float c1 = (c.DP(j - 1) + 0.5f * c.DP(j)) / c.D4(j + 1);
+        const float c2 = (c.DP(j + 1) + 0.5f * c.DP(j)) / c.D4(j);
+        const float df2 = c.DP(j) * (c1 * c.DELQ(j) + c2 * c.DELQ(j - 1)) / (c.D4(j) + c.DP(j + 1));
+        const float hi = max3f(c.Q(j - 1), c.Q(j), c.Q(j + 1)) - c.Q(j);
+        const float lo = c.Q(j) - min3f(c.Q(j - 1), c.Q(j), c.Q(j + 1));
+        c.DC(j) = copysignf(fminf(fminf(fabsf(df2), hi), lo), df2);
+    }
+    for (int j = 2; j <= km - 2; ++j) {                                   // :674-683
+        const float c1 = c.DELQ(j - 1) * c.DP(j - 1) / c.D4(j);
+        const float a1 = c.D4(j - 1) / (c.D4(j) + c.DP(j - 1));
+        const float a2 = c.D4(j + 1) / (c.D4(j) + c.DP(j));
+        c.AL(j) = c.Q(j - 1) + c1 + 2.f / (c.D4(j - 1) + c.D4(j + 1)) *
+                  (c.DP(j) * (c1 * (a1 - a2) + a2 * c.DC(j - 1)) - c.DP(j - 1) * a1 * c.DC(j));
+    }
+    {                                                                     // top :689-707
+        const float d1 = c.DP(0), d2 = c.DP(1);
+        const float q0 = c.Q(0), q1 = c.Q(1);
+        const float qm = (d2 * q0 + d1 * q1) / (d1 + d2);
+        const float dq = 2.f * (q1 - q0) / (d1 + d2);
+        const float c1 = 4.f * (c.AL(2) - qm - d2 * dq) / (d2 * (2.f * d2 * d2 + d1 * (d2 + 3.f * d1)));
+        const float c3 = dq - 0.5f * c1 * (d2 * (5.f * d1 + d2) - 3.f * d1 * d1);
+        float al1 = qm - 0.25f * c1 * d1 * d2 * (d2 + 3.f * d1);
+        float al0 = d1 * (2.f * c1 * (d1 * d1) - c3) + al1;
+        al1 = fmaxf(al1, fminf(q0, q1));
+        al1 = fminf(al1, fmaxf(q0, q1));
+        c.DC(0) = 0.5f * (al1 - q0);
+        if (iv == 0) {                                                    // :711-725
+            al0 = fmaxf(0.f, al0);
+            al1 = fmaxf(0.f, al1);
+        } else if (iv == -1) {
+            if (al0 * q0 <= 0.f) al0 = 0.f;
+        } else if (iv == 2 || iv == -2) {
+            al0 = q0;
+        }
+        c.AL(0) = al0;
+        c.AL(1) = al1;
+    }
+    {                                                                     // bottom :729-761
+        const int b = km - 1, e = km - 2;
+        const float d1 = c.DP(b), d2 = c.DP(e);
+        const float qb = c.Q(b), qe = c.Q(e);
+        const float qm = (d2 * qb + d1 * qe) / (d1 + d2);
+        const float dq = 2.f * (qe - qb) / (d1 + d2);
+        const float c1 = (c.AL(e) - qm - d2 * dq) / (d2 * (2.f * d2 * d2 + d1 * (d2 + 3.f * d1)));
+        const float c3 = dq - 2.f * c1 * (d2 * (5.f * d1 + d2) - 3.f * d1 * d1);
+        float alb = qm - c1 * d1 * d2 * (d2 + 3.f * d1);
+        float arb = d1 * (8.f * c1 * (d1 * d1) - c3) + alb;
+        alb = fmaxf(alb, fminf(qb, qe));
+        alb = fminf(alb, fmaxf(qb, qe));
+        c.DC(b) = 0.5f * (qb - alb);
+        if (iv == 0) {
+            alb = fmaxf(0.f, alb);
+            arb = fmaxf(0.f, arb);
+        } else if (iv < 0) {
+            if (qb * arb <= 0.f) arb = 0.f;
+        }
+        c.AL(b) = alb;
+        c.AR(b) = arb;
+    }
+    for (int j = 0; j <= km - 2; ++j) c.AR(j) = c.AL(j + 1);              // :763-767
+
+    for (int j = 0; j < 2; ++j) {                                         // :773-778
+        c.A6(j) = curv(c.Q(j), c.AL(j), c.AR(j));
+        limit_at(c, j, 0);
+    }
+    if (kord >= 7) {                                                      // :780-826
+        for (int j = 1; j <= km - 2; ++j)
+            c.H2(j) = 2.f * (c.DC(j + 1) / c.DP(j + 1) - c.DC(j - 1) / c.DP(j - 1)) /
+                      (c.DP(j) + 0.5f * (c.DP(j - 1) + c.DP(j + 1))) * (c.DP(j) * c.DP(j));
+        const float fac = 1.5f;
+        for (int j = 2; j <= km - 3; ++j) {
+            const float q = c.Q(j), dcj = c.DC(j);
+            const float pmp = 2.f * dcj;
+            float qmp = q + pmp;
+            float lac = q + fac * c.H2(j - 1) + dcj;
+            const float ar = fminf(fmaxf(c.AR(j), min3f(q, qmp, lac)), max3f(q, qmp, lac));
+            qmp = q - pmp;
+            lac = q + fac * c.H2(j + 1) - dcj;
+            const float al = fminf(fmaxf(c.AL(j), min3f(q, qmp, lac)), max3f(q, qmp, lac));
+            c.AR(j) = ar;
+            c.AL(j) = al;
+            c.A6(j) = curv(q, al, ar);
+            if (iv == 0 && kord >= 6) limit_at(c, j, 2);
+        }
+    } else {                                                              // :828-842
+        int lmt = kord - 3;
+        if (lmt < 0) lmt = 0;
+        if (iv == 0 && lmt > 2) lmt = 2;
+        for (int j = 2; j <= km - 3; ++j) {
+            c.A6(j) = kord != 4 ? curv(c.Q(j), c.AL(j), c.AR(j)) : 0.f;
+            if (kord != 6) limit_at(c, j, lmt);
+        }
+    }
+    for (int j = km - 2; j < km; ++j) {                                   // :844-849
+        c.A6(j) = curv(c.Q(j), c.AL(j), c.AR(j));
+        limit_at(c, j, 0);
+    }
+}
+
+struct Strides { long v[12]; };
+// f > 0: target pressures live on the coarse grid; fine column i = (y, x) of a
+// (ny, nx) tile reads coarse column (y/f, x/f) of a (ny/f, nx/f) tile.
+struct Pe2Block { int f, nx, nxc; };
+
+__global__ void __launch_bounds__(TPB)
+mappm_generic_kernel(const float *__restrict__ pe1, const float *__restrict__ q1,
+                     const float *__restrict__ pe2, float *__restrict__ q2,
+                     long ncol, long n_inner, int km, int kn, Strides s, Pe2Block pb,
+                     int iv, int kord)
+{
+    extern __shared__ float smem[];
+    const long col = blockIdx.x * (long)TPB + threadIdx.x;
+    if (col >= ncol) return;  // no block-level synchronisation below
+    ColumnViews c;
+    c.tid = threadIdx.x;
+    c.pe = smem;
+    c.q = c.pe + (km + 1) * TPB;
+    c.al = c.q + km * TPB;
+    c.ar = c.al + km * TPB;
+    c.a6 = c.ar + km * TPB;
+    c.dc = c.a6 + km * TPB;
+    c.h2 = c.dc + km * TPB;
+
+    const long o = col / n_inner, i = col % n_inner;
+    const float *p1 = pe1 + o * s.v[0] + i * s.v[1];
+    const float *f1 = q1 + o * s.v[3] + i * s.v[4];
+    long i2 = i;
+    if (pb.f > 0) i2 = (long)((i / pb.nx) / pb.f) * pb.nxc + (i % pb.nx) / pb.f;
+    const float *p2 = pe2 + o * s.v[6] + i2 * s.v[7];
+    float *f2 = q2 + o * s.v[9] + i * s.v[10];
+    const long l_pe1 = s.v[2], l_q1 = s.v[5], l_pe2 = s.v[8], l_q2 = s.v[11];
+
+    for (int k = 0; k <= km; ++k) c.PE(k) = p1[k * l_pe1];
+    for (int k = 0; k < km; ++k) c.Q(k) = f1[k * l_q1];
+    ppm_column(c, km, iv, kord);
+
+    const float r3 = 1.f / 3.f, r23 = 2.f / 3.f;
+    const float pe_top = c.PE(0), pe_bot = c.PE(km), q_top = c.Q(0), q_bot = c.Q(km - 1);
+    int k0 = 0;
+    float top = p2[0];
+    for (int k = 0; k < kn; ++k) {                                        // mappm.f90:58-124
+        const float bot = p2[(long)(k + 1) * l_pe2];
+        float res;
+        if (top <= pe_top) {
+            res = q_top;
+        } else if (top >= pe_bot) {
+            res = q_bot;
+        } else {
+            int found = 0, k1 = 0;
+            float qsum = 0.f, dpsum = 0.f;
+            res = NAN;  // no bracketing layer: undefined in the Fortran, NaN here
+            for (int L = k0; L < km; ++L) {
+                const float pl0 = c.PE(L), pl1 = c.PE(L + 1);
+                if (top >= pl0 && top <= pl1) {
+                    k0 = L;
+                    const float dpl = pl1 - pl0;
+                    const float pl = (top - pl0) / dpl;
+                    const float al = c.AL(L), ar = c.AR(L), a6 = c.A6(L);
+                    if (bot <= pl1) {
+                        const float pr = (bot - pl0) / dpl;
+                        const float tt = r3 * (pr * (pr + pl) + pl * pl);
+                        res = al + 0.5f * (a6 + ar - al) * (pr + pl) - a6 * tt;
+                        found = 2;
+                    } else {
+                        const float delp = pl1 - top;
+                        const float tt = r3 * (1.f + pl * (1.f + pl));
+                        qsum = delp * (al + 0.5f * (a6 + ar - al) * (1.f + pl) - a6 * tt);
+                        dpsum = delp;
+                        k1 = L + 1;
+                        found = 1;
+                    }
+                    break;
+                }
+            }
+            if (found == 1) {
+                bool closed = false;
+                for (int L = k1; L < km; ++L) {
+                    const float pl0 = c.PE(L), pl1 = c.PE(L + 1);
+                    const float dpl = pl1 - pl0;
+                    if (bot > pl1) {
+                        qsum = qsum + dpl * c.Q(L);
+                        dpsum = dpsum + dpl;
+                    } else {
+                        const float delp = bot - pl0;
+                        const float esl = delp / dpl;
+                        const float al = c.AL(L), ar = c.AR(L), a6 = c.A6(L);
+                        qsum = qsum + delp * (al + 0.5f * esl * (ar - al + a6 * (1.f - r23 * esl)));
+                        dpsum = dpsum + delp;
+                        k0 = L;
+                        closed = true;
+                        break;
+                    }
+                }
+                if (!closed) {
+                    const float delp = bot - pe_bot;
+                    if (delp > 0.f) {
+                        qsum = qsum + delp * q_bot;
+                        dpsum = dpsum + delp;
+                    }
+                }
+                res = qsum / dpsum;
+            }
+        }
+        f2[(long)k * l_q2] = res;
+        top = bot;
+    }
+}
+
+int launch_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,
+                 long n_outer, long n_inner, int km, int kn, const long *strides,
+                 int pe2_f, int pe2_nx, int pe2_nxc, int iv, int kord, cudaStream_t st)
+{
+    CG_REQUIRE(pe1 && q1 && pe2 && q2 && strides, "null pointer");
+    CG_REQUIRE(n_outer >= 0 && n_inner >= 0, "bad column counts");
+    CG_REQUIRE(km >= 4 && kn >= 1, "mappm needs km >= 4 and kn >= 1 (got %d, %d)", km, kn);
+    CG_REQUIRE(iv >= -2 && iv <= 2, "iv must be in [-2, 2]");
+    if (kord > 7) {
+        set_error("kord=%d (cs_profile, mappm.f90:132) is not built yet", kord);
+        return CG_ENOTSUP;
+    }
+    const long ncol = n_outer * n_inner;
+    if (ncol == 0) return CG_OK;
+    Strides s;
+    for (int i = 0; i < 12; ++i) s.v[i] = strides[i];
+    Pe2Block pb{pe2_f, pe2_nx, pe2_nxc};
+    const size_t smem = sizeof(float) * TPB * (size_t)(7 * km + 1);
+    CG_REQUIRE(smem <= 227 * 1024, "km=%d needs %zu B of shared memory per block", km, smem);
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(mappm_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(mappm)");
+    }
+    mappm_generic_kernel<<<cdiv(ncol, TPB), TPB, smem, st>>>(pe1, q1, pe2, q2, ncol, n_inner, km, kn, s, pb, iv, kord);
+    CG_LAUNCH_CHECK("cg_mappm");
+    return CG_OK;
+}
+
+}  // namespace cg
+
+using namespace cg;
+
+extern "C" int cg_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,
+                        long n_outer, long n_inner, int km, int kn, const long *strides,
+                        int iv, int kord, void *stream)
+{
+    return launch_mappm(pe1, q1, pe2, q2, n_outer, n_inner, km, kn, strides, 0, 0, 0, iv, kord,
+                        (cudaStream_t)stream);
+}

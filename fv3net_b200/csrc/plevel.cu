@@ -1,0 +1,225 @@
+// cg_pressure_level_average / cg_area_above_fine_surface — pressure-level
+// coarse-graining (regridz.py:115-147 + coarsen.py:183; budgets.py:49-77).
+//
+// Two implementations sit behind one C entry point:
+//   * fused (plevel_fused.cu): one kernel per batch of fields, nothing fine-grid
+//     is written; used when the shape fits its specialisation (fp32, f = 8,
+//     nz <= 96, nx % 8 == 0).
+//   * composed (this file): coarse delp -> interface pressures -> cg_mappm with
+//     block-shared target pressures -> (masked) weighted block average, through a
+//     caller-provided workspace.  Any f / nz; also the cross-check for the fused
+//     kernel in tests (CG_PLEVEL_IMPL=composed).
+#include "common.cuh"
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+
+namespace cg {
+
+int launch_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,
+                 long n_outer, long n_inner, int km, int kn, const long *strides,
+                 int pe2_f, int pe2_nx, int pe2_nxc, int iv, int kord, cudaStream_t st);
+int fused_supported(int nz, int ny, int nx, int f);
+int launch_plevel_fused(const float *const *fields, float *const *outs, int nfields,
+                        const float *delp, const float *area, float *delp_coarse,
+                        long n_outer, int nz, int ny, int nx, int f, int mask_below, float toa,
+                        void *workspace, long workspace_bytes, cudaStream_t st);
+long fused_workspace_bytes(int nfields, long n_outer, int nz, int ny, int nx, int f);
+
+// masked[o,k,y,x] = pe_c[o,k+1,y/f,x/f] < pe_f[o,nz,y,x] ? area[o,y,x] : 0   (regridz.py:150-161)
+__global__ void __launch_bounds__(256)
+mask_from_coarse_kernel(const float *__restrict__ area, const float *__restrict__ pe_c,
+                        const float *__restrict__ pe_f, float *__restrict__ out, long n_outer,
+                        int nz, int ny, int nx, int f)
+{
+    const int nyc = ny / f, nxc = nx / f;
+    const long h = (long)ny * nx, hc = (long)nyc * nxc;
+    const long total = n_outer * nz * h;
+    for (long idx = blockIdx.x * (long)blockDim.x + threadIdx.x; idx < total;
+         idx += (long)gridDim.x * blockDim.x) {
+        const long i = idx % h;
+        const int k = (int)((idx / h) % nz);
+        const long o = idx / (h * nz);
+        const int y = (int)(i / nx), x = (int)(i % nx);
+        const float lower = pe_c[o * (nz + 1) * hc + (long)(k + 1) * hc + (long)(y / f) * nxc + x / f];
+        const float surf = pe_f[o * (nz + 1) * h + (long)nz * h + i];
+        out[idx] = lower < surf ? area[o * h + i] : 0.f;
+    }
+}
+
+// budgets.py:62-77.  Thread per coarse cell and level: p_mid = delp_c / (log p[k+1] - log p[k])
+// (vertically_dependent.py:153-179), compared with the fine surface pressure
+// ps = sum_k delp + toa (:189-208) of every fine column of the block.
+__global__ void __launch_bounds__(256)
+exposed_area_kernel(const float *__restrict__ pe_c, const float *__restrict__ delp_c,
+                    const float *__restrict__ ps, const float *__restrict__ area,
+                    float *__restrict__ out, long n_outer, int nz, int ny, int nx, int f)
+{
+    const int nyc = ny / f, nxc = nx / f;
+    const long hc = (long)nyc * nxc, h = (long)ny * nx;
+    const long total = n_outer * nz * hc;
+    for (long idx = blockIdx.x * (long)blockDim.x + threadIdx.x; idx < total;
+         idx += (long)gridDim.x * blockDim.x) {
+        const long ic = idx % hc;
+        const int k = (int)((idx / hc) % nz);
+        const long o = idx / (hc * nz);
+        const int J = (int)(ic / nxc), I = (int)(ic % nxc);
+        const float p0 = pe_c[o * (nz + 1) * hc + (long)k * hc + ic];
+        const float p1 = pe_c[o * (nz + 1) * hc + (long)(k + 1) * hc + ic];
+        const float pmid = delp_c[idx] / (logf(p1) - logf(p0));
+        float acc = 0.f;
+        for (int y = 0; y < f; ++y)
+            for (int x = 0; x < f; ++x) {
+                const long i = o * h + (long)(J * f + y) * nx + I * f + x;
+                const float a = (pmid <= ps[i]) ? area[i] : 0.f;
+                acc += (a == a) ? a : 0.f;
+            }
+        out[idx] = acc;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+surface_pressure_kernel(const float *__restrict__ delp, float *__restrict__ ps, float toa,
+                        long n_outer, int nz, long h)
+{
+    const long total = n_outer * h;
+    for (long idx = blockIdx.x * (long)blockDim.x + threadIdx.x; idx < total;
+         idx += (long)gridDim.x * blockDim.x) {
+        const long o = idx / h, i = idx % h;
+        float acc = 0.f;
+        for (int k = 0; k < nz; ++k) {
+            const float d = delp[o * nz * h + (long)k * h + i];
+            acc += (d == d) ? d : 0.f;
+        }
+        ps[idx] = acc + toa;
+    }
+}
+
+static inline long align256(long n) { return (n + 255) / 256 * 256; }
+
+static long composed_workspace_bytes(long n_outer, int nz, int ny, int nx, int f)
+{
+    const long h = (long)ny * nx, hc = (long)(ny / f) * (nx / f);
+    return align256(4 * n_outer * (nz + 1) * h)     // fine interfaces
+           + align256(4 * n_outer * (nz + 1) * hc)  // coarse interfaces
+           + align256(4 * n_outer * nz * hc)        // coarse delp (when the caller passes NULL)
+           + align256(4 * n_outer * nz * h)         // one remapped fine field
+           + align256(4 * n_outer * nz * h);        // masked weights
+}
+
+static unsigned grid_for(long total)
+{
+    long b = (total + 255) / 256;
+    const long cap = (long)sm_count() * 16;
+    return (unsigned)(b > cap ? cap : (b < 1 ? 1 : b));
+}
+
+static int composed(const float *const *fields, float *const *outs, int nfields, const float *delp,
+                    const float *area, float *delp_coarse, long n_outer, int nz, int ny, int nx,
+                    int f, int mask_below, float toa, void *workspace, long workspace_bytes,
+                    cudaStream_t st)
+{
+    const long need = composed_workspace_bytes(n_outer, nz, ny, nx, f);
+    CG_REQUIRE(workspace && workspace_bytes >= need, "workspace too small: need %ld bytes, got %ld", need, workspace_bytes);
+    const int nyc = ny / f, nxc = nx / f;
+    const long h = (long)ny * nx, hc = (long)nyc * nxc;
+    char *w = (char *)workspace;
+    float *pe_f = (float *)w;  w += align256(4 * n_outer * (nz + 1) * h);
+    float *pe_c = (float *)w;  w += align256(4 * n_outer * (nz + 1) * hc);
+    float *dc_ws = (float *)w; w += align256(4 * n_outer * nz * hc);
+    float *remap = (float *)w; w += align256(4 * n_outer * nz * h);
+    float *mask = (float *)w;
+    float *dc = delp_coarse ? delp_coarse : dc_ws;
+
+    int rc;
+    {
+        const void *in[1] = {delp};
+        void *out[1] = {dc};
+        rc = cg_weighted_block_average(in, out, 1, nullptr, area, CG_W2D, n_outer, nz, ny, nx, f, f,
+                                       f, f, nyc, nxc, CG_F32, CG_F32, st);
+        if (rc) return rc;
+    }
+    if ((rc = cg_pressure_at_interface(delp, pe_f, toa, n_outer, nz, h, CG_F32, st))) return rc;
+    if ((rc = cg_pressure_at_interface(dc, pe_c, toa, n_outer, nz, hc, CG_F32, st))) return rc;
+    if (mask_below) {
+        mask_from_coarse_kernel<<<grid_for(n_outer * nz * h), 256, 0, st>>>(area, pe_c, pe_f, mask, n_outer, nz, ny, nx, f);
+        CG_LAUNCH_CHECK("mask_from_coarse");
+    }
+    const long strides[12] = {(nz + 1) * h, 1, h, nz * h, 1, h, (nz + 1) * hc, 1, hc, nz * h, 1, h};
+    for (int v = 0; v < nfields; ++v) {
+        rc = launch_mappm(pe_f, fields[v], pe_c, remap, n_outer, h, nz, nz, strides, f, nx, nxc, 1, 1, st);
+        if (rc) return rc;
+        const void *in[1] = {remap};
+        void *out[1] = {outs[v]};
+        rc = cg_weighted_block_average(in, out, 1, mask_below ? mask : nullptr, mask_below ? nullptr : area,
+                                       mask_below ? CG_W3D : CG_W2D, n_outer, nz, ny, nx, f, f, f, f,
+                                       nyc, nxc, CG_F32, CG_F32, st);
+        if (rc) return rc;
+    }
+    return CG_OK;
+}
+
+static bool want_composed()
+{
+    const char *e = getenv("CG_PLEVEL_IMPL");
+    return e && strcmp(e, "composed") == 0;
+}
+
+}  // namespace cg
+
+using namespace cg;
+
+extern "C" long cg_pressure_level_workspace_bytes(int nfields, long n_outer, int nz, int ny, int nx, int f)
+{
+    if (f < 1 || ny < 1 || nx < 1 || nz < 1 || n_outer < 0) return 0;
+    long a = composed_workspace_bytes(n_outer, nz, ny, nx, f);
+    long b = fused_supported(nz, ny, nx, f) ? fused_workspace_bytes(nfields, n_outer, nz, ny, nx, f) : 0;
+    if (!want_composed() && fused_supported(nz, ny, nx, f)) return b;
+    return a > b ? a : b;
+}
+
+extern "C" int cg_pressure_level_average(const float *const *fields, float *const *outs, int nfields,
+                                         const float *delp, const float *area, float *delp_coarse,
+                                         long n_outer, int nz, int ny, int nx, int f, int mask_below,
+                                         double toa, void *workspace, long workspace_bytes, void *stream)
+{
+    CG_REQUIRE(fields && outs && delp && area, "null pointer");
+    CG_REQUIRE(nfields >= 0 && nfields <= CG_MAX_FIELDS, "nfields must be in [0, %d]", CG_MAX_FIELDS);
+    CG_REQUIRE(n_outer >= 0 && nz >= 4 && ny >= 1 && nx >= 1 && f >= 1, "bad shape (nz >= 4 required)");
+    CG_REQUIRE(ny % f == 0 && nx % f == 0, "dimension sizes (%d, %d) are not multiples of the factor %d", ny, nx, f);
+    for (int v = 0; v < nfields; ++v) CG_REQUIRE(fields[v] && outs[v], "null field pointer");
+    if (n_outer == 0) return CG_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!want_composed() && fused_supported(nz, ny, nx, f))
+        return launch_plevel_fused(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz, ny, nx,
+                                   f, mask_below, (float)toa, workspace, workspace_bytes, st);
+    return composed(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz, ny, nx, f, mask_below,
+                    (float)toa, workspace, workspace_bytes, st);
+}
+
+extern "C" int cg_area_above_fine_surface(const float *delp, const float *delp_coarse, const float *area,
+                                          float *out, long n_outer, int nz, int ny, int nx, int f,
+                                          double toa, void *stream)
+{
+    CG_REQUIRE(delp && delp_coarse && area && out, "null pointer");
+    CG_REQUIRE(n_outer >= 0 && nz >= 1 && ny >= 1 && nx >= 1 && f >= 1, "bad shape");
+    CG_REQUIRE(ny % f == 0 && nx % f == 0, "dimension sizes (%d, %d) are not multiples of the factor %d", ny, nx, f);
+    if (n_outer == 0) return CG_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const long h = (long)ny * nx, hc = (long)(ny / f) * (nx / f);
+    float *ps = nullptr, *pe_c = nullptr;
+    cudaError_t e = cudaMallocAsync((void **)&ps, 4 * n_outer * h, st);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMallocAsync(ps)");
+    e = cudaMallocAsync((void **)&pe_c, 4 * n_outer * (nz + 1) * hc, st);
+    if (e != cudaSuccess) { cudaFreeAsync(ps, st); return cuda_fail(e, "cudaMallocAsync(pe_c)"); }
+    surface_pressure_kernel<<<grid_for(n_outer * h), 256, 0, st>>>(delp, ps, (float)toa, n_outer, nz, h);
+    int rc = cg_pressure_at_interface(delp_coarse, pe_c, toa, n_outer, nz, hc, CG_F32, st);
+    if (rc == CG_OK)
+        exposed_area_kernel<<<grid_for(n_outer * nz * hc), 256, 0, st>>>(pe_c, delp_coarse, ps, area, out, n_outer, nz, ny, nx, f);
+    cudaError_t le = cudaGetLastError();
+    cudaFreeAsync(ps, st);
+    cudaFreeAsync(pe_c, st);
+    if (rc) return rc;
+    if (le != cudaSuccess) return cuda_fail(le, "cg_area_above_fine_surface");
+    return CG_OK;
+}

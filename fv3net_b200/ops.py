@@ -1,0 +1,250 @@
+"""Array-level entry points: torch CUDA tensors (or numpy arrays, staged through
+pinned memory) in canonical layout, horizontal dims last.
+
+  3-D fields  : (n_outer, nz, ny, nx)      2-D fields / weights : (n_outer, ny, nx)
+
+Every function launches hand-written CUDA through the C ABI (include/coarsen_b200.h)
+on torch's current stream.  torch is only the allocator / stream provider.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib as L
+
+_DT = {torch.float32: L.CG_F32, torch.float64: L.CG_F64}
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def device():
+    if not torch.cuda.is_available():
+        raise L.CoarsenLibraryError("fv3net_b200 needs a CUDA device; there is no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def to_device(a, dtype=None):
+    """numpy / torch -> contiguous CUDA tensor (float32 or float64)."""
+    if isinstance(a, torch.Tensor):
+        t = a
+    else:
+        a = np.asarray(a)
+        if a.dtype.kind != "f" or a.dtype.itemsize < 4:
+            a = a.astype(np.float64 if a.dtype.kind in "iub" and a.dtype.itemsize >= 4 else np.float32)
+        t = torch.from_numpy(np.ascontiguousarray(a))
+    if dtype is not None and t.dtype != dtype:
+        t = t.to(dtype)
+    if t.dtype not in _DT:
+        t = t.to(torch.float64 if t.dtype in (torch.int32, torch.int64) else torch.float32)
+    if not t.is_cuda:
+        t = t.to(device(), non_blocking=False)
+    return t.contiguous()
+
+
+def to_host(t):
+    return t.detach().cpu().numpy()
+
+
+def _p(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _promote(a, b):
+    return torch.float64 if torch.float64 in (a, b) else torch.float32
+
+
+def weighted_block_average(objs, w2d=None, w3d=None, fy=8, fx=8, sy=None, sx=None, nyo=None, nxo=None):
+    """coarsen.py:183-218 / :221-273.  objs: list of (n_outer, nz, ny, nx) tensors of one
+    dtype sharing the weights; w2d (n_outer, ny, nx) and/or w3d (n_outer, nz, ny, nx); both
+    given = mass weighting w3d*w2d formed in the kernel.  Returns a list of coarse tensors."""
+    single = isinstance(objs, torch.Tensor)
+    objs = [objs] if single else list(objs)
+    n_outer, nz, ny, nx = objs[0].shape
+    sy = fy if sy is None else sy
+    sx = fx if sx is None else sx
+    if nyo is None:
+        if ny % sy or (fy != sy):
+            raise ValueError("nyo must be given for non-tiling windows")
+        nyo = ny // sy
+    if nxo is None:
+        if nx % sx or (fx != sx):
+            raise ValueError("nxo must be given for non-tiling windows")
+        nxo = nx // sx
+    if w2d is not None and w3d is not None:
+        mode, wdt = L.CG_WMASS, w3d.dtype
+        if w2d.dtype != w3d.dtype:
+            wdt = _promote(w2d.dtype, w3d.dtype)
+            w2d, w3d = w2d.to(wdt), w3d.to(wdt)
+    elif w3d is not None:
+        mode, wdt = L.CG_W3D, w3d.dtype
+    elif w2d is not None:
+        mode, wdt = L.CG_W2D, w2d.dtype
+    else:
+        raise ValueError("weights are required")
+    if w2d is not None and tuple(w2d.shape) != (n_outer, ny, nx):
+        raise ValueError(f"2-D weights have shape {tuple(w2d.shape)}, expected {(n_outer, ny, nx)}")
+    if w3d is not None and tuple(w3d.shape) != (n_outer, nz, ny, nx):
+        raise ValueError(f"3-D weights have shape {tuple(w3d.shape)}, expected {(n_outer, nz, ny, nx)}")
+    dt = objs[0].dtype
+    out_dt = _promote(dt, wdt)
+    outs = []
+    for i in range(0, len(objs), L.CG_MAX_FIELDS):
+        chunk = objs[i:i + L.CG_MAX_FIELDS]
+        for o in chunk:
+            if o.dtype != dt or tuple(o.shape) != (n_outer, nz, ny, nx) or not o.is_contiguous():
+                raise ValueError("all fields of one call must share dtype, shape and be contiguous")
+        res = [torch.empty((n_outer, nz, nyo, nxo), dtype=out_dt, device=o.device) for o in chunk]
+        pin, _k1 = L.ptr_array([o.data_ptr() for o in chunk])
+        pout, _k2 = L.ptr_array([r.data_ptr() for r in res])
+        L.check(L.lib().cg_weighted_block_average(
+            pin, pout, len(chunk), _p(w3d), _p(w2d), mode, n_outer, nz, ny, nx,
+            fy, fx, sy, sx, nyo, nxo, _DT[dt], _DT[wdt], _stream()))
+        outs.extend(res)
+    return outs[0] if single else outs
+
+
+def block_reduce(a, method, fy, fx, sy=None, sx=None, nyo=None, nxo=None, skipna=True):
+    """Window reduction of (n_outer, ny, nx); method in sum/min/max/mean.  skipna=True is
+    xarray's coarsen (nansum...), False is numpy's plain reduction (NaN propagates)."""
+    code = {"sum": L.CG_SUM, "min": L.CG_MIN, "max": L.CG_MAX, "mean": L.CG_MEAN}[method]
+    if not skipna:
+        code |= L.CG_NAN_PROPAGATE
+    n_outer, ny, nx = a.shape
+    sy = fy if sy is None else sy
+    sx = fx if sx is None else sx
+    nyo = (ny - fy) // sy + 1 if nyo is None else nyo
+    nxo = (nx - fx) // sx + 1 if nxo is None else nxo
+    out = torch.empty((n_outer, nyo, nxo), dtype=a.dtype, device=a.device)
+    L.check(L.lib().cg_block_reduce(_p(a), _p(out), code, n_outer, ny, nx, fy, fx, sy, sx, nyo, nxo,
+                                    _DT[a.dtype], _stream()))
+    return out
+
+
+def block_median(a, f):
+    n_outer, ny, nx = a.shape
+    if ny % f or nx % f:
+        raise ValueError(f"dimension sizes ({ny}, {nx}) are not multiples of the block size {f}")
+    out = torch.empty((n_outer, ny // f, nx // f), dtype=a.dtype, device=a.device)
+    L.check(L.lib().cg_block_median(_p(a), _p(out), n_outer, ny, nx, f, _DT[a.dtype], _stream()))
+    return out
+
+
+def block_mode(a, f, nan_policy="propagate"):
+    if nan_policy not in ("propagate", "omit"):
+        raise ValueError("nan_policy must be 'propagate' or 'omit' on the device path")
+    n_outer, ny, nx = a.shape
+    if ny % f or nx % f:
+        raise ValueError(f"dimension sizes ({ny}, {nx}) are not multiples of the block size {f}")
+    out = torch.empty((n_outer, ny // f, nx // f), dtype=a.dtype, device=a.device)
+    L.check(L.lib().cg_block_mode(_p(a), _p(out), n_outer, ny, nx, f, int(nan_policy == "omit"),
+                                  _DT[a.dtype], _stream()))
+    return out
+
+
+def block_upsample(a, fy, fx, stag_y=False, stag_x=False):
+    n_outer, nyc, nxc = a.shape
+    ny = (nyc - 1) * fy + 1 if stag_y else nyc * fy
+    nx = (nxc - 1) * fx + 1 if stag_x else nxc * fx
+    out = torch.empty((n_outer, ny, nx), dtype=a.dtype, device=a.device)
+    L.check(L.lib().cg_block_upsample(_p(a), _p(out), n_outer, nyc, nxc, fy, fx, int(stag_y),
+                                      int(stag_x), _DT[a.dtype], _stream()))
+    return out
+
+
+def pressure_at_interface(delp, toa=300.0):
+    """(n_outer, nz, *h) -> (n_outer, nz+1, *h)."""
+    n_outer, nz = delp.shape[:2]
+    h = int(np.prod(delp.shape[2:], dtype=np.int64))
+    out = torch.empty((n_outer, nz + 1) + tuple(delp.shape[2:]), dtype=delp.dtype, device=delp.device)
+    L.check(L.lib().cg_pressure_at_interface(_p(delp), _p(out), float(toa), n_outer, nz, h,
+                                             _DT[delp.dtype], _stream()))
+    return out
+
+
+def mask_weights(w2d, pc, pf):
+    """regridz.py:150-161: w2d (n_outer,*h), pc (n_outer,nz+1,*h), pf (n_outer,nzf+1,*h)."""
+    n_outer, nz1 = pc.shape[:2]
+    h = int(np.prod(pc.shape[2:], dtype=np.int64))
+    if pf.dtype != pc.dtype:
+        dt = _promote(pf.dtype, pc.dtype)
+        pc, pf = pc.to(dt), pf.to(dt)
+    out = torch.empty((n_outer, nz1 - 1) + tuple(pc.shape[2:]), dtype=w2d.dtype, device=pc.device)
+    L.check(L.lib().cg_mask_weights(_p(w2d), _p(pc), _p(pf), _p(out), n_outer, nz1 - 1,
+                                    pf.shape[1] - 1, h, _DT[pc.dtype], _DT[w2d.dtype], _stream()))
+    return out
+
+
+def interp_to_edges(c, axis):
+    """(6, nz, n, n) cell-centred -> y-edges (axis='y') or x-edges (axis='x')."""
+    t, nz, n, n2 = c.shape
+    if t != 6 or n != n2:
+        raise ValueError("interp_to_edges needs (6, nz, n, n) data on all six tiles")
+    ax = {"y": 0, "x": 1}[axis]
+    shape = (6, nz, n + 1, n) if ax == 0 else (6, nz, n, n + 1)
+    out = torch.empty(shape, dtype=c.dtype, device=c.device)
+    L.check(L.lib().cg_interp_to_edges(_p(c), _p(out), nz, n, ax, _DT[c.dtype], _stream()))
+    return out
+
+
+def mappm(pe1, q1, pe2, n_outer, n_inner, km, kn, s_pe1, s_q1, s_pe2, s_q2, out, iv=1, kord=1):
+    """Strided PPM remap (fp32); s_* = (outer, column, level) element strides."""
+    for t in (pe1, q1, pe2, out):
+        if t.dtype != torch.float32:
+            raise ValueError("mappm runs in float32 (the Fortran `real`)")
+    strides = (ctypes.c_long * 12)(*s_pe1, *s_q1, *s_pe2, *s_q2)
+    L.check(L.lib().cg_mappm(_p(pe1), _p(q1), _p(pe2), _p(out), n_outer, n_inner, km, kn, strides,
+                             int(iv), int(kord), _stream()))
+    return out
+
+
+_WORKSPACE = {}
+
+
+def _workspace(nbytes, dev):
+    key = (dev.index, torch.cuda.current_stream().cuda_stream)
+    ws = _WORKSPACE.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
+        _WORKSPACE[key] = ws
+    return ws
+
+
+def pressure_level_average(fields, delp, area, f, mask_below=False, toa=300.0, want_delp_coarse=True):
+    """Fused regrid-to-coarse-pressure + (masked) area-weighted block average.
+    fields: list of (n_outer, nz, ny, nx) float32; delp same shape; area (n_outer, ny, nx).
+    Returns (list of coarse fields, delp_coarse or None)."""
+    fields = list(fields)
+    n_outer, nz, ny, nx = delp.shape
+    if ny % f or nx % f:
+        raise ValueError(f"dimension sizes ({ny}, {nx}) are not multiples of the factor {f}")
+    for t in fields + [delp, area]:
+        if t.dtype != torch.float32 or not t.is_contiguous():
+            raise ValueError("pressure_level_average needs contiguous float32 tensors")
+    dev = delp.device
+    dcoarse = torch.empty((n_outer, nz, ny // f, nx // f), dtype=torch.float32, device=dev) \
+        if want_delp_coarse else None
+    outs = [torch.empty((n_outer, nz, ny // f, nx // f), dtype=torch.float32, device=dev) for _ in fields]
+    step = L.CG_MAX_FIELDS
+    first = True
+    for i in range(0, max(len(fields), 1), step):
+        chunk, res = fields[i:i + step], outs[i:i + step]
+        nbytes = L.lib().cg_pressure_level_workspace_bytes(len(chunk), n_outer, nz, ny, nx, f)
+        ws = _workspace(nbytes, dev)
+        pin, _k1 = L.ptr_array([t.data_ptr() for t in chunk])
+        pout, _k2 = L.ptr_array([t.data_ptr() for t in res])
+        L.check(L.lib().cg_pressure_level_average(
+            pin, pout, len(chunk), _p(delp), _p(area), _p(dcoarse) if first else None,
+            n_outer, nz, ny, nx, f, int(mask_below), float(toa), _p(ws), ws.numel(), _stream()))
+        first = False
+    return outs, dcoarse
+
+
+def area_above_fine_surface(delp, delp_coarse, area, f, toa=300.0):
+    n_outer, nz, ny, nx = delp.shape
+    out = torch.empty((n_outer, nz, ny // f, nx // f), dtype=torch.float32, device=delp.device)
+    L.check(L.lib().cg_area_above_fine_surface(_p(delp), _p(delp_coarse), _p(area), _p(out), n_outer,
+                                               nz, ny, nx, f, float(toa), _stream()))
+    return out

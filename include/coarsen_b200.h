@@ -1,0 +1,148 @@
+/* coarsen_b200.h — C ABI of libcoarsen_b200.so (CUDA, sm_100a).
+ *
+ * Drop-in boundary for the coarse-graining hot path of fv3net's `vcm` package
+ * (paths below are relative to the reference checkout):
+ *   external/vcm/vcm/cubedsphere/coarsen.py   block reductions (numpy/xarray there)
+ *   external/vcm/vcm/cubedsphere/regridz.py   pressure-level glue
+ *   external/mappm/mappm/mappm.f90            Fortran PPM remapper (f2py ABI:
+ *       mappm.mappm(pe1, q1, pe2, i1, i2, iv, kord, ptop) -> q2, regridz.py:273)
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer owned by the caller (no allocation here
+ *     except cg_malloc/cg_free helpers); `stream` is a cudaStream_t passed as
+ *     void* (NULL = legacy default stream); calls are asynchronous on it;
+ *   - arrays are dense, row-major, horizontal dims last: (n_outer, nz, ny, nx),
+ *     2-D weights (n_outer, ny, nx); n_outer folds tile/time/anything else;
+ *   - dtype codes: CG_F32 / CG_F64; "wdtype" is the dtype of the weights
+ *     (the reference mixes f64 restart fields with f32 grid weights);
+ *   - return value: CG_OK or a negative CG_E* code; cg_last_error() gives the
+ *     text for the calling thread.  No exceptions, no global state besides the
+ *     thread-local error string.  There is NO CPU fallback anywhere.
+ */
+#ifndef COARSEN_B200_H
+#define COARSEN_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CG_OK 0
+#define CG_EINVAL (-1)   /* bad shape / factor / enum */
+#define CG_ENOTSUP (-2)  /* valid in the reference but not built yet (e.g. kord > 7) */
+#define CG_ECUDA (-3)    /* CUDA runtime error; see cg_last_error() */
+
+#define CG_F32 0
+#define CG_F64 1
+
+/* reduction methods of cg_block_reduce (xarray coarsen names; NaN-skipping) */
+#define CG_SUM 0
+#define CG_MIN 1
+#define CG_MAX 2
+#define CG_MEAN 3
+#define CG_NAN_PROPAGATE 16 /* OR into the method: numpy's plain sum/mean/min/max */
+
+/* weight modes of cg_weighted_block_average */
+#define CG_W2D 0   /* w: (n_outer, ny, nx), broadcast over z (area)            */
+#define CG_W3D 1   /* w: (n_outer, nz, ny, nx) (masked area, precomputed mass) */
+#define CG_WMASS 2 /* w = w3d * w2d formed on the fly (delp * area)            */
+
+#define CG_MAX_FIELDS 32
+
+const char *cg_last_error(void);
+int cg_version(void);
+/* sm count, major*10+minor compute capability; any may be NULL */
+int cg_device_info(int *sm_count, int *cc, long *total_mem_bytes);
+
+/* coarsen.py:183-218 weighted_block_average and :221-273 edge_weighted_block_average.
+ *   out[o,k,J,I] = nansum_{win}(obj*w) / nansum_{win}(w)
+ * window (fy, fx) anchored at (J*sy, I*sx); cell-centred: fy=fx=sy=sx=f;
+ * edge='x': fy=1, fx=f, sy=sx=f on (ny = nyc*f+1) rows; edge='y' symmetric.
+ * nfields objects share one weight array (read once per block, not per field).
+ * objs/outs: HOST arrays of nfields device pointers.  Output (n_outer,nz,nyo,nxo)
+ * in the promoted dtype of (dtype, wdtype); the denominator is summed in wdtype. */
+int cg_weighted_block_average(const void *const *objs, void *const *outs, int nfields,
+                              const void *w3d, const void *w2d, int wmode,
+                              long n_outer, int nz, int ny, int nx,
+                              int fy, int fx, int sy, int sx, int nyo, int nxo,
+                              int dtype, int wdtype, void *stream);
+
+/* coarsen.py:629-683 block_edge_coarsen / :795-840 block_coarsen(sum|min|max|mean),
+ * budgets.py:59 block_sum: NaN-skipping window reduction, same window rule. */
+int cg_block_reduce(const void *in, void *out, int method,
+                    long n_outer, int ny, int nx,
+                    int fy, int fx, int sy, int sx, int nyo, int nxo,
+                    int dtype, void *stream);
+
+/* coarsen.py:557-588 block_median (np.median over f x f blocks; any NaN -> NaN;
+ * even count -> (lo+hi)/2 in the input dtype).  Bit-exact selection. */
+int cg_block_median(const void *in, void *out, long n_outer, int ny, int nx, int f,
+                    int dtype, void *stream);
+
+/* coarsen.py:750-786 _block_mode (scipy.stats.mode: most frequent value, ties ->
+ * smallest).  nan_omit=0: 'propagate' as in the reference's pinned scipy 1.7.3 (NaN is an
+ * ordinary candidate sorted last), 1: 'omit' (NaNs ignored; all-NaN block -> NaN). */
+int cg_block_mode(const void *in, void *out, long n_outer, int ny, int nx, int f,
+                  int nan_omit, int dtype, void *stream);
+
+/* coarsen.py:843-897 block_upsample: repeat f times along y and/or x; a
+ * staggered (odd-sized) dim repeats all but its last line.  fy or fx = 1 leaves
+ * that dim alone.  Output dims: stag ? (n-1)*f+1 : n*f. */
+int cg_block_upsample(const void *in, void *out, long n_outer, int nyc, int nxc,
+                      int fy, int fx, int stag_y, int stag_x, int dtype, void *stream);
+
+/* calc/thermo/vertically_dependent.py:41-66 pressure_at_interface:
+ * (n_outer, nz, h) -> (n_outer, nz+1, h), sequential cumsum from toa in dtype. */
+int cg_pressure_at_interface(const void *delp, void *pe, double toa,
+                             long n_outer, int nz, long h, int dtype, void *stream);
+
+/* regridz.py:150-161 _mask_weights: out[o,k,i] = pc[o,k+1,i] < pf[o,nzf,i] ? w[o,i] : 0
+ * pc: (n_outer, nz+1, h) coarse interfaces on the fine grid, pf: (n_outer, nzf+1, h). */
+int cg_mask_weights(const void *w2d, const void *pc, const void *pf, void *out,
+                    long n_outer, int nz, int nzf, long h, int dtype, int wdtype, void *stream);
+
+/* regridz.py:86-100 (xgcm.Grid.interp with xgcm.py:7-34 face connections):
+ * cell-centred (6, nz, n, n) -> edges; axis 0: y-edges (6,nz,n+1,n), 1: x-edges
+ * (6,nz,n,n+1); tile-face lines come from the neighbour tile. */
+int cg_interp_to_edges(const void *c, void *out, int nz, int n, int axis,
+                       int dtype, void *stream);
+
+/* mappm.f90:10-126 (ppm_profile :614, ppm_limiters :854): conservative PPM remap,
+ * fp32 arithmetic like the Fortran `real`.  Strided columns: column (o,i) level k
+ * of array A is A[o*os_A + i*cs_A + k*ls_A]; (ncol,nz) z-last and (tile,z,y,x)
+ * layouts both work without a transpose; cs_pe2 = 0 shares target pressures.
+ * strides: {os,cs,ls} for pe1, q1, pe2, q2 in that order (12 longs, elements).
+ * kord <= 7; kord > 7 (cs_profile) -> CG_ENOTSUP. km >= 4.
+ * A target layer no source layer brackets (NaN / non-monotone pressure: undefined
+ * behaviour in the Fortran) yields NaN. */
+int cg_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,
+             long n_outer, long n_inner, int km, int kn, const long *strides,
+             int iv, int kord, void *stream);
+
+/* Fused pressure-level coarse-graining (iv=1, kord=1, the only combination the
+ * reference's callers use: regridz.py:168-169, budgets.py:45):
+ *   regridz.py:115-147 (+ coarsen.py:183 with the masked weights)  mask_below=1
+ *   workflows/fine_res_budget/budget/budgets.py:49-57               mask_below=0
+ * For every f x f block: coarse delp = area-weighted block mean of delp; both
+ * interface pressures by cumsum from `toa`; every field remapped column by
+ * column onto the block's coarse pressures; area(-masked)-weighted block mean.
+ * Nothing fine-grid is written.  fields/outs: HOST arrays of device pointers,
+ * fields (n_outer,nz,ny,nx) f32 -> outs (n_outer,nz,ny/f,nx/f) f32.
+ * delp_coarse: optional (n_outer,nz,ny/f,nx/f) output, may be NULL.
+ * workspace: see cg_pressure_level_workspace_bytes (may be 0). */
+long cg_pressure_level_workspace_bytes(int nfields, long n_outer, int nz, int ny, int nx, int f);
+int cg_pressure_level_average(const float *const *fields, float *const *outs, int nfields,
+                              const float *delp, const float *area, float *delp_coarse,
+                              long n_outer, int nz, int ny, int nx, int f,
+                              int mask_below, double toa,
+                              void *workspace, long workspace_bytes, void *stream);
+
+/* budgets.py:62-77 area_above_fine_surface: block sum of area where the coarse
+ * log-midpoint pressure (upsampled) <= fine surface pressure. */
+int cg_area_above_fine_surface(const float *delp, const float *delp_coarse, const float *area,
+                               float *out, long n_outer, int nz, int ny, int nx, int f,
+                               double toa, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -106,16 +106,28 @@ def block_median(obj, f):
 
 
 def block_mode(obj, f, nan_policy="propagate"):
-    """cubedsphere/coarsen.py:686-786 (scipy.stats.mode over the flattened block;
-    ties -> smallest value; 'propagate': any NaN -> NaN; 'omit': ignore NaNs)."""
-    import scipy.stats
-
+    """cubedsphere/coarsen.py:686-786: scipy.stats.mode over the flattened block, as the
+    reference's pinned scipy 1.7.3 / numpy 1.21.5 compute it (constraints.txt:181,250):
+      'propagate': np.unique(..., return_counts) then argmax — NaN is an ordinary candidate
+                   that sorts last, so it wins only when strictly more frequent than every
+                   other value; ties go to the smallest value;
+      'omit'     : NaNs are ignored; an all-NaN block gives NaN.
+    (Pure-Python loop over blocks: the oracle is for small cases.)"""
     obj = np.asarray(obj)
     v = block_view(obj, f, f)
     v = np.moveaxis(v, -3, -2)  # (..., nyc, nxc, f, f)
     flat = v.reshape(v.shape[:-2] + (f * f,))
-    res = scipy.stats.mode(flat, axis=-1, nan_policy=nan_policy, keepdims=False).mode
-    return np.asarray(res).astype(obj.dtype)
+    out = np.empty(flat.shape[:-1], dtype=obj.dtype)
+    for idx in np.ndindex(*out.shape):
+        blk = flat[idx]
+        if nan_policy == "omit":
+            blk = blk[~np.isnan(blk)]
+            if blk.size == 0:
+                out[idx] = np.nan
+                continue
+        vals, cnts = np.unique(blk, return_counts=True)
+        out[idx] = vals[cnts.argmax()]
+    return out
 
 
 def block_coarsen(obj, f, method="sum"):
