@@ -1,0 +1,379 @@
+#!/usr/bin/env python
+"""bench.py — C384->C48 pressure-level coarse-graining of one fine_res_budget timestep.
+
+    python bench.py --gpus N --steps K --warmup W            (ours; torchrun for N > 1)
+    python bench.py --impl reference --steps K --warmup W    (CPU port of the reference path)
+
+A step = one pass of `fv3net_b200.budget.recoarsen_budget_inputs` over one timestep of
+synthetic C384 data (6 tiles x 79 levels x 384 x 384, fp32): 22 first-moment 3-D fields,
+2 products and 2 storage terms formed on the fly, 10 2-D fields, delp, area, exposed area.
+Weak scaling: every rank owns its own timestep (the reference partitions by time,
+budget/pipeline.py:46-53); there is no data-path collective.
+One JSON line on stdout (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "fine-grid cells/s, C384->C48 pressure-level coarsen (fine_res_budget timestep)"
+UNIT = "cells/s"
+
+
+def workload(args):
+    from fv3net_b200 import budget as B
+
+    n3 = len(B.FIRST_MOMENTS_3D)
+    spec = dict(n_tile=args.tiles, nz=79, n=args.n, f=B.FACTOR, n3_first=n3,
+                n3_out=n3 + len(B.SECOND_MOMENTS) + len(B.STORAGE_TERMS),
+                n3_reads=n3 + 2 * len(B.STORAGE_TERMS), n2=len(B.GFSPHYSICS_2D))
+    fine3 = spec["n_tile"] * spec["nz"] * spec["n"] ** 2
+    fine2 = spec["n_tile"] * spec["n"] ** 2
+    # fine-grid cells of every coarse-grained field: 26 pressure-level fields + delp,
+    # 10 2-D fields + exposed area (3-D output of a 2-D input, counted once) + area
+    spec["cells"] = (spec["n3_out"] + 1) * fine3 + (spec["n2"] + 2) * fine2
+    spec["plevel_cells"] = spec["n3_out"] * fine3
+    spec["bytes"] = B.algorithmic_bytes(spec["n_tile"], spec["nz"], spec["n"], spec["n"],
+                                        spec["n3_reads"], spec["n3_out"], spec["n2"], spec["f"])
+    # dominant kernel group (pressure-level): its reads + delp + area, its outputs + delp_coarse
+    hc = (spec["n"] // spec["f"]) ** 2
+    spec["plevel_bytes"] = 4 * ((spec["n3_reads"] + 1) * fine3 + fine2
+                                + (spec["n3_out"] + 1) * spec["n_tile"] * spec["nz"] * hc)
+    return spec
+
+
+def make_inputs(spec, device, seed):
+    """Synthetic timestep created directly in HBM."""
+    import torch
+    from fv3net_b200 import budget as B, synthetic as syn
+
+    nt, nz, n = spec["n_tile"], spec["nz"], spec["n"]
+    shape3 = (nt, nz, n, n)
+    delp = syn.torch_delp(nt, n, n, seed, device)
+    area = syn.torch_area((nt, n, n), seed + 1, device)
+    exposed = area * (torch.rand((nt, n, n), device=device) < 0.98).to(torch.float32)
+    middle3d = {name: syn.torch_field(shape3, seed + 10 + i, device, scale=10.0 ** (i % 4 - 2))
+                for i, name in enumerate(B.FIRST_MOMENTS_3D)}
+    middle2d = {name: syn.torch_field((nt, n, n), seed + 100 + i, device, scale=100.0)
+                for i, name in enumerate(B.GFSPHYSICS_2D)}
+    begin = {k: middle3d[k] - 0.01 * syn.torch_field(shape3, seed + 200 + i, device)
+             for i, k in enumerate(B.STORAGE_TERMS)}
+    end = {k: middle3d[k] + 0.01 * syn.torch_field(shape3, seed + 300 + i, device)
+           for i, k in enumerate(B.STORAGE_TERMS)}
+    return dict(middle3d=middle3d, middle2d=middle2d, delp=delp, area=area,
+                exposed_area_fine=exposed, begin=begin, end=end)
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx, self.rows, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:  # noqa: BLE001
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx.append(float(r[2]))
+                for nm, v in zip(names, r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+            except (ValueError, IndexError):
+                continue
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------ CPU side (oracle port)
+def cpu_sample_inputs(spec, n_fields, seed=0):
+    """Tile 0 of the same synthetic workload, `n_fields` 3-D fields, on the host."""
+    from fv3net_b200 import synthetic as syn
+
+    n, nz = spec["n"], spec["nz"]
+    delp = syn.delp_from_ps(syn.surface_pressure((1, n, n), seed=seed))
+    area = syn.area((1, n, n), seed=seed + 1)
+    fields = [syn.field((1, nz, n, n), seed + 10 + i, scale=10.0 ** (i % 4 - 2)) for i in range(n_fields)]
+    return fields, delp, area
+
+
+def cpu_pass(fields, delp, area, f, threads):
+    """The reference's per-field pipeline (budgets.py:49-57), one numpy pass per xarray step
+    with the same temporaries, the Fortran remapper replaced by its C restatement."""
+    import oracle
+    from oracle import recipes
+
+    dc = oracle.weighted_block_average(delp, area[:, None], f)
+    return [recipes.pressure_level_average(x, delp, dc, area, f, threads=threads) for x in fields]
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import oracle
+
+    oracle.build_library()
+    spec = workload(args)
+    threads = os.cpu_count() or 1
+    n_fields = args.cpu_fields
+    fields, delp, area = cpu_sample_inputs(spec, n_fields)
+    for _ in range(args.warmup):
+        cpu_pass(fields[:1], delp, area, spec["f"], threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_pass(fields, delp, area, spec["f"], threads)
+    dt = (time.perf_counter() - t0) / args.steps
+    cells = n_fields * spec["nz"] * spec["n"] ** 2
+    sample = (f"tile 0 of 6, {n_fields} of {spec['n3_out']} 3-D fields per step, reference-shaped "
+              f"numpy passes + C restatement of mappm.f90 (gfortran absent: oracle port)")
+    val = cells / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": config_dict(spec, args),
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def config_dict(spec, args):
+    return {"workload": "configs[2]: C384->C48 (f=8) pressure-level coarse-graining of one "
+                        "fine_res_budget timestep, 6 tiles x 79 levels, 26 remapped 3-D fields "
+                        "(22 first moments + 2 products + 2 storage terms), 10 2-D fields",
+            "tiles": spec["n_tile"], "levels": spec["nz"], "fine_n": spec["n"], "factor": spec["f"],
+            "fields_3d": spec["n3_out"], "fields_2d": spec["n2"],
+            "cells_per_step": spec["cells"], "algorithmic_bytes_per_step": spec["bytes"],
+            "sharding": "one timestep per rank (time), no data-path collective",
+            "l2": "inputs (7.7 GB per step) exceed the 126 MB L2; no flush needed"}
+
+
+# ------------------------------------------------------------------ GPU side (ours)
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from fv3net_b200 import _lib, budget as B, ops
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    lib = _lib.lib()                                   # fails loudly if the .so is missing
+    spec = workload(args)
+    inp = make_inputs(spec, device, seed=1000 * rank)   # each rank: its own timestep
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(ev=None):
+        if ev is None:
+            return B.recoarsen_budget_inputs(**inp)
+        # same work, with events around the dominant kernel group (pressure-level)
+        names3d = list(inp["middle3d"])
+        fields = [inp["middle3d"][n] for n in names3d]
+        for a, b in B.SECOND_MOMENTS:
+            fields.append(ops.product(inp["middle3d"][a], inp["middle3d"][b]))
+        for n in B.STORAGE_TERMS:
+            fields.append(ops.storage(inp["end"][n], inp["begin"][n], B.DT))
+        ev[0].record()
+        coarse3d, dcoarse = ops.pressure_level_average(fields, inp["delp"], inp["area"], B.FACTOR)
+        ev[1].record()
+        c2 = ops.weighted_block_average([t.unsqueeze(1) for t in inp["middle2d"].values()],
+                                        w2d=inp["area"], fy=B.FACTOR, fx=B.FACTOR)
+        ea = ops.area_above_fine_surface(inp["delp"], dcoarse, inp["exposed_area_fine"], B.FACTOR)
+        ar = ops.block_reduce(inp["area"], "sum", B.FACTOR, B.FACTOR)
+        return coarse3d, dcoarse, c2, ea, ar
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = lib.cg_launch_count()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+           for _ in range(args.steps)]
+    t_start, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_start.record()
+    for k in range(args.steps):
+        step(evs[k])
+    t_end.record()
+    barrier()
+    launches = lib.cg_launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    total_ms = t_start.elapsed_time(t_end)
+    plevel_ms = sum(a.elapsed_time(b) for a, b in evs) / args.steps
+    t = torch.tensor([total_ms, plevel_ms], device=device, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, plevel_ms = t.tolist()
+    ms_per_step = total_ms / args.steps
+
+    # ---- end to end through the public API with host buffers (pinned) --------------------
+    e2e = e2e_run(args, spec, inp, device, world, barrier)
+
+    # ---- CPU baseline beside it (rank 0, N = 1 only; bounded sample) ---------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        import oracle
+
+        oracle.build_library()
+        threads = os.cpu_count() or 1
+        fields, delp, area = cpu_sample_inputs(spec, args.cpu_fields)
+        cpu_pass(fields[:1], delp, area, spec["f"], threads)       # warm
+        t0 = time.perf_counter()
+        cpu_pass(fields, delp, area, spec["f"], threads)
+        dt = time.perf_counter() - t0
+        cpu = {"value": args.cpu_fields * spec["nz"] * spec["n"] ** 2 / dt, "unit": UNIT,
+               "cores": threads, "kind": "port",
+               "sample": f"tile 0 of 6, {args.cpu_fields} of {spec['n3_out']} 3-D fields, "
+                         f"reference-shaped numpy passes + C restatement of mappm.f90, {dt:.1f} s"}
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        achieved = spec["plevel_bytes"] / (plevel_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": world * spec["cells"] / (ms_per_step * 1e-3), "unit": UNIT,
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": config_dict(spec, args), "clocks": clocks, "e2e": e2e,
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": args.traffic,
+                         "kernel": "pressure-level group (cg_pressure_level_average)",
+                         "ms": plevel_ms, "algorithmic_bytes": spec["plevel_bytes"],
+                         "peak_source": peak_src,
+                         "impl": os.environ.get("CG_PLEVEL_IMPL", "default")},
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def e2e_run(args, spec, inp, device, world, barrier):
+    """Same metric through the public API with HOST buffers: per step, every input goes
+    pinned host -> device, the step runs, every coarse output comes back to the host."""
+    import torch
+    from fv3net_b200 import budget as B
+
+    try:
+        flat = {}
+        for group in ("middle3d", "middle2d", "begin", "end"):
+            for k, v in inp[group].items():
+                flat[(group, k)] = v
+        for k in ("delp", "area", "exposed_area_fine"):
+            flat[(k, None)] = inp[k]
+        host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in flat.items()}
+        for k, v in flat.items():
+            host[k].copy_(v)
+        torch.cuda.synchronize()
+        h2d = sum(v.numel() * v.element_size() for v in host.values())
+
+        def e2e_step(out_host):
+            for k, v in flat.items():
+                v.copy_(host[k], non_blocking=True)
+            out = B.recoarsen_budget_inputs(**inp)
+            if out_host is None:
+                out_host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True) for k, v in out.items()}
+            for k, v in out.items():
+                out_host[k].copy_(v, non_blocking=True)
+            return out_host
+
+        out_host = e2e_step(None)
+        barrier()
+        d2h = sum(v.numel() * v.element_size() for v in out_host.values())
+        steps = max(1, min(args.steps, args.e2e_steps))
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        a.record()
+        for _ in range(steps):
+            e2e_step(out_host)
+        b.record()
+        barrier()
+        ms = torch.tensor([a.elapsed_time(b) / steps], device=device, dtype=torch.float64)
+        if world > 1:
+            import torch.distributed as dist
+
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return {"value": world * spec["cells"] / (ms.item() * 1e-3), "unit": UNIT,
+                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": ms.item(), "steps": steps}
+    except RuntimeError as e:  # e.g. pinned allocation refused
+        return {"value": None, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
+                "error": str(e)[:200]}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--tiles", type=int, default=6)
+    ap.add_argument("--n", type=int, default=384, help="fine grid size per tile edge (C384)")
+    ap.add_argument("--cpu-fields", type=int, default=2, help="3-D fields in the bounded CPU sample")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--traffic", type=float, default=None,
+                    help="dram bytes per launch of the dominant kernel from an ncu capture")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -26,6 +26,7 @@ _pp = _c.POINTER(_c.c_void_p)
 SIGNATURES = {
     "cg_last_error": (_c.c_char_p, []),
     "cg_version": (_i, []),
+    "cg_launch_count": (_l, []),
     "cg_device_info": (_i, [_c.POINTER(_i), _c.POINTER(_i), _c.POINTER(_l)]),
     "cg_weighted_block_average": (_i, [_pp, _pp, _i, _vp, _vp, _i, _l, _i, _i, _i,
                                        _i, _i, _i, _i, _i, _i, _i, _i, _vp]),
@@ -38,10 +39,18 @@ SIGNATURES = {
     "cg_interp_to_edges": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "cg_mappm": (_i, [_vp, _vp, _vp, _vp, _l, _l, _i, _i, _c.POINTER(_l), _i, _i, _vp]),
     "cg_pressure_level_workspace_bytes": (_l, [_i, _l, _i, _i, _i, _i]),
-    "cg_pressure_level_average": (_i, [_pp, _pp, _i, _vp, _vp, _vp, _l, _i, _i, _i, _i, _i, _d,
+    "cg_pressure_level_average": (_i, [_vp, _pp, _i, _vp, _vp, _vp, _l, _i, _i, _i, _i, _i, _d,
                                        _vp, _l, _vp]),
     "cg_area_above_fine_surface": (_i, [_vp, _vp, _vp, _vp, _l, _i, _i, _i, _i, _d, _vp]),
 }
+
+CG_FIELD_PLAIN, CG_FIELD_PRODUCT, CG_FIELD_DIFF = 0, 1, 2
+
+
+class CgField(ctypes.Structure):
+    _fields_ = [("a", ctypes.c_void_p), ("b", ctypes.c_void_p), ("op", ctypes.c_int),
+                ("scale", ctypes.c_float)]
+
 
 _LIB = None
 

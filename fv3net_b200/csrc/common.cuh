@@ -25,8 +25,12 @@ inline int cuda_fail(cudaError_t e, const char *what)
         }                                     \
     } while (0)
 
+// every kernel launch of the library passes through here once (cg_launch_count())
+void count_launch();
+
 #define CG_LAUNCH_CHECK(what)                                  \
     do {                                                       \
+        cg::count_launch();                                    \
         cudaError_t e__ = cudaGetLastError();                  \
         if (e__ != cudaSuccess) return cg::cuda_fail(e__, what); \
     } while (0)

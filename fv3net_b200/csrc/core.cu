@@ -1,6 +1,7 @@
 // Library-wide helpers: thread-local error text, device queries.
 #include "common.cuh"
 #include <cstring>
+#include <atomic>
 
 namespace cg {
 
@@ -13,6 +14,9 @@ void set_error(const char *fmt, ...)
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
 }
+
+static std::atomic<long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 int sm_count()
 {
@@ -33,6 +37,8 @@ int sm_count()
 extern "C" const char *cg_last_error(void) { return cg::g_err; }
 
 extern "C" int cg_version(void) { return 100; }
+
+extern "C" long cg_launch_count(void) { return cg::g_launches.load(std::memory_order_relaxed); }
 
 extern "C" int cg_device_info(int *sm, int *cc, long *total_mem_bytes)
 {

@@ -20,7 +20,7 @@ int launch_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,
                  long n_outer, long n_inner, int km, int kn, const long *strides,
                  int pe2_f, int pe2_nx, int pe2_nxc, int iv, int kord, cudaStream_t st);
 int fused_supported(int nz, int ny, int nx, int f);
-int launch_plevel_fused(const float *const *fields, float *const *outs, int nfields,
+int launch_plevel_fused(const cg_field *fields, float *const *outs, int nfields,
                         const float *delp, const float *area, float *delp_coarse,
                         long n_outer, int nz, int ny, int nx, int f, int mask_below, float toa,
                         void *workspace, long workspace_bytes, cudaStream_t st);
@@ -95,6 +95,16 @@ surface_pressure_kernel(const float *__restrict__ delp, float *__restrict__ ps, 
     }
 }
 
+// derived budget inputs (budgets.py:80,151) materialised for the composed path only
+__global__ void __launch_bounds__(256)
+derive_field_kernel(const float *__restrict__ a, const float *__restrict__ b, float *__restrict__ out,
+                    int op, float scale, long total)
+{
+    for (long idx = blockIdx.x * (long)blockDim.x + threadIdx.x; idx < total;
+         idx += (long)gridDim.x * blockDim.x)
+        out[idx] = op == CG_FIELD_PRODUCT ? a[idx] * b[idx] : (a[idx] - b[idx]) / scale;
+}
+
 static inline long align256(long n) { return (n + 255) / 256 * 256; }
 
 static long composed_workspace_bytes(long n_outer, int nz, int ny, int nx, int f)
@@ -104,6 +114,7 @@ static long composed_workspace_bytes(long n_outer, int nz, int ny, int nx, int f
            + align256(4 * n_outer * (nz + 1) * hc)  // coarse interfaces
            + align256(4 * n_outer * nz * hc)        // coarse delp (when the caller passes NULL)
            + align256(4 * n_outer * nz * h)         // one remapped fine field
+           + align256(4 * n_outer * nz * h)         // one derived fine field
            + align256(4 * n_outer * nz * h);        // masked weights
 }
 
@@ -114,7 +125,7 @@ static unsigned grid_for(long total)
     return (unsigned)(b > cap ? cap : (b < 1 ? 1 : b));
 }
 
-static int composed(const float *const *fields, float *const *outs, int nfields, const float *delp,
+static int composed(const cg_field *fields, float *const *outs, int nfields, const float *delp,
                     const float *area, float *delp_coarse, long n_outer, int nz, int ny, int nx,
                     int f, int mask_below, float toa, void *workspace, long workspace_bytes,
                     cudaStream_t st)
@@ -128,6 +139,7 @@ static int composed(const float *const *fields, float *const *outs, int nfields,
     float *pe_c = (float *)w;  w += align256(4 * n_outer * (nz + 1) * hc);
     float *dc_ws = (float *)w; w += align256(4 * n_outer * nz * hc);
     float *remap = (float *)w; w += align256(4 * n_outer * nz * h);
+    float *derived = (float *)w; w += align256(4 * n_outer * nz * h);
     float *mask = (float *)w;
     float *dc = delp_coarse ? delp_coarse : dc_ws;
 
@@ -147,7 +159,13 @@ static int composed(const float *const *fields, float *const *outs, int nfields,
     }
     const long strides[12] = {(nz + 1) * h, 1, h, nz * h, 1, h, (nz + 1) * hc, 1, hc, nz * h, 1, h};
     for (int v = 0; v < nfields; ++v) {
-        rc = launch_mappm(pe_f, fields[v], pe_c, remap, n_outer, h, nz, nz, strides, f, nx, nxc, 1, 1, st);
+        const float *src = fields[v].a;
+        if (fields[v].op != CG_FIELD_PLAIN) {
+            derive_field_kernel<<<grid_for(n_outer * nz * h), 256, 0, st>>>(fields[v].a, fields[v].b, derived, fields[v].op, fields[v].scale, n_outer * nz * h);
+            CG_LAUNCH_CHECK("derive_field");
+            src = derived;
+        }
+        rc = launch_mappm(pe_f, src, pe_c, remap, n_outer, h, nz, nz, strides, f, nx, nxc, 1, 1, st);
         if (rc) return rc;
         const void *in[1] = {remap};
         void *out[1] = {outs[v]};
@@ -178,7 +196,7 @@ extern "C" long cg_pressure_level_workspace_bytes(int nfields, long n_outer, int
     return a > b ? a : b;
 }
 
-extern "C" int cg_pressure_level_average(const float *const *fields, float *const *outs, int nfields,
+extern "C" int cg_pressure_level_average(const cg_field *fields, float *const *outs, int nfields,
                                          const float *delp, const float *area, float *delp_coarse,
                                          long n_outer, int nz, int ny, int nx, int f, int mask_below,
                                          double toa, void *workspace, long workspace_bytes, void *stream)
@@ -187,7 +205,12 @@ extern "C" int cg_pressure_level_average(const float *const *fields, float *cons
     CG_REQUIRE(nfields >= 0 && nfields <= CG_MAX_FIELDS, "nfields must be in [0, %d]", CG_MAX_FIELDS);
     CG_REQUIRE(n_outer >= 0 && nz >= 4 && ny >= 1 && nx >= 1 && f >= 1, "bad shape (nz >= 4 required)");
     CG_REQUIRE(ny % f == 0 && nx % f == 0, "dimension sizes (%d, %d) are not multiples of the factor %d", ny, nx, f);
-    for (int v = 0; v < nfields; ++v) CG_REQUIRE(fields[v] && outs[v], "null field pointer");
+    for (int v = 0; v < nfields; ++v) {
+        CG_REQUIRE(fields[v].a && outs[v], "null field pointer");
+        CG_REQUIRE(fields[v].op >= CG_FIELD_PLAIN && fields[v].op <= CG_FIELD_DIFF, "bad field op");
+        CG_REQUIRE(fields[v].op == CG_FIELD_PLAIN || fields[v].b, "derived field needs a second parent");
+        CG_REQUIRE(fields[v].op != CG_FIELD_DIFF || fields[v].scale != 0.f, "storage term needs a non-zero dt");
+    }
     if (n_outer == 0) return CG_OK;
     cudaStream_t st = (cudaStream_t)stream;
     if (!want_composed() && fused_supported(nz, ny, nx, f))
@@ -213,9 +236,13 @@ extern "C" int cg_area_above_fine_surface(const float *delp, const float *delp_c
     e = cudaMallocAsync((void **)&pe_c, 4 * n_outer * (nz + 1) * hc, st);
     if (e != cudaSuccess) { cudaFreeAsync(ps, st); return cuda_fail(e, "cudaMallocAsync(pe_c)"); }
     surface_pressure_kernel<<<grid_for(n_outer * h), 256, 0, st>>>(delp, ps, (float)toa, n_outer, nz, h);
+    count_launch();
     int rc = cg_pressure_at_interface(delp_coarse, pe_c, toa, n_outer, nz, hc, CG_F32, st);
     if (rc == CG_OK)
+    {
         exposed_area_kernel<<<grid_for(n_outer * nz * hc), 256, 0, st>>>(pe_c, delp_coarse, ps, area, out, n_outer, nz, ny, nx, f);
+        count_launch();
+    }
     cudaError_t le = cudaGetLastError();
     cudaFreeAsync(ps, st);
     cudaFreeAsync(pe_c, st);

@@ -4,7 +4,7 @@
 namespace cg {
 int fused_supported(int, int, int, int) { return 0; }
 long fused_workspace_bytes(int, long, int, int, int, int) { return 0; }
-int launch_plevel_fused(const float *const *, float *const *, int, const float *, const float *, float *,
+int launch_plevel_fused(const cg_field *, float *const *, int, const float *, const float *, float *,
                         long, int, int, int, int, int, float, void *, long, cudaStream_t)
 {
     set_error("fused pressure-level kernel not built");

@@ -212,15 +212,46 @@ def _workspace(nbytes, dev):
     return ws
 
 
+def product(a, b):
+    """Field descriptor: q = a * b, formed inside the kernel (budgets.py:151)."""
+    return ("product", a, b, 1.0)
+
+
+def storage(end, begin, dt):
+    """Field descriptor: q = (end - begin) / dt, formed inside the kernel (budgets.py:80)."""
+    return ("diff", end, begin, float(dt))
+
+
+def _describe(fields):
+    descs = (L.CgField * max(len(fields), 1))()
+    keep = []
+    for i, fld in enumerate(fields):
+        if isinstance(fld, tuple):
+            kind, a, b, scale = fld
+            op = {"product": L.CG_FIELD_PRODUCT, "diff": L.CG_FIELD_DIFF}[kind]
+        else:
+            a, b, op, scale = fld, None, L.CG_FIELD_PLAIN, 1.0
+        for t in (a, b):
+            if t is not None and (t.dtype != torch.float32 or not t.is_contiguous()):
+                raise ValueError("pressure_level_average needs contiguous float32 tensors")
+        descs[i].a = a.data_ptr()
+        descs[i].b = b.data_ptr() if b is not None else None
+        descs[i].op = op
+        descs[i].scale = scale
+        keep.append((a, b))
+    return descs, keep
+
+
 def pressure_level_average(fields, delp, area, f, mask_below=False, toa=300.0, want_delp_coarse=True):
     """Fused regrid-to-coarse-pressure + (masked) area-weighted block average.
-    fields: list of (n_outer, nz, ny, nx) float32; delp same shape; area (n_outer, ny, nx).
+    fields: list of (n_outer, nz, ny, nx) float32 tensors or descriptors from product() /
+    storage(); delp same shape; area (n_outer, ny, nx).
     Returns (list of coarse fields, delp_coarse or None)."""
     fields = list(fields)
     n_outer, nz, ny, nx = delp.shape
     if ny % f or nx % f:
         raise ValueError(f"dimension sizes ({ny}, {nx}) are not multiples of the factor {f}")
-    for t in fields + [delp, area]:
+    for t in (delp, area):
         if t.dtype != torch.float32 or not t.is_contiguous():
             raise ValueError("pressure_level_average needs contiguous float32 tensors")
     dev = delp.device
@@ -233,10 +264,11 @@ def pressure_level_average(fields, delp, area, f, mask_below=False, toa=300.0, w
         chunk, res = fields[i:i + step], outs[i:i + step]
         nbytes = L.lib().cg_pressure_level_workspace_bytes(len(chunk), n_outer, nz, ny, nx, f)
         ws = _workspace(nbytes, dev)
-        pin, _k1 = L.ptr_array([t.data_ptr() for t in chunk])
+        descs, _keep = _describe(chunk)
         pout, _k2 = L.ptr_array([t.data_ptr() for t in res])
         L.check(L.lib().cg_pressure_level_average(
-            pin, pout, len(chunk), _p(delp), _p(area), _p(dcoarse) if first else None,
+            ctypes.cast(descs, ctypes.c_void_p), pout, len(chunk), _p(delp), _p(area),
+            _p(dcoarse) if first else None,
             n_outer, nz, ny, nx, f, int(mask_below), float(toa), _p(ws), ws.numel(), _stream()))
         first = False
     return outs, dcoarse

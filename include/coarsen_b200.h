@@ -50,6 +50,8 @@ extern "C" {
 
 const char *cg_last_error(void);
 int cg_version(void);
+/* number of CUDA kernels this library has launched in this process (monotonic) */
+long cg_launch_count(void);
 /* sm count, major*10+minor compute capability; any may be NULL */
 int cg_device_info(int *sm_count, int *cc, long *total_mem_bytes);
 
@@ -125,12 +127,28 @@ int cg_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,
  * For every f x f block: coarse delp = area-weighted block mean of delp; both
  * interface pressures by cumsum from `toa`; every field remapped column by
  * column onto the block's coarse pressures; area(-masked)-weighted block mean.
- * Nothing fine-grid is written.  fields/outs: HOST arrays of device pointers,
- * fields (n_outer,nz,ny,nx) f32 -> outs (n_outer,nz,ny/f,nx/f) f32.
+ * Nothing fine-grid is written (fused path).  A field is described by a cg_field so the
+ * budget workflow's derived inputs are formed on the fly from their parents instead of
+ * being materialised (budgets.py:151 second moments, :80 storage terms):
+ *   CG_FIELD_PLAIN   q = a
+ *   CG_FIELD_PRODUCT q = a * b                      (T * omega ...)
+ *   CG_FIELD_DIFF    q = (a - b) / scale            (storage: (end - begin) / dt)
+ * fields: HOST array of nfields descriptors (device pointers inside), each
+ * (n_outer,nz,ny,nx) f32; outs: HOST array of device pointers (n_outer,nz,ny/f,nx/f) f32.
  * delp_coarse: optional (n_outer,nz,ny/f,nx/f) output, may be NULL.
  * workspace: see cg_pressure_level_workspace_bytes (may be 0). */
+#define CG_FIELD_PLAIN 0
+#define CG_FIELD_PRODUCT 1
+#define CG_FIELD_DIFF 2
+typedef struct cg_field {
+    const float *a;
+    const float *b; /* NULL for CG_FIELD_PLAIN */
+    int op;
+    float scale;
+} cg_field;
+
 long cg_pressure_level_workspace_bytes(int nfields, long n_outer, int nz, int ny, int nx, int f);
-int cg_pressure_level_average(const float *const *fields, float *const *outs, int nfields,
+int cg_pressure_level_average(const cg_field *fields, float *const *outs, int nfields,
                               const float *delp, const float *area, float *delp_coarse,
                               long n_outer, int nz, int ny, int nx, int f,
                               int mask_below, double toa,
