@@ -260,7 +260,7 @@ def run_ours(args):
     ms_per_step = total_ms / args.steps
 
     # ---- end to end through the public API with host buffers (pinned) --------------------
-    e2e = e2e_run(args, spec, inp, device, world, barrier)
+    e2e = e2e_run(args, spec, inp, device, world, barrier) if args.e2e_steps > 0 else None
 
     # ---- CPU baseline beside it (rank 0, N = 1 only; bounded sample) ---------------------
     cpu = None

@@ -192,8 +192,7 @@ extern "C" long cg_pressure_level_workspace_bytes(int nfields, long n_outer, int
     if (f < 1 || ny < 1 || nx < 1 || nz < 1 || n_outer < 0) return 0;
     long a = composed_workspace_bytes(n_outer, nz, ny, nx, f);
     long b = fused_supported(nz, ny, nx, f) ? fused_workspace_bytes(nfields, n_outer, nz, ny, nx, f) : 0;
-    if (!want_composed() && fused_supported(nz, ny, nx, f)) return b;
-    return a > b ? a : b;
+    return a > b ? a : b;   // composed-path size: also the fallback for misaligned inputs
 }
 
 extern "C" int cg_pressure_level_average(const cg_field *fields, float *const *outs, int nfields,
@@ -213,9 +212,11 @@ extern "C" int cg_pressure_level_average(const cg_field *fields, float *const *o
     }
     if (n_outer == 0) return CG_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    if (!want_composed() && fused_supported(nz, ny, nx, f))
-        return launch_plevel_fused(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz, ny, nx,
-                                   f, mask_below, (float)toa, workspace, workspace_bytes, st);
+    if (!want_composed() && fused_supported(nz, ny, nx, f)) {
+        const int rc = launch_plevel_fused(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz,
+                                           ny, nx, f, mask_below, (float)toa, workspace, workspace_bytes, st);
+        if (rc != CG_ENOTSUP) return rc;        // misaligned pointers: use the composed path
+    }
     return composed(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz, ny, nx, f, mask_below,
                     (float)toa, workspace, workspace_bytes, st);
 }
