@@ -25,6 +25,13 @@ int launch_plevel_fused(const cg_field *fields, float *const *outs, int nfields,
                         long n_outer, int nz, int ny, int nx, int f, int mask_below, float toa,
                         void *workspace, long workspace_bytes, cudaStream_t st);
 long fused_workspace_bytes(int nfields, long n_outer, int nz, int ny, int nx, int f);
+// plevel_stream.cu: lanes-over-fields streaming kernel (TMA ring, shared-memory geometry)
+int stream_supported(int nfields, int nz, int ny, int nx, int f);
+long stream_workspace_bytes(long n_outer, int nz, int ny, int nx);
+int launch_surface_pressure_seq(const float *delp, float *ps, float toa, long n_outer, int nz, long h, cudaStream_t st);
+int launch_plevel_stream(const cg_field *fields, float *const *outs, int nfields, const float *delp,
+                         const float *area, const float *delp_coarse, const float *psurf, long n_outer,
+                         int nz, int ny, int nx, int mask_below, float toa, cudaStream_t st);
 
 // masked[o,k,y,x] = pe_c[o,k+1,y/f,x/f] < pe_f[o,nz,y,x] ? area[o,y,x] : 0   (regridz.py:150-161)
 __global__ void __launch_bounds__(256)
@@ -177,10 +184,33 @@ static int composed(const cg_field *fields, float *const *outs, int nfields, con
     return CG_OK;
 }
 
-static bool want_composed()
+// CG_PLEVEL_IMPL = composed | fused | stream pins one implementation (tests, A/B timing);
+// default: stream where its shape constraints hold, else fused, else composed.
+static bool impl_is(const char *name)
 {
     const char *e = getenv("CG_PLEVEL_IMPL");
-    return e && strcmp(e, "composed") == 0;
+    return e && strcmp(e, name) == 0;
+}
+static bool want_composed() { return impl_is("composed"); }
+
+static int stream_path(const cg_field *fields, float *const *outs, int nfields, const float *delp,
+                       const float *area, float *delp_coarse, long n_outer, int nz, int ny, int nx,
+                       int mask_below, float toa, void *workspace, long workspace_bytes, cudaStream_t st)
+{
+    if (!workspace || workspace_bytes < stream_workspace_bytes(n_outer, nz, ny, nx)) return CG_ENOTSUP;
+    const int nyc = ny / 8, nxc = nx / 8;
+    const long h = (long)ny * nx, hc = (long)nyc * nxc;
+    char *w = (char *)workspace;
+    float *dc = delp_coarse ? delp_coarse : (float *)w;
+    float *ps = (float *)(w + align256(4 * n_outer * nz * hc));
+    const void *in[1] = {delp};
+    void *out[1] = {dc};
+    int rc = cg_weighted_block_average(in, out, 1, nullptr, area, CG_W2D, n_outer, nz, ny, nx, 8, 8, 8, 8,
+                                       nyc, nxc, CG_F32, CG_F32, st);
+    if (rc) return rc;
+    if (mask_below && (rc = launch_surface_pressure_seq(delp, ps, toa, n_outer, nz, h, st))) return rc;
+    return launch_plevel_stream(fields, outs, nfields, delp, area, dc, mask_below ? ps : nullptr, n_outer, nz,
+                                ny, nx, mask_below, toa, st);
 }
 
 }  // namespace cg
@@ -212,7 +242,12 @@ extern "C" int cg_pressure_level_average(const cg_field *fields, float *const *o
     }
     if (n_outer == 0) return CG_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    if (!want_composed() && fused_supported(nz, ny, nx, f)) {
+    if (!want_composed() && !impl_is("fused") && nfields > 0 && stream_supported(nfields, nz, ny, nx, f)) {
+        const int rc = stream_path(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz, ny, nx,
+                                   mask_below, (float)toa, workspace, workspace_bytes, st);
+        if (rc != CG_ENOTSUP) return rc;        // misaligned pointers / no workspace: next implementation
+    }
+    if (!want_composed() && !impl_is("stream") && fused_supported(nz, ny, nx, f)) {
         const int rc = launch_plevel_fused(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz,
                                            ny, nx, f, mask_below, (float)toa, workspace, workspace_bytes, st);
         if (rc != CG_ENOTSUP) return rc;        // misaligned pointers: use the composed path

@@ -1,0 +1,674 @@
+// Streaming pressure-level coarse-graining for sm_100a: f = 8, iv = 1, kord = 1, nx % 32 == 0.
+// (regridz.py:115-147 + coarsen.py:183, budgets.py:49-57; mappm.f90:10-126, :614-851, :854-931)
+//
+// Mapping ("lanes over fields").  A CTA owns 4 x-adjacent coarse cells; consumer warp w owns
+// cell w for the whole launch and walks its 8 rows one after the other.  Inside a warp,
+// LANE v IS FIELD v and every thread carries the 8 fine columns of the current row, so
+//   * everything that depends only on pressure (the geometry: PPM stencil coefficients of
+//     every layer, where each coarse interface cuts the fine column and with which weight)
+//     is the same for all lanes of a warp.  It is built once per (column, level) by the
+//     warp itself (lane = (column, level of the chunk)), parked in shared memory and read
+//     back by all lanes with broadcast loads: no per-field integer work, no divergence;
+//   * field data is fetched by TMA (cp.async.bulk.tensor, one [4 levels][32 columns] box
+//     per source array and stage, 128B-swizzled) into a 2-stage ring shared by the 4
+//     warps; a lane reads its own field's 8 columns with two conflict-free LDS.128;
+//   * the vertical walk is a tandem walk: source layers in order (rolling PPM state in
+//     registers), coarse interfaces met on the way close one target layer and open the
+//     next ("events"); per-target sums live in a per-warp shared-memory accumulator
+//     [target level][lane], so the 64 columns of a cell are summed by one warp in a
+//     fixed order (bitwise reproducible) and no cross-warp reduction exists.
+// Every fine input element is read from HBM exactly once per launch; products / storage
+// terms of the budget workflow are formed from their parents in registers.
+// The prepass (plevel.cu) supplies delp_coarse and, for mask_below, the fine surface pressure.
+#include "common.cuh"
+#include <cuda.h>
+#include <cmath>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+namespace cg {
+namespace stream {
+
+constexpr int C = 8;                 // fine columns per thread (one row of a coarse cell)
+constexpr int NCELL = 4;             // coarse cells per CTA = consumer warps
+constexpr int KC = 4;                // levels per pipeline stage
+constexpr int BOX_ROWS = KC + 1;     // 128-B rows per source box: odd stride -> 8 distinct swizzle phases over 8 lanes
+constexpr int BOX_BYTES = BOX_ROWS * 128;
+constexpr int NSTAGE = 2;
+constexpr int MAXF = CG_MAX_FIELDS;  // output fields per launch (lanes)
+constexpr int MAXSRC = 2 * MAXF + 1; // distinct source arrays (+ delp)
+constexpr int EVCAP = 4;             // precomputed events per (column, layer); more are formed on the fly
+constexpr int PRING = 16;            // levels kept in the interface-pressure ring
+constexpr int NTHREADS = (NCELL + 1) * 32;
+constexpr int DUMMY_SLOT = 0;        // accumulator slot k + 1 belongs to target level k
+
+struct Params {
+    CUtensorMap maps[MAXSRC];
+    float *outs[MAXF];
+    int fa[MAXF], fb[MAXF], fop[MAXF];
+    float finv[MAXF];                // 1 / scale of CG_FIELD_DIFF
+    const float *area;               // (n_outer, ny, nx)
+    const float *psurf;              // (n_outer, ny, nx) sequential-cumsum surface pressure, mask_below only
+    const float *delp_coarse;        // (n_outer, nz, ny/8, nx/8)
+    int nsrc;                        // TMA sources, delp last
+    int nfields, nz, ny, nx, mask_below;
+    float toa;
+};
+
+// ---- shared-memory carve-up --------------------------------------------------------------------
+struct Layout {
+    int ring, bars, warp0, warp_bytes;
+    int acc, rec, ev, pe1, pe2, rdp2, den, edge, colw, colps, q0, total;
+};
+
+__host__ __device__ inline Layout make_layout(int nsrc, int nz, int V)
+{
+    Layout L;
+    int o = 0;
+    L.ring = o;  o += NSTAGE * nsrc * BOX_BYTES;
+    L.bars = o;  o += 64;
+    L.warp0 = o;
+    int w = 0;
+    L.acc = w;   w += (nz + 1) * V * 4;          w = (w + 15) & ~15;
+    L.rec = w;   w += C * KC * 32;
+    L.ev = w;    w += C * KC * EVCAP * 16;
+    L.pe1 = w;   w += PRING * C * 4;
+    L.pe2 = w;   w += (nz + 2) * 4;              w = (w + 15) & ~15;
+    L.rdp2 = w;  w += (nz + 1) * 4;              w = (w + 15) & ~15;
+    L.den = w;   w += (nz + 1) * 4;              w = (w + 15) & ~15;
+    L.edge = w;  w += C * 24 * 4;
+    L.colw = w;  w += 64 * 4;                    // 64 columns at cell start, 8 per row afterwards
+    L.colps = w; w += 64 * 4;
+    L.q0 = w;    w += C * 32 * 4;
+    L.warp_bytes = (w + 127) & ~127;
+    L.total = L.warp0 + NCELL * L.warp_bytes;
+    return L;
+}
+
+// ---- PTX helpers ---------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, int bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, int parity)
+{
+    uint32_t done = 0;
+    while (!done)
+        asm volatile("{.reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p;}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, int x, int y, int z, uint32_t bar)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+        ::"r"(dst), "l"(map), "r"(x), "r"(y), "r"(z), "r"(bar) : "memory");
+}
+__device__ __forceinline__ float4 lds128(uint32_t addr)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ float lds32(uint32_t addr)
+{
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ float max3(float a, float b, float c)
+{
+    float r;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+__device__ __forceinline__ float min3(float a, float b, float c)
+{
+    float r;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+// byte address of 16-B chunk `chunk` of the 128-B row starting at absolute shared address `row`
+// under CU_TENSOR_MAP_SWIZZLE_128B (chunk index xor row index mod 8; verified by tools/tma_probe.cu)
+__device__ __forceinline__ uint32_t swz(uint32_t row, int chunk)
+{
+    return row + ((((row >> 7) ^ (uint32_t)chunk) & 7u) << 4);
+}
+
+// ---- geometry: what the whole warp shares ------------------------------------------------------
+// All of it is a function of pressure only (mappm.f90:41-46, :58-124, :651-683).
+struct WarpGeo {
+    float *acc, *rec, *ev, *pe1, *pe2, *rdp2, *den, *edge, *colw, *colps, *q0;
+};
+
+__device__ __forceinline__ int count_le(const float *pe2, int n, float p)
+{   // number of target interfaces i in [0, n) with pe2[i] <= p (pe2 ascending)
+    int lo = 0, hi = n;
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (pe2[mid] <= p) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// weight of fine column c in target level k times 1 / thickness of that level
+__device__ __forceinline__ float level_scale(const WarpGeo &g, int c, int k, int mask_below)
+{
+    const float w = (!mask_below || g.pe2[k + 1] < g.colps[c]) ? g.colw[c] : 0.f;   // regridz.py:150-161
+    return w * g.rdp2[k];
+}
+__device__ __forceinline__ float level_weight(const WarpGeo &g, int c, int k, int mask_below)
+{
+    return (!mask_below || g.pe2[k + 1] < g.colps[c]) ? g.colw[c] : 0.f;
+}
+
+// Event of target interface i met in source layer L of column c (L == nz: below the surface).
+// Record: I = x*q + y*x' + z*y' is added (with the running sum) to the accumulator slot in the low
+// 7 bits of z; the running sum of the next target level restarts at -w * I.
+__device__ __noinline__ float4 make_event(const WarpGeo &g, int c, int L, int i, int nz, int mask_below, float toa)
+{
+    const int kn = nz;
+    float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
+    int slot = DUMMY_SLOT;
+    const float ptop_col = toa;                                         // pe1[0] of every column
+    if (L < nz) {
+        const float pt = g.pe1[(L & (PRING - 1)) * C + c], pb = g.pe1[((L + 1) & (PRING - 1)) * C + c];
+        const float pi = g.pe2[i];
+        if (pi <= ptop_col) {                                           // mappm.f90:62-64, only met in L == 0
+            if (i < kn) { e.x = level_weight(g, c, i, mask_below); slot = i + 1; }
+        } else {
+            const float dpl = pb - pt;
+            const float s = (pi - pt) / dpl;
+            const int ke = i - 1;
+            const bool end_ok = ke >= 0 && g.pe2[ke] > ptop_col;
+            const bool start_ok = i < kn;
+            const float sc_e = end_ok ? level_scale(g, c, ke, mask_below) : 0.f;
+            const float sc_s = start_ok ? level_scale(g, c, i, mask_below) : 0.f;
+            const float sc = end_ok ? sc_e : sc_s;
+            const float a = sc * dpl * s, oms = 1.f - s;
+            e.x = a;
+            e.y = a * oms * oms;
+            e.z = -a * s * oms;
+            e.w = end_ok ? (sc_e != 0.f ? sc_s / sc_e : 0.f) : 1.f;
+            slot = end_ok ? ke + 1 : DUMMY_SLOT;
+        }
+    } else {                                                            // mappm.f90:65-67, :115-120
+        const float psf = g.pe1[(nz & (PRING - 1)) * C + c];
+        const int ke = i - 1;                                           // level whose bottom is interface i
+        if (ke >= 0 && ke < kn) {
+            const float top = g.pe2[ke];
+            if (top >= psf) { e.x = level_weight(g, c, ke, mask_below); slot = ke + 1; }
+            else if (top > ptop_col) { e.x = level_scale(g, c, ke, mask_below) * (g.pe2[i] - psf); slot = ke + 1; }
+        }
+    }
+    e.z = __int_as_float((__float_as_int(e.z) & ~127) | slot);
+    return e;
+}
+
+// Build the records of steps t0 .. t0+KC-1 (lane = (column c, step kk)); see the step loop.
+__device__ void build_chunk(const WarpGeo &g, uint32_t delp_rows /* shared addr of the delp box */,
+                            int w, int lane, int t0, int nz, int mask_below, float toa)
+{
+    const int c = lane & 7, kk = lane >> 3, t = t0 + kk;
+    // interface pressures by the reference's sequential cumsum (vertically_dependent.py:61-63)
+    if (kk == 0) {
+        float pe = (t0 == 0) ? toa : g.pe1[(t0 & (PRING - 1)) * C + c];
+        if (t0 == 0) g.pe1[c] = toa;
+#pragma unroll
+        for (int j = 0; j < KC; ++j) {
+            const int lvl = t0 + j;
+            if (lvl < nz) {
+                const uint32_t row = delp_rows + j * 128;
+                const float d = lds32(swz(row, 2 * w + (c >> 2)) + (c & 3) * 4);
+                pe = pe + d;
+                g.pe1[((lvl + 1) & (PRING - 1)) * C + c] = pe;
+            }
+        }
+    }
+    __syncwarp();
+    auto P = [&](int m) { return g.pe1[(m & (PRING - 1)) * C + c]; };
+    auto DP = [&](int m) { return P(m + 1) - P(m); };                   // mappm.f90:43 (from the rounded sums)
+
+    // PPM stencil of layer j = t - 1 (mappm.f90:651-683 with the delp-only factors folded)
+    float E1 = 0.f, E2 = 0.f, Fm = 0.f, G = 0.f, H = 0.f;
+    const int j = t - 1;
+    if (j >= 1 && j <= nz - 2) {
+        const float dm1 = DP(j - 1), d0 = DP(j), dp1 = DP(j + 1);
+        const float d4 = dm1 + d0, d4p = d0 + dp1;
+        const float c1 = (dm1 + 0.5f * d0) / d4p, c2 = (dp1 + 0.5f * d0) / d4;
+        const float inv = d0 / (d4 + dp1);
+        E1 = c1 * inv;
+        E2 = c2 * inv;
+        if (j >= 2) {
+            const float dm2 = DP(j - 2), d4m = dm2 + dm1;
+            const float cq = dm1 / d4, a1 = d4m / (d4 + dm1), a2 = d4p / (d4 + d0), gg = 2.f / (d4m + d4p);
+            Fm = cq * (1.f + gg * d0 * (a1 - a2)) - 1.f;
+            G = gg * d0 * a2;
+            H = gg * dm1 * a1;
+        }
+    }
+    // one-sided cubics at the column ends (mappm.f90:689-747), once per column
+    if (t == 3 || t == nz) {
+        const bool top = (t == 3);
+        const float d1 = top ? DP(0) : DP(nz - 1), d2 = top ? DP(1) : DP(nz - 2);
+        const float D = d2 * (2.f * d2 * d2 + d1 * (d2 + 3.f * d1));
+        const float Pq = d2 * (5.f * d1 + d2) - 3.f * d1 * d1;
+        const float Rr = d1 * d2 * (d2 + 3.f * d1);
+        float *e = g.edge + c * 24 + (top ? 0 : 12);
+        e[0] = d2 / (d1 + d2);
+        e[1] = d1 / (d1 + d2);
+        e[2] = 2.f / (d1 + d2);
+        e[3] = (top ? 4.f : 1.f) / D;
+        e[4] = d2;
+        e[5] = (top ? 0.5f : 2.f) * Pq;
+        e[6] = (top ? 0.25f : 1.f) * Rr;
+        e[7] = (top ? 2.f : 8.f) * d1 * d1 * d1;
+        e[8] = d1;
+    }
+    // events of layer L = t - 2 and its whole-layer weight
+    const int L = t - 2, kn = nz;
+    float dpw = 0.f;
+    int i0 = 0, n = 0;
+    if (L >= 0 && L <= nz) {
+        if (L < nz) {
+            const float pt = P(L), pb = P(L + 1);
+            i0 = (L == 0) ? 0 : count_le(g.pe2, kn + 1, pt);
+            const int i1 = count_le(g.pe2, kn + 1, pb);
+            n = i1 - i0;
+            const int ko = i1 - 1;                                      // level open at the bottom of L
+            if (ko >= 0 && ko < kn && g.pe2[ko] > toa) dpw = level_scale(g, c, ko, mask_below) * (pb - pt);
+        } else {
+            i0 = count_le(g.pe2, kn + 1, P(nz));
+            n = kn + 1 - i0;
+        }
+        if (n < 0) n = 0;                                               // NaN / non-monotone pressures
+        if (n <= EVCAP)
+            for (int e = 0; e < n; ++e)
+                reinterpret_cast<float4 *>(g.ev)[(c * KC + kk) * EVCAP + e] = make_event(g, c, L, i0 + e, nz, mask_below, toa);
+    }
+    float4 *r = reinterpret_cast<float4 *>(g.rec) + (c * KC + kk) * 2;
+    r[0] = make_float4(E1, E2, Fm, G);
+    r[1] = make_float4(H, dpw, __int_as_float(i0 | (n << 8)), 0.f);
+    __syncwarp();
+}
+
+// ---- per-field work -----------------------------------------------------------------------------
+// Limited parabola of one layer in deviation form, x = AL - q, y = AR - q, A6 = -3 (x + y)
+// (ppm_limiters lmt = 0, mappm.f90:875-894), then the events of the layer and its whole-layer term.
+__device__ __forceinline__ void finish_layer(const WarpGeo &g, int c, int kk, int L, float q, float x, float y,
+                                             float dc, float &run, float dpw, int evinfo, int lane, int V,
+                                             int nz, int mask_below, float toa)
+{
+    const float da1 = y - x, s = x + y;
+    const float t = s * da1, da2 = da1 * (da1 * (1.f / 3.f));
+    const float m2x = -2.f * x, m2y = -2.f * y;
+    if (t > da2) y = m2x;              // a6da < -da2: AR = AL - 3 (AL - q)
+    else if (-t > da2) x = m2y;        // a6da >  da2: AL = AR - 3 (AR - q)
+    if (dc == 0.f) { x = 0.f; y = 0.f; }
+    const int n = evinfo >> 8;
+    if (n) {
+        const int i0 = evinfo & 255;
+        const float4 *evp = reinterpret_cast<const float4 *>(g.ev) + (c * KC + kk) * EVCAP;
+        for (int e = 0; e < n; ++e) {
+            const float4 ev = (n <= EVCAP) ? evp[e] : make_event(g, c, L, i0 + e, nz, mask_below, toa);
+            const float I = ev.x * q + ev.y * x + ev.z * y;
+            const float tot = run + I;
+            const int slot = __float_as_int(ev.z) & 127;
+            if (lane < V && tot == tot) g.acc[slot * V + lane] += tot;     // NaN-skipping block sum (coarsen.py:211)
+            run = -ev.w * I;
+        }
+    }
+    run = fmaf(dpw, q, run);
+}
+
+__global__ void __launch_bounds__(NTHREADS, 2)
+plevel_stream_kernel(const __grid_constant__ Params p)
+{
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nz = p.nz, V = p.nfields, nsrc = p.nsrc;
+    const Layout lay = make_layout(nsrc, nz, V);
+    const uint32_t ring = smem_u32(smem + lay.ring);
+    const uint32_t bars = smem_u32(smem + lay.bars);           // full[NSTAGE], empty[NSTAGE]
+    const int stage_bytes = nsrc * BOX_BYTES;
+    const int nch = (nz + 3 + KC - 1) / KC;                     // steps t = 0 .. nz + 2
+    const int bx = blockIdx.x, by = blockIdx.y;
+    const long o = blockIdx.z;
+
+    if (tid == 0) {
+        for (int s = 0; s < NSTAGE; ++s) {
+            mbar_init(bars + 8 * s, 1);
+            mbar_init(bars + 8 * (NSTAGE + s), NCELL);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;");
+    }
+    __syncthreads();
+
+    if (warp == NCELL) {
+        // ---------------- producer: one TMA box per source array and stage -------------------
+        const int total = 8 * nch;
+        for (int it = 0; it < total; ++it) {
+            const int s = it % NSTAGE;
+            if (it >= NSTAGE) mbar_wait(bars + 8 * (NSTAGE + s), ((it / NSTAGE) - 1) & 1);
+            const int row = it / nch, chunk = it - row * nch;
+            if (lane == 0) mbar_expect_tx(bars + 8 * s, nsrc * KC * 128);
+            __syncwarp();
+            for (int src = lane; src < nsrc; src += 32)
+                tma_load_3d(ring + s * stage_bytes + src * BOX_BYTES, &p.maps[src], 32 * bx, 8 * by + row,
+                            (int)(o * nz) + chunk * KC, bars + 8 * s);
+        }
+        return;
+    }
+
+    // ---------------- consumers: warp w owns coarse cell (by, 4 bx + w) --------------------------
+    const int w = warp;
+    unsigned char *wb = smem + lay.warp0 + w * lay.warp_bytes;
+    WarpGeo g;
+    g.acc = (float *)(wb + lay.acc);    g.rec = (float *)(wb + lay.rec);    g.ev = (float *)(wb + lay.ev);
+    g.pe1 = (float *)(wb + lay.pe1);    g.pe2 = (float *)(wb + lay.pe2);    g.rdp2 = (float *)(wb + lay.rdp2);
+    g.den = (float *)(wb + lay.den);    g.edge = (float *)(wb + lay.edge);  g.colw = (float *)(wb + lay.colw);
+    g.colps = (float *)(wb + lay.colps); g.q0 = (float *)(wb + lay.q0);
+    const int ny = p.ny, nx = p.nx, nyc = ny >> 3, nxc = nx >> 3;
+    const long h = (long)ny * nx, hc = (long)nyc * nxc;
+    const int cx = 4 * bx + w;
+    const float toa = p.toa;
+    const int mask_below = p.mask_below;
+
+    // cell prologue: coarse interfaces (sequential cumsum, vertically_dependent.py:61-63), 1/thickness,
+    // weights of the 64 columns, sum of weights per target level (coarsen.py:212)
+    for (int k = lane; k < nz; k += 32) g.rdp2[k] = p.delp_coarse[(o * nz + k) * hc + (long)by * nxc + cx];
+    for (int i = lane; i < (nz + 1) * V; i += 32) g.acc[i] = 0.f;
+    for (int i = lane; i < 64; i += 32) {
+        const long col = o * h + (long)(8 * by + (i >> 3)) * nx + 8 * cx + (i & 7);
+        const float a = p.area[col];
+        g.colw[i] = (a == a) ? a : 0.f;
+        g.colps[i] = mask_below ? p.psurf[col] : 0.f;
+    }
+    __syncwarp();
+    if (lane == 0) {
+        float pe = toa;
+        g.pe2[0] = pe;
+        for (int k = 0; k < nz; ++k) { pe = pe + g.rdp2[k]; g.pe2[k + 1] = pe; }
+    }
+    __syncwarp();
+    for (int k = lane; k < nz; k += 32) {
+        g.rdp2[k] = 1.f / (g.pe2[k + 1] - g.pe2[k]);
+        const float lower = g.pe2[k + 1];
+        float d = 0.f;
+        for (int i = 0; i < 64; ++i) d += (!mask_below || lower < g.colps[i]) ? g.colw[i] : 0.f;
+        g.den[k] = d;
+    }
+    __syncwarp();
+
+    const int fa = lane < V ? p.fa[lane] : 0, fb = lane < V ? p.fb[lane] : 0, fop = lane < V ? p.fop[lane] : 0;
+    const float finv = lane < V ? p.finv[lane] : 1.f;
+
+    for (int row = 0; row < 8; ++row) {
+        // this row's 8 columns
+        __syncwarp();
+        float cwv = 0.f, cpv = 0.f;
+        if (lane < C) {
+            const long col = o * h + (long)(8 * by + row) * nx + 8 * cx + lane;
+            const float a = p.area[col];
+            cwv = (a == a) ? a : 0.f;
+            cpv = mask_below ? p.psurf[col] : 0.f;
+        }
+        __syncwarp();
+        if (lane < C) { g.colw[lane] = cwv; g.colps[lane] = cpv; }
+        __syncwarp();
+
+        float A[C], B[C], dq1[C], dcp[C], xp[C], run[C];
+#pragma unroll
+        for (int c = 0; c < C; ++c) { A[c] = 0.f; B[c] = 0.f; dq1[c] = 0.f; dcp[c] = 0.f; xp[c] = 0.f; run[c] = 0.f; }
+
+        for (int chunk = 0; chunk < nch; ++chunk) {
+            const int it = row * nch + chunk, s = it % NSTAGE, t0 = chunk * KC;
+            mbar_wait(bars + 8 * s, (it / NSTAGE) & 1);
+            const uint32_t stage = ring + s * stage_bytes;
+            build_chunk(g, stage + (nsrc - 1) * BOX_BYTES, w, lane, t0, nz, mask_below, toa);
+
+            for (int kk = 0; kk < KC; ++kk) {
+                const int t = t0 + kk;
+                if (t > nz + 2) break;
+                const float4 *recs = reinterpret_cast<const float4 *>(g.rec);
+                if (t < nz) {
+                    float qv[C];
+                    {
+                        const uint32_t ra = stage + fa * BOX_BYTES + kk * 128;
+                        const float4 lo = lds128(swz(ra, 2 * w)), hi = lds128(swz(ra, 2 * w + 1));
+                        qv[0] = lo.x; qv[1] = lo.y; qv[2] = lo.z; qv[3] = lo.w;
+                        qv[4] = hi.x; qv[5] = hi.y; qv[6] = hi.z; qv[7] = hi.w;
+                        if (fop != CG_FIELD_PLAIN) {              // budgets.py:151 products, :80 storage terms
+                            const uint32_t rb = stage + fb * BOX_BYTES + kk * 128;
+                            const float4 l2 = lds128(swz(rb, 2 * w)), h2 = lds128(swz(rb, 2 * w + 1));
+                            const float bv[C] = {l2.x, l2.y, l2.z, l2.w, h2.x, h2.y, h2.z, h2.w};
+#pragma unroll
+                            for (int c = 0; c < C; ++c)
+                                qv[c] = (fop == CG_FIELD_PRODUCT) ? qv[c] * bv[c] : (qv[c] - bv[c]) * finv;
+                        }
+                    }
+                    if (t == 0) {
+#pragma unroll
+                        for (int c = 0; c < C; ++c) g.q0[c * 32 + lane] = qv[c];
+                    }
+#pragma unroll
+                    for (int c = 0; c < C; ++c) {
+                        const float4 r0 = recs[(c * KC + kk) * 2], r1 = recs[(c * KC + kk) * 2 + 1];
+                        const float qn = qv[c];
+                        const float dqn = qn - A[c];                                    // delq(t)
+                        const float df2 = r0.x * dqn + r0.y * dq1[c];                   // layer t-1, mappm.f90:661
+                        const float na = -dq1[c];
+                        const float hi3 = max3(na, dqn, 0.f), nlo = min3(na, dqn, 0.f);
+                        const float dcn = max3(min3(df2, hi3, -nlo), -hi3, nlo);        // :663-665
+                        const float xn = r0.z * dq1[c] + r0.w * dcp[c] - r1.x * dcn;    // AL(t-1) - q(t-1), :674-683
+                        const float yp = xn + dq1[c];                                   // AR(t-2) - q(t-2)
+                        if (t >= 3) {
+                            float x = xp[c];
+                            if (t == 3) {                                               // column top, :689-707
+                                const float *e = g.edge + c * 24;
+                                const float q0 = g.q0[c * 32 + lane], qi = B[c], al2 = A[c] + xn;
+                                const float qm = e[0] * q0 + e[1] * qi, dq = e[2] * (qi - q0);
+                                const float c1 = (al2 - qm - e[4] * dq) * e[3];
+                                const float c3 = dq - c1 * e[5];
+                                const float inner = qm - c1 * e[6];
+                                const float edge = c1 * e[7] - c3 * e[8] + inner;
+                                const float al1 = fminf(fmaxf(inner, fminf(q0, qi)), fmaxf(q0, qi));
+                                const float4 rt = recs[(c * KC + 2) * 2 + 1];
+                                finish_layer(g, c, 2, 0, q0, edge - q0, al1 - q0, 0.5f * (al1 - q0), run[c], rt.y,
+                                             __float_as_int(rt.z), lane, V, nz, mask_below, toa);
+                                x = al1 - qi;
+                            }
+                            finish_layer(g, c, kk, t - 2, B[c], x, yp, dcp[c], run[c], r1.y, __float_as_int(r1.z),
+                                         lane, V, nz, mask_below, toa);
+                        }
+                        B[c] = A[c]; A[c] = qn; dq1[c] = dqn; dcp[c] = dcn; xp[c] = xn;
+                    }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < C; ++c) {
+                        const float4 r1 = recs[(c * KC + kk) * 2 + 1];
+                        if (t == nz) {                                                  // column bottom, :729-747
+                            const float *e = g.edge + c * 24 + 12;
+                            const float qe = A[c], qi = B[c], ali = qi + xp[c];
+                            const float qm = e[0] * qe + e[1] * qi, dq = e[2] * (qi - qe);
+                            const float c1 = (ali - qm - e[4] * dq) * e[3];
+                            const float c3 = dq - c1 * e[5];
+                            const float inner = qm - c1 * e[6];
+                            const float edge = c1 * e[7] - c3 * e[8] + inner;
+                            const float alb = fminf(fmaxf(inner, fminf(qe, qi)), fmaxf(qe, qi));
+                            finish_layer(g, c, kk, nz - 2, qi, xp[c], alb - qi, dcp[c], run[c], r1.y,
+                                         __float_as_int(r1.z), lane, V, nz, mask_below, toa);
+                            B[c] = qe; xp[c] = alb - qe; dcp[c] = 0.5f * (qe - alb); dq1[c] = edge - qe;
+                        } else if (t == nz + 1) {
+                            finish_layer(g, c, kk, nz - 1, B[c], xp[c], dq1[c], dcp[c], run[c], r1.y,
+                                         __float_as_int(r1.z), lane, V, nz, mask_below, toa);
+                        } else {                                                        // below the surface
+                            finish_layer(g, c, kk, nz, B[c], 0.f, 0.f, 0.f, run[c], 0.f, __float_as_int(r1.z),
+                                         lane, V, nz, mask_below, toa);
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bars + 8 * (NSTAGE + s));
+        }
+    }
+
+    // coarse outputs: block sum / weight sum (coarsen.py:213); 0/0 -> NaN like the reference
+    __syncwarp();
+    if (lane < V) {
+        float *out = p.outs[lane];
+        for (int k = 0; k < nz; ++k)
+            out[(o * nz + k) * hc + (long)by * nxc + cx] = g.acc[(k + 1) * V + lane] / g.den[k];
+    }
+}
+
+// fine surface pressure as regridz.py:127-147 sees it: the last interface of the sequential
+// cumsum from toa (vertically_dependent.py:61-63), bitwise
+__global__ void __launch_bounds__(256)
+surface_pressure_seq_kernel(const float *__restrict__ delp, float *__restrict__ ps, float toa,
+                            long n_outer, int nz, long h)
+{
+    const long total = n_outer * h;
+    for (long idx = blockIdx.x * (long)blockDim.x + threadIdx.x; idx < total;
+         idx += (long)gridDim.x * blockDim.x) {
+        const long o = idx / h, i = idx - o * h;
+        const float *d = delp + o * nz * h + i;
+        float pe = toa;
+        for (int k = 0; k < nz; ++k) pe = pe + ldg_stream(d + (long)k * h);
+        ps[idx] = pe;
+    }
+}
+
+// ---- host side ----------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn()
+{
+    static EncodeTiledFn fn = [] {
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess) f = nullptr;
+        return (EncodeTiledFn)f;
+    }();
+    return fn;
+}
+
+struct MapKey {
+    const void *ptr;
+    long n_outer;
+    int nz, ny, nx;
+    bool operator==(const MapKey &o) const
+    { return ptr == o.ptr && n_outer == o.n_outer && nz == o.nz && ny == o.ny && nx == o.nx; }
+};
+
+// (n_outer, nz, ny, nx) fp32 as a 3-D tensor (x, y, outer*z); box = [KC][1][32], 128B swizzle
+static int tensor_map_for(CUtensorMap *out, const float *ptr, long n_outer, int nz, int ny, int nx)
+{
+    static thread_local std::vector<std::pair<MapKey, CUtensorMap>> cache;
+    const MapKey key{ptr, n_outer, nz, ny, nx};
+    for (auto &e : cache)
+        if (e.first == key) { *out = e.second; return CG_OK; }
+    EncodeTiledFn enc = encode_fn();
+    if (!enc) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return CG_ECUDA; }
+    const cuuint64_t dims[3] = {(cuuint64_t)nx, (cuuint64_t)ny, (cuuint64_t)(n_outer * nz)};
+    const cuuint64_t strides[2] = {(cuuint64_t)nx * 4, (cuuint64_t)nx * ny * 4};
+    const cuuint32_t box[3] = {32, 1, KC};
+    const cuuint32_t es[3] = {1, 1, 1};
+    CUtensorMap m;
+    const CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void *)ptr, dims, strides, box, es,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return CG_ECUDA; }
+    if (cache.size() >= 256) cache.erase(cache.begin(), cache.begin() + 128);
+    cache.emplace_back(key, m);
+    *out = m;
+    return CG_OK;
+}
+
+}  // namespace stream
+
+int stream_supported(int nfields, int nz, int ny, int nx, int f)
+{
+    if (!(f == 8 && nx % 32 == 0 && ny % 8 == 0 && nz >= 6 && nz <= 126 && nfields >= 1)) return 0;
+    // worst case: every field has two parents
+    const stream::Layout lay = stream::make_layout(2 * nfields + 1, nz, nfields);
+    return lay.total <= 227 * 1024 - 1024;
+}
+
+long stream_workspace_bytes(long n_outer, int nz, int ny, int nx)
+{
+    const long h = (long)ny * nx, hc = (long)(ny / 8) * (nx / 8);
+    return 4 * n_outer * nz * hc + 256 + 4 * n_outer * h + 256;
+}
+
+int launch_surface_pressure_seq(const float *delp, float *ps, float toa, long n_outer, int nz, long h, cudaStream_t st)
+{
+    long b = (n_outer * h + 255) / 256;
+    const long cap = (long)sm_count() * 16;
+    stream::surface_pressure_seq_kernel<<<(unsigned)(b > cap ? cap : (b < 1 ? 1 : b)), 256, 0, st>>>(delp, ps, toa, n_outer, nz, h);
+    CG_LAUNCH_CHECK("surface_pressure_seq");
+    return CG_OK;
+}
+
+// fields/outs as in cg_pressure_level_average; delp_coarse (and psurf when mask_below) already computed
+int launch_plevel_stream(const cg_field *fields, float *const *outs, int nfields, const float *delp,
+                         const float *area, const float *delp_coarse, const float *psurf, long n_outer,
+                         int nz, int ny, int nx, int mask_below, float toa, cudaStream_t st)
+{
+    using namespace stream;
+    if (n_outer > 65535 || n_outer * nz > 0x7fffffffL) return CG_ENOTSUP;
+    static Params p;                       // ~10 KB: keep it off the stack; filled under a lock
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
+    const float *srcs[MAXSRC];
+    int nsrc = 0;
+    auto source_index = [&](const float *ptr) {
+        for (int i = 0; i < nsrc; ++i)
+            if (srcs[i] == ptr) return i;
+        srcs[nsrc] = ptr;
+        return nsrc++;
+    };
+    for (int v = 0; v < nfields; ++v) {
+        p.fa[v] = source_index(fields[v].a);
+        p.fb[v] = fields[v].op != CG_FIELD_PLAIN ? source_index(fields[v].b) : p.fa[v];
+        p.fop[v] = fields[v].op;
+        p.finv[v] = fields[v].op == CG_FIELD_DIFF ? 1.f / fields[v].scale : 1.f;
+        p.outs[v] = outs[v];
+    }
+    srcs[nsrc++] = delp;                   // delp is the last source
+    for (int i = 0; i < nsrc; ++i) {
+        if (((uintptr_t)srcs[i]) & 15) return CG_ENOTSUP;
+        const int rc = tensor_map_for(&p.maps[i], srcs[i], n_outer, nz, ny, nx);
+        if (rc) return rc;
+    }
+    const Layout lay = make_layout(nsrc, nz, nfields);
+    if (lay.total > 227 * 1024 - 1024) return CG_ENOTSUP;
+    p.area = area; p.psurf = psurf; p.delp_coarse = delp_coarse;
+    p.nsrc = nsrc; p.nfields = nfields; p.nz = nz; p.ny = ny; p.nx = nx; p.mask_below = mask_below; p.toa = toa;
+    static int max_set = 0;
+    if (lay.total > max_set) {
+        cudaError_t e = cudaFuncSetAttribute(plevel_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(plevel_stream)");
+        max_set = 227 * 1024 - 1024;
+    }
+    dim3 grid(nx / 32, ny / 8, (unsigned)n_outer);
+    plevel_stream_kernel<<<grid, NTHREADS, lay.total, st>>>(p);
+    CG_LAUNCH_CHECK("cg_pressure_level_average(stream)");
+    return CG_OK;
+}
+
+}  // namespace cg

@@ -118,14 +118,20 @@ def _plevel_case(nt, nc, f, seed, nfields=3):
     return fields, delp, area
 
 
-@pytest.mark.parametrize("impl", ["composed", "default"])
+def _pin_impl(monkeypatch, impl):
+    """composed | fused | stream pin one implementation where its shape constraints hold
+    (otherwise the next one runs); default = the library's own choice."""
+    if impl == "default":
+        monkeypatch.delenv("CG_PLEVEL_IMPL", raising=False)
+    else:
+        monkeypatch.setenv("CG_PLEVEL_IMPL", impl)
+
+
+@pytest.mark.parametrize("impl", ["composed", "fused", "stream", "default"])
 @pytest.mark.parametrize("mask_below", [False, True])
 @pytest.mark.parametrize("f,nc", [(8, 4), (2, 4), (16, 2)])  # even coarse sizes: odd = staggered in the reference
 def test_pressure_level_average_vs_oracle(ops, monkeypatch, impl, mask_below, f, nc):
-    if impl == "composed":
-        monkeypatch.setenv("CG_PLEVEL_IMPL", "composed")
-    else:
-        monkeypatch.delenv("CG_PLEVEL_IMPL", raising=False)
+    _pin_impl(monkeypatch, impl)
     fields, delp, area = _plevel_case(2, nc, f, seed=5)
     outs, dcoarse = ops.pressure_level_average([dev(x) for x in fields], dev(delp), dev(area), f,
                                                mask_below=mask_below)
@@ -142,6 +148,98 @@ def test_pressure_level_average_vs_oracle(ops, monkeypatch, impl, mask_below, f,
         ok = np.isfinite(e)
         assert np.array_equal(np.isfinite(g), ok)       # fully-masked blocks: 0/0 = NaN both sides
         assert np.abs(g[ok] - e[ok]).max() <= 3e-5 * scale
+
+
+def _check_plevel(ops, fields, delp, area, f, mask_below, descr=None, tol=3e-5):
+    """fields: numpy parents; descr: list of ("plain", i) | ("product", i, j) | ("diff", i, j, dt)."""
+    d = [dev(x) for x in fields]
+    descr = descr or [("plain", i) for i in range(len(fields))]
+    args, cpu = [], []
+    for e in descr:
+        if e[0] == "plain":
+            args.append(d[e[1]]); cpu.append(fields[e[1]])
+        elif e[0] == "product":
+            args.append(ops.product(d[e[1]], d[e[2]])); cpu.append(fields[e[1]] * fields[e[2]])
+        else:
+            args.append(ops.storage(d[e[1]], d[e[2]], e[3]))
+            cpu.append(((fields[e[1]] - fields[e[2]]) / np.float32(e[3])).astype(np.float32))
+    outs, dcoarse = ops.pressure_level_average(args, dev(delp), dev(area), f, mask_below=mask_below)
+    dc_exp = oracle.weighted_block_average(delp, area[:, None], f)
+    np.testing.assert_allclose(host(dcoarse), dc_exp, rtol=2e-6)
+    if mask_below:
+        remapped, masked = recipes.regrid_given_delp(cpu, delp, dc_exp, area)
+        exp = [oracle.weighted_block_average(r, masked, f) for r in remapped]
+    else:
+        exp = [recipes.pressure_level_average(x, delp, dc_exp, area, f) for x in cpu]
+    for g, e, x in zip(outs, exp, cpu):
+        g = host(g)
+        scale = np.nanmax(np.abs(x))
+        ok = np.isfinite(e)
+        assert np.array_equal(np.isfinite(g), ok)
+        assert np.abs(g[ok] - e[ok]).max() <= tol * scale
+
+
+@pytest.mark.parametrize("impl", ["fused", "stream"])
+@pytest.mark.parametrize("mask_below", [False, True])
+def test_pressure_level_budget_shaped_fields(ops, monkeypatch, impl, mask_below):
+    """26 output fields like a fine_res_budget timestep: 22 first moments, 2 products and 2
+    storage terms formed in the kernel from their parents (budgets.py:80, :151)."""
+    _pin_impl(monkeypatch, impl)
+    nt, nc, f = 1, 8, 8
+    ny = nx = nc * f
+    delp = syn.delp_from_ps(syn.surface_pressure((nt, ny, nx), seed=21))
+    area = syn.area((nt, ny, nx), seed=22)
+    parents = [syn.field((nt, syn.NZ, ny, nx), 30 + i, scale=10.0 ** (i % 4 - 2)) for i in range(22)]
+    begin = [parents[1] - 0.01 * syn.field((nt, syn.NZ, ny, nx), 60 + i) for i in range(2)]
+    end = [parents[1] + 0.01 * syn.field((nt, syn.NZ, ny, nx), 70 + i) for i in range(2)]
+    fields = parents + begin + end
+    descr = [("plain", i) for i in range(22)] + [("product", 1, 10), ("product", 0, 10),
+                                                  ("diff", 24, 22, 900.0), ("diff", 25, 23, 900.0)]
+    _check_plevel(ops, fields, delp, area, f, mask_below, descr)
+
+
+@pytest.mark.parametrize("impl", ["composed", "stream"])
+@pytest.mark.parametrize("mask_below", [False, True])
+@pytest.mark.parametrize("case", ["rough", "steep", "shifted_top"])
+def test_pressure_level_hard_columns(ops, monkeypatch, impl, mask_below, case):
+    """Fine columns far from their coarse mean: many coarse interfaces inside one fine layer,
+    several coarse levels below the fine surface, coarse levels above the fine top."""
+    _pin_impl(monkeypatch, impl)
+    nt, nc, f = 1, 4, 8
+    ny = nx = nc * f
+    rng = np.random.RandomState(3)
+    if case == "rough":
+        ps = 1e5 * (1.0 + 0.25 * rng.uniform(-1, 1, (nt, ny, nx)))
+        delp = syn.delp_from_ps(ps)
+    elif case == "steep":           # one thick column per block: its layers hold many coarse interfaces
+        ps = np.full((nt, ny, nx), 4e4)
+        ps[:, ::8, ::8] = 1.05e5
+        delp = syn.delp_from_ps(ps)
+    else:                           # uneven thickness profile: interfaces wander through many layers
+        delp = syn.delp_from_ps(syn.surface_pressure((nt, ny, nx), seed=4))
+        delp = (delp * rng.uniform(0.2, 3.0, delp.shape)).astype(np.float32)
+    area = syn.area((nt, ny, nx), seed=5)
+    fields = [syn.field((nt, syn.NZ, ny, nx), 80 + i, scale=10.0 ** i) for i in range(3)]
+    # thin target levels inside thick fine layers divide a small difference of pressures
+    # (mappm.f90:76-83): the 1e-6 summation-order difference in the coarse pressures is amplified
+    # by p/dp, for the CUDA paths and for the fp32 oracle alike -> 1e-4 here instead of 3e-5
+    _check_plevel(ops, fields, delp, area, f, mask_below, tol=1e-4)
+
+
+@pytest.mark.parametrize("impl", ["composed", "stream"])
+def test_pressure_level_nan_columns_are_skipped(ops, monkeypatch, impl):
+    """NaN in a fine column: the block sum skips it where the remapped value is NaN
+    (xarray's coarsen().sum() is nansum, coarsen.py:211), other levels keep the column."""
+    _pin_impl(monkeypatch, impl)
+    nt, nc, f = 1, 4, 8
+    ny = nx = nc * f
+    delp = syn.delp_from_ps(syn.surface_pressure((nt, ny, nx), seed=6))
+    area = syn.area((nt, ny, nx), seed=7)
+    fld = syn.field((nt, syn.NZ, ny, nx), 90)
+    fld[0, 40, 3, 5] = np.nan
+    fld[0, 10:14, 9, 17] = np.nan
+    area[0, 20, 20] = np.nan
+    _check_plevel(ops, [fld], delp, area, f, False)
 
 
 def test_pressure_level_golden_restart_T(ops):
