@@ -59,7 +59,7 @@ struct Params {
 // ---- shared-memory carve-up --------------------------------------------------------------------
 struct Layout {
     int ring, bars, warp0, warp_bytes;
-    int acc, rec, ev, pe1, pe2, rdp2, den, edge, colw, colps, q0, total;
+    int acc, rec, ev, pe1, pe2, rdp2, den, edge, colw, colps, nmax, total;
 };
 
 __host__ __device__ inline Layout make_layout(int nsrc, int nz, int V)
@@ -80,7 +80,7 @@ __host__ __device__ inline Layout make_layout(int nsrc, int nz, int V)
     L.edge = w;  w += C * 24 * 4;
     L.colw = w;  w += 64 * 4;                    // 64 columns at cell start, 8 per row afterwards
     L.colps = w; w += 64 * 4;
-    L.q0 = w;    w += C * 32 * 4;
+    L.nmax = w;  w += KC * 4;
     L.warp_bytes = (w + 127) & ~127;
     L.total = L.warp0 + NCELL * L.warp_bytes;
     return L;
@@ -105,7 +105,7 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, int parity)
 {
     uint32_t done = 0;
     while (!done)
-        asm volatile("{.reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p;}"
+        asm volatile("{.reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 0x989680; selp.u32 %0, 1, 0, p;}"
                      : "=r"(done) : "r"(bar), "r"(parity) : "memory");
 }
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, int x, int y, int z, uint32_t bar)
@@ -145,52 +145,64 @@ __device__ __forceinline__ uint32_t swz(uint32_t row, int chunk)
     return row + ((((row >> 7) ^ (uint32_t)chunk) & 7u) << 4);
 }
 
+__device__ __forceinline__ void sts32(uint32_t addr, float v)
+{
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void sts128(uint32_t addr, float4 v)
+{
+    asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
 // ---- geometry: what the whole warp shares ------------------------------------------------------
-// All of it is a function of pressure only (mappm.f90:41-46, :58-124, :651-683).
-struct WarpGeo {
-    float *acc, *rec, *ev, *pe1, *pe2, *rdp2, *den, *edge, *colw, *colps, *q0;
+// All of it is a function of pressure only (mappm.f90:41-46, :58-124, :651-683).  Shared-window
+// byte addresses of the warp's private arrays (uniform across the warp):
+struct WG {
+    uint32_t acc, rec, ev, pe1, pe2, rdp2, den, edge, colw, colps, nmax;
 };
 
-__device__ __forceinline__ int count_le(const float *pe2, int n, float p)
+__device__ __forceinline__ int count_le(uint32_t pe2, int n, float p)
 {   // number of target interfaces i in [0, n) with pe2[i] <= p (pe2 ascending)
     int lo = 0, hi = n;
     while (lo < hi) {
         const int mid = (lo + hi) >> 1;
-        if (pe2[mid] <= p) lo = mid + 1; else hi = mid;
+        if (lds32(pe2 + 4 * mid) <= p) lo = mid + 1; else hi = mid;
     }
     return lo;
 }
 
-// weight of fine column c in target level k times 1 / thickness of that level
-__device__ __forceinline__ float level_scale(const WarpGeo &g, int c, int k, int mask_below)
+// weight of fine column c in target level k (regridz.py:150-161 when mask_below)
+__device__ __forceinline__ float level_weight(const WG &g, int c, int k, int mask_below)
 {
-    const float w = (!mask_below || g.pe2[k + 1] < g.colps[c]) ? g.colw[c] : 0.f;   // regridz.py:150-161
-    return w * g.rdp2[k];
+    const float w = lds32(g.colw + 4 * c);
+    if (!mask_below) return w;
+    return lds32(g.pe2 + 4 * (k + 1)) < lds32(g.colps + 4 * c) ? w : 0.f;
 }
-__device__ __forceinline__ float level_weight(const WarpGeo &g, int c, int k, int mask_below)
+// ... times 1 / thickness of that level
+__device__ __forceinline__ float level_scale(const WG &g, int c, int k, int mask_below)
 {
-    return (!mask_below || g.pe2[k + 1] < g.colps[c]) ? g.colw[c] : 0.f;
+    return level_weight(g, c, k, mask_below) * lds32(g.rdp2 + 4 * k);
 }
 
 // Event of target interface i met in source layer L of column c (L == nz: below the surface).
-// Record: I = x*q + y*x' + z*y' is added (with the running sum) to the accumulator slot in the low
-// 7 bits of z; the running sum of the next target level restarts at -w * I.
-__device__ __noinline__ float4 make_event(const WarpGeo &g, int c, int L, int i, int nz, int mask_below, float toa)
+// Record (x, y, z, w):  I = x*q + y*x' + z*y'  closes a target level: run + I goes to the accumulator
+// slot held in the low 7 bits of z; the running sum of the next level restarts at -w * I.
+__device__ __forceinline__ float4 event_record(const WG &g, int c, int L, int i, int nz, int mask_below, float toa)
 {
     const int kn = nz;
     float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
     int slot = DUMMY_SLOT;
-    const float ptop_col = toa;                                         // pe1[0] of every column
     if (L < nz) {
-        const float pt = g.pe1[(L & (PRING - 1)) * C + c], pb = g.pe1[((L + 1) & (PRING - 1)) * C + c];
-        const float pi = g.pe2[i];
-        if (pi <= ptop_col) {                                           // mappm.f90:62-64, only met in L == 0
+        const float pt = lds32(g.pe1 + 4 * ((L & (PRING - 1)) * C + c));
+        const float pb = lds32(g.pe1 + 4 * (((L + 1) & (PRING - 1)) * C + c));
+        const float pi = lds32(g.pe2 + 4 * i);
+        if (pi <= toa) {                                                // mappm.f90:62-64, only met in L == 0
             if (i < kn) { e.x = level_weight(g, c, i, mask_below); slot = i + 1; }
         } else {
             const float dpl = pb - pt;
             const float s = (pi - pt) / dpl;
             const int ke = i - 1;
-            const bool end_ok = ke >= 0 && g.pe2[ke] > ptop_col;
+            const bool end_ok = ke >= 0 && lds32(g.pe2 + 4 * (ke < 0 ? 0 : ke)) > toa;
             const bool start_ok = i < kn;
             const float sc_e = end_ok ? level_scale(g, c, ke, mask_below) : 0.f;
             const float sc_s = start_ok ? level_scale(g, c, i, mask_below) : 0.f;
@@ -203,54 +215,55 @@ __device__ __noinline__ float4 make_event(const WarpGeo &g, int c, int L, int i,
             slot = end_ok ? ke + 1 : DUMMY_SLOT;
         }
     } else {                                                            // mappm.f90:65-67, :115-120
-        const float psf = g.pe1[(nz & (PRING - 1)) * C + c];
+        const float psf = lds32(g.pe1 + 4 * ((nz & (PRING - 1)) * C + c));
         const int ke = i - 1;                                           // level whose bottom is interface i
         if (ke >= 0 && ke < kn) {
-            const float top = g.pe2[ke];
+            const float top = lds32(g.pe2 + 4 * ke);
             if (top >= psf) { e.x = level_weight(g, c, ke, mask_below); slot = ke + 1; }
-            else if (top > ptop_col) { e.x = level_scale(g, c, ke, mask_below) * (g.pe2[i] - psf); slot = ke + 1; }
+            else if (top > toa) { e.x = level_scale(g, c, ke, mask_below) * (lds32(g.pe2 + 4 * i) - psf); slot = ke + 1; }
         }
     }
     e.z = __int_as_float((__float_as_int(e.z) & ~127) | slot);
     return e;
 }
-
-// Build the records of steps t0 .. t0+KC-1 (lane = (column c, step kk)); see the step loop.
-__device__ void build_chunk(const WarpGeo &g, uint32_t delp_rows /* shared addr of the delp box */,
-                            int w, int lane, int t0, int nz, int mask_below, float toa)
+// Build the records of steps t0 .. t0+KC-1; lane = (column c, step kk).  Record of step t:
+//   r0 = (E1, E2, F-1, G) and r1.x = H: PPM stencil of layer t-1 (mappm.f90:651-683, delp-only factors)
+//   r1.y = weight of the whole layer t-2 in the target level open at its bottom
+//   r1.z = first interface | count << 8 of the events of layer t-2;  r1.w = 1 if it has none
+// plus up to EVCAP event records of layer t-2 (the first one is a no-op when the layer has none).
+__device__ __forceinline__ void build_chunk(const WG &g, uint32_t delp_rows, int w, int lane, int t0, int nz,
+                                            int mask_below, float toa)
 {
     const int c = lane & 7, kk = lane >> 3, t = t0 + kk;
     // interface pressures by the reference's sequential cumsum (vertically_dependent.py:61-63)
     if (kk == 0) {
-        float pe = (t0 == 0) ? toa : g.pe1[(t0 & (PRING - 1)) * C + c];
-        if (t0 == 0) g.pe1[c] = toa;
+        float pe = (t0 == 0) ? toa : lds32(g.pe1 + 4 * ((t0 & (PRING - 1)) * C + c));
+        if (t0 == 0) sts32(g.pe1 + 4 * c, toa);
 #pragma unroll
         for (int j = 0; j < KC; ++j) {
             const int lvl = t0 + j;
             if (lvl < nz) {
                 const uint32_t row = delp_rows + j * 128;
-                const float d = lds32(swz(row, 2 * w + (c >> 2)) + (c & 3) * 4);
-                pe = pe + d;
-                g.pe1[((lvl + 1) & (PRING - 1)) * C + c] = pe;
+                pe = pe + lds32(swz(row, 2 * w + (c >> 2)) + (c & 3) * 4);
+                sts32(g.pe1 + 4 * (((lvl + 1) & (PRING - 1)) * C + c), pe);
             }
         }
     }
     __syncwarp();
-    auto P = [&](int m) { return g.pe1[(m & (PRING - 1)) * C + c]; };
-    auto DP = [&](int m) { return P(m + 1) - P(m); };                   // mappm.f90:43 (from the rounded sums)
+    auto P = [&](int m) { return lds32(g.pe1 + 4 * ((m & (PRING - 1)) * C + c)); };
 
-    // PPM stencil of layer j = t - 1 (mappm.f90:651-683 with the delp-only factors folded)
     float E1 = 0.f, E2 = 0.f, Fm = 0.f, G = 0.f, H = 0.f;
     const int j = t - 1;
     if (j >= 1 && j <= nz - 2) {
-        const float dm1 = DP(j - 1), d0 = DP(j), dp1 = DP(j + 1);
+        const float p0 = P(j - 1), p1 = P(j), p2 = P(j + 1), p3 = P(j + 2);
+        const float dm1 = p1 - p0, d0 = p2 - p1, dp1 = p3 - p2;        // mappm.f90:43 (from the rounded sums)
         const float d4 = dm1 + d0, d4p = d0 + dp1;
         const float c1 = (dm1 + 0.5f * d0) / d4p, c2 = (dp1 + 0.5f * d0) / d4;
         const float inv = d0 / (d4 + dp1);
         E1 = c1 * inv;
         E2 = c2 * inv;
         if (j >= 2) {
-            const float dm2 = DP(j - 2), d4m = dm2 + dm1;
+            const float dm2 = p0 - P(j - 2), d4m = dm2 + dm1;
             const float cq = dm1 / d4, a1 = d4m / (d4 + dm1), a2 = d4p / (d4 + d0), gg = 2.f / (d4m + d4p);
             Fm = cq * (1.f + gg * d0 * (a1 - a2)) - 1.f;
             G = gg * d0 * a2;
@@ -258,22 +271,18 @@ __device__ void build_chunk(const WarpGeo &g, uint32_t delp_rows /* shared addr 
         }
     }
     // one-sided cubics at the column ends (mappm.f90:689-747), once per column
-    if (t == 3 || t == nz) {
-        const bool top = (t == 3);
-        const float d1 = top ? DP(0) : DP(nz - 1), d2 = top ? DP(1) : DP(nz - 2);
+    if (t == 2 || t == nz) {
+        const bool top = (t == 2);
+        const int m = top ? 0 : nz - 2;
+        const float q0 = P(m), q1 = P(m + 1), q2 = P(m + 2);
+        const float d1 = top ? q1 - q0 : q2 - q1, d2 = top ? q2 - q1 : q1 - q0;
         const float D = d2 * (2.f * d2 * d2 + d1 * (d2 + 3.f * d1));
         const float Pq = d2 * (5.f * d1 + d2) - 3.f * d1 * d1;
         const float Rr = d1 * d2 * (d2 + 3.f * d1);
-        float *e = g.edge + c * 24 + (top ? 0 : 12);
-        e[0] = d2 / (d1 + d2);
-        e[1] = d1 / (d1 + d2);
-        e[2] = 2.f / (d1 + d2);
-        e[3] = (top ? 4.f : 1.f) / D;
-        e[4] = d2;
-        e[5] = (top ? 0.5f : 2.f) * Pq;
-        e[6] = (top ? 0.25f : 1.f) * Rr;
-        e[7] = (top ? 2.f : 8.f) * d1 * d1 * d1;
-        e[8] = d1;
+        const uint32_t e = g.edge + 4 * (c * 24 + (top ? 0 : 12));
+        sts128(e, make_float4(d2 / (d1 + d2), d1 / (d1 + d2), 2.f / (d1 + d2), (top ? 4.f : 1.f) / D));
+        sts128(e + 16, make_float4(d2, (top ? 0.5f : 2.f) * Pq, (top ? 0.25f : 1.f) * Rr, (top ? 2.f : 8.f) * d1 * d1 * d1));
+        sts32(e + 32, d1);
     }
     // events of layer L = t - 2 and its whole-layer weight
     const int L = t - 2, kn = nz;
@@ -286,49 +295,177 @@ __device__ void build_chunk(const WarpGeo &g, uint32_t delp_rows /* shared addr 
             const int i1 = count_le(g.pe2, kn + 1, pb);
             n = i1 - i0;
             const int ko = i1 - 1;                                      // level open at the bottom of L
-            if (ko >= 0 && ko < kn && g.pe2[ko] > toa) dpw = level_scale(g, c, ko, mask_below) * (pb - pt);
+            if (ko >= 0 && ko < kn && lds32(g.pe2 + 4 * ko) > toa) dpw = level_scale(g, c, ko, mask_below) * (pb - pt);
         } else {
             i0 = count_le(g.pe2, kn + 1, P(nz));
             n = kn + 1 - i0;
         }
         if (n < 0) n = 0;                                               // NaN / non-monotone pressures
-        if (n <= EVCAP)
-            for (int e = 0; e < n; ++e)
-                reinterpret_cast<float4 *>(g.ev)[(c * KC + kk) * EVCAP + e] = make_event(g, c, L, i0 + e, nz, mask_below, toa);
     }
-    float4 *r = reinterpret_cast<float4 *>(g.rec) + (c * KC + kk) * 2;
-    r[0] = make_float4(E1, E2, Fm, G);
-    r[1] = make_float4(H, dpw, __int_as_float(i0 | (n << 8)), 0.f);
+    const uint32_t evp = g.ev + 16 * ((c * KC + kk) * EVCAP);
+    if (n == 0) sts128(evp, make_float4(0.f, 0.f, __int_as_float(DUMMY_SLOT), 0.f));
+    const int nw = n < EVCAP ? n : EVCAP;
+    for (int e = 0; e < nw; ++e) sts128(evp + 16 * e, event_record(g, c, L, i0 + e, nz, mask_below, toa));
+    const uint32_t r = g.rec + 32 * (c * KC + kk);
+    sts128(r, make_float4(E1, E2, Fm, G));
+    sts128(r + 16, make_float4(H, dpw, __int_as_float(i0 | (n << 8)), n == 0 ? 1.f : 0.f));
+    int nm = n;                                                         // most events of any column at this step
+    nm = max(nm, __shfl_xor_sync(0xffffffffu, nm, 1));
+    nm = max(nm, __shfl_xor_sync(0xffffffffu, nm, 2));
+    nm = max(nm, __shfl_xor_sync(0xffffffffu, nm, 4));
+    if (c == 0) sts32(g.nmax + 4 * kk, (float)nm);
     __syncwarp();
 }
 
 // ---- per-field work -----------------------------------------------------------------------------
-// Limited parabola of one layer in deviation form, x = AL - q, y = AR - q, A6 = -3 (x + y)
+// one event: close a target level with run + I (NaN-skipping block sum, coarsen.py:211), restart the
+// running sum of the next one.  acc_lane = &acc[0][lane]; slot 0 collects what belongs to no level.
+__device__ __forceinline__ void apply_event(const float4 ev, float q, float x, float y, float keep, float &run,
+                                            uint32_t acc_lane, int V4, bool active)
+{
+    const float I = ev.x * q + ev.y * x + ev.z * y;
+    const float tot = run + I;
+    const uint32_t a = acc_lane + (__float_as_int(ev.z) & 127) * V4;
+    const float upd = lds32(a) + (tot == tot ? tot : 0.f);
+    asm volatile("{.reg .pred p; setp.ne.s32 p, %2, 0; @p st.shared.f32 [%0], %1;}" ::"r"(a), "f"(upd), "r"((int)active) : "memory");
+    run = keep != 0.f ? run : -(ev.w * I);
+}
+
+// events 1 .. n-1 of a layer cut by several coarse interfaces (out of line: rare)
+__device__ __noinline__ float extra_events(WG g, int c, int kk, int L, int evinfo, float q, float x, float y, float run,
+                                           uint32_t acc_lane, int V4, bool active, int nz, int mask_below, float toa)
+{
+    const int n = evinfo >> 8, i0 = evinfo & 255;
+    const uint32_t evp = g.ev + 16 * ((c * KC + kk) * EVCAP);
+    for (int e = 1; e < n; ++e) {
+        const float4 ev = e < EVCAP ? lds128(evp + 16 * e) : event_record(g, c, L, i0 + e, nz, mask_below, toa);
+        apply_event(ev, q, x, y, 0.f, run, acc_lane, V4, active);
+    }
+    return run;
+}
+
+// Limited parabola of layer L in deviation form, x = AL - q, y = AR - q, A6 = -3 (x + y)
 // (ppm_limiters lmt = 0, mappm.f90:875-894), then the events of the layer and its whole-layer term.
-__device__ __forceinline__ void finish_layer(const WarpGeo &g, int c, int kk, int L, float q, float x, float y,
-                                             float dc, float &run, float dpw, int evinfo, int lane, int V,
-                                             int nz, int mask_below, float toa)
+template <bool MULTI>
+__device__ __forceinline__ void finish_layer(const WG &g, int c, int kk, int L, float q, float x, float y, float dc,
+                                             float &run, const float4 r1, const float4 ev0, uint32_t acc_lane, int V4,
+                                             bool active, int nz, int mask_below, float toa)
 {
     const float da1 = y - x, s = x + y;
     const float t = s * da1, da2 = da1 * (da1 * (1.f / 3.f));
     const float m2x = -2.f * x, m2y = -2.f * y;
-    if (t > da2) y = m2x;              // a6da < -da2: AR = AL - 3 (AL - q)
-    else if (-t > da2) x = m2y;        // a6da >  da2: AL = AR - 3 (AR - q)
-    if (dc == 0.f) { x = 0.f; y = 0.f; }
-    const int n = evinfo >> 8;
-    if (n) {
-        const int i0 = evinfo & 255;
-        const float4 *evp = reinterpret_cast<const float4 *>(g.ev) + (c * KC + kk) * EVCAP;
-        for (int e = 0; e < n; ++e) {
-            const float4 ev = (n <= EVCAP) ? evp[e] : make_event(g, c, L, i0 + e, nz, mask_below, toa);
-            const float I = ev.x * q + ev.y * x + ev.z * y;
-            const float tot = run + I;
-            const int slot = __float_as_int(ev.z) & 127;
-            if (lane < V && tot == tot) g.acc[slot * V + lane] += tot;     // NaN-skipping block sum (coarsen.py:211)
-            run = -ev.w * I;
-        }
+    const bool c1 = t > da2, c2 = -t > da2, flat = dc == 0.f;
+    y = c1 ? m2x : y;                  // a6da < -da2: AR = AL - 3 (AL - q)
+    x = (c2 && !c1) ? m2y : x;         // a6da >  da2: AL = AR - 3 (AR - q)
+    x = flat ? 0.f : x;
+    y = flat ? 0.f : y;
+    apply_event(ev0, q, x, y, r1.w, run, acc_lane, V4, active);
+    if (MULTI) {
+        const int evinfo = __float_as_int(r1.z);
+        if ((evinfo >> 8) > 1)
+            run = extra_events(g, c, kk, L, evinfo, q, x, y, run, acc_lane, V4, active, nz, mask_below, toa);
     }
-    run = fmaf(dpw, q, run);
+    run = fmaf(r1.y, q, run);
+}
+
+// one 128-B row of a lane's own field: its 8 columns of the warp's cell
+__device__ __forceinline__ void load_row(float (&qv)[C], uint32_t stage, int kk, int w, int fa, int fb, int fop, float finv)
+{
+    const uint32_t ra = stage + fa * BOX_BYTES + kk * 128;
+    const float4 lo = lds128(swz(ra, 2 * w)), hi = lds128(swz(ra, 2 * w + 1));
+    qv[0] = lo.x; qv[1] = lo.y; qv[2] = lo.z; qv[3] = lo.w;
+    qv[4] = hi.x; qv[5] = hi.y; qv[6] = hi.z; qv[7] = hi.w;
+    if (fop != CG_FIELD_PLAIN) {                  // budgets.py:151 products, :80 storage terms
+        const uint32_t rb = stage + fb * BOX_BYTES + kk * 128;
+        const float4 l2 = lds128(swz(rb, 2 * w)), h2 = lds128(swz(rb, 2 * w + 1));
+        const float bv[C] = {l2.x, l2.y, l2.z, l2.w, h2.x, h2.y, h2.z, h2.w};
+#pragma unroll
+        for (int c = 0; c < C; ++c) qv[c] = (fop == CG_FIELD_PRODUCT) ? qv[c] * bv[c] : (qv[c] - bv[c]) * finv;
+    }
+}
+
+__device__ __forceinline__ float limited_slope(float df2, float dq_lo, float dq_hi)
+{   // mappm.f90:663-665: sign(min(|df2|, max(q-,q,q+) - q, q - min(q-,q,q+)), df2)
+    const float na = -dq_lo;
+    const float hi3 = max3(na, dq_hi, 0.f), nlo = min3(na, dq_hi, 0.f);
+    return max3(min3(df2, hi3, -nlo), -hi3, nlo);
+}
+
+
+// One step of the tandem walk for the 8 columns of a row: level t arrives, layer t-2 is finished.
+// RARE = the steps at the ends of the column (t <= 2, t >= nz); the others run the branch-free body.
+template <bool RARE>
+__device__ __forceinline__ void level_step(const WG &g, uint32_t stage, int t, int kk, int w, int fa, int fb, int fop,
+                                           float finv, float (&A)[C], float (&B)[C], float (&dq1)[C], float (&dcp)[C],
+                                           float (&xp)[C], float (&run)[C], uint32_t acc_lane, int V4,
+                                           bool active, int nz, int mask_below, float toa)
+{
+    float qv[C], q3[C];
+    if (!RARE || t < nz) load_row(qv, stage, kk, w, fa, fb, fop, finv);
+    else {
+#pragma unroll
+        for (int c = 0; c < C; ++c) qv[c] = A[c];
+    }
+    if (RARE && t == 2) load_row(q3, stage, 3, w, fa, fb, fop, finv);           // level 3 is in the same stage (KC = 4)
+    const uint32_t rk = g.rec + 32 * kk, ek = g.ev + 16 * EVCAP * kk;
+    float4 r0 = lds128(rk), r1 = lds128(rk + 16), e0 = lds128(ek);
+#pragma unroll
+    for (int c = 0; c < C; ++c) {
+        float4 r0n = r0, r1n = r1, e0n = e0;
+        if (c + 1 < C) {
+            r0n = lds128(rk + 32 * KC * (c + 1));
+            r1n = lds128(rk + 32 * KC * (c + 1) + 16);
+            e0n = lds128(ek + 16 * EVCAP * KC * (c + 1));
+        }
+        const float qn = qv[c];
+        float dqn = qn - A[c];                                              // delq(t)
+        const float df2 = r0.x * dqn + r0.y * dq1[c];                       // layer t-1, mappm.f90:661
+        float dcn = limited_slope(df2, dq1[c], dqn);                        // dc(t-1)
+        float xn = r0.z * dq1[c] + r0.w * dcp[c] - r1.x * dcn;              // AL(t-1) - q(t-1), :674-683
+        float x = xp[c], y = xn + dq1[c], dc = dcp[c];                      // layer t-2
+        if (RARE) {
+            if (t == 2) {                                                   // column top, :689-707
+                const float4 r0p = lds128(g.rec + 32 * (c * KC + 3));
+                const float Hp = lds32(g.rec + 32 * (c * KC + 3) + 16);
+                const float dq3 = q3[c] - qn;
+                const float dc2 = limited_slope(r0p.x * dq3 + r0p.y * dqn, dqn, dq3);
+                const float al2 = qn + (r0p.z * dqn + r0p.w * dcn - Hp * dc2);
+                const uint32_t e = g.edge + 4 * (c * 24);
+                const float4 ea = lds128(e), eb = lds128(e + 16);
+                const float sd1 = lds32(e + 32);
+                const float qe = B[c], qi = A[c];
+                const float qm = ea.x * qe + ea.y * qi, dq = ea.z * (qi - qe);
+                const float c1 = (al2 - qm - eb.x * dq) * ea.w;
+                const float c3 = dq - c1 * eb.y;
+                const float inner = qm - c1 * eb.z;
+                const float edge = c1 * eb.w - c3 * sd1 + inner;
+                const float al1 = fminf(fmaxf(inner, fminf(qe, qi)), fmaxf(qe, qi));
+                x = edge - qe; y = al1 - qe; dc = 0.5f * (al1 - qe);
+                xn = al1 - qi;
+            } else if (t == nz) {                                           // column bottom, :729-747
+                const uint32_t e = g.edge + 4 * (c * 24 + 12);
+                const float4 ea = lds128(e), eb = lds128(e + 16);
+                const float sd1 = lds32(e + 32);
+                const float qe = A[c], qi = B[c], ali = qi + xp[c];
+                const float qm = ea.x * qe + ea.y * qi, dq = ea.z * (qi - qe);
+                const float c1 = (ali - qm - eb.x * dq) * ea.w;
+                const float c3 = dq - c1 * eb.y;
+                const float inner = qm - c1 * eb.z;
+                const float edge = c1 * eb.w - c3 * sd1 + inner;
+                const float alb = fminf(fmaxf(inner, fminf(qe, qi)), fmaxf(qe, qi));
+                y = alb - qi;
+                xn = alb - qe; dcn = 0.5f * (qe - alb); dqn = edge - qe;    // layer nz-1, finished next step
+            } else if (t == nz + 1) {
+                y = dq1[c];
+            } else if (t > nz + 1) {                                        // below the surface
+                x = 0.f; y = 0.f; dc = 0.f;
+            }
+        }
+        if (!RARE || t >= 2)
+            finish_layer<RARE>(g, c, kk, t - 2, B[c], x, y, dc, run[c], r1, e0, acc_lane, V4, active, nz, mask_below, toa);
+        B[c] = A[c]; A[c] = qn; dq1[c] = dqn; dcp[c] = dcn; xp[c] = xn;
+        r0 = r0n; r1 = r1n; e0 = e0n;
+    }
 }
 
 __global__ void __launch_bounds__(NTHREADS, 2)
@@ -338,8 +475,9 @@ plevel_stream_kernel(const __grid_constant__ Params p)
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int nz = p.nz, V = p.nfields, nsrc = p.nsrc;
     const Layout lay = make_layout(nsrc, nz, V);
-    const uint32_t ring = smem_u32(smem + lay.ring);
-    const uint32_t bars = smem_u32(smem + lay.bars);           // full[NSTAGE], empty[NSTAGE]
+    const uint32_t sbase = smem_u32(smem);
+    const uint32_t ring = sbase + lay.ring;
+    const uint32_t bars = sbase + lay.bars;                    // full[NSTAGE], empty[NSTAGE]
     const int stage_bytes = nsrc * BOX_BYTES;
     const int nch = (nz + 3 + KC - 1) / KC;                     // steps t = 0 .. nz + 2
     const int bx = blockIdx.x, by = blockIdx.y;
@@ -372,46 +510,48 @@ plevel_stream_kernel(const __grid_constant__ Params p)
 
     // ---------------- consumers: warp w owns coarse cell (by, 4 bx + w) --------------------------
     const int w = warp;
-    unsigned char *wb = smem + lay.warp0 + w * lay.warp_bytes;
-    WarpGeo g;
-    g.acc = (float *)(wb + lay.acc);    g.rec = (float *)(wb + lay.rec);    g.ev = (float *)(wb + lay.ev);
-    g.pe1 = (float *)(wb + lay.pe1);    g.pe2 = (float *)(wb + lay.pe2);    g.rdp2 = (float *)(wb + lay.rdp2);
-    g.den = (float *)(wb + lay.den);    g.edge = (float *)(wb + lay.edge);  g.colw = (float *)(wb + lay.colw);
-    g.colps = (float *)(wb + lay.colps); g.q0 = (float *)(wb + lay.q0);
+    const uint32_t wb = sbase + lay.warp0 + w * lay.warp_bytes;
+    WG g;
+    g.acc = wb + lay.acc;   g.rec = wb + lay.rec;   g.ev = wb + lay.ev;     g.pe1 = wb + lay.pe1;
+    g.pe2 = wb + lay.pe2;   g.rdp2 = wb + lay.rdp2; g.den = wb + lay.den;   g.edge = wb + lay.edge;
+    g.colw = wb + lay.colw; g.colps = wb + lay.colps; g.nmax = wb + lay.nmax;
     const int ny = p.ny, nx = p.nx, nyc = ny >> 3, nxc = nx >> 3;
     const long h = (long)ny * nx, hc = (long)nyc * nxc;
     const int cx = 4 * bx + w;
     const float toa = p.toa;
     const int mask_below = p.mask_below;
+    const bool active = lane < V;
+    const int V4 = 4 * V;
+    const uint32_t acc_lane = g.acc + 4 * lane;
 
     // cell prologue: coarse interfaces (sequential cumsum, vertically_dependent.py:61-63), 1/thickness,
     // weights of the 64 columns, sum of weights per target level (coarsen.py:212)
-    for (int k = lane; k < nz; k += 32) g.rdp2[k] = p.delp_coarse[(o * nz + k) * hc + (long)by * nxc + cx];
-    for (int i = lane; i < (nz + 1) * V; i += 32) g.acc[i] = 0.f;
+    for (int k = lane; k < nz; k += 32) sts32(g.rdp2 + 4 * k, p.delp_coarse[(o * nz + k) * hc + (long)by * nxc + cx]);
+    for (int i = lane; i < (nz + 1) * V; i += 32) sts32(g.acc + 4 * i, 0.f);
     for (int i = lane; i < 64; i += 32) {
         const long col = o * h + (long)(8 * by + (i >> 3)) * nx + 8 * cx + (i & 7);
         const float a = p.area[col];
-        g.colw[i] = (a == a) ? a : 0.f;
-        g.colps[i] = mask_below ? p.psurf[col] : 0.f;
+        sts32(g.colw + 4 * i, (a == a) ? a : 0.f);
+        sts32(g.colps + 4 * i, mask_below ? p.psurf[col] : 0.f);
     }
     __syncwarp();
     if (lane == 0) {
         float pe = toa;
-        g.pe2[0] = pe;
-        for (int k = 0; k < nz; ++k) { pe = pe + g.rdp2[k]; g.pe2[k + 1] = pe; }
+        sts32(g.pe2, pe);
+        for (int k = 0; k < nz; ++k) { pe = pe + lds32(g.rdp2 + 4 * k); sts32(g.pe2 + 4 * (k + 1), pe); }
     }
     __syncwarp();
     for (int k = lane; k < nz; k += 32) {
-        g.rdp2[k] = 1.f / (g.pe2[k + 1] - g.pe2[k]);
-        const float lower = g.pe2[k + 1];
+        const float lower = lds32(g.pe2 + 4 * (k + 1));
+        sts32(g.rdp2 + 4 * k, 1.f / (lower - lds32(g.pe2 + 4 * k)));
         float d = 0.f;
-        for (int i = 0; i < 64; ++i) d += (!mask_below || lower < g.colps[i]) ? g.colw[i] : 0.f;
-        g.den[k] = d;
+        for (int i = 0; i < 64; ++i) d += (!mask_below || lower < lds32(g.colps + 4 * i)) ? lds32(g.colw + 4 * i) : 0.f;
+        sts32(g.den + 4 * k, d);
     }
     __syncwarp();
 
-    const int fa = lane < V ? p.fa[lane] : 0, fb = lane < V ? p.fb[lane] : 0, fop = lane < V ? p.fop[lane] : 0;
-    const float finv = lane < V ? p.finv[lane] : 1.f;
+    const int fa = active ? p.fa[lane] : 0, fb = active ? p.fb[lane] : 0, fop = active ? p.fop[lane] : 0;
+    const float finv = active ? p.finv[lane] : 1.f;
 
     for (int row = 0; row < 8; ++row) {
         // this row's 8 columns
@@ -424,9 +564,10 @@ plevel_stream_kernel(const __grid_constant__ Params p)
             cpv = mask_below ? p.psurf[col] : 0.f;
         }
         __syncwarp();
-        if (lane < C) { g.colw[lane] = cwv; g.colps[lane] = cpv; }
+        if (lane < C) { sts32(g.colw + 4 * lane, cwv); sts32(g.colps + 4 * lane, cpv); }
         __syncwarp();
 
+        // rolling state of the 8 columns: A = q(t-1), B = q(t-2), dq1 = delq(t-1), dcp = dc(t-2), xp = x(t-2)
         float A[C], B[C], dq1[C], dcp[C], xp[C], run[C];
 #pragma unroll
         for (int c = 0; c < C; ++c) { A[c] = 0.f; B[c] = 0.f; dq1[c] = 0.f; dcp[c] = 0.f; xp[c] = 0.f; run[c] = 0.f; }
@@ -437,87 +578,16 @@ plevel_stream_kernel(const __grid_constant__ Params p)
             const uint32_t stage = ring + s * stage_bytes;
             build_chunk(g, stage + (nsrc - 1) * BOX_BYTES, w, lane, t0, nz, mask_below, toa);
 
+#pragma unroll 1
             for (int kk = 0; kk < KC; ++kk) {
                 const int t = t0 + kk;
                 if (t > nz + 2) break;
-                const float4 *recs = reinterpret_cast<const float4 *>(g.rec);
-                if (t < nz) {
-                    float qv[C];
-                    {
-                        const uint32_t ra = stage + fa * BOX_BYTES + kk * 128;
-                        const float4 lo = lds128(swz(ra, 2 * w)), hi = lds128(swz(ra, 2 * w + 1));
-                        qv[0] = lo.x; qv[1] = lo.y; qv[2] = lo.z; qv[3] = lo.w;
-                        qv[4] = hi.x; qv[5] = hi.y; qv[6] = hi.z; qv[7] = hi.w;
-                        if (fop != CG_FIELD_PLAIN) {              // budgets.py:151 products, :80 storage terms
-                            const uint32_t rb = stage + fb * BOX_BYTES + kk * 128;
-                            const float4 l2 = lds128(swz(rb, 2 * w)), h2 = lds128(swz(rb, 2 * w + 1));
-                            const float bv[C] = {l2.x, l2.y, l2.z, l2.w, h2.x, h2.y, h2.z, h2.w};
-#pragma unroll
-                            for (int c = 0; c < C; ++c)
-                                qv[c] = (fop == CG_FIELD_PRODUCT) ? qv[c] * bv[c] : (qv[c] - bv[c]) * finv;
-                        }
-                    }
-                    if (t == 0) {
-#pragma unroll
-                        for (int c = 0; c < C; ++c) g.q0[c * 32 + lane] = qv[c];
-                    }
-#pragma unroll
-                    for (int c = 0; c < C; ++c) {
-                        const float4 r0 = recs[(c * KC + kk) * 2], r1 = recs[(c * KC + kk) * 2 + 1];
-                        const float qn = qv[c];
-                        const float dqn = qn - A[c];                                    // delq(t)
-                        const float df2 = r0.x * dqn + r0.y * dq1[c];                   // layer t-1, mappm.f90:661
-                        const float na = -dq1[c];
-                        const float hi3 = max3(na, dqn, 0.f), nlo = min3(na, dqn, 0.f);
-                        const float dcn = max3(min3(df2, hi3, -nlo), -hi3, nlo);        // :663-665
-                        const float xn = r0.z * dq1[c] + r0.w * dcp[c] - r1.x * dcn;    // AL(t-1) - q(t-1), :674-683
-                        const float yp = xn + dq1[c];                                   // AR(t-2) - q(t-2)
-                        if (t >= 3) {
-                            float x = xp[c];
-                            if (t == 3) {                                               // column top, :689-707
-                                const float *e = g.edge + c * 24;
-                                const float q0 = g.q0[c * 32 + lane], qi = B[c], al2 = A[c] + xn;
-                                const float qm = e[0] * q0 + e[1] * qi, dq = e[2] * (qi - q0);
-                                const float c1 = (al2 - qm - e[4] * dq) * e[3];
-                                const float c3 = dq - c1 * e[5];
-                                const float inner = qm - c1 * e[6];
-                                const float edge = c1 * e[7] - c3 * e[8] + inner;
-                                const float al1 = fminf(fmaxf(inner, fminf(q0, qi)), fmaxf(q0, qi));
-                                const float4 rt = recs[(c * KC + 2) * 2 + 1];
-                                finish_layer(g, c, 2, 0, q0, edge - q0, al1 - q0, 0.5f * (al1 - q0), run[c], rt.y,
-                                             __float_as_int(rt.z), lane, V, nz, mask_below, toa);
-                                x = al1 - qi;
-                            }
-                            finish_layer(g, c, kk, t - 2, B[c], x, yp, dcp[c], run[c], r1.y, __float_as_int(r1.z),
-                                         lane, V, nz, mask_below, toa);
-                        }
-                        B[c] = A[c]; A[c] = qn; dq1[c] = dqn; dcp[c] = dcn; xp[c] = xn;
-                    }
-                } else {
-#pragma unroll
-                    for (int c = 0; c < C; ++c) {
-                        const float4 r1 = recs[(c * KC + kk) * 2 + 1];
-                        if (t == nz) {                                                  // column bottom, :729-747
-                            const float *e = g.edge + c * 24 + 12;
-                            const float qe = A[c], qi = B[c], ali = qi + xp[c];
-                            const float qm = e[0] * qe + e[1] * qi, dq = e[2] * (qi - qe);
-                            const float c1 = (ali - qm - e[4] * dq) * e[3];
-                            const float c3 = dq - c1 * e[5];
-                            const float inner = qm - c1 * e[6];
-                            const float edge = c1 * e[7] - c3 * e[8] + inner;
-                            const float alb = fminf(fmaxf(inner, fminf(qe, qi)), fmaxf(qe, qi));
-                            finish_layer(g, c, kk, nz - 2, qi, xp[c], alb - qi, dcp[c], run[c], r1.y,
-                                         __float_as_int(r1.z), lane, V, nz, mask_below, toa);
-                            B[c] = qe; xp[c] = alb - qe; dcp[c] = 0.5f * (qe - alb); dq1[c] = edge - qe;
-                        } else if (t == nz + 1) {
-                            finish_layer(g, c, kk, nz - 1, B[c], xp[c], dq1[c], dcp[c], run[c], r1.y,
-                                         __float_as_int(r1.z), lane, V, nz, mask_below, toa);
-                        } else {                                                        // below the surface
-                            finish_layer(g, c, kk, nz, B[c], 0.f, 0.f, 0.f, run[c], 0.f, __float_as_int(r1.z),
-                                         lane, V, nz, mask_below, toa);
-                        }
-                    }
-                }
+                if (t >= 3 && t < nz && lds32(g.nmax + 4 * kk) <= 1.f)
+                    level_step<false>(g, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4,
+                                      active, nz, mask_below, toa);
+                else
+                    level_step<true>(g, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4,
+                                     active, nz, mask_below, toa);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bars + 8 * (NSTAGE + s));
@@ -526,12 +596,13 @@ plevel_stream_kernel(const __grid_constant__ Params p)
 
     // coarse outputs: block sum / weight sum (coarsen.py:213); 0/0 -> NaN like the reference
     __syncwarp();
-    if (lane < V) {
+    if (active) {
         float *out = p.outs[lane];
         for (int k = 0; k < nz; ++k)
-            out[(o * nz + k) * hc + (long)by * nxc + cx] = g.acc[(k + 1) * V + lane] / g.den[k];
+            out[(o * nz + k) * hc + (long)by * nxc + cx] = lds32(acc_lane + (k + 1) * V4) / lds32(g.den + 4 * k);
     }
 }
+
 
 // fine surface pressure as regridz.py:127-147 sees it: the last interface of the sequential
 // cumsum from toa (vertically_dependent.py:61-63), bitwise
