@@ -35,12 +35,14 @@ constexpr int NCELL = 4;             // coarse cells per CTA = consumer warps
 constexpr int KC = 4;                // levels per pipeline stage
 constexpr int BOX_ROWS = KC + 1;     // 128-B rows per source box: odd stride -> 8 distinct swizzle phases over 8 lanes
 constexpr int BOX_BYTES = BOX_ROWS * 128;
-constexpr int NSTAGE = 2;
+constexpr int NSTAGE = 2;            // == geometry buffers: both are released by the same barrier
 constexpr int MAXF = CG_MAX_FIELDS;  // output fields per launch (lanes)
-constexpr int MAXSRC = 2 * MAXF + 1; // distinct source arrays (+ delp)
+constexpr int MAXSRC = 2 * MAXF;     // distinct parent arrays
 constexpr int EVCAP = 4;             // precomputed events per (column, layer); more are formed on the fly
 constexpr int PRING = 16;            // levels kept in the interface-pressure ring
-constexpr int NTHREADS = (NCELL + 1) * 32;
+constexpr int NTHREADS = 2 * NCELL * 32;         // consumer warps + geometry warps (which also issue the TMA loads)
+constexpr int CONSUMER_REGS = 168, HELPER_REGS = 88;   // setmaxnreg targets; launch value 128 x 256 threads
+constexpr int REC_BYTES = C * KC * 32, EV_BYTES = C * KC * EVCAP * 16;
 constexpr int DUMMY_SLOT = 0;        // accumulator slot k + 1 belongs to target level k
 
 struct Params {
@@ -51,7 +53,8 @@ struct Params {
     const float *area;               // (n_outer, ny, nx)
     const float *psurf;              // (n_outer, ny, nx) sequential-cumsum surface pressure, mask_below only
     const float *delp_coarse;        // (n_outer, nz, ny/8, nx/8)
-    int nsrc;                        // TMA sources, delp last
+    const float *delp;               // (n_outer, nz, ny, nx), read by the geometry warps
+    int nsrc;                        // TMA sources (field parents)
     int nfields, nz, ny, nx, mask_below;
     float toa;
 };
@@ -67,20 +70,20 @@ __host__ __device__ inline Layout make_layout(int nsrc, int nz, int V)
     Layout L;
     int o = 0;
     L.ring = o;  o += NSTAGE * nsrc * BOX_BYTES;
-    L.bars = o;  o += 64;
+    L.bars = o;  o += 256;
     L.warp0 = o;
     int w = 0;
     L.acc = w;   w += (nz + 1) * V * 4;          w = (w + 15) & ~15;
-    L.rec = w;   w += C * KC * 32;
-    L.ev = w;    w += C * KC * EVCAP * 16;
+    L.rec = w;   w += 2 * REC_BYTES;             // double-buffered between a geometry warp and its consumer
+    L.ev = w;    w += 2 * EV_BYTES;
+    L.nmax = w;  w += 2 * KC * 4;
     L.pe1 = w;   w += PRING * C * 4;
     L.pe2 = w;   w += (nz + 2) * 4;              w = (w + 15) & ~15;
     L.rdp2 = w;  w += (nz + 1) * 4;              w = (w + 15) & ~15;
     L.den = w;   w += (nz + 1) * 4;              w = (w + 15) & ~15;
     L.edge = w;  w += C * 24 * 4;
-    L.colw = w;  w += 64 * 4;                    // 64 columns at cell start, 8 per row afterwards
+    L.colw = w;  w += 64 * 4;                    // 64 columns at cell start; [row parity][8] afterwards
     L.colps = w; w += 64 * 4;
-    L.nmax = w;  w += KC * 4;
     L.warp_bytes = (w + 127) & ~127;
     L.total = L.warp0 + NCELL * L.warp_bytes;
     return L;
@@ -200,7 +203,7 @@ __device__ __forceinline__ float4 event_record(const WG &g, int c, int L, int i,
             if (i < kn) { e.x = level_weight(g, c, i, mask_below); slot = i + 1; }
         } else {
             const float dpl = pb - pt;
-            const float s = (pi - pt) / dpl;
+            const float s = __fdividef(pi - pt, dpl);
             const int ke = i - 1;
             const bool end_ok = ke >= 0 && lds32(g.pe2 + 4 * (ke < 0 ? 0 : ke)) > toa;
             const bool start_ok = i < kn;
@@ -211,7 +214,7 @@ __device__ __forceinline__ float4 event_record(const WG &g, int c, int L, int i,
             e.x = a;
             e.y = a * oms * oms;
             e.z = -a * s * oms;
-            e.w = end_ok ? (sc_e != 0.f ? sc_s / sc_e : 0.f) : 1.f;
+            e.w = end_ok ? (sc_e != 0.f ? __fdividef(sc_s, sc_e) : 0.f) : 1.f;
             slot = end_ok ? ke + 1 : DUMMY_SLOT;
         }
     } else {                                                            // mappm.f90:65-67, :115-120
@@ -231,40 +234,40 @@ __device__ __forceinline__ float4 event_record(const WG &g, int c, int L, int i,
 //   r1.y = weight of the whole layer t-2 in the target level open at its bottom
 //   r1.z = first interface | count << 8 of the events of layer t-2;  r1.w = 1 if it has none
 // plus up to EVCAP event records of layer t-2 (the first one is a no-op when the layer has none).
-__device__ __forceinline__ void build_chunk(const WG &g, uint32_t delp_rows, int w, int lane, int t0, int nz,
+__device__ __forceinline__ void build_chunk(const WG &g, float d /* delp(t0 + kk, column c) */, int lane, int t0, int nz,
                                             int mask_below, float toa)
 {
     const int c = lane & 7, kk = lane >> 3, t = t0 + kk;
-    // interface pressures by the reference's sequential cumsum (vertically_dependent.py:61-63)
-    if (kk == 0) {
-        float pe = (t0 == 0) ? toa : lds32(g.pe1 + 4 * ((t0 & (PRING - 1)) * C + c));
-        if (t0 == 0) sts32(g.pe1 + 4 * c, toa);
+    // interface pressures by the reference's sequential cumsum (vertically_dependent.py:61-63):
+    // the running sum is handed from level to level, same order of additions
+    {
+        if (t0 == 0 && kk == 0) sts32(g.pe1 + 4 * c, toa);
+        const float pe0 = (t0 == 0) ? toa : lds32(g.pe1 + 4 * ((t0 & (PRING - 1)) * C + c));
+        float pe = 0.f;
 #pragma unroll
         for (int j = 0; j < KC; ++j) {
-            const int lvl = t0 + j;
-            if (lvl < nz) {
-                const uint32_t row = delp_rows + j * 128;
-                pe = pe + lds32(swz(row, 2 * w + (c >> 2)) + (c & 3) * 4);
-                sts32(g.pe1 + 4 * (((lvl + 1) & (PRING - 1)) * C + c), pe);
-            }
+            const float prev = __shfl_up_sync(0xffffffffu, pe, 8);
+            if (kk == j) pe = (j == 0 ? pe0 : prev) + d;
         }
+        if (t < nz) sts32(g.pe1 + 4 * (((t + 1) & (PRING - 1)) * C + c), pe);
     }
     __syncwarp();
     auto P = [&](int m) { return lds32(g.pe1 + 4 * ((m & (PRING - 1)) * C + c)); };
 
+    // (approximate division, 2 ulp: these factors multiply differences of q)
     float E1 = 0.f, E2 = 0.f, Fm = 0.f, G = 0.f, H = 0.f;
     const int j = t - 1;
     if (j >= 1 && j <= nz - 2) {
         const float p0 = P(j - 1), p1 = P(j), p2 = P(j + 1), p3 = P(j + 2);
         const float dm1 = p1 - p0, d0 = p2 - p1, dp1 = p3 - p2;        // mappm.f90:43 (from the rounded sums)
         const float d4 = dm1 + d0, d4p = d0 + dp1;
-        const float c1 = (dm1 + 0.5f * d0) / d4p, c2 = (dp1 + 0.5f * d0) / d4;
-        const float inv = d0 / (d4 + dp1);
-        E1 = c1 * inv;
-        E2 = c2 * inv;
+        const float r4 = __fdividef(1.f, d4), inv = __fdividef(d0, d4 + dp1);
+        E1 = __fdividef(dm1 + 0.5f * d0, d4p) * inv;
+        E2 = (dp1 + 0.5f * d0) * r4 * inv;
         if (j >= 2) {
             const float dm2 = p0 - P(j - 2), d4m = dm2 + dm1;
-            const float cq = dm1 / d4, a1 = d4m / (d4 + dm1), a2 = d4p / (d4 + d0), gg = 2.f / (d4m + d4p);
+            const float cq = dm1 * r4, a1 = __fdividef(d4m, d4 + dm1), a2 = __fdividef(d4p, d4 + d0);
+            const float gg = __fdividef(2.f, d4m + d4p);
             Fm = cq * (1.f + gg * d0 * (a1 - a2)) - 1.f;
             G = gg * d0 * a2;
             H = gg * dm1 * a1;
@@ -279,28 +282,28 @@ __device__ __forceinline__ void build_chunk(const WG &g, uint32_t delp_rows, int
         const float D = d2 * (2.f * d2 * d2 + d1 * (d2 + 3.f * d1));
         const float Pq = d2 * (5.f * d1 + d2) - 3.f * d1 * d1;
         const float Rr = d1 * d2 * (d2 + 3.f * d1);
+        const float r12 = 1.f / (d1 + d2);
         const uint32_t e = g.edge + 4 * (c * 24 + (top ? 0 : 12));
-        sts128(e, make_float4(d2 / (d1 + d2), d1 / (d1 + d2), 2.f / (d1 + d2), (top ? 4.f : 1.f) / D));
+        sts128(e, make_float4(d2 * r12, d1 * r12, 2.f * r12, (top ? 4.f : 1.f) / D));
         sts128(e + 16, make_float4(d2, (top ? 0.5f : 2.f) * Pq, (top ? 0.25f : 1.f) * Rr, (top ? 2.f : 8.f) * d1 * d1 * d1));
         sts32(e + 32, d1);
     }
-    // events of layer L = t - 2 and its whole-layer weight
+    // events of layer L = t - 2 and its whole-layer weight.  Interfaces at or above the bottom of a
+    // layer are counted once (binary search); the count of the layer above comes from the lane above.
     const int L = t - 2, kn = nz;
-    float dpw = 0.f;
-    int i0 = 0, n = 0;
-    if (L >= 0 && L <= nz) {
-        if (L < nz) {
-            const float pt = P(L), pb = P(L + 1);
-            i0 = (L == 0) ? 0 : count_le(g.pe2, kn + 1, pt);
-            const int i1 = count_le(g.pe2, kn + 1, pb);
-            n = i1 - i0;
-            const int ko = i1 - 1;                                      // level open at the bottom of L
-            if (ko >= 0 && ko < kn && lds32(g.pe2 + 4 * ko) > toa) dpw = level_scale(g, c, ko, mask_below) * (pb - pt);
-        } else {
-            i0 = count_le(g.pe2, kn + 1, P(nz));
-            n = kn + 1 - i0;
-        }
-        if (n < 0) n = 0;                                               // NaN / non-monotone pressures
+    float dpw = 0.f, pt = 0.f, pb = 0.f;
+    int i1 = 0;
+    if (L >= 0 && L < nz) { pt = P(L); pb = P(L + 1); i1 = count_le(g.pe2, kn + 1, pb); }
+    else if (L == nz) i1 = kn + 1;
+    int i0 = __shfl_up_sync(0xffffffffu, i1, 8);
+    if (kk == 0) i0 = __float_as_int(lds32(g.edge + 4 * (c * 24 + 22)));       // last layer of the previous chunk
+    if (L <= 0) i0 = 0;
+    if (kk == KC - 1) sts32(g.edge + 4 * (c * 24 + 22), __int_as_float(i1));
+    int n = (L >= 0 && L <= nz) ? i1 - i0 : 0;
+    if (n < 0) n = 0;                                                   // NaN / non-monotone pressures
+    if (L >= 0 && L < nz) {
+        const int ko = i1 - 1;                                          // level open at the bottom of L
+        if (ko >= 0 && ko < kn && lds32(g.pe2 + 4 * ko) > toa) dpw = level_scale(g, c, ko, mask_below) * (pb - pt);
     }
     const uint32_t evp = g.ev + 16 * ((c * KC + kk) * EVCAP);
     if (n == 0) sts128(evp, make_float4(0.f, 0.f, __int_as_float(DUMMY_SLOT), 0.f));
@@ -393,13 +396,15 @@ __device__ __forceinline__ float limited_slope(float df2, float dq_lo, float dq_
 
 
 // One step of the tandem walk for the 8 columns of a row: level t arrives, layer t-2 is finished.
-// RARE = the steps at the ends of the column (t <= 2, t >= nz); the others run the branch-free body.
-template <bool RARE>
+// MODE 0: interior level, at most one event per column (branch-free body); 1: interior level, some
+// column cut by several interfaces; 2: the ends of the column (t <= 2, t >= nz).
+template <int MODE>
 __device__ __forceinline__ void level_step(const WG &g, uint32_t stage, int t, int kk, int w, int fa, int fb, int fop,
                                            float finv, float (&A)[C], float (&B)[C], float (&dq1)[C], float (&dcp)[C],
                                            float (&xp)[C], float (&run)[C], uint32_t acc_lane, int V4,
                                            bool active, int nz, int mask_below, float toa)
 {
+    constexpr bool RARE = MODE == 2;
     float qv[C], q3[C];
     if (!RARE || t < nz) load_row(qv, stage, kk, w, fa, fb, fop, finv);
     else {
@@ -462,13 +467,15 @@ __device__ __forceinline__ void level_step(const WG &g, uint32_t stage, int t, i
             }
         }
         if (!RARE || t >= 2)
-            finish_layer<RARE>(g, c, kk, t - 2, B[c], x, y, dc, run[c], r1, e0, acc_lane, V4, active, nz, mask_below, toa);
+            finish_layer<MODE != 0>(g, c, kk, t - 2, B[c], x, y, dc, run[c], r1, e0, acc_lane, V4, active, nz, mask_below, toa);
         B[c] = A[c]; A[c] = qn; dq1[c] = dqn; dcp[c] = dcn; xp[c] = xn;
         r0 = r0n; r1 = r1n; e0 = e0n;
     }
 }
 
-__global__ void __launch_bounds__(NTHREADS, 2)
+// 128 registers at launch (2 CTAs of 256 threads per SM); the consumer warpgroup then takes 168 and the
+// geometry warpgroup drops to 88 (setmaxnreg)
+__global__ void __maxnreg__(128)
 plevel_stream_kernel(const __grid_constant__ Params p)
 {
     extern __shared__ __align__(1024) unsigned char smem[];
@@ -477,7 +484,9 @@ plevel_stream_kernel(const __grid_constant__ Params p)
     const Layout lay = make_layout(nsrc, nz, V);
     const uint32_t sbase = smem_u32(smem);
     const uint32_t ring = sbase + lay.ring;
-    const uint32_t bars = sbase + lay.bars;                    // full[NSTAGE], empty[NSTAGE]
+    // barriers: full[NSTAGE], empty[NSTAGE] (field ring); gfull[NCELL][2], gempty[NCELL][2] (geometry buffers)
+    const uint32_t bars = sbase + lay.bars;
+    const uint32_t gbars = bars + 8 * 2 * NSTAGE;
     const int stage_bytes = nsrc * BOX_BYTES;
     const int nch = (nz + 3 + KC - 1) / KC;                     // steps t = 0 .. nz + 2
     const int bx = blockIdx.x, by = blockIdx.y;
@@ -485,109 +494,143 @@ plevel_stream_kernel(const __grid_constant__ Params p)
 
     if (tid == 0) {
         for (int s = 0; s < NSTAGE; ++s) {
-            mbar_init(bars + 8 * s, 1);
-            mbar_init(bars + 8 * (NSTAGE + s), NCELL);
+            mbar_init(bars + 8 * s, NCELL);                 // full: one expect_tx arrival per geometry warp
+            mbar_init(bars + 8 * (NSTAGE + s), NCELL);      // empty: one arrival per consumer warp
         }
+        for (int i = 0; i < 2 * NCELL; ++i) mbar_init(gbars + 8 * i, 1);
         asm volatile("fence.mbarrier_init.release.cluster;");
     }
     __syncthreads();
 
-    if (warp == NCELL) {
-        // ---------------- producer: one TMA box per source array and stage -------------------
-        const int total = 8 * nch;
-        for (int it = 0; it < total; ++it) {
-            const int s = it % NSTAGE;
-            if (it >= NSTAGE) mbar_wait(bars + 8 * (NSTAGE + s), ((it / NSTAGE) - 1) & 1);
-            const int row = it / nch, chunk = it - row * nch;
-            if (lane == 0) mbar_expect_tx(bars + 8 * s, nsrc * KC * 128);
-            __syncwarp();
-            for (int src = lane; src < nsrc; src += 32)
-                tma_load_3d(ring + s * stage_bytes + src * BOX_BYTES, &p.maps[src], 32 * bx, 8 * by + row,
-                            (int)(o * nz) + chunk * KC, bars + 8 * s);
-        }
-        return;
-    }
-
-    // ---------------- consumers: warp w owns coarse cell (by, 4 bx + w) --------------------------
-    const int w = warp;
+    const int w = warp & (NCELL - 1);                           // the cell this warp works for
     const uint32_t wb = sbase + lay.warp0 + w * lay.warp_bytes;
     WG g;
     g.acc = wb + lay.acc;   g.rec = wb + lay.rec;   g.ev = wb + lay.ev;     g.pe1 = wb + lay.pe1;
     g.pe2 = wb + lay.pe2;   g.rdp2 = wb + lay.rdp2; g.den = wb + lay.den;   g.edge = wb + lay.edge;
     g.colw = wb + lay.colw; g.colps = wb + lay.colps; g.nmax = wb + lay.nmax;
+    const uint32_t gfull = gbars + 8 * (2 * w);
     const int ny = p.ny, nx = p.nx, nyc = ny >> 3, nxc = nx >> 3;
     const long h = (long)ny * nx, hc = (long)nyc * nxc;
     const int cx = 4 * bx + w;
     const float toa = p.toa;
     const int mask_below = p.mask_below;
+
+    if (warp >= NCELL) {
+        // ---------------- geometry warp of cell w: everything that depends on pressure only ---------
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(HELPER_REGS));
+        // cell prologue: coarse interfaces (sequential cumsum, vertically_dependent.py:61-63), 1/thickness,
+        // sum of the 64 columns' weights per target level (coarsen.py:212)
+        for (int k = lane; k < nz; k += 32) sts32(g.rdp2 + 4 * k, p.delp_coarse[(o * nz + k) * hc + (long)by * nxc + cx]);
+        for (int i = lane; i < 64; i += 32) {
+            const long col = o * h + (long)(8 * by + (i >> 3)) * nx + 8 * cx + (i & 7);
+            const float a = p.area[col];
+            sts32(g.colw + 4 * i, (a == a) ? a : 0.f);
+            sts32(g.colps + 4 * i, mask_below ? p.psurf[col] : 0.f);
+        }
+        __syncwarp();
+        if (lane == 0) {
+            float pe = toa;
+            sts32(g.pe2, pe);
+            for (int k = 0; k < nz; ++k) { pe = pe + lds32(g.rdp2 + 4 * k); sts32(g.pe2 + 4 * (k + 1), pe); }
+        }
+        __syncwarp();
+        for (int k = lane; k < nz; k += 32) {
+            const float lower = lds32(g.pe2 + 4 * (k + 1));
+            sts32(g.rdp2 + 4 * k, 1.f / (lower - lds32(g.pe2 + 4 * k)));
+            float d = 0.f;
+            for (int i = 0; i < 64; ++i) d += (!mask_below || lower < lds32(g.colps + 4 * i)) ? lds32(g.colw + 4 * i) : 0.f;
+            sts32(g.den + 4 * k, d);
+        }
+        __syncwarp();
+
+        const int c = lane & 7, kk = lane >> 3;
+        const float *dcol = p.delp + o * nz * h + (long)(8 * by) * nx + 8 * cx + c;
+        auto load_delp = [&](int row, int chunk) {
+            const int lvl = chunk * KC + kk;
+            return lvl < nz ? ldg_stream(dcol + (long)lvl * h + (long)row * nx) : 0.f;
+        };
+        float dnext = load_delp(0, 0);
+        for (int row = 0; row < 8; ++row) {
+            // this row's 8 columns, double-buffered by row parity (the consumer may still be on the previous row)
+            WG gr = g;
+            gr.colw = g.colw + 32 * (row & 1);
+            gr.colps = g.colps + 32 * (row & 1);
+            if (lane < C) {
+                const long col = o * h + (long)(8 * by + row) * nx + 8 * cx + lane;
+                const float a = p.area[col];
+                sts32(gr.colw + 4 * lane, (a == a) ? a : 0.f);
+                sts32(gr.colps + 4 * lane, mask_below ? p.psurf[col] : 0.f);
+            }
+            __syncwarp();
+            for (int chunk = 0; chunk < nch; ++chunk) {
+                const int it = row * nch + chunk, b = it & 1;
+                const float d = dnext;
+                if (chunk + 1 < nch) dnext = load_delp(row, chunk + 1);
+                else if (row + 1 < 8) dnext = load_delp(row + 1, 0);
+                // stage b of the field ring and geometry buffer b are released together by the consumers
+                if (it >= 2) mbar_wait(bars + 8 * (NSTAGE + b), ((it >> 1) - 1) & 1);
+                {   // this warp's share of the TMA boxes: parents w, w + 4, ...
+                    const int mine = (nsrc - w + NCELL - 1) / NCELL;
+                    if (lane == 0) mbar_expect_tx(bars + 8 * b, mine * KC * 128);
+                    __syncwarp();
+                    const int src = w + NCELL * lane;
+                    if (lane < mine)
+                        tma_load_3d(ring + b * stage_bytes + src * BOX_BYTES, &p.maps[src], 32 * bx, 8 * by + row,
+                                    (int)(o * nz) + chunk * KC, bars + 8 * b);
+                }
+                WG gb = gr;
+                gb.rec = g.rec + b * REC_BYTES;
+                gb.ev = g.ev + b * EV_BYTES;
+                gb.nmax = g.nmax + b * KC * 4;
+                build_chunk(gb, d, lane, chunk * KC, nz, mask_below, toa);
+                if (lane == 0) mbar_arrive(gfull + 8 * b);
+            }
+        }
+        return;
+    }
+
+    // ---------------- consumer warp of cell (by, 4 bx + w): lanes = fields ----------------------------
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CONSUMER_REGS));
     const bool active = lane < V;
     const int V4 = 4 * V;
     const uint32_t acc_lane = g.acc + 4 * lane;
-
-    // cell prologue: coarse interfaces (sequential cumsum, vertically_dependent.py:61-63), 1/thickness,
-    // weights of the 64 columns, sum of weights per target level (coarsen.py:212)
-    for (int k = lane; k < nz; k += 32) sts32(g.rdp2 + 4 * k, p.delp_coarse[(o * nz + k) * hc + (long)by * nxc + cx]);
     for (int i = lane; i < (nz + 1) * V; i += 32) sts32(g.acc + 4 * i, 0.f);
-    for (int i = lane; i < 64; i += 32) {
-        const long col = o * h + (long)(8 * by + (i >> 3)) * nx + 8 * cx + (i & 7);
-        const float a = p.area[col];
-        sts32(g.colw + 4 * i, (a == a) ? a : 0.f);
-        sts32(g.colps + 4 * i, mask_below ? p.psurf[col] : 0.f);
-    }
     __syncwarp();
-    if (lane == 0) {
-        float pe = toa;
-        sts32(g.pe2, pe);
-        for (int k = 0; k < nz; ++k) { pe = pe + lds32(g.rdp2 + 4 * k); sts32(g.pe2 + 4 * (k + 1), pe); }
-    }
-    __syncwarp();
-    for (int k = lane; k < nz; k += 32) {
-        const float lower = lds32(g.pe2 + 4 * (k + 1));
-        sts32(g.rdp2 + 4 * k, 1.f / (lower - lds32(g.pe2 + 4 * k)));
-        float d = 0.f;
-        for (int i = 0; i < 64; ++i) d += (!mask_below || lower < lds32(g.colps + 4 * i)) ? lds32(g.colw + 4 * i) : 0.f;
-        sts32(g.den + 4 * k, d);
-    }
-    __syncwarp();
-
     const int fa = active ? p.fa[lane] : 0, fb = active ? p.fb[lane] : 0, fop = active ? p.fop[lane] : 0;
     const float finv = active ? p.finv[lane] : 1.f;
 
     for (int row = 0; row < 8; ++row) {
-        // this row's 8 columns
-        __syncwarp();
-        float cwv = 0.f, cpv = 0.f;
-        if (lane < C) {
-            const long col = o * h + (long)(8 * by + row) * nx + 8 * cx + lane;
-            const float a = p.area[col];
-            cwv = (a == a) ? a : 0.f;
-            cpv = mask_below ? p.psurf[col] : 0.f;
-        }
-        __syncwarp();
-        if (lane < C) { sts32(g.colw + 4 * lane, cwv); sts32(g.colps + 4 * lane, cpv); }
-        __syncwarp();
-
         // rolling state of the 8 columns: A = q(t-1), B = q(t-2), dq1 = delq(t-1), dcp = dc(t-2), xp = x(t-2)
         float A[C], B[C], dq1[C], dcp[C], xp[C], run[C];
 #pragma unroll
         for (int c = 0; c < C; ++c) { A[c] = 0.f; B[c] = 0.f; dq1[c] = 0.f; dcp[c] = 0.f; xp[c] = 0.f; run[c] = 0.f; }
+        WG gr = g;
+        gr.colw = g.colw + 32 * (row & 1);
+        gr.colps = g.colps + 32 * (row & 1);
 
         for (int chunk = 0; chunk < nch; ++chunk) {
-            const int it = row * nch + chunk, s = it % NSTAGE, t0 = chunk * KC;
+            const int it = row * nch + chunk, s = it % NSTAGE, b = it & 1, t0 = chunk * KC;
+            mbar_wait(gfull + 8 * b, (it >> 1) & 1);
             mbar_wait(bars + 8 * s, (it / NSTAGE) & 1);
             const uint32_t stage = ring + s * stage_bytes;
-            build_chunk(g, stage + (nsrc - 1) * BOX_BYTES, w, lane, t0, nz, mask_below, toa);
-
+            WG gb = gr;
+            gb.rec = g.rec + b * REC_BYTES;
+            gb.ev = g.ev + b * EV_BYTES;
+            gb.nmax = g.nmax + b * KC * 4;
 #pragma unroll 1
             for (int kk = 0; kk < KC; ++kk) {
                 const int t = t0 + kk;
                 if (t > nz + 2) break;
-                if (t >= 3 && t < nz && lds32(g.nmax + 4 * kk) <= 1.f)
-                    level_step<false>(g, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4,
-                                      active, nz, mask_below, toa);
+                const bool interior = t >= 3 && t < nz;
+                if (interior && lds32(gb.nmax + 4 * kk) <= 1.f)
+                    level_step<0>(gb, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4, active,
+                                  nz, mask_below, toa);
+                else if (interior)
+                    level_step<1>(gb, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4, active,
+                                  nz, mask_below, toa);
                 else
-                    level_step<true>(g, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4,
-                                     active, nz, mask_below, toa);
+                    level_step<2>(gb, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4, active,
+                                  nz, mask_below, toa);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bars + 8 * (NSTAGE + s));
@@ -602,7 +645,6 @@ plevel_stream_kernel(const __grid_constant__ Params p)
             out[(o * nz + k) * hc + (long)by * nxc + cx] = lds32(acc_lane + (k + 1) * V4) / lds32(g.den + 4 * k);
     }
 }
-
 
 // fine surface pressure as regridz.py:127-147 sees it: the last interface of the sequential
 // cumsum from toa (vertically_dependent.py:61-63), bitwise
@@ -676,7 +718,7 @@ int stream_supported(int nfields, int nz, int ny, int nx, int f)
 {
     if (!(f == 8 && nx % 32 == 0 && ny % 8 == 0 && nz >= 6 && nz <= 126 && nfields >= 1)) return 0;
     // worst case: every field has two parents
-    const stream::Layout lay = stream::make_layout(2 * nfields + 1, nz, nfields);
+    const stream::Layout lay = stream::make_layout(2 * nfields, nz, nfields);
     return lay.total <= 227 * 1024 - 1024;
 }
 
@@ -720,7 +762,7 @@ int launch_plevel_stream(const cg_field *fields, float *const *outs, int nfields
         p.finv[v] = fields[v].op == CG_FIELD_DIFF ? 1.f / fields[v].scale : 1.f;
         p.outs[v] = outs[v];
     }
-    srcs[nsrc++] = delp;                   // delp is the last source
+    if (((uintptr_t)delp) & 3) return CG_ENOTSUP;
     for (int i = 0; i < nsrc; ++i) {
         if (((uintptr_t)srcs[i]) & 15) return CG_ENOTSUP;
         const int rc = tensor_map_for(&p.maps[i], srcs[i], n_outer, nz, ny, nx);
@@ -728,12 +770,14 @@ int launch_plevel_stream(const cg_field *fields, float *const *outs, int nfields
     }
     const Layout lay = make_layout(nsrc, nz, nfields);
     if (lay.total > 227 * 1024 - 1024) return CG_ENOTSUP;
-    p.area = area; p.psurf = psurf; p.delp_coarse = delp_coarse;
+    p.area = area; p.psurf = psurf; p.delp_coarse = delp_coarse; p.delp = delp;
     p.nsrc = nsrc; p.nfields = nfields; p.nz = nz; p.ny = ny; p.nx = nx; p.mask_below = mask_below; p.toa = toa;
     static int max_set = 0;
     if (lay.total > max_set) {
         cudaError_t e = cudaFuncSetAttribute(plevel_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
         if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(plevel_stream)");
+        e = cudaFuncSetAttribute(plevel_stream_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(carveout)");
         max_set = 227 * 1024 - 1024;
     }
     dim3 grid(nx / 32, ny / 8, (unsigned)n_outer);
