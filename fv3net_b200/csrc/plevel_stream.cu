@@ -111,6 +111,17 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, int parity)
         asm volatile("{.reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 0x989680; selp.u32 %0, 1, 0, p;}"
                      : "=r"(done) : "r"(bar), "r"(parity) : "memory");
 }
+// wait of a warp that is ahead of its partner: sleep between polls instead of spinning on the issue port
+__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, int parity)
+{
+    uint32_t done = 0;
+    for (;;) {
+        asm volatile("{.reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p;}"
+                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+        if (done) break;
+        __nanosleep(400);
+    }
+}
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, int x, int y, int z, uint32_t bar)
 {
     asm volatile(
@@ -349,7 +360,6 @@ __device__ __noinline__ float extra_events(WG g, int c, int kk, int L, int evinf
 
 // Limited parabola of layer L in deviation form, x = AL - q, y = AR - q, A6 = -3 (x + y)
 // (ppm_limiters lmt = 0, mappm.f90:875-894), then the events of the layer and its whole-layer term.
-template <bool MULTI>
 __device__ __forceinline__ void finish_layer(const WG &g, int c, int kk, int L, float q, float x, float y, float dc,
                                              float &run, const float4 r1, const float4 ev0, uint32_t acc_lane, int V4,
                                              bool active, int nz, int mask_below, float toa)
@@ -363,12 +373,48 @@ __device__ __forceinline__ void finish_layer(const WG &g, int c, int kk, int L, 
     x = flat ? 0.f : x;
     y = flat ? 0.f : y;
     apply_event(ev0, q, x, y, r1.w, run, acc_lane, V4, active);
-    if (MULTI) {
-        const int evinfo = __float_as_int(r1.z);
-        if ((evinfo >> 8) > 1)
-            run = extra_events(g, c, kk, L, evinfo, q, x, y, run, acc_lane, V4, active, nz, mask_below, toa);
-    }
+    const int evinfo = __float_as_int(r1.z);
+    if (evinfo >= (2 << 8))            // a layer cut by several coarse interfaces: the others out of line
+        run = extra_events(g, c, kk, L, evinfo, q, x, y, run, acc_lane, V4, active, nz, mask_below, toa);
     run = fmaf(r1.y, q, run);
+}
+
+// one-sided cubic at the column top (mappm.f90:689-707), evaluated at step t = 2 once level 3 is
+// visible: returns (x, y, dc) of layer 0 and x of layer 1
+__device__ __noinline__ float4 top_fix(uint32_t rec3, uint32_t edge, float qn, float dqn, float dcn, float q1, float q0, float q3)
+{
+    const float4 r0p = lds128(rec3);
+    const float Hp = lds32(rec3 + 16);
+    const float dq3 = q3 - qn;
+    const float df2 = r0p.x * dq3 + r0p.y * dqn;
+    const float na = -dqn;
+    const float hi3 = max3(na, dq3, 0.f), nlo = min3(na, dq3, 0.f);
+    const float dc2 = max3(min3(df2, hi3, -nlo), -hi3, nlo);
+    const float al2 = qn + (r0p.z * dqn + r0p.w * dcn - Hp * dc2);
+    const float4 ea = lds128(edge), eb = lds128(edge + 16);
+    const float sd1 = lds32(edge + 32);
+    const float qm = ea.x * q0 + ea.y * q1, dq = ea.z * (q1 - q0);
+    const float c1 = (al2 - qm - eb.x * dq) * ea.w;
+    const float c3 = dq - c1 * eb.y;
+    const float inner = qm - c1 * eb.z;
+    const float top = c1 * eb.w - c3 * sd1 + inner;
+    const float al1 = fminf(fmaxf(inner, fminf(q0, q1)), fmaxf(q0, q1));
+    return make_float4(top - q0, al1 - q0, 0.5f * (al1 - q0), al1 - q1);
+}
+
+// ... and at the bottom (:729-747), at step t = nz: returns y of layer nz-2 and (x, dc, y) of layer nz-1
+__device__ __noinline__ float4 bottom_fix(uint32_t edge, float qe, float qi, float xi)
+{
+    const float4 ea = lds128(edge), eb = lds128(edge + 16);
+    const float sd1 = lds32(edge + 32);
+    const float ali = qi + xi;
+    const float qm = ea.x * qe + ea.y * qi, dq = ea.z * (qi - qe);
+    const float c1 = (ali - qm - eb.x * dq) * ea.w;
+    const float c3 = dq - c1 * eb.y;
+    const float inner = qm - c1 * eb.z;
+    const float bot = c1 * eb.w - c3 * sd1 + inner;
+    const float alb = fminf(fmaxf(inner, fminf(qe, qi)), fmaxf(qe, qi));
+    return make_float4(alb - qi, alb - qe, 0.5f * (qe - alb), bot - qe);
 }
 
 // one 128-B row of a lane's own field: its 8 columns of the warp's cell
@@ -396,22 +442,21 @@ __device__ __forceinline__ float limited_slope(float df2, float dq_lo, float dq_
 
 
 // One step of the tandem walk for the 8 columns of a row: level t arrives, layer t-2 is finished.
-// MODE 0: interior level, at most one event per column (branch-free body); 1: interior level, some
-// column cut by several interfaces; 2: the ends of the column (t <= 2, t >= nz).
-template <int MODE>
+// Steps t < 2 finish nothing (their records hold a no-op event and zero weights); the steps at the ends
+// of the column (t == 2, t >= nz) patch in the one-sided cubics.
 __device__ __forceinline__ void level_step(const WG &g, uint32_t stage, int t, int kk, int w, int fa, int fb, int fop,
                                            float finv, float (&A)[C], float (&B)[C], float (&dq1)[C], float (&dcp)[C],
                                            float (&xp)[C], float (&run)[C], uint32_t acc_lane, int V4,
                                            bool active, int nz, int mask_below, float toa)
 {
-    constexpr bool RARE = MODE == 2;
     float qv[C], q3[C];
-    if (!RARE || t < nz) load_row(qv, stage, kk, w, fa, fb, fop, finv);
+    const bool ends = (t == 2) || (t >= nz);
+    if (t < nz) load_row(qv, stage, kk, w, fa, fb, fop, finv);
     else {
 #pragma unroll
         for (int c = 0; c < C; ++c) qv[c] = A[c];
     }
-    if (RARE && t == 2) load_row(q3, stage, 3, w, fa, fb, fop, finv);           // level 3 is in the same stage (KC = 4)
+    if (t == 2) load_row(q3, stage, 3, w, fa, fb, fop, finv);           // level 3 is in the same stage (KC = 4)
     const uint32_t rk = g.rec + 32 * kk, ek = g.ev + 16 * EVCAP * kk;
     float4 r0 = lds128(rk), r1 = lds128(rk + 16), e0 = lds128(ek);
 #pragma unroll
@@ -428,46 +473,20 @@ __device__ __forceinline__ void level_step(const WG &g, uint32_t stage, int t, i
         float dcn = limited_slope(df2, dq1[c], dqn);                        // dc(t-1)
         float xn = r0.z * dq1[c] + r0.w * dcp[c] - r1.x * dcn;              // AL(t-1) - q(t-1), :674-683
         float x = xp[c], y = xn + dq1[c], dc = dcp[c];                      // layer t-2
-        if (RARE) {
-            if (t == 2) {                                                   // column top, :689-707
-                const float4 r0p = lds128(g.rec + 32 * (c * KC + 3));
-                const float Hp = lds32(g.rec + 32 * (c * KC + 3) + 16);
-                const float dq3 = q3[c] - qn;
-                const float dc2 = limited_slope(r0p.x * dq3 + r0p.y * dqn, dqn, dq3);
-                const float al2 = qn + (r0p.z * dqn + r0p.w * dcn - Hp * dc2);
-                const uint32_t e = g.edge + 4 * (c * 24);
-                const float4 ea = lds128(e), eb = lds128(e + 16);
-                const float sd1 = lds32(e + 32);
-                const float qe = B[c], qi = A[c];
-                const float qm = ea.x * qe + ea.y * qi, dq = ea.z * (qi - qe);
-                const float c1 = (al2 - qm - eb.x * dq) * ea.w;
-                const float c3 = dq - c1 * eb.y;
-                const float inner = qm - c1 * eb.z;
-                const float edge = c1 * eb.w - c3 * sd1 + inner;
-                const float al1 = fminf(fmaxf(inner, fminf(qe, qi)), fmaxf(qe, qi));
-                x = edge - qe; y = al1 - qe; dc = 0.5f * (al1 - qe);
-                xn = al1 - qi;
-            } else if (t == nz) {                                           // column bottom, :729-747
-                const uint32_t e = g.edge + 4 * (c * 24 + 12);
-                const float4 ea = lds128(e), eb = lds128(e + 16);
-                const float sd1 = lds32(e + 32);
-                const float qe = A[c], qi = B[c], ali = qi + xp[c];
-                const float qm = ea.x * qe + ea.y * qi, dq = ea.z * (qi - qe);
-                const float c1 = (ali - qm - eb.x * dq) * ea.w;
-                const float c3 = dq - c1 * eb.y;
-                const float inner = qm - c1 * eb.z;
-                const float edge = c1 * eb.w - c3 * sd1 + inner;
-                const float alb = fminf(fmaxf(inner, fminf(qe, qi)), fmaxf(qe, qi));
-                y = alb - qi;
-                xn = alb - qe; dcn = 0.5f * (qe - alb); dqn = edge - qe;    // layer nz-1, finished next step
+        if (ends) {
+            if (t == 2) {
+                const float4 r = top_fix(g.rec + 32 * (c * KC + 3), g.edge + 4 * (c * 24), qn, dqn, dcn, A[c], B[c], q3[c]);
+                x = r.x; y = r.y; dc = r.z; xn = r.w;
+            } else if (t == nz) {
+                const float4 r = bottom_fix(g.edge + 4 * (c * 24 + 12), A[c], B[c], xp[c]);
+                y = r.x; xn = r.y; dcn = r.z; dqn = r.w;                    // layer nz-1 is finished next step
             } else if (t == nz + 1) {
                 y = dq1[c];
-            } else if (t > nz + 1) {                                        // below the surface
+            } else {                                                        // below the surface
                 x = 0.f; y = 0.f; dc = 0.f;
             }
         }
-        if (!RARE || t >= 2)
-            finish_layer<MODE != 0>(g, c, kk, t - 2, B[c], x, y, dc, run[c], r1, e0, acc_lane, V4, active, nz, mask_below, toa);
+        finish_layer(g, c, kk, t - 2, B[c], x, y, dc, run[c], r1, e0, acc_lane, V4, active, nz, mask_below, toa);
         B[c] = A[c]; A[c] = qn; dq1[c] = dqn; dcp[c] = dcn; xp[c] = xn;
         r0 = r0n; r1 = r1n; e0 = e0n;
     }
@@ -568,7 +587,7 @@ plevel_stream_kernel(const __grid_constant__ Params p)
                 if (chunk + 1 < nch) dnext = load_delp(row, chunk + 1);
                 else if (row + 1 < 8) dnext = load_delp(row + 1, 0);
                 // stage b of the field ring and geometry buffer b are released together by the consumers
-                if (it >= 2) mbar_wait(bars + 8 * (NSTAGE + b), ((it >> 1) - 1) & 1);
+                if (it >= 2) mbar_wait_relaxed(bars + 8 * (NSTAGE + b), ((it >> 1) - 1) & 1);
                 {   // this warp's share of the TMA boxes: parents w, w + 4, ...
                     const int mine = (nsrc - w + NCELL - 1) / NCELL;
                     if (lane == 0) mbar_expect_tx(bars + 8 * b, mine * KC * 128);
@@ -621,16 +640,8 @@ plevel_stream_kernel(const __grid_constant__ Params p)
             for (int kk = 0; kk < KC; ++kk) {
                 const int t = t0 + kk;
                 if (t > nz + 2) break;
-                const bool interior = t >= 3 && t < nz;
-                if (interior && lds32(gb.nmax + 4 * kk) <= 1.f)
-                    level_step<0>(gb, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4, active,
-                                  nz, mask_below, toa);
-                else if (interior)
-                    level_step<1>(gb, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4, active,
-                                  nz, mask_below, toa);
-                else
-                    level_step<2>(gb, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4, active,
-                                  nz, mask_below, toa);
+                level_step(gb, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4, active,
+                           nz, mask_below, toa);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bars + 8 * (NSTAGE + s));
