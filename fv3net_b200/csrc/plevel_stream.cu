@@ -119,7 +119,7 @@ __device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, int parity)
         asm volatile("{.reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p;}"
                      : "=r"(done) : "r"(bar), "r"(parity) : "memory");
         if (done) break;
-        __nanosleep(400);
+        __nanosleep(1500);
     }
 }
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, int x, int y, int z, uint32_t bar)
@@ -360,6 +360,7 @@ __device__ __noinline__ float extra_events(WG g, int c, int kk, int L, int evinf
 
 // Limited parabola of layer L in deviation form, x = AL - q, y = AR - q, A6 = -3 (x + y)
 // (ppm_limiters lmt = 0, mappm.f90:875-894), then the events of the layer and its whole-layer term.
+template <bool GENERAL>
 __device__ __forceinline__ void finish_layer(const WG &g, int c, int kk, int L, float q, float x, float y, float dc,
                                              float &run, const float4 r1, const float4 ev0, uint32_t acc_lane, int V4,
                                              bool active, int nz, int mask_below, float toa)
@@ -373,9 +374,11 @@ __device__ __forceinline__ void finish_layer(const WG &g, int c, int kk, int L, 
     x = flat ? 0.f : x;
     y = flat ? 0.f : y;
     apply_event(ev0, q, x, y, r1.w, run, acc_lane, V4, active);
-    const int evinfo = __float_as_int(r1.z);
-    if (evinfo >= (2 << 8))            // a layer cut by several coarse interfaces: the others out of line
-        run = extra_events(g, c, kk, L, evinfo, q, x, y, run, acc_lane, V4, active, nz, mask_below, toa);
+    if (GENERAL) {
+        const int evinfo = __float_as_int(r1.z);
+        if (evinfo >= (2 << 8))        // a layer cut by several coarse interfaces: the others out of line
+            run = extra_events(g, c, kk, L, evinfo, q, x, y, run, acc_lane, V4, active, nz, mask_below, toa);
+    }
     run = fmaf(r1.y, q, run);
 }
 
@@ -443,20 +446,22 @@ __device__ __forceinline__ float limited_slope(float df2, float dq_lo, float dq_
 
 // One step of the tandem walk for the 8 columns of a row: level t arrives, layer t-2 is finished.
 // Steps t < 2 finish nothing (their records hold a no-op event and zero weights); the steps at the ends
-// of the column (t == 2, t >= nz) patch in the one-sided cubics.
+// of the column (t == 2, t >= nz) patch in the one-sided cubics.  GENERAL = false is the straight-line body
+// for interior levels where no column is cut by more than one coarse interface (the 8 columns interleave).
+template <bool GENERAL>
 __device__ __forceinline__ void level_step(const WG &g, uint32_t stage, int t, int kk, int w, int fa, int fb, int fop,
                                            float finv, float (&A)[C], float (&B)[C], float (&dq1)[C], float (&dcp)[C],
                                            float (&xp)[C], float (&run)[C], uint32_t acc_lane, int V4,
                                            bool active, int nz, int mask_below, float toa)
 {
     float qv[C], q3[C];
-    const bool ends = (t == 2) || (t >= nz);
-    if (t < nz) load_row(qv, stage, kk, w, fa, fb, fop, finv);
+    const bool ends = GENERAL && ((t == 2) || (t >= nz));
+    if (!GENERAL || t < nz) load_row(qv, stage, kk, w, fa, fb, fop, finv);
     else {
 #pragma unroll
         for (int c = 0; c < C; ++c) qv[c] = A[c];
     }
-    if (t == 2) load_row(q3, stage, 3, w, fa, fb, fop, finv);           // level 3 is in the same stage (KC = 4)
+    if (GENERAL && t == 2) load_row(q3, stage, 3, w, fa, fb, fop, finv);           // level 3 is in the same stage (KC = 4)
     const uint32_t rk = g.rec + 32 * kk, ek = g.ev + 16 * EVCAP * kk;
     float4 r0 = lds128(rk), r1 = lds128(rk + 16), e0 = lds128(ek);
 #pragma unroll
@@ -473,7 +478,7 @@ __device__ __forceinline__ void level_step(const WG &g, uint32_t stage, int t, i
         float dcn = limited_slope(df2, dq1[c], dqn);                        // dc(t-1)
         float xn = r0.z * dq1[c] + r0.w * dcp[c] - r1.x * dcn;              // AL(t-1) - q(t-1), :674-683
         float x = xp[c], y = xn + dq1[c], dc = dcp[c];                      // layer t-2
-        if (ends) {
+        if (GENERAL && ends) {
             if (t == 2) {
                 const float4 r = top_fix(g.rec + 32 * (c * KC + 3), g.edge + 4 * (c * 24), qn, dqn, dcn, A[c], B[c], q3[c]);
                 x = r.x; y = r.y; dc = r.z; xn = r.w;
@@ -486,7 +491,7 @@ __device__ __forceinline__ void level_step(const WG &g, uint32_t stage, int t, i
                 x = 0.f; y = 0.f; dc = 0.f;
             }
         }
-        finish_layer(g, c, kk, t - 2, B[c], x, y, dc, run[c], r1, e0, acc_lane, V4, active, nz, mask_below, toa);
+        finish_layer<GENERAL>(g, c, kk, t - 2, B[c], x, y, dc, run[c], r1, e0, acc_lane, V4, active, nz, mask_below, toa);
         B[c] = A[c]; A[c] = qn; dq1[c] = dqn; dcp[c] = dcn; xp[c] = xn;
         r0 = r0n; r1 = r1n; e0 = e0n;
     }
@@ -640,8 +645,12 @@ plevel_stream_kernel(const __grid_constant__ Params p)
             for (int kk = 0; kk < KC; ++kk) {
                 const int t = t0 + kk;
                 if (t > nz + 2) break;
-                level_step(gb, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4, active,
-                           nz, mask_below, toa);
+                if (t >= 3 && t < nz && lds32(gb.nmax + 4 * kk) <= 1.f)
+                    level_step<false>(gb, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4,
+                                      active, nz, mask_below, toa);
+                else
+                    level_step<true>(gb, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4,
+                                     active, nz, mask_below, toa);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bars + 8 * (NSTAGE + s));
