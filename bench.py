@@ -82,7 +82,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "10",
                  "-i", str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -112,6 +112,20 @@ class ClockSampler:
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def traffic_from_profiles(spec):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the
+    committed `ncu --set full` capture (profiles/traffic.json names the capture and its workload);
+    None when the workload differs from the captured one."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(path):
+        return None, None
+    with open(path) as f:
+        t = json.load(f)
+    if t.get("plevel_cells") != spec["plevel_cells"]:
+        return None, None
+    return float(t["dram_bytes_read"]) + float(t["dram_bytes_write"]), t.get("source")
 
 
 def peaks():
@@ -271,17 +285,20 @@ def run_ours(args):
         threads = os.cpu_count() or 1
         fields, delp, area = cpu_sample_inputs(spec, args.cpu_fields)
         cpu_pass(fields[:1], delp, area, spec["f"], threads)       # warm
-        t0 = time.perf_counter()
-        cpu_pass(fields, delp, area, spec["f"], threads)
+        t0, passes = time.perf_counter(), 0
+        while passes < 4 and time.perf_counter() - t0 < 10.0:      # about 10-20 s of CPU work
+            cpu_pass(fields, delp, area, spec["f"], threads)
+            passes += 1
         dt = time.perf_counter() - t0
-        cpu = {"value": args.cpu_fields * spec["nz"] * spec["n"] ** 2 / dt, "unit": UNIT,
+        cpu = {"value": passes * args.cpu_fields * spec["nz"] * spec["n"] ** 2 / dt, "unit": UNIT,
                "cores": threads, "kind": "port",
-               "sample": f"tile 0 of 6, {args.cpu_fields} of {spec['n3_out']} 3-D fields, "
+               "sample": f"tile 0 of 6, {args.cpu_fields} of {spec['n3_out']} 3-D fields, {passes} passes, "
                          f"reference-shaped numpy passes + C restatement of mappm.f90, {dt:.1f} s"}
 
     if rank == 0:
         peak, peak_src = peaks()
         achieved = spec["plevel_bytes"] / (plevel_ms * 1e-3) / 1e9
+        traffic, traffic_src = (args.traffic, "--traffic") if args.traffic else traffic_from_profiles(spec)
         line = {
             "metric": METRIC, "value": world * spec["cells"] / (ms_per_step * 1e-3), "unit": UNIT,
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
@@ -289,8 +306,10 @@ def run_ours(args):
             "data": "synthetic", "config": config_dict(spec, args), "clocks": clocks, "e2e": e2e,
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": args.traffic,
-                         "kernel": "pressure-level group (cg_pressure_level_average)",
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "kernel": "cg::stream::plevel_stream_kernel, timed with its two small "
+                                   "prologue launches (delp block average, surface pressure) as "
+                                   "one cg_pressure_level_average call",
                          "ms": plevel_ms, "algorithmic_bytes": spec["plevel_bytes"],
                          "peak_source": peak_src,
                          "impl": os.environ.get("CG_PLEVEL_IMPL", "default")},
@@ -363,11 +382,13 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--tiles", type=int, default=6)
     ap.add_argument("--n", type=int, default=384, help="fine grid size per tile edge (C384)")
-    ap.add_argument("--cpu-fields", type=int, default=2, help="3-D fields in the bounded CPU sample")
+    ap.add_argument("--cpu-fields", type=int, default=26,
+                    help="3-D fields of tile 0 in the bounded CPU sample (26 = every remapped field)")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--traffic", type=float, default=None,
-                    help="dram bytes per launch of the dominant kernel from an ncu capture")
+                    help="dram bytes per launch of the dominant kernel; default: the committed "
+                         "ncu capture named in profiles/traffic.json")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
