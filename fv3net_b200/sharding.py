@@ -1,0 +1,155 @@
+"""Sharding of the coarse-graining path over the GPUs of one box (one process per GPU).
+
+Every coarse cell depends only on its own f x f block of fine columns, so the path
+partitions with no data-path exchange.  Work is split the way the reference
+splits it - by time first (fine_res_budget/budget/pipeline.py:46-53 hands one timestep to
+one worker) - then by tile, then by bands of rows that are multiples of the coarsening
+factor.  The only collective is an optional gather of the (64x smaller) coarse outputs onto
+one rank for a consumer that wants the global coarse field; ranks that write their own
+region, as the reference's workers do, never communicate.
+"""
+from collections import OrderedDict, namedtuple
+
+import torch
+import torch.distributed as dist
+
+Shard = namedtuple("Shard", "time tile0 tile1 row0 row1")
+
+
+def split_range(n, parts, index, multiple=1):
+    """[start, stop) of part `index` of `n` items in `parts` contiguous, balanced pieces whose
+    boundaries are multiples of `multiple` (the remainder goes to the leading pieces)."""
+    if n % multiple:
+        raise ValueError(f"{n} is not a multiple of {multiple}")
+    units = n // multiple
+    base, extra = divmod(units, parts)
+    start = index * base + min(index, extra)
+    stop = start + base + (1 if index < extra else 0)
+    return start * multiple, stop * multiple
+
+
+def plan(n_time, world, n_tile=6, ny=None, factor=1):
+    """Shards for every rank: a list (one entry per rank) of lists of `Shard`.
+
+    n_time >= world: whole timesteps, dealt in contiguous runs.  Fewer timesteps than ranks:
+    the ranks are divided among the timesteps and each group splits its timestep by tile, and
+    (more ranks than tiles) each tile by row bands that are multiples of `factor`."""
+    if world < 1 or n_time < 1:
+        raise ValueError("need at least one rank and one timestep")
+    shards = [[] for _ in range(world)]
+    if n_time >= world:
+        for r in range(world):
+            t0, t1 = split_range(n_time, world, r)
+            shards[r] = [Shard(t, 0, n_tile, 0, ny) for t in range(t0, t1)]
+        return shards
+    for t in range(n_time):
+        r0, r1 = split_range(world, n_time, t)                 # ranks working on timestep t
+        group = r1 - r0
+        if group <= n_tile:
+            for g in range(group):
+                a, b = split_range(n_tile, group, g)
+                shards[r0 + g].append(Shard(t, a, b, 0, ny))
+            continue
+        if ny is None:
+            raise ValueError("ny is needed to split tiles into row bands")
+        for tile in range(n_tile):                             # ranks of the group over one tile
+            g0, g1 = split_range(group, n_tile, tile)
+            bands = g1 - g0
+            if bands == 0:
+                raise ValueError(f"{group} ranks cannot be divided over {n_tile} tiles")
+            if ny // factor < bands:
+                raise ValueError(f"{ny} rows give fewer than {bands} bands of {factor} rows")
+            for b in range(bands):
+                y0, y1 = split_range(ny, bands, b, multiple=factor)
+                shards[r0 + g0 + b].append(Shard(t, tile, tile + 1, y0, y1))
+    return shards
+
+
+def take(shard, array, time_axis=0, tile_axis=1, row_axis=-2):
+    """The part of a (time, tile, ..., y, x) array a shard owns (a view).  `time_axis=None`:
+    the array has no time dim (grid data such as area: (tile, y, x), tile_axis=0)."""
+    if time_axis is not None:
+        idx = [slice(None)] * array.ndim
+        idx[time_axis] = shard.time
+        array = array[tuple(idx)]
+        tile_axis = tile_axis - 1 if tile_axis > time_axis else tile_axis
+    idx = [slice(None)] * array.ndim
+    idx[tile_axis] = slice(shard.tile0, shard.tile1)
+    if shard.row1 is not None:
+        idx[row_axis] = slice(shard.row0, shard.row1)
+    return array[tuple(idx)]
+
+
+def coarse_shape(shard, lead, ny, nx, factor):
+    """Shape of a shard's coarse output: (tiles, *lead, rows / f, nx / f)."""
+    rows = (shard.row1 if shard.row1 is not None else ny) - shard.row0
+    return (shard.tile1 - shard.tile0,) + tuple(lead) + (rows // factor, nx // factor)
+
+
+def gather_coarse(local, shards, shapes, dst=0, group=None):
+    """One collective per step: every rank's coarse outputs onto rank `dst`.
+
+    local:  {name: [tensor per shard of this rank]} in the order of `shards[rank]`
+    shapes: {name: (lead, ny, nx, factor)} describing every output (same on all ranks)
+    Returns on `dst` {name: {shard: tensor}} for every shard of every rank, elsewhere None.
+    The buffers are padded to the largest rank's size so a plain gather (NCCL or gloo) works
+    for ragged plans; the plan is known everywhere, so no sizes are exchanged."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    names = list(shapes)
+
+    def rank_numel(r):
+        total = 0
+        for name in names:
+            lead, ny, nx, f = shapes[name]
+            for s in shards[r]:
+                n = 1
+                for d in coarse_shape(s, lead, ny, nx, f):
+                    n *= d
+                total += n
+        return total
+
+    longest = max(rank_numel(r) for r in range(world))
+    first = next(iter(local.values()))[0] if local and shards[rank] else None
+    device = first.device if first is not None else torch.device("cpu")
+    dtype = first.dtype if first is not None else torch.float32
+    buf = torch.zeros(max(longest, 1), dtype=dtype, device=device)
+    pos = 0
+    for name in names:
+        for t in local.get(name, []):
+            flat = t.reshape(-1)
+            buf[pos:pos + flat.numel()] = flat
+            pos += flat.numel()
+    if pos != rank_numel(rank):
+        raise ValueError(f"rank {rank} packed {pos} values, the plan says {rank_numel(rank)}")
+    parts = [torch.empty_like(buf) for _ in range(world)] if rank == dst else None
+    if world > 1:
+        dist.gather(buf, parts, dst=dst, group=group)
+    else:
+        parts = [buf]
+    if rank != dst:
+        return None
+    out = OrderedDict((name, OrderedDict()) for name in names)
+    for r in range(world):
+        pos = 0
+        for name in names:
+            lead, ny, nx, f = shapes[name]
+            for s in shards[r]:
+                shape = coarse_shape(s, lead, ny, nx, f)
+                n = 1
+                for d in shape:
+                    n *= d
+                out[name][s] = parts[r][pos:pos + n].reshape(shape)
+                pos += n
+    return out
+
+
+def assemble(gathered, n_time, n_tile, lead, ny, nx, factor):
+    """{shard: tensor} of one output -> the global (time, tile, *lead, ny/f, nx/f) tensor."""
+    first = next(iter(gathered.values()))
+    full = torch.empty((n_time, n_tile) + tuple(lead) + (ny // factor, nx // factor),
+                       dtype=first.dtype, device=first.device)
+    for s, t in gathered.items():
+        r0 = s.row0 // factor
+        r1 = (s.row1 if s.row1 is not None else ny) // factor
+        full[s.time, s.tile0:s.tile1, ..., r0:r1, :] = t
+    return full

@@ -1,0 +1,85 @@
+"""Multi-GPU host logic on CPU: the shard plan, and a world_size-2 `gloo` run in which each
+rank coarse-grains its shards (the oracle stands in for the kernels here: tests may use it)
+and the gathered, re-assembled result equals the unsharded one bit for bit."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import oracle
+from fv3net_b200 import sharding as S
+
+
+def test_split_range_balanced_and_aligned():
+    assert [S.split_range(10, 3, i) for i in range(3)] == [(0, 4), (4, 7), (7, 10)]
+    assert [S.split_range(384, 5, i, multiple=8) for i in range(5)] == [
+        (0, 80), (80, 160), (160, 240), (240, 312), (312, 384)]
+    with pytest.raises(ValueError):
+        S.split_range(10, 2, 0, multiple=4)
+
+
+@pytest.mark.parametrize("n_time,world", [(8, 8), (12, 8), (1, 1), (3, 2), (1, 2), (1, 6), (2, 8), (1, 8), (1, 12)])
+def test_plan_covers_everything_once(n_time, world):
+    n_tile, ny, f = 6, 48, 8
+    shards = S.plan(n_time, world, n_tile=n_tile, ny=ny, factor=f)
+    assert len(shards) == world
+    cover = np.zeros((n_time, n_tile, ny), int)
+    for rank_shards in shards:
+        for s in rank_shards:
+            r1 = ny if s.row1 is None else s.row1
+            assert s.row0 % f == 0 and r1 % f == 0
+            cover[s.time, s.tile0:s.tile1, s.row0:r1] += 1
+    assert (cover == 1).all()
+    if n_time >= world:                                   # the reference's partition: whole timesteps
+        assert all(s.tile0 == 0 and s.tile1 == n_tile for r in shards for s in r)
+        counts = [len(r) for r in shards]
+        assert max(counts) - min(counts) <= 1
+    else:
+        assert all(len(r) >= 1 for r in shards)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, n_time, n_tile, case, result_file):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        nz, ny, nx, f = 3, 16, 16, 4
+        rng = np.random.RandomState(7)
+        field = rng.uniform(-1000, 1000, (n_time, n_tile, nz, ny, nx)).astype(np.float32)
+        area = rng.uniform(0.5, 1, (n_tile, ny, nx)).astype(np.float32)
+        shards = S.plan(n_time, world, n_tile=n_tile, ny=ny, factor=f)
+        local = {"q": [], "area": []}
+        for s in shards[rank]:
+            q = S.take(s, field)                                           # (tiles, nz, rows, nx)
+            a = S.take(s, area, time_axis=None, tile_axis=0)               # same tiles / rows of area
+            local["q"].append(torch.from_numpy(oracle.weighted_block_average(q, a[:, None], f)))
+            local["area"].append(torch.from_numpy(oracle.block_sum(a, f)))
+        shapes = {"q": ((nz,), ny, nx, f), "area": ((), ny, nx, f)}
+        gathered = S.gather_coarse(local, shards, shapes, dst=0)
+        if rank == 0:
+            got_q = S.assemble(gathered["q"], n_time, n_tile, (nz,), ny, nx, f).numpy()
+            got_a = S.assemble(gathered["area"], n_time, n_tile, (), ny, nx, f).numpy()
+            exp_q = np.stack([oracle.weighted_block_average(field[t], area[:, None], f) for t in range(n_time)])
+            exp_a = np.stack([oracle.block_sum(area, f)] * n_time)
+            np.save(result_file, np.array([np.array_equal(got_q, exp_q), np.array_equal(got_a, exp_a)]))
+        else:
+            assert gathered is None
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n_time,n_tile,case", [(4, 6, "by time"), (3, 6, "ragged by time"),
+                                                (1, 6, "by tile"), (1, 1, "by row band")])
+def test_world_size_2_gloo_matches_unsharded(tmp_path, n_time, n_tile, case):
+    result_file = str(tmp_path / "ok.npy")
+    mp.spawn(_worker, args=(2, _free_port(), n_time, n_tile, case, result_file), nprocs=2, join=True)
+    assert np.load(result_file).all(), case
