@@ -8,8 +8,9 @@
  *       mappm.mappm(pe1, q1, pe2, i1, i2, iv, kord, ptop) -> q2, regridz.py:273)
  *
  * Conventions
- *   - every pointer is a DEVICE pointer owned by the caller (no allocation here
- *     except cg_malloc/cg_free helpers); `stream` is a cudaStream_t passed as
+ *   - every pointer is a DEVICE pointer owned by the caller (scratch is either a
+ *     caller-provided workspace or stream-ordered cudaMallocAsync/cudaFreeAsync
+ *     inside the call); `stream` is a cudaStream_t passed as
  *     void* (NULL = legacy default stream); calls are asynchronous on it;
  *   - arrays are dense, row-major, horizontal dims last: (n_outer, nz, ny, nx),
  *     2-D weights (n_outer, ny, nx); n_outer folds tile/time/anything else;

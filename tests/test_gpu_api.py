@@ -479,3 +479,40 @@ def test_regrid_to_edge_weighted_pressure(edge):
     exp_fields, exp_masked = recipes.regrid_to_edge_weighted_pressure([wind], delp, length, f, edge=edge)
     np.testing.assert_array_equal(masked.values, exp_masked)
     assert np.abs(regridded["w"].values - exp_fields[0]).max() <= 3e-5 * 1000
+
+
+# ================================================================= the f2py ABI (test_mappm.py)
+def test_mappm_module_is_a_drop_in_for_the_f2py_one():
+    """external/vcm/tests/test_mappm.py:5-44 verbatim, against `fv3net_b200.mappm`."""
+    from fv3net_b200 import mappm
+
+    p_in = np.asarray([0.0, 1.0, 2.0, 3.0, 4.0, 5.0])[None, :]
+    f_in = np.asarray([0.0, 1.0, 2.0, 3.0, 4.0])[None, :]
+    p_out = np.asarray([0.5, 1.2, 2.4, 2.8, 3.2, 4.5])[None, :]
+    n_columns, iv, kord, dummy_ptop = 1.0, 1.0, 1.0, 0.0
+    result = mappm.mappm(p_in, f_in, p_out, 1, n_columns, iv, kord, dummy_ptop)
+    assert result.dtype == np.float32
+    np.testing.assert_almost_equal(result, np.asarray([[0.35, 1.3, 2.1, 2.5, 3.35]], np.float32), decimal=5)
+
+    p_in = np.asarray([1.0, 2.0, 3.0, 4.0, 5.0])[None, :]
+    f_in = np.asarray([1.5, 2.5, 3.5, 4.5])[None, :]
+    p_out = np.asarray([0.0, 2.5, 3.5, 4.5, 50.0])[None, :]
+    result = mappm.mappm(p_in, f_in, p_out, 1, n_columns, iv, kord, dummy_ptop)
+    np.testing.assert_almost_equal(result, np.asarray([[1.5, 3.0, 4.0, 4.502747]], np.float32), decimal=5)
+
+    p_in = np.asarray([1.0, 2.0, 3.0, 2.0, 5.0])[None, :]
+    f_in = np.asarray([np.nan, np.nan, np.nan, np.nan])[None, :]
+    result = mappm.mappm(p_in, f_in, p_out, 1, n_columns, iv, kord, dummy_ptop)
+    np.testing.assert_almost_equal(result, np.asarray([[np.nan] * 4], np.float32))
+
+
+def test_mappm_module_many_columns_bit_exact():
+    from fv3net_b200 import mappm
+
+    rng = np.random.RandomState(2)
+    n, km, kn = 1000, 79, 40
+    pe1 = 300 + np.concatenate([np.zeros((n, 1)), np.cumsum(rng.uniform(50, 2000, (n, km)), 1)], 1)
+    pe2 = 300 + np.concatenate([np.zeros((n, 1)), np.cumsum(rng.uniform(100, 4000, (n, kn)), 1)], 1)
+    q1 = rng.uniform(-1000, 1000, (n, km))
+    got = mappm.mappm(pe1, q1, pe2, 1, n, 1, 1, 0.0)
+    np.testing.assert_array_equal(got, oracle.mappm(pe1, q1, pe2))
