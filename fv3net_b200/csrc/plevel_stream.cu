@@ -38,22 +38,28 @@ constexpr int BOX_BYTES = BOX_ROWS * 128;
 constexpr int NSTAGE = 2;            // == geometry buffers: both are released by the same barrier
 constexpr int MAXF = CG_MAX_FIELDS;  // output fields per launch (lanes)
 constexpr int MAXSRC = 2 * MAXF;     // distinct parent arrays
-constexpr int EVCAP = 4;             // precomputed events per (column, layer); more are formed on the fly
 constexpr int PRING = 16;            // levels kept in the interface-pressure ring
 constexpr int NTHREADS = 2 * NCELL * 32;         // consumer warps + geometry warps (which also issue the TMA loads)
-constexpr int CONSUMER_REGS = 168, HELPER_REGS = 88;   // setmaxnreg targets; launch value 128 x 256 threads
-constexpr int REC_BYTES = C * KC * 32, EV_BYTES = C * KC * EVCAP * 16;
+constexpr int CONSUMER_REGS = 184, HELPER_REGS = 72;   // setmaxnreg targets; launch value 128 x 256 threads
+// geometry record of one step and one PAIR of adjacent columns (a, b): 6 x 16 B, pair-interleaved so that
+// the field warps load every coefficient as an f32x2 operand
+//   +0  E1a E1b E2a E2b | +16 Fa Fb Ga Gb | +32 -Ha -Hb dpwa dpwb | +48 exa exb eya eyb
+//   +64 eza ezb -ewa -ewb | +80 offa offb infoa infob   (off = accumulator byte offset, info = i0 | n << 8)
+constexpr int REC_BLOCK = 96;
+constexpr int REC_BYTES = KC * (C / 2) * REC_BLOCK;
+constexpr int ACC_STRIDE = 128;      // bytes per accumulator slot: one float per lane
 constexpr int DUMMY_SLOT = 0;        // accumulator slot k + 1 belongs to target level k
 
 struct Params {
     CUtensorMap maps[MAXSRC];
     float *outs[MAXF];
-    int fa[MAXF], fb[MAXF], fop[MAXF];
-    float finv[MAXF];                // 1 / scale of CG_FIELD_DIFF
+    int fa[MAXF], fb[MAXF];          // TMA sources of the parents (fb = fa for a plain field)
     const float *area;               // (n_outer, ny, nx)
     const float *psurf;              // (n_outer, ny, nx) sequential-cumsum surface pressure, mask_below only
     const float *delp_coarse;        // (n_outer, nz, ny/8, nx/8)
     const float *delp;               // (n_outer, nz, ny, nx), read by the geometry warps
+    float fc1[MAXF], fc2[MAXF], fc3[MAXF];   // q = (a - c1 b) (c2 b + c3): plain (0,0,1), product (0,1,0), diff (1,0,1/scale)
+    int any_derived;                 // some field is a product or a difference
     int nsrc;                        // TMA sources (field parents)
     int nfields, nz, ny, nx, mask_below;
     float toa;
@@ -62,20 +68,20 @@ struct Params {
 // ---- shared-memory carve-up --------------------------------------------------------------------
 struct Layout {
     int ring, bars, warp0, warp_bytes;
-    int acc, rec, ev, pe1, pe2, rdp2, den, edge, colw, colps, nmax, total;
+    int acc, rec, pe1, pe2, rdp2, den, edge, colw, colps, nmax, total;
 };
 
 __host__ __device__ inline Layout make_layout(int nsrc, int nz, int V)
 {
     Layout L;
+    (void)V;
     int o = 0;
     L.ring = o;  o += NSTAGE * nsrc * BOX_BYTES;
     L.bars = o;  o += 256;
     L.warp0 = o;
     int w = 0;
-    L.acc = w;   w += (nz + 1) * V * 4;          w = (w + 15) & ~15;
+    L.acc = w;   w += (nz + 1) * ACC_STRIDE;
     L.rec = w;   w += 2 * REC_BYTES;             // double-buffered between a geometry warp and its consumer
-    L.ev = w;    w += 2 * EV_BYTES;
     L.nmax = w;  w += 2 * KC * 4;
     L.pe1 = w;   w += PRING * C * 4;
     L.pe2 = w;   w += (nz + 2) * 4;              w = (w + 15) & ~15;
@@ -168,11 +174,58 @@ __device__ __forceinline__ void sts128(uint32_t addr, float4 v)
     asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 
+// ---- f32x2: two adjacent columns per instruction (FFMA2 / FADD2 / FMUL2: one issue slot, two results) ----
+typedef unsigned long long u64;
+__device__ __forceinline__ u64 pk(float lo, float hi)
+{
+    u64 r;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void upk(u64 v, float &lo, float &hi)
+{
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c)
+{
+    u64 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ u64 add2(u64 a, u64 b)
+{
+    u64 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ u64 sub2(u64 a, u64 b)
+{
+    u64 r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ u64 mul2(u64 a, u64 b)
+{
+    u64 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ void lds2x64(uint32_t addr, u64 &a, u64 &b)
+{
+    asm volatile("ld.shared.v2.b64 {%0,%1}, [%2];" : "=l"(a), "=l"(b) : "r"(addr));
+}
+__device__ __forceinline__ int4 lds128i(uint32_t addr)
+{
+    int4 v;
+    asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+
 // ---- geometry: what the whole warp shares ------------------------------------------------------
 // All of it is a function of pressure only (mappm.f90:41-46, :58-124, :651-683).  Shared-window
 // byte addresses of the warp's private arrays (uniform across the warp):
 struct WG {
-    uint32_t acc, rec, ev, pe1, pe2, rdp2, den, edge, colw, colps, nmax;
+    uint32_t acc, rec, pe1, pe2, rdp2, den, edge, colw, colps, nmax;
 };
 
 __device__ __forceinline__ int count_le(uint32_t pe2, int n, float p)
@@ -199,13 +252,14 @@ __device__ __forceinline__ float level_scale(const WG &g, int c, int k, int mask
 }
 
 // Event of target interface i met in source layer L of column c (L == nz: below the surface).
-// Record (x, y, z, w):  I = x*q + y*x' + z*y'  closes a target level: run + I goes to the accumulator
-// slot held in the low 7 bits of z; the running sum of the next level restarts at -w * I.
-__device__ __forceinline__ float4 event_record(const WG &g, int c, int L, int i, int nz, int mask_below, float toa)
+// Record (x, y, z, w):  I = x*q + y*x' + z*y'  closes a target level: run + I goes to accumulator
+// slot `slot`; the running sum of the next level restarts at -w * I.
+__device__ __forceinline__ float4 event_record(const WG &g, int c, int L, int i, int nz, int mask_below, float toa,
+                                               int &slot)
 {
     const int kn = nz;
     float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
-    int slot = DUMMY_SLOT;
+    slot = DUMMY_SLOT;
     if (L < nz) {
         const float pt = lds32(g.pe1 + 4 * ((L & (PRING - 1)) * C + c));
         const float pb = lds32(g.pe1 + 4 * (((L + 1) & (PRING - 1)) * C + c));
@@ -237,14 +291,13 @@ __device__ __forceinline__ float4 event_record(const WG &g, int c, int L, int i,
             else if (top > toa) { e.x = level_scale(g, c, ke, mask_below) * (lds32(g.pe2 + 4 * i) - psf); slot = ke + 1; }
         }
     }
-    e.z = __int_as_float((__float_as_int(e.z) & ~127) | slot);
     return e;
 }
-// Build the records of steps t0 .. t0+KC-1; lane = (column c, step kk).  Record of step t:
-//   r0 = (E1, E2, F-1, G) and r1.x = H: PPM stencil of layer t-1 (mappm.f90:651-683, delp-only factors)
-//   r1.y = weight of the whole layer t-2 in the target level open at its bottom
-//   r1.z = first interface | count << 8 of the events of layer t-2;  r1.w = 1 if it has none
-// plus up to EVCAP event records of layer t-2 (the first one is a no-op when the layer has none).
+// Build the records of steps t0 .. t0+KC-1; lane = (column c, step kk).  Record of step t (REC_BLOCK):
+//   E1, E2, F-1, G, H: PPM stencil of layer t-1 (mappm.f90:651-683, delp-only factors)
+//   dpw: weight of the whole layer t-2 in the target level open at its bottom
+//   ex, ey, ez, ew, off: the first event of layer t-2 (a no-op when it has none)
+//   info = first interface | count << 8 of the events of layer t-2 (further events are formed on the fly)
 __device__ __forceinline__ void build_chunk(const WG &g, float d /* delp(t0 + kk, column c) */, int lane, int t0, int nz,
                                             int mask_below, float toa)
 {
@@ -316,13 +369,17 @@ __device__ __forceinline__ void build_chunk(const WG &g, float d /* delp(t0 + kk
         const int ko = i1 - 1;                                          // level open at the bottom of L
         if (ko >= 0 && ko < kn && lds32(g.pe2 + 4 * ko) > toa) dpw = level_scale(g, c, ko, mask_below) * (pb - pt);
     }
-    const uint32_t evp = g.ev + 16 * ((c * KC + kk) * EVCAP);
-    if (n == 0) sts128(evp, make_float4(0.f, 0.f, __int_as_float(DUMMY_SLOT), 0.f));
-    const int nw = n < EVCAP ? n : EVCAP;
-    for (int e = 0; e < nw; ++e) sts128(evp + 16 * e, event_record(g, c, L, i0 + e, nz, mask_below, toa));
-    const uint32_t r = g.rec + 32 * (c * KC + kk);
-    sts128(r, make_float4(E1, E2, Fm, G));
-    sts128(r + 16, make_float4(H, dpw, __int_as_float(i0 | (n << 8)), n == 0 ? 1.f : 0.f));
+    float4 e0 = make_float4(0.f, 0.f, 0.f, 0.f);
+    int slot = DUMMY_SLOT;
+    if (n > 0) e0 = event_record(g, c, L, i0, nz, mask_below, toa, slot);
+    const uint32_t r = g.rec + (kk * (C / 2) + (c >> 1)) * REC_BLOCK + 4 * (c & 1);
+    sts32(r, E1);           sts32(r + 8, E2);
+    sts32(r + 16, Fm);      sts32(r + 24, G);
+    sts32(r + 32, -H);      sts32(r + 40, dpw);
+    sts32(r + 48, e0.x);    sts32(r + 56, e0.y);
+    sts32(r + 64, e0.z);    sts32(r + 72, -e0.w);
+    sts32(r + 80, __int_as_float(slot * ACC_STRIDE));
+    sts32(r + 88, __int_as_float(i0 | (n << 8)));
     int nm = n;                                                         // most events of any column at this step
     nm = max(nm, __shfl_xor_sync(0xffffffffu, nm, 1));
     nm = max(nm, __shfl_xor_sync(0xffffffffu, nm, 2));
@@ -332,68 +389,82 @@ __device__ __forceinline__ void build_chunk(const WG &g, float d /* delp(t0 + kk
 }
 
 // ---- per-field work -----------------------------------------------------------------------------
+// the record of one column at one step, gathered from its pair block (general step only)
+struct Rec {
+    float E1, E2, Fm, G, H, dpw;
+    float4 ev;
+    int off, info;
+};
+__device__ __forceinline__ Rec load_rec(uint32_t rec, int kk, int c)
+{
+    const uint32_t b = rec + (kk * (C / 2) + (c >> 1)) * REC_BLOCK + 4 * (c & 1);
+    Rec r;
+    r.E1 = lds32(b);        r.E2 = lds32(b + 8);
+    r.Fm = lds32(b + 16);   r.G = lds32(b + 24);
+    r.H = -lds32(b + 32);   r.dpw = lds32(b + 40);
+    r.ev = make_float4(lds32(b + 48), lds32(b + 56), lds32(b + 64), -lds32(b + 72));
+    r.off = __float_as_int(lds32(b + 80));
+    r.info = __float_as_int(lds32(b + 88));
+    return r;
+}
+
 // one event: close a target level with run + I (NaN-skipping block sum, coarsen.py:211), restart the
 // running sum of the next one.  acc_lane = &acc[0][lane]; slot 0 collects what belongs to no level.
-__device__ __forceinline__ void apply_event(const float4 ev, float q, float x, float y, float keep, float &run,
-                                            uint32_t acc_lane, int V4, bool active)
+__device__ __forceinline__ void apply_event(const float4 ev, int off, float q, float x, float y, bool keep, float &run,
+                                            uint32_t acc_lane)
 {
     const float I = ev.x * q + ev.y * x + ev.z * y;
     const float tot = run + I;
-    const uint32_t a = acc_lane + (__float_as_int(ev.z) & 127) * V4;
-    const float upd = lds32(a) + (tot == tot ? tot : 0.f);
-    asm volatile("{.reg .pred p; setp.ne.s32 p, %2, 0; @p st.shared.f32 [%0], %1;}" ::"r"(a), "f"(upd), "r"((int)active) : "memory");
-    run = keep != 0.f ? run : -(ev.w * I);
+    const uint32_t a = acc_lane + off;
+    sts32(a, lds32(a) + (tot == tot ? tot : 0.f));
+    run = keep ? run : -(ev.w * I);
 }
 
-// events 1 .. n-1 of a layer cut by several coarse interfaces (out of line: rare)
-__device__ __noinline__ float extra_events(WG g, int c, int kk, int L, int evinfo, float q, float x, float y, float run,
-                                           uint32_t acc_lane, int V4, bool active, int nz, int mask_below, float toa)
+// events 1 .. n-1 of a layer cut by several coarse interfaces (rare: formed on the fly, out of line)
+__device__ __noinline__ float extra_events(WG g, int c, int L, int info, float q, float x, float y, float run,
+                                           uint32_t acc_lane, int nz, int mask_below, float toa)
 {
-    const int n = evinfo >> 8, i0 = evinfo & 255;
-    const uint32_t evp = g.ev + 16 * ((c * KC + kk) * EVCAP);
+    const int n = info >> 8, i0 = info & 255;
     for (int e = 1; e < n; ++e) {
-        const float4 ev = e < EVCAP ? lds128(evp + 16 * e) : event_record(g, c, L, i0 + e, nz, mask_below, toa);
-        apply_event(ev, q, x, y, 0.f, run, acc_lane, V4, active);
+        int slot;
+        const float4 ev = event_record(g, c, L, i0 + e, nz, mask_below, toa, slot);
+        apply_event(ev, slot * ACC_STRIDE, q, x, y, false, run, acc_lane);
     }
     return run;
 }
 
 // Limited parabola of layer L in deviation form, x = AL - q, y = AR - q, A6 = -3 (x + y)
 // (ppm_limiters lmt = 0, mappm.f90:875-894), then the events of the layer and its whole-layer term.
-template <bool GENERAL>
-__device__ __forceinline__ void finish_layer(const WG &g, int c, int kk, int L, float q, float x, float y, float dc,
-                                             float &run, const float4 r1, const float4 ev0, uint32_t acc_lane, int V4,
-                                             bool active, int nz, int mask_below, float toa)
+__device__ __forceinline__ void finish_layer(const WG &g, int c, int L, float q, float x, float y, float dc, float &run,
+                                             const Rec &r, uint32_t acc_lane, int nz, int mask_below, float toa)
 {
     const float da1 = y - x, s = x + y;
     const float t = s * da1, da2 = da1 * (da1 * (1.f / 3.f));
     const float m2x = -2.f * x, m2y = -2.f * y;
-    const bool c1 = t > da2, c2 = -t > da2, flat = dc == 0.f;
+    const bool c1 = t > da2, c2 = -t > da2, flat = dc == 0.f;      // c1 and c2 exclude each other (da2 >= 0)
     y = c1 ? m2x : y;                  // a6da < -da2: AR = AL - 3 (AL - q)
-    x = (c2 && !c1) ? m2y : x;         // a6da >  da2: AL = AR - 3 (AR - q)
+    x = c2 ? m2y : x;                  // a6da >  da2: AL = AR - 3 (AR - q)
     x = flat ? 0.f : x;
     y = flat ? 0.f : y;
-    apply_event(ev0, q, x, y, r1.w, run, acc_lane, V4, active);
-    if (GENERAL) {
-        const int evinfo = __float_as_int(r1.z);
-        if (evinfo >= (2 << 8))        // a layer cut by several coarse interfaces: the others out of line
-            run = extra_events(g, c, kk, L, evinfo, q, x, y, run, acc_lane, V4, active, nz, mask_below, toa);
-    }
-    run = fmaf(r1.y, q, run);
+    apply_event(r.ev, r.off, q, x, y, r.info < 256, run, acc_lane);
+    if (r.info >= (2 << 8))            // a layer cut by several coarse interfaces: the others out of line
+        run = extra_events(g, c, L, r.info, q, x, y, run, acc_lane, nz, mask_below, toa);
+    run = fmaf(r.dpw, q, run);
 }
 
 // one-sided cubic at the column top (mappm.f90:689-707), evaluated at step t = 2 once level 3 is
 // visible: returns (x, y, dc) of layer 0 and x of layer 1
-__device__ __noinline__ float4 top_fix(uint32_t rec3, uint32_t edge, float qn, float dqn, float dcn, float q1, float q0, float q3)
+__device__ __noinline__ float4 top_fix(uint32_t rec, int c, uint32_t edge, float qn, float dqn, float dcn, float q1, float q0,
+                                       float q3)
 {
-    const float4 r0p = lds128(rec3);
-    const float Hp = lds32(rec3 + 16);
+    const uint32_t b = rec + (3 * (C / 2) + (c >> 1)) * REC_BLOCK + 4 * (c & 1);      // record of step 3
+    const float E1 = lds32(b), E2 = lds32(b + 8), Fm = lds32(b + 16), G = lds32(b + 24), nH = lds32(b + 32);
     const float dq3 = q3 - qn;
-    const float df2 = r0p.x * dq3 + r0p.y * dqn;
+    const float df2 = E1 * dq3 + E2 * dqn;
     const float na = -dqn;
     const float hi3 = max3(na, dq3, 0.f), nlo = min3(na, dq3, 0.f);
     const float dc2 = max3(min3(df2, hi3, -nlo), -hi3, nlo);
-    const float al2 = qn + (r0p.z * dqn + r0p.w * dcn - Hp * dc2);
+    const float al2 = qn + (Fm * dqn + G * dcn + nH * dc2);
     const float4 ea = lds128(edge), eb = lds128(edge + 16);
     const float sd1 = lds32(edge + 32);
     const float qm = ea.x * q0 + ea.y * q1, dq = ea.z * (q1 - q0);
@@ -420,19 +491,27 @@ __device__ __noinline__ float4 bottom_fix(uint32_t edge, float qe, float qi, flo
     return make_float4(alb - qi, alb - qe, 0.5f * (qe - alb), bot - qe);
 }
 
-// one 128-B row of a lane's own field: its 8 columns of the warp's cell
-__device__ __forceinline__ void load_row(float (&qv)[C], uint32_t stage, int kk, int w, int fa, int fb, int fop, float finv)
+// the per-lane description of a field: parents' boxes and q = (a - c1 b) (c2 b + c3)
+struct Field {
+    int fa, fb;
+    float c1, c2, c3;
+};
+
+// one 128-B row of a lane's own field: its 8 columns of the warp's cell, as 4 column pairs
+// (budgets.py:151 products and :80 storage terms are formed here; exact for plain fields: (a - 0)(0 + 1))
+__device__ __forceinline__ void load_row(u64 (&q)[4], uint32_t stage, int kk, int w, const Field &f, int any_derived)
 {
-    const uint32_t ra = stage + fa * BOX_BYTES + kk * 128;
-    const float4 lo = lds128(swz(ra, 2 * w)), hi = lds128(swz(ra, 2 * w + 1));
-    qv[0] = lo.x; qv[1] = lo.y; qv[2] = lo.z; qv[3] = lo.w;
-    qv[4] = hi.x; qv[5] = hi.y; qv[6] = hi.z; qv[7] = hi.w;
-    if (fop != CG_FIELD_PLAIN) {                  // budgets.py:151 products, :80 storage terms
-        const uint32_t rb = stage + fb * BOX_BYTES + kk * 128;
-        const float4 l2 = lds128(swz(rb, 2 * w)), h2 = lds128(swz(rb, 2 * w + 1));
-        const float bv[C] = {l2.x, l2.y, l2.z, l2.w, h2.x, h2.y, h2.z, h2.w};
+    const uint32_t ra = stage + f.fa * BOX_BYTES + kk * 128;
+    lds2x64(swz(ra, 2 * w), q[0], q[1]);
+    lds2x64(swz(ra, 2 * w + 1), q[2], q[3]);
+    if (any_derived) {                                   // uniform across the launch
+        const uint32_t rb = stage + f.fb * BOX_BYTES + kk * 128;
+        u64 b[4];
+        lds2x64(swz(rb, 2 * w), b[0], b[1]);
+        lds2x64(swz(rb, 2 * w + 1), b[2], b[3]);
+        const u64 n1 = pk(-f.c1, -f.c1), m2 = pk(f.c2, f.c2), a3 = pk(f.c3, f.c3);
 #pragma unroll
-        for (int c = 0; c < C; ++c) qv[c] = (fop == CG_FIELD_PRODUCT) ? qv[c] * bv[c] : (qv[c] - bv[c]) * finv;
+        for (int p = 0; p < 4; ++p) q[p] = mul2(fma2(b[p], n1, q[p]), fma2(b[p], m2, a3));
     }
 }
 
@@ -443,62 +522,139 @@ __device__ __forceinline__ float limited_slope(float df2, float dq_lo, float dq_
     return max3(min3(df2, hi3, -nlo), -hi3, nlo);
 }
 
+// Rolling state of a lane's 8 columns as 4 column pairs: A = q(t-1), B = q(t-2), dq = delq(t-1),
+// dc = dc(t-2), xp = AL(t-2) - q(t-2), run = running integral of the target level that is open
+struct State {
+    u64 A[4], B[4], dq[4], dc[4], xp[4], run[4];
+};
 
 // One step of the tandem walk for the 8 columns of a row: level t arrives, layer t-2 is finished.
-// Steps t < 2 finish nothing (their records hold a no-op event and zero weights); the steps at the ends
-// of the column (t == 2, t >= nz) patch in the one-sided cubics.  GENERAL = false is the straight-line body
-// for interior levels where no column is cut by more than one coarse interface (the 8 columns interleave).
-template <bool GENERAL>
-__device__ __forceinline__ void level_step(const WG &g, uint32_t stage, int t, int kk, int w, int fa, int fb, int fop,
-                                           float finv, float (&A)[C], float (&B)[C], float (&dq1)[C], float (&dcp)[C],
-                                           float (&xp)[C], float (&run)[C], uint32_t acc_lane, int V4,
-                                           bool active, int nz, int mask_below, float toa)
+// Interior levels where no column is cut by more than one coarse interface: straight line, two columns
+// per arithmetic instruction; the min/max, compare and select parts run on the halves.
+__device__ __forceinline__ void hot_step(uint32_t rec, uint32_t stage, int kk, int w, const Field &f, int any_derived,
+                                         State &s, uint32_t acc_lane)
 {
-    float qv[C], q3[C];
-    const bool ends = GENERAL && ((t == 2) || (t >= nz));
-    if (!GENERAL || t < nz) load_row(qv, stage, kk, w, fa, fb, fop, finv);
-    else {
+    u64 q[4];
+    load_row(q, stage, kk, w, f, any_derived);
+    const uint32_t rb = rec + kk * (C / 2) * REC_BLOCK;
+    const u64 third = pk(1.f / 3.f, 1.f / 3.f), neg2 = pk(-2.f, -2.f);
+    u64 E1, E2, Fm, G, NH, DPW, EX, EY, EZ, NW;
+    int4 oi;
+    lds2x64(rb, E1, E2);        lds2x64(rb + 16, Fm, G);    lds2x64(rb + 32, NH, DPW);
+    lds2x64(rb + 48, EX, EY);   lds2x64(rb + 64, EZ, NW);   oi = lds128i(rb + 80);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        u64 E1n = E1, E2n = E2, Fmn = Fm, Gn = G, NHn = NH, DPWn = DPW, EXn = EX, EYn = EY, EZn = EZ, NWn = NW;
+        int4 oin = oi;
+        if (p + 1 < 4) {
+            const uint32_t rn = rb + (p + 1) * REC_BLOCK;
+            lds2x64(rn, E1n, E2n);        lds2x64(rn + 16, Fmn, Gn);    lds2x64(rn + 32, NHn, DPWn);
+            lds2x64(rn + 48, EXn, EYn);   lds2x64(rn + 64, EZn, NWn);   oin = lds128i(rn + 80);
+        }
+        const u64 qn = q[p], dq1 = s.dq[p];
+        const u64 dqn = sub2(qn, s.A[p]);                                   // delq(t)
+        const u64 df2 = fma2(E1, dqn, mul2(E2, dq1));                       // layer t-1, mappm.f90:661
+        float dfa, dfb, d1a, d1b, dna, dnb;
+        upk(df2, dfa, dfb); upk(dq1, d1a, d1b); upk(dqn, dna, dnb);
+        const u64 dcn = pk(limited_slope(dfa, d1a, dna), limited_slope(dfb, d1b, dnb));    // dc(t-1)
+        const u64 xn = fma2(NH, dcn, fma2(G, s.dc[p], mul2(Fm, dq1)));      // AL(t-1) - q(t-1), :674-683
+        // layer t-2: limiter in deviation form (ppm_limiters lmt = 0)
+        const u64 x = s.xp[p], y = add2(xn, dq1);
+        const u64 da1 = sub2(y, x), sm = add2(x, y);
+        const u64 tt = mul2(sm, da1), da2 = mul2(da1, mul2(da1, third));
+        const u64 m2x = mul2(x, neg2), m2y = mul2(y, neg2);
+        float xa, xb, ya, yb, ta, tb, ga, gb, mxa, mxb, mya, myb, ca, cb;
+        upk(x, xa, xb); upk(y, ya, yb); upk(tt, ta, tb); upk(da2, ga, gb);
+        upk(m2x, mxa, mxb); upk(m2y, mya, myb); upk(s.dc[p], ca, cb);
+        ya = ta > ga ? mxa : ya;    xa = -ta > ga ? mya : xa;
+        yb = tb > gb ? mxb : yb;    xb = -tb > gb ? myb : xb;
+        xa = ca == 0.f ? 0.f : xa;  ya = ca == 0.f ? 0.f : ya;
+        xb = cb == 0.f ? 0.f : xb;  yb = cb == 0.f ? 0.f : yb;
+        const u64 xl = pk(xa, xb), yl = pk(ya, yb), qB = s.B[p];
+        // the (at most one) event of each column: close a target level, restart the next
+        const u64 I = fma2(EZ, yl, fma2(EY, xl, mul2(EX, qB)));
+        const u64 tot = add2(s.run[p], I);
+        float tota, totb;
+        upk(tot, tota, totb);
+        const uint32_t aa = acc_lane + oi.x, ab = acc_lane + oi.y;
+        sts32(aa, lds32(aa) + (tota == tota ? tota : 0.f));
+        sts32(ab, lds32(ab) + (totb == totb ? totb : 0.f));
+        float ra, rb_, na, nb;
+        upk(s.run[p], ra, rb_);
+        upk(mul2(NW, I), na, nb);
+        ra = oi.z < 256 ? ra : na;
+        rb_ = oi.w < 256 ? rb_ : nb;
+        s.run[p] = fma2(DPW, qB, pk(ra, rb_));
+        s.B[p] = s.A[p]; s.A[p] = qn; s.dq[p] = dqn; s.dc[p] = dcn; s.xp[p] = xn;
+        E1 = E1n; E2 = E2n; Fm = Fmn; G = Gn; NH = NHn; DPW = DPWn; EX = EXn; EY = EYn; EZ = EZn; NW = NWn;
+        oi = oin;
+    }
+}
+
+// The same step for the ends of the column (t < 3, t >= nz: one-sided cubics, nothing to finish, below the
+// surface) and for levels where some column is cut by several coarse interfaces: column by column.
+__device__ __forceinline__ void general_step(const WG &g, uint32_t stage, int t, int kk, int w, const Field &f,
+                                             int any_derived, State &s, uint32_t acc_lane, int nz, int mask_below,
+                                             float toa)
+{
+    float A[C], B[C], dq1[C], dcp[C], xp[C], run[C], qv[C], q3[C];
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        upk(s.A[p], A[2 * p], A[2 * p + 1]);       upk(s.B[p], B[2 * p], B[2 * p + 1]);
+        upk(s.dq[p], dq1[2 * p], dq1[2 * p + 1]);  upk(s.dc[p], dcp[2 * p], dcp[2 * p + 1]);
+        upk(s.xp[p], xp[2 * p], xp[2 * p + 1]);    upk(s.run[p], run[2 * p], run[2 * p + 1]);
+    }
+    const bool ends = (t == 2) || (t >= nz);
+    if (t < nz) {
+        u64 q[4];
+        load_row(q, stage, kk, w, f, any_derived);
+#pragma unroll
+        for (int p = 0; p < 4; ++p) upk(q[p], qv[2 * p], qv[2 * p + 1]);
+    } else {
 #pragma unroll
         for (int c = 0; c < C; ++c) qv[c] = A[c];
     }
-    if (GENERAL && t == 2) load_row(q3, stage, 3, w, fa, fb, fop, finv);           // level 3 is in the same stage (KC = 4)
-    const uint32_t rk = g.rec + 32 * kk, ek = g.ev + 16 * EVCAP * kk;
-    float4 r0 = lds128(rk), r1 = lds128(rk + 16), e0 = lds128(ek);
+    if (t == 2) {                                                   // level 3 is in the same stage (KC = 4)
+        u64 q[4];
+        load_row(q, stage, 3, w, f, any_derived);
+#pragma unroll
+        for (int p = 0; p < 4; ++p) upk(q[p], q3[2 * p], q3[2 * p + 1]);
+    }
 #pragma unroll
     for (int c = 0; c < C; ++c) {
-        float4 r0n = r0, r1n = r1, e0n = e0;
-        if (c + 1 < C) {
-            r0n = lds128(rk + 32 * KC * (c + 1));
-            r1n = lds128(rk + 32 * KC * (c + 1) + 16);
-            e0n = lds128(ek + 16 * EVCAP * KC * (c + 1));
-        }
+        const Rec r = load_rec(g.rec, kk, c);
         const float qn = qv[c];
         float dqn = qn - A[c];                                              // delq(t)
-        const float df2 = r0.x * dqn + r0.y * dq1[c];                       // layer t-1, mappm.f90:661
+        const float df2 = r.E1 * dqn + r.E2 * dq1[c];                       // layer t-1, mappm.f90:661
         float dcn = limited_slope(df2, dq1[c], dqn);                        // dc(t-1)
-        float xn = r0.z * dq1[c] + r0.w * dcp[c] - r1.x * dcn;              // AL(t-1) - q(t-1), :674-683
+        float xn = r.Fm * dq1[c] + r.G * dcp[c] - r.H * dcn;                // AL(t-1) - q(t-1), :674-683
         float x = xp[c], y = xn + dq1[c], dc = dcp[c];                      // layer t-2
-        if (GENERAL && ends) {
+        if (ends) {
             if (t == 2) {
-                const float4 r = top_fix(g.rec + 32 * (c * KC + 3), g.edge + 4 * (c * 24), qn, dqn, dcn, A[c], B[c], q3[c]);
-                x = r.x; y = r.y; dc = r.z; xn = r.w;
+                const float4 v = top_fix(g.rec, c, g.edge + 4 * (c * 24), qn, dqn, dcn, A[c], B[c], q3[c]);
+                x = v.x; y = v.y; dc = v.z; xn = v.w;
             } else if (t == nz) {
-                const float4 r = bottom_fix(g.edge + 4 * (c * 24 + 12), A[c], B[c], xp[c]);
-                y = r.x; xn = r.y; dcn = r.z; dqn = r.w;                    // layer nz-1 is finished next step
+                const float4 v = bottom_fix(g.edge + 4 * (c * 24 + 12), A[c], B[c], xp[c]);
+                y = v.x; xn = v.y; dcn = v.z; dqn = v.w;                    // layer nz-1 is finished next step
             } else if (t == nz + 1) {
                 y = dq1[c];
             } else {                                                        // below the surface
                 x = 0.f; y = 0.f; dc = 0.f;
             }
         }
-        finish_layer<GENERAL>(g, c, kk, t - 2, B[c], x, y, dc, run[c], r1, e0, acc_lane, V4, active, nz, mask_below, toa);
+        finish_layer(g, c, t - 2, B[c], x, y, dc, run[c], r, acc_lane, nz, mask_below, toa);
         B[c] = A[c]; A[c] = qn; dq1[c] = dqn; dcp[c] = dcn; xp[c] = xn;
-        r0 = r0n; r1 = r1n; e0 = e0n;
+    }
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        s.A[p] = pk(A[2 * p], A[2 * p + 1]);       s.B[p] = pk(B[2 * p], B[2 * p + 1]);
+        s.dq[p] = pk(dq1[2 * p], dq1[2 * p + 1]);  s.dc[p] = pk(dcp[2 * p], dcp[2 * p + 1]);
+        s.xp[p] = pk(xp[2 * p], xp[2 * p + 1]);    s.run[p] = pk(run[2 * p], run[2 * p + 1]);
     }
 }
 
-// 128 registers at launch (2 CTAs of 256 threads per SM); the consumer warpgroup then takes 168 and the
-// geometry warpgroup drops to 88 (setmaxnreg)
+// 128 registers at launch (2 CTAs of 256 threads per SM); the consumer warpgroup then takes 184 and the
+// geometry warpgroup drops to 72 (setmaxnreg)
 __global__ void __maxnreg__(128)
 plevel_stream_kernel(const __grid_constant__ Params p)
 {
@@ -529,7 +685,7 @@ plevel_stream_kernel(const __grid_constant__ Params p)
     const int w = warp & (NCELL - 1);                           // the cell this warp works for
     const uint32_t wb = sbase + lay.warp0 + w * lay.warp_bytes;
     WG g;
-    g.acc = wb + lay.acc;   g.rec = wb + lay.rec;   g.ev = wb + lay.ev;     g.pe1 = wb + lay.pe1;
+    g.acc = wb + lay.acc;   g.rec = wb + lay.rec;   g.pe1 = wb + lay.pe1;
     g.pe2 = wb + lay.pe2;   g.rdp2 = wb + lay.rdp2; g.den = wb + lay.den;   g.edge = wb + lay.edge;
     g.colw = wb + lay.colw; g.colps = wb + lay.colps; g.nmax = wb + lay.nmax;
     const uint32_t gfull = gbars + 8 * (2 * w);
@@ -604,7 +760,6 @@ plevel_stream_kernel(const __grid_constant__ Params p)
                 }
                 WG gb = gr;
                 gb.rec = g.rec + b * REC_BYTES;
-                gb.ev = g.ev + b * EV_BYTES;
                 gb.nmax = g.nmax + b * KC * 4;
                 build_chunk(gb, d, lane, chunk * KC, nz, mask_below, toa);
                 if (lane == 0) mbar_arrive(gfull + 8 * b);
@@ -616,18 +771,21 @@ plevel_stream_kernel(const __grid_constant__ Params p)
     // ---------------- consumer warp of cell (by, 4 bx + w): lanes = fields ----------------------------
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CONSUMER_REGS));
     const bool active = lane < V;
-    const int V4 = 4 * V;
-    const uint32_t acc_lane = g.acc + 4 * lane;
-    for (int i = lane; i < (nz + 1) * V; i += 32) sts32(g.acc + 4 * i, 0.f);
+    const uint32_t acc_lane = g.acc + 4 * lane;                 // every lane owns a column of the accumulator
+    for (int i = lane; i < (nz + 1) * 32; i += 32) sts32(g.acc + 4 * i, 0.f);
     __syncwarp();
-    const int fa = active ? p.fa[lane] : 0, fb = active ? p.fb[lane] : 0, fop = active ? p.fop[lane] : 0;
-    const float finv = active ? p.finv[lane] : 1.f;
+    Field fld;
+    fld.fa = active ? p.fa[lane] : 0;
+    fld.fb = active ? p.fb[lane] : 0;
+    fld.c1 = active ? p.fc1[lane] : 0.f;
+    fld.c2 = active ? p.fc2[lane] : 0.f;
+    fld.c3 = active ? p.fc3[lane] : 1.f;
+    const int any_derived = p.any_derived;
 
     for (int row = 0; row < 8; ++row) {
-        // rolling state of the 8 columns: A = q(t-1), B = q(t-2), dq1 = delq(t-1), dcp = dc(t-2), xp = x(t-2)
-        float A[C], B[C], dq1[C], dcp[C], xp[C], run[C];
+        State st;
 #pragma unroll
-        for (int c = 0; c < C; ++c) { A[c] = 0.f; B[c] = 0.f; dq1[c] = 0.f; dcp[c] = 0.f; xp[c] = 0.f; run[c] = 0.f; }
+        for (int i = 0; i < 4; ++i) { st.A[i] = 0; st.B[i] = 0; st.dq[i] = 0; st.dc[i] = 0; st.xp[i] = 0; st.run[i] = 0; }
         WG gr = g;
         gr.colw = g.colw + 32 * (row & 1);
         gr.colps = g.colps + 32 * (row & 1);
@@ -639,18 +797,15 @@ plevel_stream_kernel(const __grid_constant__ Params p)
             const uint32_t stage = ring + s * stage_bytes;
             WG gb = gr;
             gb.rec = g.rec + b * REC_BYTES;
-            gb.ev = g.ev + b * EV_BYTES;
             gb.nmax = g.nmax + b * KC * 4;
 #pragma unroll 1
             for (int kk = 0; kk < KC; ++kk) {
                 const int t = t0 + kk;
                 if (t > nz + 2) break;
                 if (t >= 3 && t < nz && lds32(gb.nmax + 4 * kk) <= 1.f)
-                    level_step<false>(gb, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4,
-                                      active, nz, mask_below, toa);
+                    hot_step(gb.rec, stage, kk, w, fld, any_derived, st, acc_lane);
                 else
-                    level_step<true>(gb, stage, t, kk, w, fa, fb, fop, finv, A, B, dq1, dcp, xp, run, acc_lane, V4,
-                                     active, nz, mask_below, toa);
+                    general_step(gb, stage, t, kk, w, fld, any_derived, st, acc_lane, nz, mask_below, toa);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bars + 8 * (NSTAGE + s));
@@ -662,7 +817,7 @@ plevel_stream_kernel(const __grid_constant__ Params p)
     if (active) {
         float *out = p.outs[lane];
         for (int k = 0; k < nz; ++k)
-            out[(o * nz + k) * hc + (long)by * nxc + cx] = lds32(acc_lane + (k + 1) * V4) / lds32(g.den + 4 * k);
+            out[(o * nz + k) * hc + (long)by * nxc + cx] = lds32(acc_lane + (k + 1) * ACC_STRIDE) / lds32(g.den + 4 * k);
     }
 }
 
@@ -768,7 +923,7 @@ int launch_plevel_stream(const cg_field *fields, float *const *outs, int nfields
     static std::mutex mu;
     std::lock_guard<std::mutex> lock(mu);
     const float *srcs[MAXSRC];
-    int nsrc = 0;
+    int nsrc = 0, any_derived = 0;
     auto source_index = [&](const float *ptr) {
         for (int i = 0; i < nsrc; ++i)
             if (srcs[i] == ptr) return i;
@@ -778,10 +933,13 @@ int launch_plevel_stream(const cg_field *fields, float *const *outs, int nfields
     for (int v = 0; v < nfields; ++v) {
         p.fa[v] = source_index(fields[v].a);
         p.fb[v] = fields[v].op != CG_FIELD_PLAIN ? source_index(fields[v].b) : p.fa[v];
-        p.fop[v] = fields[v].op;
-        p.finv[v] = fields[v].op == CG_FIELD_DIFF ? 1.f / fields[v].scale : 1.f;
+        p.fc1[v] = fields[v].op == CG_FIELD_DIFF ? 1.f : 0.f;
+        p.fc2[v] = fields[v].op == CG_FIELD_PRODUCT ? 1.f : 0.f;
+        p.fc3[v] = fields[v].op == CG_FIELD_DIFF ? 1.f / fields[v].scale : (fields[v].op == CG_FIELD_PRODUCT ? 0.f : 1.f);
+        any_derived |= fields[v].op != CG_FIELD_PLAIN;
         p.outs[v] = outs[v];
     }
+    p.any_derived = any_derived;
     if (((uintptr_t)delp) & 3) return CG_ENOTSUP;
     for (int i = 0; i < nsrc; ++i) {
         if (((uintptr_t)srcs[i]) & 15) return CG_ENOTSUP;
