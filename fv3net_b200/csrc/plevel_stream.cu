@@ -1,18 +1,21 @@
 // Streaming pressure-level coarse-graining for sm_100a: f = 8, iv = 1, kord = 1, nx % 32 == 0.
 // (regridz.py:115-147 + coarsen.py:183, budgets.py:49-57; mappm.f90:10-126, :614-851, :854-931)
 //
-// Mapping ("lanes over fields").  A CTA owns 4 x-adjacent coarse cells; consumer warp w owns
-// cell w for the whole launch and walks its 8 rows one after the other.  Inside a warp,
-// LANE v IS FIELD v and every thread carries the 8 fine columns of the current row, so
-//   * everything that depends only on pressure (the geometry: PPM stencil coefficients of
-//     every layer, where each coarse interface cuts the fine column and with which weight)
-//     is the same for all lanes of a warp.  It is built once per (column, level) by the
-//     warp itself (lane = (column, level of the chunk)), parked in shared memory and read
-//     back by all lanes with broadcast loads: no per-field integer work, no divergence;
-//   * field data is fetched by TMA (cp.async.bulk.tensor, one [4 levels][32 columns] box
-//     per source array and stage, 128B-swizzled) into a 2-stage ring shared by the 4
-//     warps; a lane reads its own field's 8 columns with two conflict-free LDS.128;
-//   * the vertical walk is a tandem walk: source layers in order (rolling PPM state in
+// A CTA owns 4 x-adjacent coarse cells = 32 fine columns x 8 rows x nz levels, walked row by row.
+//
+//   * Field warps ("lanes over fields"): warp w owns cell w for the whole launch.  LANE v IS
+//     FIELD v and every thread carries the 8 fine columns of the current row, so everything
+//     that depends only on pressure (the geometry: PPM stencil coefficients of every layer,
+//     where each coarse interface cuts the fine column and with which weight) is the same
+//     for all lanes.  It is read from shared memory with broadcast loads: no per-field integer
+//     work, no divergence.  Field data arrives by TMA (cp.async.bulk.tensor, one
+//     [4 levels][32 columns] box per source array and stage, 128B-swizzled) into a 2-stage
+//     ring; a lane reads its own field's 8 columns with two conflict-free LDS.128.
+//   * One geometry warp ("lanes over columns"): lane x walks fine column x of the row from
+//     the top with its interface pressures, the two-pointer merge against the coarse
+//     interfaces and the PPM stencil in registers, and writes one record per (column, level)
+//     for the field warps; it also issues the TMA loads.
+//   * The vertical walk is a tandem walk: source layers in order (rolling PPM state in
 //     registers), coarse interfaces met on the way close one target layer and open the
 //     next ("events"); per-target sums live in a per-warp shared-memory accumulator
 //     [target level][lane], so the 64 columns of a cell are summed by one warp in a
@@ -31,24 +34,32 @@ namespace cg {
 namespace stream {
 
 constexpr int C = 8;                 // fine columns per thread (one row of a coarse cell)
-constexpr int NCELL = 4;             // coarse cells per CTA = consumer warps
+constexpr int NCELL = 4;             // coarse cells per CTA = field warps
+constexpr int NCOL = NCELL * C;      // fine columns per CTA row = lanes of the geometry warp
 constexpr int KC = 4;                // levels per pipeline stage
 constexpr int BOX_ROWS = KC + 1;     // 128-B rows per source box: odd stride -> 8 distinct swizzle phases over 8 lanes
 constexpr int BOX_BYTES = BOX_ROWS * 128;
 constexpr int NSTAGE = 2;            // == geometry buffers: both are released by the same barrier
 constexpr int MAXF = CG_MAX_FIELDS;  // output fields per launch (lanes)
 constexpr int MAXSRC = 2 * MAXF;     // distinct parent arrays
-constexpr int PRING = 16;            // levels kept in the interface-pressure ring
-constexpr int NTHREADS = 2 * NCELL * 32;         // consumer warps + geometry warps (which also issue the TMA loads)
+constexpr int NTHREADS = 2 * NCELL * 32;         // field warpgroup + helper warpgroup (its first warp builds the geometry)
 constexpr int CONSUMER_REGS = 184, HELPER_REGS = 72;   // setmaxnreg targets; launch value 128 x 256 threads
 // geometry record of one step and one PAIR of adjacent columns (a, b): 6 x 16 B, pair-interleaved so that
 // the field warps load every coefficient as an f32x2 operand
 //   +0  E1a E1b E2a E2b | +16 Fa Fb Ga Gb | +32 -Ha -Hb dpwa dpwb | +48 exa exb eya eyb
-//   +64 eza ezb -ewa -ewb | +80 offa offb infoa infob   (off = accumulator byte offset, info = i0 | n << 8)
+//   +64 eza ezb -ewa -ewb | +80 offa offb infoa infob
+// off = accumulator byte offset of the level the first event closes; info = number of coarse interfaces in
+// the layer (0: none, the running sum is kept; n >= 2: n - 1 further events sit in the overflow list;
+// INFO_SLOW: more than MAXE of them, formed on the fly from the column's pressures parked in the list)
 constexpr int REC_BLOCK = 96;
-constexpr int REC_BYTES = KC * (C / 2) * REC_BLOCK;
+constexpr int REC_BYTES = KC * (NCOL / 2) * REC_BLOCK;
+constexpr int MAXE = 2;              // listed further events per (column, layer)
+constexpr int INFO_SLOW = 255;
+constexpr int OVA_BYTES = KC * NCOL * MAXE * 16;     // (x, y, z, -w) per event
+constexpr int OVB_BYTES = KC * NCOL * MAXE * 4;      // accumulator byte offset per event
 constexpr int ACC_STRIDE = 128;      // bytes per accumulator slot: one float per lane
 constexpr int DUMMY_SLOT = 0;        // accumulator slot k + 1 belongs to target level k
+constexpr int EDGE_WORDS = 24;       // per column: one-sided cubic coefficients, top (0..8) and bottom (12..20)
 
 struct Params {
     CUtensorMap maps[MAXSRC];
@@ -57,7 +68,7 @@ struct Params {
     const float *area;               // (n_outer, ny, nx)
     const float *psurf;              // (n_outer, ny, nx) sequential-cumsum surface pressure, mask_below only
     const float *delp_coarse;        // (n_outer, nz, ny/8, nx/8)
-    const float *delp;               // (n_outer, nz, ny, nx), read by the geometry warps
+    const float *delp;               // (n_outer, nz, ny, nx), read by the geometry warp
     float fc1[MAXF], fc2[MAXF], fc3[MAXF];   // q = (a - c1 b) (c2 b + c3): plain (0,0,1), product (0,1,0), diff (1,0,1/scale)
     int any_derived;                 // some field is a product or a difference
     int nsrc;                        // TMA sources (field parents)
@@ -67,31 +78,32 @@ struct Params {
 
 // ---- shared-memory carve-up --------------------------------------------------------------------
 struct Layout {
-    int ring, bars, warp0, warp_bytes;
-    int acc, rec, pe1, pe2, rdp2, den, edge, colw, colps, nmax, total;
+    int ring, bars, cell0, cell_bytes;          // per cell: acc, pe2, rdp2, den
+    int acc, pe2, rdp2, den;
+    int rec, ova, ovb, edge, colw, colps, total;
 };
 
-__host__ __device__ inline Layout make_layout(int nsrc, int nz, int V)
+__host__ __device__ inline Layout make_layout(int nsrc, int nz)
 {
     Layout L;
-    (void)V;
     int o = 0;
     L.ring = o;  o += NSTAGE * nsrc * BOX_BYTES;
-    L.bars = o;  o += 256;
-    L.warp0 = o;
+    L.bars = o;  o += 128;
+    L.cell0 = o;
     int w = 0;
     L.acc = w;   w += (nz + 1) * ACC_STRIDE;
-    L.rec = w;   w += 2 * REC_BYTES;             // double-buffered between a geometry warp and its consumer
-    L.nmax = w;  w += 2 * KC * 4;
-    L.pe1 = w;   w += PRING * C * 4;
     L.pe2 = w;   w += (nz + 2) * 4;              w = (w + 15) & ~15;
     L.rdp2 = w;  w += (nz + 1) * 4;              w = (w + 15) & ~15;
-    L.den = w;   w += (nz + 1) * 4;              w = (w + 15) & ~15;
-    L.edge = w;  w += C * 24 * 4;
-    L.colw = w;  w += 64 * 4;                    // 64 columns at cell start; [row parity][8] afterwards
-    L.colps = w; w += 64 * 4;
-    L.warp_bytes = (w + 127) & ~127;
-    L.total = L.warp0 + NCELL * L.warp_bytes;
+    L.den = w;   w += (nz + 1) * 4;
+    L.cell_bytes = (w + 127) & ~127;
+    o += NCELL * L.cell_bytes;
+    L.rec = o;   o += 2 * REC_BYTES;             // double-buffered between the geometry warp and the field warps
+    L.ova = o;   o += 2 * OVA_BYTES;
+    L.ovb = o;   o += 2 * OVB_BYTES;
+    L.edge = o;  o += NCOL * EDGE_WORDS * 4;
+    L.colw = o;  o += 8 * NCOL * 4;              // [row][column of the CTA]
+    L.colps = o; o += 8 * NCOL * 4;
+    L.total = o;
     return L;
 }
 
@@ -116,17 +128,6 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, int parity)
     while (!done)
         asm volatile("{.reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 0x989680; selp.u32 %0, 1, 0, p;}"
                      : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-}
-// wait of a warp that is ahead of its partner: sleep between polls instead of spinning on the issue port
-__device__ __forceinline__ void mbar_wait_relaxed(uint32_t bar, int parity)
-{
-    uint32_t done = 0;
-    for (;;) {
-        asm volatile("{.reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p;}"
-                     : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-        if (done) break;
-        __nanosleep(1500);
-    }
 }
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *map, int x, int y, int z, uint32_t bar)
 {
@@ -220,116 +221,109 @@ __device__ __forceinline__ int4 lds128i(uint32_t addr)
     asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
     return v;
 }
+__device__ __forceinline__ int ldsi32(uint32_t addr)
+{
+    int v;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void stsi32(uint32_t addr, int v)
+{
+    asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
 
-// ---- geometry: what the whole warp shares ------------------------------------------------------
-// All of it is a function of pressure only (mappm.f90:41-46, :58-124, :651-683).  Shared-window
-// byte addresses of the warp's private arrays (uniform across the warp):
-struct WG {
-    uint32_t acc, rec, pe1, pe2, rdp2, den, edge, colw, colps, nmax;
+// ---- geometry: what all fields share -----------------------------------------------------------
+// All of it is a function of pressure only (mappm.f90:41-46, :58-124, :651-683).
+struct CellG {                       // shared-window byte addresses of one coarse cell's arrays
+    uint32_t pe2, rdp2;              // coarse interfaces (nz + 1), 1 / thickness of every coarse level
+};
+struct ColG {                        // one fine column
+    float w, ps;                     // block-average weight (NaN -> 0); fine surface pressure (mask_below)
 };
 
-__device__ __forceinline__ int count_le(uint32_t pe2, int n, float p)
-{   // number of target interfaces i in [0, n) with pe2[i] <= p (pe2 ascending)
-    int lo = 0, hi = n;
-    while (lo < hi) {
-        const int mid = (lo + hi) >> 1;
-        if (lds32(pe2 + 4 * mid) <= p) lo = mid + 1; else hi = mid;
-    }
-    return lo;
-}
-
-// weight of fine column c in target level k (regridz.py:150-161 when mask_below)
-__device__ __forceinline__ float level_weight(const WG &g, int c, int k, int mask_below)
+// weight of a fine column in target level k (regridz.py:150-161 when mask_below)
+__device__ __forceinline__ float level_weight(const CellG &g, const ColG &col, int k, int mask_below)
 {
-    const float w = lds32(g.colw + 4 * c);
-    if (!mask_below) return w;
-    return lds32(g.pe2 + 4 * (k + 1)) < lds32(g.colps + 4 * c) ? w : 0.f;
+    if (!mask_below) return col.w;
+    return lds32(g.pe2 + 4 * (k + 1)) < col.ps ? col.w : 0.f;
 }
 // ... times 1 / thickness of that level
-__device__ __forceinline__ float level_scale(const WG &g, int c, int k, int mask_below)
+__device__ __forceinline__ float level_scale(const CellG &g, const ColG &col, int k, int mask_below)
 {
-    return level_weight(g, c, k, mask_below) * lds32(g.rdp2 + 4 * k);
+    return level_weight(g, col, k, mask_below) * lds32(g.rdp2 + 4 * k);
 }
 
-// Event of target interface i met in source layer L of column c (L == nz: below the surface).
-// Record (x, y, z, w):  I = x*q + y*x' + z*y'  closes a target level: run + I goes to accumulator
-// slot `slot`; the running sum of the next level restarts at -w * I.
-__device__ __forceinline__ float4 event_record(const WG &g, int c, int L, int i, int nz, int mask_below, float toa,
-                                               int &slot)
+// Event of target interface i met in source layer L = [pt, pb] of a column (L == nz: below the
+// surface, pt = surface pressure).  I = x*q + y*x' + z*y' closes a target level: run + I goes to
+// accumulator slot `slot`; the running sum of the next level restarts at -w * I.
+struct Event {
+    float x, y, z, w;
+    int slot;
+};
+__device__ __forceinline__ Event make_event(const CellG &g, const ColG &col, float pt, float pb, int L, int i, int nz,
+                                            int mask_below, float toa)
 {
     const int kn = nz;
-    float4 e = make_float4(0.f, 0.f, 0.f, 0.f);
-    slot = DUMMY_SLOT;
+    Event e = {0.f, 0.f, 0.f, 0.f, DUMMY_SLOT};
     if (L < nz) {
-        const float pt = lds32(g.pe1 + 4 * ((L & (PRING - 1)) * C + c));
-        const float pb = lds32(g.pe1 + 4 * (((L + 1) & (PRING - 1)) * C + c));
         const float pi = lds32(g.pe2 + 4 * i);
         if (pi <= toa) {                                                // mappm.f90:62-64, only met in L == 0
-            if (i < kn) { e.x = level_weight(g, c, i, mask_below); slot = i + 1; }
+            if (i < kn) { e.x = level_weight(g, col, i, mask_below); e.slot = i + 1; }
         } else {
             const float dpl = pb - pt;
             const float s = __fdividef(pi - pt, dpl);
             const int ke = i - 1;
             const bool end_ok = ke >= 0 && lds32(g.pe2 + 4 * (ke < 0 ? 0 : ke)) > toa;
             const bool start_ok = i < kn;
-            const float sc_e = end_ok ? level_scale(g, c, ke, mask_below) : 0.f;
-            const float sc_s = start_ok ? level_scale(g, c, i, mask_below) : 0.f;
+            const float sc_e = end_ok ? level_scale(g, col, ke, mask_below) : 0.f;
+            const float sc_s = start_ok ? level_scale(g, col, i, mask_below) : 0.f;
             const float sc = end_ok ? sc_e : sc_s;
             const float a = sc * dpl * s, oms = 1.f - s;
             e.x = a;
             e.y = a * oms * oms;
             e.z = -a * s * oms;
             e.w = end_ok ? (sc_e != 0.f ? __fdividef(sc_s, sc_e) : 0.f) : 1.f;
-            slot = end_ok ? ke + 1 : DUMMY_SLOT;
+            e.slot = end_ok ? ke + 1 : DUMMY_SLOT;
         }
     } else {                                                            // mappm.f90:65-67, :115-120
-        const float psf = lds32(g.pe1 + 4 * ((nz & (PRING - 1)) * C + c));
+        const float psf = pt;
         const int ke = i - 1;                                           // level whose bottom is interface i
         if (ke >= 0 && ke < kn) {
             const float top = lds32(g.pe2 + 4 * ke);
-            if (top >= psf) { e.x = level_weight(g, c, ke, mask_below); slot = ke + 1; }
-            else if (top > toa) { e.x = level_scale(g, c, ke, mask_below) * (lds32(g.pe2 + 4 * i) - psf); slot = ke + 1; }
+            if (top >= psf) { e.x = level_weight(g, col, ke, mask_below); e.slot = ke + 1; }
+            else if (top > toa) { e.x = level_scale(g, col, ke, mask_below) * (lds32(g.pe2 + 4 * i) - psf); e.slot = ke + 1; }
         }
     }
     return e;
 }
-// Build the records of steps t0 .. t0+KC-1; lane = (column c, step kk).  Record of step t (REC_BLOCK):
+
+// Lane state of the geometry warp: fine column x of the current row, walked from the top
+struct Walk {
+    float pm3, pm2, pm1, p0;         // interface pressures P(t-3) .. P(t)
+    int icnt;                        // coarse interfaces at or above the top of layer t - 2
+};
+
+// Step t of column x: level t (thickness d) arrives.  Writes the column's half of the pair record:
 //   E1, E2, F-1, G, H: PPM stencil of layer t-1 (mappm.f90:651-683, delp-only factors)
 //   dpw: weight of the whole layer t-2 in the target level open at its bottom
-//   ex, ey, ez, ew, off: the first event of layer t-2 (a no-op when it has none)
-//   info = first interface | count << 8 of the events of layer t-2 (further events are formed on the fly)
-__device__ __forceinline__ void build_chunk(const WG &g, float d /* delp(t0 + kk, column c) */, int lane, int t0, int nz,
-                                            int mask_below, float toa)
+//   ex, ey, ez, ew, off: the first event of layer t-2 (a no-op when it has none); further events go to the list
+__device__ __forceinline__ void geometry_step(Walk &s, const CellG &g, const ColG &col, float d, int t, int kk, int x,
+                                              uint32_t rec, uint32_t ova, uint32_t ovb, uint32_t edge, int nz,
+                                              int mask_below, float toa)
 {
-    const int c = lane & 7, kk = lane >> 3, t = t0 + kk;
-    // interface pressures by the reference's sequential cumsum (vertically_dependent.py:61-63):
-    // the running sum is handed from level to level, same order of additions
-    {
-        if (t0 == 0 && kk == 0) sts32(g.pe1 + 4 * c, toa);
-        const float pe0 = (t0 == 0) ? toa : lds32(g.pe1 + 4 * ((t0 & (PRING - 1)) * C + c));
-        float pe = 0.f;
-#pragma unroll
-        for (int j = 0; j < KC; ++j) {
-            const float prev = __shfl_up_sync(0xffffffffu, pe, 8);
-            if (kk == j) pe = (j == 0 ? pe0 : prev) + d;
-        }
-        if (t < nz) sts32(g.pe1 + 4 * (((t + 1) & (PRING - 1)) * C + c), pe);
-    }
-    __syncwarp();
-    auto P = [&](int m) { return lds32(g.pe1 + 4 * ((m & (PRING - 1)) * C + c)); };
-
+    // interface pressures by the reference's sequential cumsum (vertically_dependent.py:61-63)
+    const float pp1 = t < nz ? s.p0 + d : s.p0;                         // P(t+1)
     // (approximate division, 2 ulp: these factors multiply differences of q)
     float E1 = 0.f, E2 = 0.f, Fm = 0.f, G = 0.f, H = 0.f;
     const int j = t - 1;
     if (j >= 1 && j <= nz - 2) {
-        const float p0 = P(j - 1), p1 = P(j), p2 = P(j + 1), p3 = P(j + 2);
-        const float dm1 = p1 - p0, d0 = p2 - p1, dp1 = p3 - p2;        // mappm.f90:43 (from the rounded sums)
+        const float dm1 = s.pm1 - s.pm2, d0 = s.p0 - s.pm1, dp1 = pp1 - s.p0;     // mappm.f90:43 (from the rounded sums)
         const float d4 = dm1 + d0, d4p = d0 + dp1;
         const float r4 = __fdividef(1.f, d4), inv = __fdividef(d0, d4 + dp1);
         E1 = __fdividef(dm1 + 0.5f * d0, d4p) * inv;
         E2 = (dp1 + 0.5f * d0) * r4 * inv;
         if (j >= 2) {
-            const float dm2 = p0 - P(j - 2), d4m = dm2 + dm1;
+            const float dm2 = s.pm2 - s.pm3, d4m = dm2 + dm1;
             const float cq = dm1 * r4, a1 = __fdividef(d4m, d4 + dm1), a2 = __fdividef(d4p, d4 + d0);
             const float gg = __fdividef(2.f, d4m + d4p);
             Fm = cq * (1.f + gg * d0 * (a1 - a2)) - 1.f;
@@ -340,103 +334,140 @@ __device__ __forceinline__ void build_chunk(const WG &g, float d /* delp(t0 + kk
     // one-sided cubics at the column ends (mappm.f90:689-747), once per column
     if (t == 2 || t == nz) {
         const bool top = (t == 2);
-        const int m = top ? 0 : nz - 2;
-        const float q0 = P(m), q1 = P(m + 1), q2 = P(m + 2);
+        const float q0 = s.pm2, q1 = s.pm1, q2 = s.p0;                  // P(m), P(m+1), P(m+2), m = 0 or nz - 2
         const float d1 = top ? q1 - q0 : q2 - q1, d2 = top ? q2 - q1 : q1 - q0;
         const float D = d2 * (2.f * d2 * d2 + d1 * (d2 + 3.f * d1));
         const float Pq = d2 * (5.f * d1 + d2) - 3.f * d1 * d1;
         const float Rr = d1 * d2 * (d2 + 3.f * d1);
         const float r12 = 1.f / (d1 + d2);
-        const uint32_t e = g.edge + 4 * (c * 24 + (top ? 0 : 12));
+        const uint32_t e = edge + 4 * (x * EDGE_WORDS + (top ? 0 : 12));
         sts128(e, make_float4(d2 * r12, d1 * r12, 2.f * r12, (top ? 4.f : 1.f) / D));
         sts128(e + 16, make_float4(d2, (top ? 0.5f : 2.f) * Pq, (top ? 0.25f : 1.f) * Rr, (top ? 2.f : 8.f) * d1 * d1 * d1));
         sts32(e + 32, d1);
     }
-    // events of layer L = t - 2 and its whole-layer weight.  Interfaces at or above the bottom of a
-    // layer are counted once (binary search); the count of the layer above comes from the lane above.
+    // events of layer L = t - 2: the coarse interfaces in (top, bottom] of the layer, by the two-pointer merge
+    // (mappm.f90:70-75 keeps k0 the same way); L == nz is everything below the surface
     const int L = t - 2, kn = nz;
-    float dpw = 0.f, pt = 0.f, pb = 0.f;
-    int i1 = 0;
-    if (L >= 0 && L < nz) { pt = P(L); pb = P(L + 1); i1 = count_le(g.pe2, kn + 1, pb); }
-    else if (L == nz) i1 = kn + 1;
-    int i0 = __shfl_up_sync(0xffffffffu, i1, 8);
-    if (kk == 0) i0 = __float_as_int(lds32(g.edge + 4 * (c * 24 + 22)));       // last layer of the previous chunk
-    if (L <= 0) i0 = 0;
-    if (kk == KC - 1) sts32(g.edge + 4 * (c * 24 + 22), __int_as_float(i1));
-    int n = (L >= 0 && L <= nz) ? i1 - i0 : 0;
-    if (n < 0) n = 0;                                                   // NaN / non-monotone pressures
+    const float pt = s.pm2, pb = s.pm1;
+    int i1 = s.icnt;
+    float dpw = 0.f;
     if (L >= 0 && L < nz) {
+        while (i1 <= kn && lds32(g.pe2 + 4 * i1) <= pb) ++i1;
         const int ko = i1 - 1;                                          // level open at the bottom of L
-        if (ko >= 0 && ko < kn && lds32(g.pe2 + 4 * ko) > toa) dpw = level_scale(g, c, ko, mask_below) * (pb - pt);
+        if (ko >= 0 && ko < kn && lds32(g.pe2 + 4 * ko) > toa) dpw = level_scale(g, col, ko, mask_below) * (pb - pt);
+    } else if (L == nz) {
+        i1 = kn + 1;
     }
-    float4 e0 = make_float4(0.f, 0.f, 0.f, 0.f);
-    int slot = DUMMY_SLOT;
-    if (n > 0) e0 = event_record(g, c, L, i0, nz, mask_below, toa, slot);
-    const uint32_t r = g.rec + (kk * (C / 2) + (c >> 1)) * REC_BLOCK + 4 * (c & 1);
+    const int n = i1 - s.icnt;
+    Event e0 = {0.f, 0.f, 0.f, 0.f, DUMMY_SLOT};
+    if (n > 0) e0 = make_event(g, col, pt, pb, L, s.icnt, nz, mask_below, toa);
+    int info = n;
+    if (n > 1) {
+        const uint32_t oa = ova + (kk * NCOL + x) * (MAXE * 16), ob = ovb + (kk * NCOL + x) * (MAXE * 4);
+        if (n - 1 <= MAXE) {
+            for (int e = 1; e < n; ++e) {
+                const Event ev = make_event(g, col, pt, pb, L, s.icnt + e, nz, mask_below, toa);
+                sts128(oa + 16 * (e - 1), make_float4(ev.x, ev.y, ev.z, -ev.w));
+                stsi32(ob + 4 * (e - 1), ev.slot * ACC_STRIDE);
+            }
+        } else {                                                        // park what the field warps need to form them
+            sts128(oa, make_float4(pt, pb, col.w, col.ps));
+            stsi32(ob, s.icnt);
+            stsi32(ob + 4, n);
+            info = INFO_SLOW;
+        }
+    }
+    const uint32_t r = rec + (kk * (NCOL / 2) + (x >> 1)) * REC_BLOCK + 4 * (x & 1);
     sts32(r, E1);           sts32(r + 8, E2);
     sts32(r + 16, Fm);      sts32(r + 24, G);
     sts32(r + 32, -H);      sts32(r + 40, dpw);
     sts32(r + 48, e0.x);    sts32(r + 56, e0.y);
     sts32(r + 64, e0.z);    sts32(r + 72, -e0.w);
-    sts32(r + 80, __int_as_float(slot * ACC_STRIDE));
-    sts32(r + 88, __int_as_float(i0 | (n << 8)));
-    int nm = n;                                                         // most events of any column at this step
-    nm = max(nm, __shfl_xor_sync(0xffffffffu, nm, 1));
-    nm = max(nm, __shfl_xor_sync(0xffffffffu, nm, 2));
-    nm = max(nm, __shfl_xor_sync(0xffffffffu, nm, 4));
-    if (c == 0) sts32(g.nmax + 4 * kk, (float)nm);
-    __syncwarp();
+    stsi32(r + 80, e0.slot * ACC_STRIDE);
+    stsi32(r + 88, info);
+    s.icnt = i1;
+    s.pm3 = s.pm2; s.pm2 = s.pm1; s.pm1 = s.p0; s.p0 = pp1;
 }
 
 // ---- per-field work -----------------------------------------------------------------------------
+struct Ctx {                         // what a field warp needs besides its registers
+    uint32_t rec, ova, ovb;          // this chunk's geometry buffers
+    uint32_t edge;                   // one-sided cubic coefficients of the CTA's columns
+    CellG g;
+    int w;                           // cell of the warp
+    int nz, mask_below;
+    float toa;
+};
+
 // the record of one column at one step, gathered from its pair block (general step only)
 struct Rec {
     float E1, E2, Fm, G, H, dpw;
     float4 ev;
     int off, info;
 };
-__device__ __forceinline__ Rec load_rec(uint32_t rec, int kk, int c)
+__device__ __forceinline__ Rec load_rec(const Ctx &cx, int kk, int c)
 {
-    const uint32_t b = rec + (kk * (C / 2) + (c >> 1)) * REC_BLOCK + 4 * (c & 1);
+    const uint32_t b = cx.rec + (kk * (NCOL / 2) + 4 * cx.w + (c >> 1)) * REC_BLOCK + 4 * (c & 1);
     Rec r;
     r.E1 = lds32(b);        r.E2 = lds32(b + 8);
     r.Fm = lds32(b + 16);   r.G = lds32(b + 24);
     r.H = -lds32(b + 32);   r.dpw = lds32(b + 40);
-    r.ev = make_float4(lds32(b + 48), lds32(b + 56), lds32(b + 64), -lds32(b + 72));
-    r.off = __float_as_int(lds32(b + 80));
-    r.info = __float_as_int(lds32(b + 88));
+    r.ev = make_float4(lds32(b + 48), lds32(b + 56), lds32(b + 64), lds32(b + 72));
+    r.off = ldsi32(b + 80);
+    r.info = ldsi32(b + 88);
     return r;
 }
 
-// one event: close a target level with run + I (NaN-skipping block sum, coarsen.py:211), restart the
-// running sum of the next one.  acc_lane = &acc[0][lane]; slot 0 collects what belongs to no level.
-__device__ __forceinline__ void apply_event(const float4 ev, int off, float q, float x, float y, bool keep, float &run,
-                                            uint32_t acc_lane)
+// close a target level with `tot` (NaN-skipping block sum, coarsen.py:211).  acc_lane = &acc[0][lane];
+// slot 0 collects what belongs to no level.
+__device__ __forceinline__ void flush(uint32_t acc_lane, int off, float tot)
 {
-    const float I = ev.x * q + ev.y * x + ev.z * y;
-    const float tot = run + I;
     const uint32_t a = acc_lane + off;
     sts32(a, lds32(a) + (tot == tot ? tot : 0.f));
-    run = keep ? run : -(ev.w * I);
 }
 
-// events 1 .. n-1 of a layer cut by several coarse interfaces (rare: formed on the fly, out of line)
-__device__ __noinline__ float extra_events(WG g, int c, int L, int info, float q, float x, float y, float run,
-                                           uint32_t acc_lane, int nz, int mask_below, float toa)
+// events 1 .. n-1 of a layer cut by more than MAXE + 1 coarse interfaces (rare: formed on the fly, out of line)
+__device__ __noinline__ float extras_slow(uint32_t oa, uint32_t ob, uint32_t pe2, uint32_t rdp2, int L, float q, float x,
+                                          float y, float r, uint32_t acc_lane, int nz, int mask_below, float toa)
 {
-    const int n = info >> 8, i0 = info & 255;
+    const float4 pp = lds128(oa);                                       // pt, pb, weight, surface pressure
+    const int i0 = ldsi32(ob), n = ldsi32(ob + 4);
+    CellG g; g.pe2 = pe2; g.rdp2 = rdp2;
+    ColG col; col.w = pp.z; col.ps = pp.w;
     for (int e = 1; e < n; ++e) {
-        int slot;
-        const float4 ev = event_record(g, c, L, i0 + e, nz, mask_below, toa, slot);
-        apply_event(ev, slot * ACC_STRIDE, q, x, y, false, run, acc_lane);
+        const Event ev = make_event(g, col, pp.x, pp.y, L, i0 + e, nz, mask_below, toa);
+        const float I = ev.x * q + ev.y * x + ev.z * y;
+        flush(acc_lane, ev.slot * ACC_STRIDE, r + I);
+        r = -(ev.w * I);
     }
-    return run;
+    return r;
+}
+
+// events 1 .. n-1 of column c (of the warp's cell) at step kk; r = restart value left by event 0
+__device__ __forceinline__ float apply_extras(const Ctx &cx, int kk, int c, int info, int L, float q, float x, float y,
+                                              float r, uint32_t acc_lane)
+{
+    const int xc = 8 * cx.w + c;
+    const uint32_t oa = cx.ova + (kk * NCOL + xc) * (MAXE * 16), ob = cx.ovb + (kk * NCOL + xc) * (MAXE * 4);
+    if (info == INFO_SLOW)
+        return extras_slow(oa, ob, cx.g.pe2, cx.g.rdp2, L, q, x, y, r, acc_lane, cx.nz, cx.mask_below, cx.toa);
+#pragma unroll
+    for (int e = 0; e < MAXE; ++e) {
+        if (e + 2 <= info) {
+            const float4 ev = lds128(oa + 16 * e);
+            const int off = ldsi32(ob + 4 * e);
+            const float I = ev.x * q + ev.y * x + ev.z * y;
+            flush(acc_lane, off, r + I);
+            r = ev.w * I;                                               // stored negated
+        }
+    }
+    return r;
 }
 
 // Limited parabola of layer L in deviation form, x = AL - q, y = AR - q, A6 = -3 (x + y)
 // (ppm_limiters lmt = 0, mappm.f90:875-894), then the events of the layer and its whole-layer term.
-__device__ __forceinline__ void finish_layer(const WG &g, int c, int L, float q, float x, float y, float dc, float &run,
-                                             const Rec &r, uint32_t acc_lane, int nz, int mask_below, float toa)
+__device__ __forceinline__ void finish_layer(const Ctx &cx, int kk, int c, int L, float q, float x, float y, float dc,
+                                             float &run, const Rec &r, uint32_t acc_lane)
 {
     const float da1 = y - x, s = x + y;
     const float t = s * da1, da2 = da1 * (da1 * (1.f / 3.f));
@@ -446,18 +477,19 @@ __device__ __forceinline__ void finish_layer(const WG &g, int c, int L, float q,
     x = c2 ? m2y : x;                  // a6da >  da2: AL = AR - 3 (AR - q)
     x = flat ? 0.f : x;
     y = flat ? 0.f : y;
-    apply_event(r.ev, r.off, q, x, y, r.info < 256, run, acc_lane);
-    if (r.info >= (2 << 8))            // a layer cut by several coarse interfaces: the others out of line
-        run = extra_events(g, c, L, r.info, q, x, y, run, acc_lane, nz, mask_below, toa);
-    run = fmaf(r.dpw, q, run);
+    const float I = r.ev.x * q + r.ev.y * x + r.ev.z * y;
+    flush(acc_lane, r.off, run + I);
+    float rs = r.info == 0 ? run : r.ev.w * I;                          // ev.w is stored negated
+    if (r.info > 1) rs = apply_extras(cx, kk, c, r.info, L, q, x, y, rs, acc_lane);
+    run = fmaf(r.dpw, q, rs);
 }
 
 // one-sided cubic at the column top (mappm.f90:689-707), evaluated at step t = 2 once level 3 is
 // visible: returns (x, y, dc) of layer 0 and x of layer 1
-__device__ __noinline__ float4 top_fix(uint32_t rec, int c, uint32_t edge, float qn, float dqn, float dcn, float q1, float q0,
+__device__ __noinline__ float4 top_fix(uint32_t rec3, uint32_t edge, float qn, float dqn, float dcn, float q1, float q0,
                                        float q3)
 {
-    const uint32_t b = rec + (3 * (C / 2) + (c >> 1)) * REC_BLOCK + 4 * (c & 1);      // record of step 3
+    const uint32_t b = rec3;                                            // the column's record of step 3
     const float E1 = lds32(b), E2 = lds32(b + 8), Fm = lds32(b + 16), G = lds32(b + 24), nH = lds32(b + 32);
     const float dq3 = q3 - qn;
     const float df2 = E1 * dq3 + E2 * dqn;
@@ -529,14 +561,14 @@ struct State {
 };
 
 // One step of the tandem walk for the 8 columns of a row: level t arrives, layer t-2 is finished.
-// Interior levels where no column is cut by more than one coarse interface: straight line, two columns
-// per arithmetic instruction; the min/max, compare and select parts run on the halves.
-__device__ __forceinline__ void hot_step(uint32_t rec, uint32_t stage, int kk, int w, const Field &f, int any_derived,
+// Interior levels: straight line, two columns per arithmetic instruction; the min/max, compare and
+// select parts run on the halves; further events of a layer behind warp-uniform branches.
+__device__ __forceinline__ void hot_step(const Ctx &cx, uint32_t stage, int t, int kk, const Field &f, int any_derived,
                                          State &s, uint32_t acc_lane)
 {
     u64 q[4];
-    load_row(q, stage, kk, w, f, any_derived);
-    const uint32_t rb = rec + kk * (C / 2) * REC_BLOCK;
+    load_row(q, stage, kk, cx.w, f, any_derived);
+    const uint32_t rb = cx.rec + (kk * (NCOL / 2) + 4 * cx.w) * REC_BLOCK;
     const u64 third = pk(1.f / 3.f, 1.f / 3.f), neg2 = pk(-2.f, -2.f);
     u64 E1, E2, Fm, G, NH, DPW, EX, EY, EZ, NW;
     int4 oi;
@@ -571,19 +603,24 @@ __device__ __forceinline__ void hot_step(uint32_t rec, uint32_t stage, int kk, i
         xa = ca == 0.f ? 0.f : xa;  ya = ca == 0.f ? 0.f : ya;
         xb = cb == 0.f ? 0.f : xb;  yb = cb == 0.f ? 0.f : yb;
         const u64 xl = pk(xa, xb), yl = pk(ya, yb), qB = s.B[p];
-        // the (at most one) event of each column: close a target level, restart the next
+        // the first event of each column: close a target level, restart the next
         const u64 I = fma2(EZ, yl, fma2(EY, xl, mul2(EX, qB)));
         const u64 tot = add2(s.run[p], I);
         float tota, totb;
         upk(tot, tota, totb);
-        const uint32_t aa = acc_lane + oi.x, ab = acc_lane + oi.y;
-        sts32(aa, lds32(aa) + (tota == tota ? tota : 0.f));
-        sts32(ab, lds32(ab) + (totb == totb ? totb : 0.f));
+        flush(acc_lane, oi.x, tota);
+        flush(acc_lane, oi.y, totb);
         float ra, rb_, na, nb;
         upk(s.run[p], ra, rb_);
         upk(mul2(NW, I), na, nb);
-        ra = oi.z < 256 ? ra : na;
-        rb_ = oi.w < 256 ? rb_ : nb;
+        ra = oi.z == 0 ? ra : na;
+        rb_ = oi.w == 0 ? rb_ : nb;
+        if ((oi.z | oi.w) > 1) {                                            // layers cut by several coarse interfaces
+            float qa, qb;
+            upk(qB, qa, qb);
+            if (oi.z > 1) ra = apply_extras(cx, kk, 2 * p, oi.z, t - 2, qa, xa, ya, ra, acc_lane);
+            if (oi.w > 1) rb_ = apply_extras(cx, kk, 2 * p + 1, oi.w, t - 2, qb, xb, yb, rb_, acc_lane);
+        }
         s.run[p] = fma2(DPW, qB, pk(ra, rb_));
         s.B[p] = s.A[p]; s.A[p] = qn; s.dq[p] = dqn; s.dc[p] = dcn; s.xp[p] = xn;
         E1 = E1n; E2 = E2n; Fm = Fmn; G = Gn; NH = NHn; DPW = DPWn; EX = EXn; EY = EYn; EZ = EZn; NW = NWn;
@@ -592,11 +629,11 @@ __device__ __forceinline__ void hot_step(uint32_t rec, uint32_t stage, int kk, i
 }
 
 // The same step for the ends of the column (t < 3, t >= nz: one-sided cubics, nothing to finish, below the
-// surface) and for levels where some column is cut by several coarse interfaces: column by column.
-__device__ __forceinline__ void general_step(const WG &g, uint32_t stage, int t, int kk, int w, const Field &f,
-                                             int any_derived, State &s, uint32_t acc_lane, int nz, int mask_below,
-                                             float toa)
+// surface): column by column.
+__device__ __forceinline__ void general_step(const Ctx &cx, uint32_t stage, int t, int kk, const Field &f,
+                                          int any_derived, State &s, uint32_t acc_lane)
 {
+    const int nz = cx.nz, w = cx.w;
     float A[C], B[C], dq1[C], dcp[C], xp[C], run[C], qv[C], q3[C];
 #pragma unroll
     for (int p = 0; p < 4; ++p) {
@@ -622,7 +659,7 @@ __device__ __forceinline__ void general_step(const WG &g, uint32_t stage, int t,
     }
 #pragma unroll
     for (int c = 0; c < C; ++c) {
-        const Rec r = load_rec(g.rec, kk, c);
+        const Rec r = load_rec(cx, kk, c);
         const float qn = qv[c];
         float dqn = qn - A[c];                                              // delq(t)
         const float df2 = r.E1 * dqn + r.E2 * dq1[c];                       // layer t-1, mappm.f90:661
@@ -630,11 +667,13 @@ __device__ __forceinline__ void general_step(const WG &g, uint32_t stage, int t,
         float xn = r.Fm * dq1[c] + r.G * dcp[c] - r.H * dcn;                // AL(t-1) - q(t-1), :674-683
         float x = xp[c], y = xn + dq1[c], dc = dcp[c];                      // layer t-2
         if (ends) {
+            const uint32_t edge = cx.edge + 4 * ((8 * w + c) * EDGE_WORDS);
             if (t == 2) {
-                const float4 v = top_fix(g.rec, c, g.edge + 4 * (c * 24), qn, dqn, dcn, A[c], B[c], q3[c]);
+                const uint32_t rec3 = cx.rec + (3 * (NCOL / 2) + 4 * w + (c >> 1)) * REC_BLOCK + 4 * (c & 1);
+                const float4 v = top_fix(rec3, edge, qn, dqn, dcn, A[c], B[c], q3[c]);
                 x = v.x; y = v.y; dc = v.z; xn = v.w;
             } else if (t == nz) {
-                const float4 v = bottom_fix(g.edge + 4 * (c * 24 + 12), A[c], B[c], xp[c]);
+                const float4 v = bottom_fix(edge + 48, A[c], B[c], xp[c]);
                 y = v.x; xn = v.y; dcn = v.z; dqn = v.w;                    // layer nz-1 is finished next step
             } else if (t == nz + 1) {
                 y = dq1[c];
@@ -642,7 +681,7 @@ __device__ __forceinline__ void general_step(const WG &g, uint32_t stage, int t,
                 x = 0.f; y = 0.f; dc = 0.f;
             }
         }
-        finish_layer(g, c, t - 2, B[c], x, y, dc, run[c], r, acc_lane, nz, mask_below, toa);
+        finish_layer(cx, kk, c, t - 2, B[c], x, y, dc, run[c], r, acc_lane);
         B[c] = A[c]; A[c] = qn; dq1[c] = dqn; dcp[c] = dcn; xp[c] = xn;
     }
 #pragma unroll
@@ -653,20 +692,21 @@ __device__ __forceinline__ void general_step(const WG &g, uint32_t stage, int t,
     }
 }
 
-// 128 registers at launch (2 CTAs of 256 threads per SM); the consumer warpgroup then takes 184 and the
-// geometry warpgroup drops to 72 (setmaxnreg)
+// 128 registers at launch (2 CTAs of 256 threads per SM); the field warpgroup then takes 184 and the
+// helper warpgroup drops to 72 (setmaxnreg).  Only the first helper warp works (the geometry warp);
+// the other three exist so that both setmaxnreg instructions are issued by whole warpgroups.
 __global__ void __maxnreg__(128)
 plevel_stream_kernel(const __grid_constant__ Params p)
 {
     extern __shared__ __align__(1024) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int nz = p.nz, V = p.nfields, nsrc = p.nsrc;
-    const Layout lay = make_layout(nsrc, nz, V);
+    const Layout lay = make_layout(nsrc, nz);
     const uint32_t sbase = smem_u32(smem);
     const uint32_t ring = sbase + lay.ring;
-    // barriers: full[NSTAGE], empty[NSTAGE] (field ring); gfull[NCELL][2], gempty[NCELL][2] (geometry buffers)
+    // barriers: full[NSTAGE], empty[NSTAGE] (field ring + geometry buffers), gfull[2] (geometry buffers)
     const uint32_t bars = sbase + lay.bars;
-    const uint32_t gbars = bars + 8 * 2 * NSTAGE;
+    const uint32_t gfull = bars + 8 * 2 * NSTAGE;
     const int stage_bytes = nsrc * BOX_BYTES;
     const int nch = (nz + 3 + KC - 1) / KC;                     // steps t = 0 .. nz + 2
     const int bx = blockIdx.x, by = blockIdx.y;
@@ -674,105 +714,134 @@ plevel_stream_kernel(const __grid_constant__ Params p)
 
     if (tid == 0) {
         for (int s = 0; s < NSTAGE; ++s) {
-            mbar_init(bars + 8 * s, NCELL);                 // full: one expect_tx arrival per geometry warp
-            mbar_init(bars + 8 * (NSTAGE + s), NCELL);      // empty: one arrival per consumer warp
+            mbar_init(bars + 8 * s, 1);                     // full: the geometry warp's expect_tx arrival
+            mbar_init(bars + 8 * (NSTAGE + s), NCELL);      // empty: one arrival per field warp
+            mbar_init(gfull + 8 * s, 1);
         }
-        for (int i = 0; i < 2 * NCELL; ++i) mbar_init(gbars + 8 * i, 1);
         asm volatile("fence.mbarrier_init.release.cluster;");
     }
     __syncthreads();
 
-    const int w = warp & (NCELL - 1);                           // the cell this warp works for
-    const uint32_t wb = sbase + lay.warp0 + w * lay.warp_bytes;
-    WG g;
-    g.acc = wb + lay.acc;   g.rec = wb + lay.rec;   g.pe1 = wb + lay.pe1;
-    g.pe2 = wb + lay.pe2;   g.rdp2 = wb + lay.rdp2; g.den = wb + lay.den;   g.edge = wb + lay.edge;
-    g.colw = wb + lay.colw; g.colps = wb + lay.colps; g.nmax = wb + lay.nmax;
-    const uint32_t gfull = gbars + 8 * (2 * w);
     const int ny = p.ny, nx = p.nx, nyc = ny >> 3, nxc = nx >> 3;
     const long h = (long)ny * nx, hc = (long)nyc * nxc;
-    const int cx = 4 * bx + w;
     const float toa = p.toa;
     const int mask_below = p.mask_below;
+    const uint32_t rec0 = sbase + lay.rec, ova0 = sbase + lay.ova, ovb0 = sbase + lay.ovb, edge = sbase + lay.edge;
 
     if (warp >= NCELL) {
-        // ---------------- geometry warp of cell w: everything that depends on pressure only ---------
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(HELPER_REGS));
-        // cell prologue: coarse interfaces (sequential cumsum, vertically_dependent.py:61-63), 1/thickness,
-        // sum of the 64 columns' weights per target level (coarsen.py:212)
-        for (int k = lane; k < nz; k += 32) sts32(g.rdp2 + 4 * k, p.delp_coarse[(o * nz + k) * hc + (long)by * nxc + cx]);
-        for (int i = lane; i < 64; i += 32) {
-            const long col = o * h + (long)(8 * by + (i >> 3)) * nx + 8 * cx + (i & 7);
+        if (warp != NCELL) return;
+        // ---------------- geometry warp: lane = fine column x of the CTA's 32 ------------------------
+        const int x = lane, cell = x >> 3, c = x & 7;
+        const uint32_t colw = sbase + lay.colw, colps = sbase + lay.colps;
+        auto cellbase = [&](int cl) { return sbase + lay.cell0 + cl * lay.cell_bytes; };
+        CellG g;
+        g.pe2 = cellbase(cell) + lay.pe2;
+        g.rdp2 = cellbase(cell) + lay.rdp2;
+        // CTA prologue: coarse interfaces of the 4 cells (sequential cumsum, vertically_dependent.py:61-63),
+        // 1 / thickness, sum of the 64 columns' weights per target level (coarsen.py:212)
+        for (int idx = lane; idx < NCELL * nz; idx += 32) {
+            const int cl = idx & (NCELL - 1), k = idx / NCELL;
+            sts32(cellbase(cl) + lay.rdp2 + 4 * k, p.delp_coarse[(o * nz + k) * hc + (long)by * nxc + NCELL * bx + cl]);
+        }
+        float wr[8], pr[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const long col = o * h + (long)(8 * by + r) * nx + NCOL * bx + x;
             const float a = p.area[col];
-            sts32(g.colw + 4 * i, (a == a) ? a : 0.f);
-            sts32(g.colps + 4 * i, mask_below ? p.psurf[col] : 0.f);
+            wr[r] = (a == a) ? a : 0.f;
+            pr[r] = mask_below ? p.psurf[col] : 0.f;
+            sts32(colw + 4 * (r * NCOL + x), wr[r]);
+            sts32(colps + 4 * (r * NCOL + x), pr[r]);
         }
         __syncwarp();
-        if (lane == 0) {
+        if (lane < NCELL) {
+            const uint32_t cb = cellbase(lane);
             float pe = toa;
-            sts32(g.pe2, pe);
-            for (int k = 0; k < nz; ++k) { pe = pe + lds32(g.rdp2 + 4 * k); sts32(g.pe2 + 4 * (k + 1), pe); }
+            sts32(cb + lay.pe2, pe);
+            for (int k = 0; k < nz; ++k) { pe = pe + lds32(cb + lay.rdp2 + 4 * k); sts32(cb + lay.pe2 + 4 * (k + 1), pe); }
         }
         __syncwarp();
-        for (int k = lane; k < nz; k += 32) {
-            const float lower = lds32(g.pe2 + 4 * (k + 1));
-            sts32(g.rdp2 + 4 * k, 1.f / (lower - lds32(g.pe2 + 4 * k)));
-            float d = 0.f;
-            for (int i = 0; i < 64; ++i) d += (!mask_below || lower < lds32(g.colps + 4 * i)) ? lds32(g.colw + 4 * i) : 0.f;
-            sts32(g.den + 4 * k, d);
+        for (int idx = lane; idx < NCELL * nz; idx += 32) {
+            const int cl = idx & (NCELL - 1), k = idx / NCELL;
+            const uint32_t cb = cellbase(cl);
+            sts32(cb + lay.rdp2 + 4 * k, 1.f / (lds32(cb + lay.pe2 + 4 * (k + 1)) - lds32(cb + lay.pe2 + 4 * k)));
+        }
+        {
+            const uint32_t den = cellbase(cell) + lay.den;
+            if (!mask_below) {
+                float d = 0.f;
+#pragma unroll
+                for (int r = 0; r < 8; ++r) d += wr[r];
+                d += __shfl_xor_sync(0xffffffffu, d, 1);
+                d += __shfl_xor_sync(0xffffffffu, d, 2);
+                d += __shfl_xor_sync(0xffffffffu, d, 4);
+                for (int k = c; k < nz; k += C) sts32(den + 4 * k, d);
+            } else {
+                for (int k = 0; k < nz; ++k) {
+                    const float lower = lds32(g.pe2 + 4 * (k + 1));
+                    float d = 0.f;
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) d += lower < pr[r] ? wr[r] : 0.f;
+                    d += __shfl_xor_sync(0xffffffffu, d, 1);
+                    d += __shfl_xor_sync(0xffffffffu, d, 2);
+                    d += __shfl_xor_sync(0xffffffffu, d, 4);
+                    if (c == 0) sts32(den + 4 * k, d);
+                }
+            }
         }
         __syncwarp();
 
-        const int c = lane & 7, kk = lane >> 3;
-        const float *dcol = p.delp + o * nz * h + (long)(8 * by) * nx + 8 * cx + c;
+        const float *dcol = p.delp + o * nz * h + (long)(8 * by) * nx + NCOL * bx + x;
+        float dn[KC];
         auto load_delp = [&](int row, int chunk) {
-            const int lvl = chunk * KC + kk;
-            return lvl < nz ? ldg_stream(dcol + (long)lvl * h + (long)row * nx) : 0.f;
-        };
-        float dnext = load_delp(0, 0);
-        for (int row = 0; row < 8; ++row) {
-            // this row's 8 columns, double-buffered by row parity (the consumer may still be on the previous row)
-            WG gr = g;
-            gr.colw = g.colw + 32 * (row & 1);
-            gr.colps = g.colps + 32 * (row & 1);
-            if (lane < C) {
-                const long col = o * h + (long)(8 * by + row) * nx + 8 * cx + lane;
-                const float a = p.area[col];
-                sts32(gr.colw + 4 * lane, (a == a) ? a : 0.f);
-                sts32(gr.colps + 4 * lane, mask_below ? p.psurf[col] : 0.f);
+#pragma unroll
+            for (int kk = 0; kk < KC; ++kk) {
+                const int lvl = chunk * KC + kk;
+                dn[kk] = lvl < nz ? ldg_stream(dcol + (long)lvl * h + (long)row * nx) : 0.f;
             }
-            __syncwarp();
+        };
+        load_delp(0, 0);
+        for (int row = 0; row < 8; ++row) {
+            ColG col;
+            col.w = lds32(colw + 4 * (row * NCOL + x));
+            col.ps = lds32(colps + 4 * (row * NCOL + x));
+            Walk s;
+            s.pm3 = s.pm2 = s.pm1 = s.p0 = toa;
+            s.icnt = 0;
             for (int chunk = 0; chunk < nch; ++chunk) {
                 const int it = row * nch + chunk, b = it & 1;
-                const float d = dnext;
-                if (chunk + 1 < nch) dnext = load_delp(row, chunk + 1);
-                else if (row + 1 < 8) dnext = load_delp(row + 1, 0);
-                // stage b of the field ring and geometry buffer b are released together by the consumers
-                if (it >= 2) mbar_wait_relaxed(bars + 8 * (NSTAGE + b), ((it >> 1) - 1) & 1);
-                {   // this warp's share of the TMA boxes: parents w, w + 4, ...
-                    const int mine = (nsrc - w + NCELL - 1) / NCELL;
-                    if (lane == 0) mbar_expect_tx(bars + 8 * b, mine * KC * 128);
-                    __syncwarp();
-                    const int src = w + NCELL * lane;
-                    if (lane < mine)
-                        tma_load_3d(ring + b * stage_bytes + src * BOX_BYTES, &p.maps[src], 32 * bx, 8 * by + row,
-                                    (int)(o * nz) + chunk * KC, bars + 8 * b);
-                }
-                WG gb = gr;
-                gb.rec = g.rec + b * REC_BYTES;
-                gb.nmax = g.nmax + b * KC * 4;
-                build_chunk(gb, d, lane, chunk * KC, nz, mask_below, toa);
+                float d[KC];
+#pragma unroll
+                for (int kk = 0; kk < KC; ++kk) d[kk] = dn[kk];
+                if (chunk + 1 < nch) load_delp(row, chunk + 1);
+                else if (row + 1 < 8) load_delp(row + 1, 0);
+                // stage b of the field ring and geometry buffer b are released together by the field warps
+                if (it >= 2) mbar_wait(bars + 8 * (NSTAGE + b), ((it >> 1) - 1) & 1);
+                if (lane == 0) mbar_expect_tx(bars + 8 * b, nsrc * KC * 128);
+                __syncwarp();
+                for (int src = lane; src < nsrc; src += 32)
+                    tma_load_3d(ring + b * stage_bytes + src * BOX_BYTES, &p.maps[src], NCOL * bx, 8 * by + row,
+                                (int)(o * nz) + chunk * KC, bars + 8 * b);
+#pragma unroll
+                for (int kk = 0; kk < KC; ++kk)
+                    geometry_step(s, g, col, d[kk], chunk * KC + kk, kk, x, rec0 + b * REC_BYTES, ova0 + b * OVA_BYTES,
+                                  ovb0 + b * OVB_BYTES, edge, nz, mask_below, toa);
+                __syncwarp();
                 if (lane == 0) mbar_arrive(gfull + 8 * b);
             }
         }
         return;
     }
 
-    // ---------------- consumer warp of cell (by, 4 bx + w): lanes = fields ----------------------------
+    // ---------------- field warp of cell (by, 4 bx + w): lanes = fields -------------------------------
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(CONSUMER_REGS));
+    const int w = warp;
+    const uint32_t cb = sbase + lay.cell0 + w * lay.cell_bytes;
+    const int cx_ = NCELL * bx + w;
     const bool active = lane < V;
-    const uint32_t acc_lane = g.acc + 4 * lane;                 // every lane owns a column of the accumulator
-    for (int i = lane; i < (nz + 1) * 32; i += 32) sts32(g.acc + 4 * i, 0.f);
+    const uint32_t acc_lane = cb + lay.acc + 4 * lane;          // every lane owns a column of the accumulator
+    for (int i = lane; i < (nz + 1) * 32; i += 32) sts32(cb + lay.acc + 4 * i, 0.f);
     __syncwarp();
     Field fld;
     fld.fa = active ? p.fa[lane] : 0;
@@ -781,34 +850,36 @@ plevel_stream_kernel(const __grid_constant__ Params p)
     fld.c2 = active ? p.fc2[lane] : 0.f;
     fld.c3 = active ? p.fc3[lane] : 1.f;
     const int any_derived = p.any_derived;
+    Ctx cx;
+    cx.edge = edge;
+    cx.g.pe2 = cb + lay.pe2;
+    cx.g.rdp2 = cb + lay.rdp2;
+    cx.w = w; cx.nz = nz; cx.mask_below = mask_below; cx.toa = toa;
 
     for (int row = 0; row < 8; ++row) {
         State st;
 #pragma unroll
         for (int i = 0; i < 4; ++i) { st.A[i] = 0; st.B[i] = 0; st.dq[i] = 0; st.dc[i] = 0; st.xp[i] = 0; st.run[i] = 0; }
-        WG gr = g;
-        gr.colw = g.colw + 32 * (row & 1);
-        gr.colps = g.colps + 32 * (row & 1);
 
         for (int chunk = 0; chunk < nch; ++chunk) {
-            const int it = row * nch + chunk, s = it % NSTAGE, b = it & 1, t0 = chunk * KC;
+            const int it = row * nch + chunk, b = it & 1, t0 = chunk * KC;
             mbar_wait(gfull + 8 * b, (it >> 1) & 1);
-            mbar_wait(bars + 8 * s, (it / NSTAGE) & 1);
-            const uint32_t stage = ring + s * stage_bytes;
-            WG gb = gr;
-            gb.rec = g.rec + b * REC_BYTES;
-            gb.nmax = g.nmax + b * KC * 4;
+            mbar_wait(bars + 8 * b, (it >> 1) & 1);
+            const uint32_t stage = ring + b * stage_bytes;
+            cx.rec = rec0 + b * REC_BYTES;
+            cx.ova = ova0 + b * OVA_BYTES;
+            cx.ovb = ovb0 + b * OVB_BYTES;
 #pragma unroll 1
             for (int kk = 0; kk < KC; ++kk) {
                 const int t = t0 + kk;
                 if (t > nz + 2) break;
-                if (t >= 3 && t < nz && lds32(gb.nmax + 4 * kk) <= 1.f)
-                    hot_step(gb.rec, stage, kk, w, fld, any_derived, st, acc_lane);
+                if (t >= 3 && t < nz)
+                    hot_step(cx, stage, t, kk, fld, any_derived, st, acc_lane);
                 else
-                    general_step(gb, stage, t, kk, w, fld, any_derived, st, acc_lane, nz, mask_below, toa);
+                    general_step(cx, stage, t, kk, fld, any_derived, st, acc_lane);
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(bars + 8 * (NSTAGE + s));
+            if (lane == 0) mbar_arrive(bars + 8 * (NSTAGE + b));
         }
     }
 
@@ -817,7 +888,7 @@ plevel_stream_kernel(const __grid_constant__ Params p)
     if (active) {
         float *out = p.outs[lane];
         for (int k = 0; k < nz; ++k)
-            out[(o * nz + k) * hc + (long)by * nxc + cx] = lds32(acc_lane + (k + 1) * ACC_STRIDE) / lds32(g.den + 4 * k);
+            out[(o * nz + k) * hc + (long)by * nxc + cx_] = lds32(acc_lane + (k + 1) * ACC_STRIDE) / lds32(cb + lay.den + 4 * k);
     }
 }
 
@@ -893,7 +964,7 @@ int stream_supported(int nfields, int nz, int ny, int nx, int f)
 {
     if (!(f == 8 && nx % 32 == 0 && ny % 8 == 0 && nz >= 6 && nz <= 126 && nfields >= 1)) return 0;
     // worst case: every field has two parents
-    const stream::Layout lay = stream::make_layout(2 * nfields, nz, nfields);
+    const stream::Layout lay = stream::make_layout(2 * nfields, nz);
     return lay.total <= 227 * 1024 - 1024;
 }
 
@@ -946,7 +1017,7 @@ int launch_plevel_stream(const cg_field *fields, float *const *outs, int nfields
         const int rc = tensor_map_for(&p.maps[i], srcs[i], n_outer, nz, ny, nx);
         if (rc) return rc;
     }
-    const Layout lay = make_layout(nsrc, nz, nfields);
+    const Layout lay = make_layout(nsrc, nz);
     if (lay.total > 227 * 1024 - 1024) return CG_ENOTSUP;
     p.area = area; p.psurf = psurf; p.delp_coarse = delp_coarse; p.delp = delp;
     p.nsrc = nsrc; p.nfields = nfields; p.nz = nz; p.ny = ny; p.nx = nx; p.mask_below = mask_below; p.toa = toa;
