@@ -57,6 +57,11 @@ constexpr int MAXE = 2;              // listed further events per (column, layer
 constexpr int INFO_SLOW = 255;
 constexpr int OVA_BYTES = KC * NCOL * MAXE * 16;     // (x, y, z, -w) per event
 constexpr int OVB_BYTES = KC * NCOL * MAXE * 4;      // accumulator byte offset per event
+constexpr int TAILMAX = 16;          // listed further events of the layer below the surface: (x, offset) per event
+constexpr int TAIL_BYTES = NCOL * TAILMAX * 8;
+// context block in shared memory for the out-of-line paths (word offsets)
+enum { CTX_NZ, CTX_MASK, CTX_TOA, CTX_REC, CTX_OVA, CTX_OVB, CTX_EDGE, CTX_TAIL, CTX_CELL0, CTX_CELLB, CTX_ACC, CTX_PE2, CTX_RDP2,
+       CTX_WORDS };
 constexpr int ACC_STRIDE = 128;      // bytes per accumulator slot: one float per lane
 constexpr int DUMMY_SLOT = 0;        // accumulator slot k + 1 belongs to target level k
 constexpr int EDGE_WORDS = 24;       // per column: one-sided cubic coefficients, top (0..8) and bottom (12..20)
@@ -80,7 +85,7 @@ struct Params {
 struct Layout {
     int ring, bars, cell0, cell_bytes;          // per cell: acc, pe2, rdp2, den
     int acc, pe2, rdp2, den;
-    int rec, ova, ovb, edge, colw, colps, total;
+    int rec, ova, ovb, tail, ctx, edge, colw, colps, total;
 };
 
 __host__ __device__ inline Layout make_layout(int nsrc, int nz)
@@ -100,6 +105,8 @@ __host__ __device__ inline Layout make_layout(int nsrc, int nz)
     L.rec = o;   o += 2 * REC_BYTES;             // double-buffered between the geometry warp and the field warps
     L.ova = o;   o += 2 * OVA_BYTES;
     L.ovb = o;   o += 2 * OVB_BYTES;
+    L.tail = o;  o += TAIL_BYTES;
+    L.ctx = o;   o += 64;
     L.edge = o;  o += NCOL * EDGE_WORDS * 4;
     L.colw = o;  o += 8 * NCOL * 4;              // [row][column of the CTA]
     L.colps = o; o += 8 * NCOL * 4;
@@ -297,33 +304,27 @@ __device__ __forceinline__ Event make_event(const CellG &g, const ColG &col, flo
     return e;
 }
 
-// Lane state of the geometry warp: fine column x of the current row, walked from the top
-struct Walk {
-    float pm3, pm2, pm1, p0;         // interface pressures P(t-3) .. P(t)
-    int icnt;                        // coarse interfaces at or above the top of layer t - 2
-};
-
-// Step t of column x: level t (thickness d) arrives.  Writes the column's half of the pair record:
+// Step t of column x (geometry warp g handles t = 4 * chunk + g): level t arrives.  P(t-3) .. P(t+1) are the
+// column's interface pressures, i1 the coarse interfaces met so far.  Writes the column's half of the pair record:
 //   E1, E2, F-1, G, H: PPM stencil of layer t-1 (mappm.f90:651-683, delp-only factors)
 //   dpw: weight of the whole layer t-2 in the target level open at its bottom
-//   ex, ey, ez, ew, off: the first event of layer t-2 (a no-op when it has none); further events go to the list
-__device__ __forceinline__ void geometry_step(Walk &s, const CellG &g, const ColG &col, float d, int t, int kk, int x,
-                                              uint32_t rec, uint32_t ova, uint32_t ovb, uint32_t edge, int nz,
+//   ex, ey, ez, ew, off: the first event of layer t-2 (a no-op when it has none); further events go to the lists
+__device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, float pm1, float p0, float pp1,
+                                              const CellG &g, const ColG &col, int t, int kk, int x, uint32_t rec,
+                                              uint32_t ova, uint32_t ovb, uint32_t tail, uint32_t edge, int nz,
                                               int mask_below, float toa)
 {
-    // interface pressures by the reference's sequential cumsum (vertically_dependent.py:61-63)
-    const float pp1 = t < nz ? s.p0 + d : s.p0;                         // P(t+1)
     // (approximate division, 2 ulp: these factors multiply differences of q)
     float E1 = 0.f, E2 = 0.f, Fm = 0.f, G = 0.f, H = 0.f;
     const int j = t - 1;
     if (j >= 1 && j <= nz - 2) {
-        const float dm1 = s.pm1 - s.pm2, d0 = s.p0 - s.pm1, dp1 = pp1 - s.p0;     // mappm.f90:43 (from the rounded sums)
+        const float dm1 = pm1 - pm2, d0 = p0 - pm1, dp1 = pp1 - p0;     // mappm.f90:43 (from the rounded sums)
         const float d4 = dm1 + d0, d4p = d0 + dp1;
         const float r4 = __fdividef(1.f, d4), inv = __fdividef(d0, d4 + dp1);
         E1 = __fdividef(dm1 + 0.5f * d0, d4p) * inv;
         E2 = (dp1 + 0.5f * d0) * r4 * inv;
         if (j >= 2) {
-            const float dm2 = s.pm2 - s.pm3, d4m = dm2 + dm1;
+            const float dm2 = pm2 - pm3, d4m = dm2 + dm1;
             const float cq = dm1 * r4, a1 = __fdividef(d4m, d4 + dm1), a2 = __fdividef(d4p, d4 + d0);
             const float gg = __fdividef(2.f, d4m + d4p);
             Fm = cq * (1.f + gg * d0 * (a1 - a2)) - 1.f;
@@ -334,7 +335,7 @@ __device__ __forceinline__ void geometry_step(Walk &s, const CellG &g, const Col
     // one-sided cubics at the column ends (mappm.f90:689-747), once per column
     if (t == 2 || t == nz) {
         const bool top = (t == 2);
-        const float q0 = s.pm2, q1 = s.pm1, q2 = s.p0;                  // P(m), P(m+1), P(m+2), m = 0 or nz - 2
+        const float q0 = pm2, q1 = pm1, q2 = p0;                        // P(m), P(m+1), P(m+2), m = 0 or nz - 2
         const float d1 = top ? q1 - q0 : q2 - q1, d2 = top ? q2 - q1 : q1 - q0;
         const float D = d2 * (2.f * d2 * d2 + d1 * (d2 + 3.f * d1));
         const float Pq = d2 * (5.f * d1 + d2) - 3.f * d1 * d1;
@@ -348,34 +349,46 @@ __device__ __forceinline__ void geometry_step(Walk &s, const CellG &g, const Col
     // events of layer L = t - 2: the coarse interfaces in (top, bottom] of the layer, by the two-pointer merge
     // (mappm.f90:70-75 keeps k0 the same way); L == nz is everything below the surface
     const int L = t - 2, kn = nz;
-    const float pt = s.pm2, pb = s.pm1;
-    int i1 = s.icnt;
+    const float pt = pm2, pb = pm1;
+    int i0 = icnt, i1 = icnt;
     float dpw = 0.f;
-    if (L >= 0 && L < nz) {
-        while (i1 <= kn && lds32(g.pe2 + 4 * i1) <= pb) ++i1;
-        const int ko = i1 - 1;                                          // level open at the bottom of L
-        if (ko >= 0 && ko < kn && lds32(g.pe2 + 4 * ko) > toa) dpw = level_scale(g, col, ko, mask_below) * (pb - pt);
-    } else if (L == nz) {
-        i1 = kn + 1;
-    }
-    const int n = i1 - s.icnt;
-    Event e0 = {0.f, 0.f, 0.f, 0.f, DUMMY_SLOT};
-    if (n > 0) e0 = make_event(g, col, pt, pb, L, s.icnt, nz, mask_below, toa);
-    int info = n;
-    if (n > 1) {
-        const uint32_t oa = ova + (kk * NCOL + x) * (MAXE * 16), ob = ovb + (kk * NCOL + x) * (MAXE * 4);
-        if (n - 1 <= MAXE) {
-            for (int e = 1; e < n; ++e) {
-                const Event ev = make_event(g, col, pt, pb, L, s.icnt + e, nz, mask_below, toa);
-                sts128(oa + 16 * (e - 1), make_float4(ev.x, ev.y, ev.z, -ev.w));
-                stsi32(ob + 4 * (e - 1), ev.slot * ACC_STRIDE);
-            }
-        } else {                                                        // park what the field warps need to form them
-            sts128(oa, make_float4(pt, pb, col.w, col.ps));
-            stsi32(ob, s.icnt);
-            stsi32(ob + 4, n);
-            info = INFO_SLOW;
+    if (L >= 0 && L <= nz) {
+        if (L == 0) i0 = 0;
+        else while (i0 <= kn && lds32(g.pe2 + 4 * i0) <= pt) ++i0;
+        i1 = i0;
+        if (L < nz) {
+            while (i1 <= kn && lds32(g.pe2 + 4 * i1) <= pb) ++i1;
+            const int ko = i1 - 1;                                      // level open at the bottom of L
+            if (ko >= 0 && ko < kn && lds32(g.pe2 + 4 * ko) > toa) dpw = level_scale(g, col, ko, mask_below) * (pb - pt);
+        } else {
+            i1 = kn + 1;
         }
+        icnt = i1;
+    }
+    const int n = i1 - i0;
+    const bool below = L == nz;
+    const int cap = below ? TAILMAX : MAXE;
+    const uint32_t oa = ova + (kk * NCOL + x) * (MAXE * 16), ob = ovb + (kk * NCOL + x) * (MAXE * 4);
+    Event e0 = {0.f, 0.f, 0.f, 0.f, DUMMY_SLOT};
+    int info = n;
+    const int nlist = n - 1 <= cap ? n : 1;
+    for (int e = 0; e < nlist; ++e) {
+        const Event ev = make_event(g, col, pt, pb, L, i0 + e, nz, mask_below, toa);
+        if (e == 0) e0 = ev;
+        else if (below) {
+            const uint32_t a = tail + (x * TAILMAX + e - 1) * 8;
+            sts32(a, ev.x);
+            stsi32(a + 4, ev.slot * ACC_STRIDE);
+        } else {
+            sts128(oa + 16 * (e - 1), make_float4(ev.x, ev.y, ev.z, -ev.w));
+            stsi32(ob + 4 * (e - 1), ev.slot * ACC_STRIDE);
+        }
+    }
+    if (n - 1 > cap) {                                                  // park what the field warps need to form them
+        sts128(oa, make_float4(pt, pb, col.w, col.ps));
+        stsi32(ob, i0);
+        stsi32(ob + 4, n);
+        info = INFO_SLOW;
     }
     const uint32_t r = rec + (kk * (NCOL / 2) + (x >> 1)) * REC_BLOCK + 4 * (x & 1);
     sts32(r, E1);           sts32(r + 8, E2);
@@ -385,39 +398,9 @@ __device__ __forceinline__ void geometry_step(Walk &s, const CellG &g, const Col
     sts32(r + 64, e0.z);    sts32(r + 72, -e0.w);
     stsi32(r + 80, e0.slot * ACC_STRIDE);
     stsi32(r + 88, info);
-    s.icnt = i1;
-    s.pm3 = s.pm2; s.pm2 = s.pm1; s.pm1 = s.p0; s.p0 = pp1;
 }
 
 // ---- per-field work -----------------------------------------------------------------------------
-struct Ctx {                         // what a field warp needs besides its registers
-    uint32_t rec, ova, ovb;          // this chunk's geometry buffers
-    uint32_t edge;                   // one-sided cubic coefficients of the CTA's columns
-    CellG g;
-    int w;                           // cell of the warp
-    int nz, mask_below;
-    float toa;
-};
-
-// the record of one column at one step, gathered from its pair block (general step only)
-struct Rec {
-    float E1, E2, Fm, G, H, dpw;
-    float4 ev;
-    int off, info;
-};
-__device__ __forceinline__ Rec load_rec(const Ctx &cx, int kk, int c)
-{
-    const uint32_t b = cx.rec + (kk * (NCOL / 2) + 4 * cx.w + (c >> 1)) * REC_BLOCK + 4 * (c & 1);
-    Rec r;
-    r.E1 = lds32(b);        r.E2 = lds32(b + 8);
-    r.Fm = lds32(b + 16);   r.G = lds32(b + 24);
-    r.H = -lds32(b + 32);   r.dpw = lds32(b + 40);
-    r.ev = make_float4(lds32(b + 48), lds32(b + 56), lds32(b + 64), lds32(b + 72));
-    r.off = ldsi32(b + 80);
-    r.info = ldsi32(b + 88);
-    return r;
-}
-
 // close a target level with `tot` (NaN-skipping block sum, coarsen.py:211).  acc_lane = &acc[0][lane];
 // slot 0 collects what belongs to no level.
 __device__ __forceinline__ void flush(uint32_t acc_lane, int off, float tot)
@@ -425,17 +408,66 @@ __device__ __forceinline__ void flush(uint32_t acc_lane, int off, float tot)
     const uint32_t a = acc_lane + off;
     sts32(a, lds32(a) + (tot == tot ? tot : 0.f));
 }
-
-// events 1 .. n-1 of a layer cut by more than MAXE + 1 coarse interfaces (rare: formed on the fly, out of line)
-__device__ __noinline__ float extras_slow(uint32_t oa, uint32_t ob, uint32_t pe2, uint32_t rdp2, int L, float q, float x,
-                                          float y, float r, uint32_t acc_lane, int nz, int mask_below, float toa)
+// ... for two columns at once: their loads do not wait for each other's stores
+__device__ __forceinline__ void flush2(uint32_t acc_lane, int offa, int offb, float ta, float tb)
 {
+    ta = ta == ta ? ta : 0.f;
+    tb = tb == tb ? tb : 0.f;
+    const uint32_t a = acc_lane + offa, b = acc_lane + offb;
+    if (offa == offb) {                                                 // warp-uniform
+        sts32(a, lds32(a) + (ta + tb));
+    } else {
+        const float va = lds32(a), vb = lds32(b);
+        sts32(a, va + ta);
+        sts32(b, vb + tb);
+    }
+}
+
+__device__ __forceinline__ uint32_t ctx_u32(uint32_t sctx, int i) { return (uint32_t)ldsi32(sctx + 4 * i); }
+
+// Events 1 .. n-1 of column c of the warp's cell at step t (kcb = kk | c << 4 | buffer << 8); r = restart value
+// left by event 0.  Out of line: a layer cut by several coarse interfaces is the less common case.
+__device__ __noinline__ float apply_extras(uint32_t sctx, int t, int kcb, int info, float q, float x, float y, float r)
+{
+    const int kk = kcb & 15, c = (kcb >> 4) & 15, b = kcb >> 8;
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nz = ldsi32(sctx + 4 * CTX_NZ);
+    const uint32_t cb = ctx_u32(sctx, CTX_CELL0) + w * ctx_u32(sctx, CTX_CELLB);
+    const uint32_t acc_lane = cb + ctx_u32(sctx, CTX_ACC) + 4 * lane;
+    const int xc = 8 * w + c;
+    if (info != INFO_SLOW && t == nz + 2) {                             // below the surface: I = x * q, restart at 0
+        const uint32_t a = ctx_u32(sctx, CTX_TAIL) + xc * (TAILMAX * 8);
+        for (int e = 0; e + 2 <= info; ++e) {
+            const float I = lds32(a + 8 * e) * q;
+            flush(acc_lane, ldsi32(a + 8 * e + 4), r + I);
+            r = 0.f * I;
+        }
+        return r;
+    }
+    const uint32_t oa = ctx_u32(sctx, CTX_OVA) + b * OVA_BYTES + (kk * NCOL + xc) * (MAXE * 16);
+    const uint32_t ob = ctx_u32(sctx, CTX_OVB) + b * OVB_BYTES + (kk * NCOL + xc) * (MAXE * 4);
+    if (info != INFO_SLOW) {
+        for (int e = 0; e + 2 <= info; ++e) {
+            const float4 ev = lds128(oa + 16 * e);
+            const float I = ev.x * q + ev.y * x + ev.z * y;
+            flush(acc_lane, ldsi32(ob + 4 * e), r + I);
+            r = ev.w * I;                                               // stored negated
+        }
+        return r;
+    }
+    // more than the lists hold (rare): formed on the fly from the column's pressures parked in the list
     const float4 pp = lds128(oa);                                       // pt, pb, weight, surface pressure
     const int i0 = ldsi32(ob), n = ldsi32(ob + 4);
-    CellG g; g.pe2 = pe2; g.rdp2 = rdp2;
-    ColG col; col.w = pp.z; col.ps = pp.w;
+    const int mask_below = ldsi32(sctx + 4 * CTX_MASK);
+    const float toa = lds32(sctx + 4 * CTX_TOA);
+    CellG g;
+    g.pe2 = cb + ctx_u32(sctx, CTX_PE2);
+    g.rdp2 = cb + ctx_u32(sctx, CTX_RDP2);
+    ColG col;
+    col.w = pp.z;
+    col.ps = pp.w;
     for (int e = 1; e < n; ++e) {
-        const Event ev = make_event(g, col, pp.x, pp.y, L, i0 + e, nz, mask_below, toa);
+        const Event ev = make_event(g, col, pp.x, pp.y, t - 2, i0 + e, nz, mask_below, toa);
         const float I = ev.x * q + ev.y * x + ev.z * y;
         flush(acc_lane, ev.slot * ACC_STRIDE, r + I);
         r = -(ev.w * I);
@@ -443,84 +475,87 @@ __device__ __noinline__ float extras_slow(uint32_t oa, uint32_t ob, uint32_t pe2
     return r;
 }
 
-// events 1 .. n-1 of column c (of the warp's cell) at step kk; r = restart value left by event 0
-__device__ __forceinline__ float apply_extras(const Ctx &cx, int kk, int c, int info, int L, float q, float x, float y,
-                                              float r, uint32_t acc_lane)
-{
-    const int xc = 8 * cx.w + c;
-    const uint32_t oa = cx.ova + (kk * NCOL + xc) * (MAXE * 16), ob = cx.ovb + (kk * NCOL + xc) * (MAXE * 4);
-    if (info == INFO_SLOW)
-        return extras_slow(oa, ob, cx.g.pe2, cx.g.rdp2, L, q, x, y, r, acc_lane, cx.nz, cx.mask_below, cx.toa);
-#pragma unroll
-    for (int e = 0; e < MAXE; ++e) {
-        if (e + 2 <= info) {
-            const float4 ev = lds128(oa + 16 * e);
-            const int off = ldsi32(ob + 4 * e);
-            const float I = ev.x * q + ev.y * x + ev.z * y;
-            flush(acc_lane, off, r + I);
-            r = ev.w * I;                                               // stored negated
-        }
-    }
-    return r;
+__device__ __forceinline__ float limited_slope(float df2, float dq_lo, float dq_hi)
+{   // mappm.f90:663-665: sign(min(|df2|, max(q-,q,q+) - q, q - min(q-,q,q+)), df2)
+    const float na = -dq_lo;
+    const float hi3 = max3(na, dq_hi, 0.f), nlo = min3(na, dq_hi, 0.f);
+    return max3(min3(df2, hi3, -nlo), -hi3, nlo);
 }
 
-// Limited parabola of layer L in deviation form, x = AL - q, y = AR - q, A6 = -3 (x + y)
-// (ppm_limiters lmt = 0, mappm.f90:875-894), then the events of the layer and its whole-layer term.
-__device__ __forceinline__ void finish_layer(const Ctx &cx, int kk, int c, int L, float q, float x, float y, float dc,
-                                             float &run, const Rec &r, uint32_t acc_lane)
+// One column at one of the end steps of the walk (t < 3: nothing to finish yet / one-sided cubic at the top,
+// mappm.f90:689-707; t >= nz: one-sided cubic at the bottom, :729-747, and the layer below the surface).
+// State of the column: A = q(t-1), B = q(t-2), dq1 = delq(t-1), dcp = dc(t-2), xp = AL(t-2) - q(t-2), run.
+// Returns (delq(t), dc(t-1), AL(t-1) - q(t-1), run).  Out of line: 6 of nz + 3 steps.
+__device__ __noinline__ float4 end_column(uint32_t sctx, int t, int kcb, float qn, float q3, float A, float B, float dq1,
+                                          float dcp, float xp, float run)
 {
+    const int kk = kcb & 15, c = (kcb >> 4) & 15, b = kcb >> 8;
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nz = ldsi32(sctx + 4 * CTX_NZ);
+    const uint32_t rec = ctx_u32(sctx, CTX_REC) + b * REC_BYTES;
+    const uint32_t rb = rec + (kk * (NCOL / 2) + 4 * w + (c >> 1)) * REC_BLOCK + 4 * (c & 1);
+    const float E1 = lds32(rb), E2 = lds32(rb + 8), Fm = lds32(rb + 16), G = lds32(rb + 24), nH = lds32(rb + 32);
+    float dqn = qn - A;                                                     // delq(t)
+    const float df2 = E1 * dqn + E2 * dq1;                                  // layer t-1, mappm.f90:661
+    float dcn = limited_slope(df2, dq1, dqn);                               // dc(t-1)
+    float xn = Fm * dq1 + G * dcp + nH * dcn;                               // AL(t-1) - q(t-1), :674-683
+    float x = xp, y = xn + dq1, dc = dcp;                                   // layer t-2
+    const uint32_t edge = ctx_u32(sctx, CTX_EDGE) + 4 * ((8 * w + c) * EDGE_WORDS);
+    if (t == 2) {
+        // level 3 is visible (same stage): AL of layer 2 from the record of step 3, then the cubic through
+        // the top two layers and that edge
+        const uint32_t r3 = rec + (3 * (NCOL / 2) + 4 * w + (c >> 1)) * REC_BLOCK + 4 * (c & 1);
+        const float e1 = lds32(r3), e2 = lds32(r3 + 8), fm = lds32(r3 + 16), gg = lds32(r3 + 24), nh = lds32(r3 + 32);
+        const float dq3 = q3 - qn;
+        const float dc2 = limited_slope(e1 * dq3 + e2 * dqn, dqn, dq3);
+        const float al2 = qn + (fm * dqn + gg * dcn + nh * dc2);
+        const float4 ea = lds128(edge), eb = lds128(edge + 16);
+        const float sd1 = lds32(edge + 32);
+        const float q0 = B, q1 = A;
+        const float qm = ea.x * q0 + ea.y * q1, dq = ea.z * (q1 - q0);
+        const float c1 = (al2 - qm - eb.x * dq) * ea.w;
+        const float c3 = dq - c1 * eb.y;
+        const float inner = qm - c1 * eb.z;
+        const float top = c1 * eb.w - c3 * sd1 + inner;
+        const float al1 = fminf(fmaxf(inner, fminf(q0, q1)), fmaxf(q0, q1));
+        x = top - q0; y = al1 - q0; dc = 0.5f * (al1 - q0); xn = al1 - q1;
+    } else if (t == nz) {
+        const float4 ea = lds128(edge + 48), eb = lds128(edge + 64);
+        const float sd1 = lds32(edge + 80);
+        const float qe = A, qi = B;
+        const float ali = qi + xp;
+        const float qm = ea.x * qe + ea.y * qi, dq = ea.z * (qi - qe);
+        const float c1 = (ali - qm - eb.x * dq) * ea.w;
+        const float c3 = dq - c1 * eb.y;
+        const float inner = qm - c1 * eb.z;
+        const float bot = c1 * eb.w - c3 * sd1 + inner;
+        const float alb = fminf(fmaxf(inner, fminf(qe, qi)), fmaxf(qe, qi));
+        y = alb - qi; xn = alb - qe; dcn = 0.5f * (qe - alb); dqn = bot - qe;   // layer nz-1 is finished next step
+    } else if (t == nz + 1) {
+        y = dq1;
+    } else if (t > nz + 1) {                                                // below the surface
+        x = 0.f; y = 0.f; dc = 0.f;
+    }
+    // limited parabola of layer t-2 in deviation form, x = AL - q, y = AR - q, A6 = -3 (x + y)
+    // (ppm_limiters lmt = 0, mappm.f90:875-894), then the events of the layer and its whole-layer term
+    const float q = B;
     const float da1 = y - x, s = x + y;
-    const float t = s * da1, da2 = da1 * (da1 * (1.f / 3.f));
+    const float tt = s * da1, da2 = da1 * (da1 * (1.f / 3.f));
     const float m2x = -2.f * x, m2y = -2.f * y;
-    const bool c1 = t > da2, c2 = -t > da2, flat = dc == 0.f;      // c1 and c2 exclude each other (da2 >= 0)
-    y = c1 ? m2x : y;                  // a6da < -da2: AR = AL - 3 (AL - q)
-    x = c2 ? m2y : x;                  // a6da >  da2: AL = AR - 3 (AR - q)
+    const bool k1 = tt > da2, k2 = -tt > da2, flat = dc == 0.f;            // k1 and k2 exclude each other (da2 >= 0)
+    y = k1 ? m2x : y;                  // a6da < -da2: AR = AL - 3 (AL - q)
+    x = k2 ? m2y : x;                  // a6da >  da2: AL = AR - 3 (AR - q)
     x = flat ? 0.f : x;
     y = flat ? 0.f : y;
-    const float I = r.ev.x * q + r.ev.y * x + r.ev.z * y;
-    flush(acc_lane, r.off, run + I);
-    float rs = r.info == 0 ? run : r.ev.w * I;                          // ev.w is stored negated
-    if (r.info > 1) rs = apply_extras(cx, kk, c, r.info, L, q, x, y, rs, acc_lane);
-    run = fmaf(r.dpw, q, rs);
-}
-
-// one-sided cubic at the column top (mappm.f90:689-707), evaluated at step t = 2 once level 3 is
-// visible: returns (x, y, dc) of layer 0 and x of layer 1
-__device__ __noinline__ float4 top_fix(uint32_t rec3, uint32_t edge, float qn, float dqn, float dcn, float q1, float q0,
-                                       float q3)
-{
-    const uint32_t b = rec3;                                            // the column's record of step 3
-    const float E1 = lds32(b), E2 = lds32(b + 8), Fm = lds32(b + 16), G = lds32(b + 24), nH = lds32(b + 32);
-    const float dq3 = q3 - qn;
-    const float df2 = E1 * dq3 + E2 * dqn;
-    const float na = -dqn;
-    const float hi3 = max3(na, dq3, 0.f), nlo = min3(na, dq3, 0.f);
-    const float dc2 = max3(min3(df2, hi3, -nlo), -hi3, nlo);
-    const float al2 = qn + (Fm * dqn + G * dcn + nH * dc2);
-    const float4 ea = lds128(edge), eb = lds128(edge + 16);
-    const float sd1 = lds32(edge + 32);
-    const float qm = ea.x * q0 + ea.y * q1, dq = ea.z * (q1 - q0);
-    const float c1 = (al2 - qm - eb.x * dq) * ea.w;
-    const float c3 = dq - c1 * eb.y;
-    const float inner = qm - c1 * eb.z;
-    const float top = c1 * eb.w - c3 * sd1 + inner;
-    const float al1 = fminf(fmaxf(inner, fminf(q0, q1)), fmaxf(q0, q1));
-    return make_float4(top - q0, al1 - q0, 0.5f * (al1 - q0), al1 - q1);
-}
-
-// ... and at the bottom (:729-747), at step t = nz: returns y of layer nz-2 and (x, dc, y) of layer nz-1
-__device__ __noinline__ float4 bottom_fix(uint32_t edge, float qe, float qi, float xi)
-{
-    const float4 ea = lds128(edge), eb = lds128(edge + 16);
-    const float sd1 = lds32(edge + 32);
-    const float ali = qi + xi;
-    const float qm = ea.x * qe + ea.y * qi, dq = ea.z * (qi - qe);
-    const float c1 = (ali - qm - eb.x * dq) * ea.w;
-    const float c3 = dq - c1 * eb.y;
-    const float inner = qm - c1 * eb.z;
-    const float bot = c1 * eb.w - c3 * sd1 + inner;
-    const float alb = fminf(fmaxf(inner, fminf(qe, qi)), fmaxf(qe, qi));
-    return make_float4(alb - qi, alb - qe, 0.5f * (qe - alb), bot - qe);
+    const float ex = lds32(rb + 48), ey = lds32(rb + 56), ez = lds32(rb + 64), nw = lds32(rb + 72), dpw = lds32(rb + 40);
+    const int off = ldsi32(rb + 80), info = ldsi32(rb + 88);
+    const uint32_t acc_lane = ctx_u32(sctx, CTX_CELL0) + w * ctx_u32(sctx, CTX_CELLB) + ctx_u32(sctx, CTX_ACC) + 4 * lane;
+    const float I = ex * q + ey * x + ez * y;
+    flush(acc_lane, off, run + I);
+    float rs = info == 0 ? run : nw * I;                                    // -w is what the record holds
+    if (info > 1) rs = apply_extras(sctx, t, kcb, info, q, x, y, rs);
+    run = fmaf(dpw, q, rs);
+    return make_float4(dqn, dcn, xn, run);
 }
 
 // the per-lane description of a field: parents' boxes and q = (a - c1 b) (c2 b + c3)
@@ -547,13 +582,6 @@ __device__ __forceinline__ void load_row(u64 (&q)[4], uint32_t stage, int kk, in
     }
 }
 
-__device__ __forceinline__ float limited_slope(float df2, float dq_lo, float dq_hi)
-{   // mappm.f90:663-665: sign(min(|df2|, max(q-,q,q+) - q, q - min(q-,q,q+)), df2)
-    const float na = -dq_lo;
-    const float hi3 = max3(na, dq_hi, 0.f), nlo = min3(na, dq_hi, 0.f);
-    return max3(min3(df2, hi3, -nlo), -hi3, nlo);
-}
-
 // Rolling state of a lane's 8 columns as 4 column pairs: A = q(t-1), B = q(t-2), dq = delq(t-1),
 // dc = dc(t-2), xp = AL(t-2) - q(t-2), run = running integral of the target level that is open
 struct State {
@@ -562,13 +590,13 @@ struct State {
 
 // One step of the tandem walk for the 8 columns of a row: level t arrives, layer t-2 is finished.
 // Interior levels: straight line, two columns per arithmetic instruction; the min/max, compare and
-// select parts run on the halves; further events of a layer behind warp-uniform branches.
-__device__ __forceinline__ void hot_step(const Ctx &cx, uint32_t stage, int t, int kk, const Field &f, int any_derived,
-                                         State &s, uint32_t acc_lane)
+// select parts run on the halves; further events of a layer out of line behind warp-uniform branches.
+__device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t stage, int t, int kk, int b, int w,
+                                         const Field &f, int any_derived, State &s, uint32_t acc_lane)
 {
     u64 q[4];
-    load_row(q, stage, kk, cx.w, f, any_derived);
-    const uint32_t rb = cx.rec + (kk * (NCOL / 2) + 4 * cx.w) * REC_BLOCK;
+    load_row(q, stage, kk, w, f, any_derived);
+    const uint32_t rb = rec + (kk * (NCOL / 2) + 4 * w) * REC_BLOCK;
     const u64 third = pk(1.f / 3.f, 1.f / 3.f), neg2 = pk(-2.f, -2.f);
     u64 E1, E2, Fm, G, NH, DPW, EX, EY, EZ, NW;
     int4 oi;
@@ -608,8 +636,7 @@ __device__ __forceinline__ void hot_step(const Ctx &cx, uint32_t stage, int t, i
         const u64 tot = add2(s.run[p], I);
         float tota, totb;
         upk(tot, tota, totb);
-        flush(acc_lane, oi.x, tota);
-        flush(acc_lane, oi.y, totb);
+        flush2(acc_lane, oi.x, oi.y, tota, totb);
         float ra, rb_, na, nb;
         upk(s.run[p], ra, rb_);
         upk(mul2(NW, I), na, nb);
@@ -618,8 +645,8 @@ __device__ __forceinline__ void hot_step(const Ctx &cx, uint32_t stage, int t, i
         if ((oi.z | oi.w) > 1) {                                            // layers cut by several coarse interfaces
             float qa, qb;
             upk(qB, qa, qb);
-            if (oi.z > 1) ra = apply_extras(cx, kk, 2 * p, oi.z, t - 2, qa, xa, ya, ra, acc_lane);
-            if (oi.w > 1) rb_ = apply_extras(cx, kk, 2 * p + 1, oi.w, t - 2, qb, xb, yb, rb_, acc_lane);
+            if (oi.z > 1) ra = apply_extras(sctx, t, kk | (2 * p) << 4 | b << 8, oi.z, qa, xa, ya, ra);
+            if (oi.w > 1) rb_ = apply_extras(sctx, t, kk | (2 * p + 1) << 4 | b << 8, oi.w, qb, xb, yb, rb_);
         }
         s.run[p] = fma2(DPW, qB, pk(ra, rb_));
         s.B[p] = s.A[p]; s.A[p] = qn; s.dq[p] = dqn; s.dc[p] = dcn; s.xp[p] = xn;
@@ -628,73 +655,29 @@ __device__ __forceinline__ void hot_step(const Ctx &cx, uint32_t stage, int t, i
     }
 }
 
-// The same step for the ends of the column (t < 3, t >= nz: one-sided cubics, nothing to finish, below the
-// surface): column by column.
-__device__ __forceinline__ void general_step(const Ctx &cx, uint32_t stage, int t, int kk, const Field &f,
-                                          int any_derived, State &s, uint32_t acc_lane)
+// The same step at the ends of the column: column by column through end_column
+__device__ __forceinline__ void end_step(uint32_t sctx, uint32_t stage, int t, int kk, int b, int w, int nz, const Field &f,
+                                         int any_derived, State &s)
 {
-    const int nz = cx.nz, w = cx.w;
-    float A[C], B[C], dq1[C], dcp[C], xp[C], run[C], qv[C], q3[C];
+    u64 q[4], q3[4];
+#pragma unroll
+    for (int p = 0; p < 4; ++p) { q[p] = s.A[p]; q3[p] = 0; }
+    if (t < nz) load_row(q, stage, kk, w, f, any_derived);
+    if (t == 2) load_row(q3, stage, 3, w, f, any_derived);          // level 3 is in the same stage (KC = 4)
 #pragma unroll
     for (int p = 0; p < 4; ++p) {
-        upk(s.A[p], A[2 * p], A[2 * p + 1]);       upk(s.B[p], B[2 * p], B[2 * p + 1]);
-        upk(s.dq[p], dq1[2 * p], dq1[2 * p + 1]);  upk(s.dc[p], dcp[2 * p], dcp[2 * p + 1]);
-        upk(s.xp[p], xp[2 * p], xp[2 * p + 1]);    upk(s.run[p], run[2 * p], run[2 * p + 1]);
-    }
-    const bool ends = (t == 2) || (t >= nz);
-    if (t < nz) {
-        u64 q[4];
-        load_row(q, stage, kk, w, f, any_derived);
-#pragma unroll
-        for (int p = 0; p < 4; ++p) upk(q[p], qv[2 * p], qv[2 * p + 1]);
-    } else {
-#pragma unroll
-        for (int c = 0; c < C; ++c) qv[c] = A[c];
-    }
-    if (t == 2) {                                                   // level 3 is in the same stage (KC = 4)
-        u64 q[4];
-        load_row(q, stage, 3, w, f, any_derived);
-#pragma unroll
-        for (int p = 0; p < 4; ++p) upk(q[p], q3[2 * p], q3[2 * p + 1]);
-    }
-#pragma unroll
-    for (int c = 0; c < C; ++c) {
-        const Rec r = load_rec(cx, kk, c);
-        const float qn = qv[c];
-        float dqn = qn - A[c];                                              // delq(t)
-        const float df2 = r.E1 * dqn + r.E2 * dq1[c];                       // layer t-1, mappm.f90:661
-        float dcn = limited_slope(df2, dq1[c], dqn);                        // dc(t-1)
-        float xn = r.Fm * dq1[c] + r.G * dcp[c] - r.H * dcn;                // AL(t-1) - q(t-1), :674-683
-        float x = xp[c], y = xn + dq1[c], dc = dcp[c];                      // layer t-2
-        if (ends) {
-            const uint32_t edge = cx.edge + 4 * ((8 * w + c) * EDGE_WORDS);
-            if (t == 2) {
-                const uint32_t rec3 = cx.rec + (3 * (NCOL / 2) + 4 * w + (c >> 1)) * REC_BLOCK + 4 * (c & 1);
-                const float4 v = top_fix(rec3, edge, qn, dqn, dcn, A[c], B[c], q3[c]);
-                x = v.x; y = v.y; dc = v.z; xn = v.w;
-            } else if (t == nz) {
-                const float4 v = bottom_fix(edge + 48, A[c], B[c], xp[c]);
-                y = v.x; xn = v.y; dcn = v.z; dqn = v.w;                    // layer nz-1 is finished next step
-            } else if (t == nz + 1) {
-                y = dq1[c];
-            } else {                                                        // below the surface
-                x = 0.f; y = 0.f; dc = 0.f;
-            }
-        }
-        finish_layer(cx, kk, c, t - 2, B[c], x, y, dc, run[c], r, acc_lane);
-        B[c] = A[c]; A[c] = qn; dq1[c] = dqn; dcp[c] = dcn; xp[c] = xn;
-    }
-#pragma unroll
-    for (int p = 0; p < 4; ++p) {
-        s.A[p] = pk(A[2 * p], A[2 * p + 1]);       s.B[p] = pk(B[2 * p], B[2 * p + 1]);
-        s.dq[p] = pk(dq1[2 * p], dq1[2 * p + 1]);  s.dc[p] = pk(dcp[2 * p], dcp[2 * p + 1]);
-        s.xp[p] = pk(xp[2 * p], xp[2 * p + 1]);    s.run[p] = pk(run[2 * p], run[2 * p + 1]);
+        float qa, qb, ta, tb, Aa, Ab, Ba, Bb, da, db, ca, cb, xa, xb, ra, rb;
+        upk(q[p], qa, qb);      upk(q3[p], ta, tb);     upk(s.A[p], Aa, Ab);    upk(s.B[p], Ba, Bb);
+        upk(s.dq[p], da, db);   upk(s.dc[p], ca, cb);   upk(s.xp[p], xa, xb);   upk(s.run[p], ra, rb);
+        const float4 va = end_column(sctx, t, kk | (2 * p) << 4 | b << 8, qa, ta, Aa, Ba, da, ca, xa, ra);
+        const float4 vb = end_column(sctx, t, kk | (2 * p + 1) << 4 | b << 8, qb, tb, Ab, Bb, db, cb, xb, rb);
+        s.B[p] = s.A[p]; s.A[p] = q[p];
+        s.dq[p] = pk(va.x, vb.x); s.dc[p] = pk(va.y, vb.y); s.xp[p] = pk(va.z, vb.z); s.run[p] = pk(va.w, vb.w);
     }
 }
 
 // 128 registers at launch (2 CTAs of 256 threads per SM); the field warpgroup then takes 184 and the
-// helper warpgroup drops to 72 (setmaxnreg).  Only the first helper warp works (the geometry warp);
-// the other three exist so that both setmaxnreg instructions are issued by whole warpgroups.
+// geometry warpgroup drops to 72 (setmaxnreg).
 __global__ void __maxnreg__(128)
 plevel_stream_kernel(const __grid_constant__ Params p)
 {
@@ -707,126 +690,123 @@ plevel_stream_kernel(const __grid_constant__ Params p)
     // barriers: full[NSTAGE], empty[NSTAGE] (field ring + geometry buffers), gfull[2] (geometry buffers)
     const uint32_t bars = sbase + lay.bars;
     const uint32_t gfull = bars + 8 * 2 * NSTAGE;
+    const uint32_t sctx = sbase + lay.ctx;
     const int stage_bytes = nsrc * BOX_BYTES;
     const int nch = (nz + 3 + KC - 1) / KC;                     // steps t = 0 .. nz + 2
     const int bx = blockIdx.x, by = blockIdx.y;
     const long o = blockIdx.z;
+    const float toa = p.toa;
+    const int mask_below = p.mask_below;
+    const uint32_t rec0 = sbase + lay.rec, ova0 = sbase + lay.ova, ovb0 = sbase + lay.ovb, edge = sbase + lay.edge;
+    const uint32_t tail = sbase + lay.tail;
 
     if (tid == 0) {
         for (int s = 0; s < NSTAGE; ++s) {
-            mbar_init(bars + 8 * s, 1);                     // full: the geometry warp's expect_tx arrival
+            mbar_init(bars + 8 * s, NCELL);                 // full: one expect_tx arrival per geometry warp
             mbar_init(bars + 8 * (NSTAGE + s), NCELL);      // empty: one arrival per field warp
-            mbar_init(gfull + 8 * s, 1);
+            mbar_init(gfull + 8 * s, NCELL);                // geometry buffer: one arrival per geometry warp
         }
         asm volatile("fence.mbarrier_init.release.cluster;");
+        stsi32(sctx + 4 * CTX_NZ, nz);              stsi32(sctx + 4 * CTX_MASK, mask_below);
+        sts32(sctx + 4 * CTX_TOA, toa);             stsi32(sctx + 4 * CTX_REC, (int)rec0);
+        stsi32(sctx + 4 * CTX_OVA, (int)ova0);      stsi32(sctx + 4 * CTX_OVB, (int)ovb0);
+        stsi32(sctx + 4 * CTX_EDGE, (int)edge);     stsi32(sctx + 4 * CTX_TAIL, (int)tail);
+        stsi32(sctx + 4 * CTX_CELL0, (int)(sbase + lay.cell0));
+        stsi32(sctx + 4 * CTX_CELLB, lay.cell_bytes);
+        stsi32(sctx + 4 * CTX_ACC, lay.acc);        stsi32(sctx + 4 * CTX_PE2, lay.pe2);
+        stsi32(sctx + 4 * CTX_RDP2, lay.rdp2);
     }
     __syncthreads();
 
     const int ny = p.ny, nx = p.nx, nyc = ny >> 3, nxc = nx >> 3;
     const long h = (long)ny * nx, hc = (long)nyc * nxc;
-    const float toa = p.toa;
-    const int mask_below = p.mask_below;
-    const uint32_t rec0 = sbase + lay.rec, ova0 = sbase + lay.ova, ovb0 = sbase + lay.ovb, edge = sbase + lay.edge;
 
     if (warp >= NCELL) {
+        // ---------------- geometry warp gw: lane = fine column x of the CTA's 32, level 4 * chunk + gw ----
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(HELPER_REGS));
-        if (warp != NCELL) return;
-        // ---------------- geometry warp: lane = fine column x of the CTA's 32 ------------------------
-        const int x = lane, cell = x >> 3, c = x & 7;
+        const int gw = warp - NCELL;
+        const int x = lane, cell = x >> 3;
         const uint32_t colw = sbase + lay.colw, colps = sbase + lay.colps;
-        auto cellbase = [&](int cl) { return sbase + lay.cell0 + cl * lay.cell_bytes; };
-        CellG g;
-        g.pe2 = cellbase(cell) + lay.pe2;
-        g.rdp2 = cellbase(cell) + lay.rdp2;
-        // CTA prologue: coarse interfaces of the 4 cells (sequential cumsum, vertically_dependent.py:61-63),
+        // CTA prologue, warp gw for cell gw: coarse interfaces (sequential cumsum, vertically_dependent.py:61-63),
         // 1 / thickness, sum of the 64 columns' weights per target level (coarsen.py:212)
-        for (int idx = lane; idx < NCELL * nz; idx += 32) {
-            const int cl = idx & (NCELL - 1), k = idx / NCELL;
-            sts32(cellbase(cl) + lay.rdp2 + 4 * k, p.delp_coarse[(o * nz + k) * hc + (long)by * nxc + NCELL * bx + cl]);
-        }
-        float wr[8], pr[8];
-#pragma unroll
-        for (int r = 0; r < 8; ++r) {
-            const long col = o * h + (long)(8 * by + r) * nx + NCOL * bx + x;
-            const float a = p.area[col];
-            wr[r] = (a == a) ? a : 0.f;
-            pr[r] = mask_below ? p.psurf[col] : 0.f;
-            sts32(colw + 4 * (r * NCOL + x), wr[r]);
-            sts32(colps + 4 * (r * NCOL + x), pr[r]);
-        }
-        __syncwarp();
-        if (lane < NCELL) {
-            const uint32_t cb = cellbase(lane);
-            float pe = toa;
-            sts32(cb + lay.pe2, pe);
-            for (int k = 0; k < nz; ++k) { pe = pe + lds32(cb + lay.rdp2 + 4 * k); sts32(cb + lay.pe2 + 4 * (k + 1), pe); }
-        }
-        __syncwarp();
-        for (int idx = lane; idx < NCELL * nz; idx += 32) {
-            const int cl = idx & (NCELL - 1), k = idx / NCELL;
-            const uint32_t cb = cellbase(cl);
-            sts32(cb + lay.rdp2 + 4 * k, 1.f / (lds32(cb + lay.pe2 + 4 * (k + 1)) - lds32(cb + lay.pe2 + 4 * k)));
-        }
         {
-            const uint32_t den = cellbase(cell) + lay.den;
+            const uint32_t cbw = sbase + lay.cell0 + gw * lay.cell_bytes;
+            for (int k = lane; k < nz; k += 32)
+                sts32(cbw + lay.rdp2 + 4 * k, p.delp_coarse[(o * nz + k) * hc + (long)by * nxc + NCELL * bx + gw]);
+            for (int r = 2 * gw; r < 2 * gw + 2; ++r) {
+                const long col = o * h + (long)(8 * by + r) * nx + NCOL * bx + x;
+                const float a = p.area[col];
+                sts32(colw + 4 * (r * NCOL + x), (a == a) ? a : 0.f);
+                sts32(colps + 4 * (r * NCOL + x), mask_below ? p.psurf[col] : 0.f);
+            }
+            __syncwarp();
+            if (lane == 0) {
+                float pe = toa;
+                sts32(cbw + lay.pe2, pe);
+                for (int k = 0; k < nz; ++k) { pe = pe + lds32(cbw + lay.rdp2 + 4 * k); sts32(cbw + lay.pe2 + 4 * (k + 1), pe); }
+            }
+            __syncwarp();
+            for (int k = lane; k < nz; k += 32)
+                sts32(cbw + lay.rdp2 + 4 * k, 1.f / (lds32(cbw + lay.pe2 + 4 * (k + 1)) - lds32(cbw + lay.pe2 + 4 * k)));
+            asm volatile("bar.sync 1, 128;" ::: "memory");          // the geometry warpgroup: all cells' arrays are in place
+            // the cell's 64 columns: rows lane / 8 and 4 + lane / 8, column lane % 8
+            const int xc = 8 * gw + (lane & 7), r0 = lane >> 3;
+            const float w0 = lds32(colw + 4 * (r0 * NCOL + xc)), w1 = lds32(colw + 4 * ((r0 + 4) * NCOL + xc));
+            const float s0 = lds32(colps + 4 * (r0 * NCOL + xc)), s1 = lds32(colps + 4 * ((r0 + 4) * NCOL + xc));
             if (!mask_below) {
-                float d = 0.f;
+                float d = w0 + w1;
 #pragma unroll
-                for (int r = 0; r < 8; ++r) d += wr[r];
-                d += __shfl_xor_sync(0xffffffffu, d, 1);
-                d += __shfl_xor_sync(0xffffffffu, d, 2);
-                d += __shfl_xor_sync(0xffffffffu, d, 4);
-                for (int k = c; k < nz; k += C) sts32(den + 4 * k, d);
+                for (int m = 1; m < 32; m <<= 1) d += __shfl_xor_sync(0xffffffffu, d, m);
+                for (int k = lane; k < nz; k += 32) sts32(cbw + lay.den + 4 * k, d);
             } else {
                 for (int k = 0; k < nz; ++k) {
-                    const float lower = lds32(g.pe2 + 4 * (k + 1));
-                    float d = 0.f;
+                    const float lower = lds32(cbw + lay.pe2 + 4 * (k + 1));
+                    float d = (lower < s0 ? w0 : 0.f) + (lower < s1 ? w1 : 0.f);
 #pragma unroll
-                    for (int r = 0; r < 8; ++r) d += lower < pr[r] ? wr[r] : 0.f;
-                    d += __shfl_xor_sync(0xffffffffu, d, 1);
-                    d += __shfl_xor_sync(0xffffffffu, d, 2);
-                    d += __shfl_xor_sync(0xffffffffu, d, 4);
-                    if (c == 0) sts32(den + 4 * k, d);
+                    for (int m = 1; m < 32; m <<= 1) d += __shfl_xor_sync(0xffffffffu, d, m);
+                    if (lane == 0) sts32(cbw + lay.den + 4 * k, d);
                 }
             }
         }
-        __syncwarp();
-
+        CellG g;
+        g.pe2 = sbase + lay.cell0 + cell * lay.cell_bytes + lay.pe2;
+        g.rdp2 = sbase + lay.cell0 + cell * lay.cell_bytes + lay.rdp2;
         const float *dcol = p.delp + o * nz * h + (long)(8 * by) * nx + NCOL * bx + x;
         float dn[KC];
-        auto load_delp = [&](int row, int chunk) {
+        auto load_delp = [&](int row, int chunk) {                   // thicknesses of levels t-3 .. t, t = 4 chunk + gw
 #pragma unroll
-            for (int kk = 0; kk < KC; ++kk) {
-                const int lvl = chunk * KC + kk;
-                dn[kk] = lvl < nz ? ldg_stream(dcol + (long)lvl * h + (long)row * nx) : 0.f;
+            for (int i = 0; i < KC; ++i) {
+                const int lvl = chunk * KC + gw - 3 + i;
+                dn[i] = (lvl >= 0 && lvl < nz) ? ldg_stream(dcol + (long)lvl * h + (long)row * nx) : 0.f;
             }
         };
         load_delp(0, 0);
+        const int mine = (nsrc - gw + NCELL - 1) / NCELL;            // this warp's share of the TMA boxes: gw, gw + 4, ...
         for (int row = 0; row < 8; ++row) {
             ColG col;
             col.w = lds32(colw + 4 * (row * NCOL + x));
             col.ps = lds32(colps + 4 * (row * NCOL + x));
-            Walk s;
-            s.pm3 = s.pm2 = s.pm1 = s.p0 = toa;
-            s.icnt = 0;
+            float plast = toa;                                       // P(t-3); interfaces above the top sit at toa
+            int icnt = 0;
             for (int chunk = 0; chunk < nch; ++chunk) {
                 const int it = row * nch + chunk, b = it & 1;
-                float d[KC];
-#pragma unroll
-                for (int kk = 0; kk < KC; ++kk) d[kk] = dn[kk];
+                // interface pressures by the reference's sequential cumsum (vertically_dependent.py:61-63):
+                // every warp carries the running sum of its own column walk, same order of additions
+                const float pm3 = plast, pm2 = pm3 + dn[0], pm1 = pm2 + dn[1], p0 = pm1 + dn[2], pp1 = p0 + dn[3];
+                plast = pp1;
                 if (chunk + 1 < nch) load_delp(row, chunk + 1);
                 else if (row + 1 < 8) load_delp(row + 1, 0);
                 // stage b of the field ring and geometry buffer b are released together by the field warps
                 if (it >= 2) mbar_wait(bars + 8 * (NSTAGE + b), ((it >> 1) - 1) & 1);
-                if (lane == 0) mbar_expect_tx(bars + 8 * b, nsrc * KC * 128);
+                if (lane == 0) mbar_expect_tx(bars + 8 * b, mine * KC * 128);
                 __syncwarp();
-                for (int src = lane; src < nsrc; src += 32)
+                for (int l = lane; l < mine; l += 32) {
+                    const int src = gw + NCELL * l;
                     tma_load_3d(ring + b * stage_bytes + src * BOX_BYTES, &p.maps[src], NCOL * bx, 8 * by + row,
                                 (int)(o * nz) + chunk * KC, bars + 8 * b);
-#pragma unroll
-                for (int kk = 0; kk < KC; ++kk)
-                    geometry_step(s, g, col, d[kk], chunk * KC + kk, kk, x, rec0 + b * REC_BYTES, ova0 + b * OVA_BYTES,
-                                  ovb0 + b * OVB_BYTES, edge, nz, mask_below, toa);
+                }
+                geometry_step(icnt, pm3, pm2, pm1, p0, pp1, g, col, chunk * KC + gw, gw, x, rec0 + b * REC_BYTES,
+                              ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, tail, edge, nz, mask_below, toa);
                 __syncwarp();
                 if (lane == 0) mbar_arrive(gfull + 8 * b);
             }
@@ -850,11 +830,6 @@ plevel_stream_kernel(const __grid_constant__ Params p)
     fld.c2 = active ? p.fc2[lane] : 0.f;
     fld.c3 = active ? p.fc3[lane] : 1.f;
     const int any_derived = p.any_derived;
-    Ctx cx;
-    cx.edge = edge;
-    cx.g.pe2 = cb + lay.pe2;
-    cx.g.rdp2 = cb + lay.rdp2;
-    cx.w = w; cx.nz = nz; cx.mask_below = mask_below; cx.toa = toa;
 
     for (int row = 0; row < 8; ++row) {
         State st;
@@ -866,17 +841,14 @@ plevel_stream_kernel(const __grid_constant__ Params p)
             mbar_wait(gfull + 8 * b, (it >> 1) & 1);
             mbar_wait(bars + 8 * b, (it >> 1) & 1);
             const uint32_t stage = ring + b * stage_bytes;
-            cx.rec = rec0 + b * REC_BYTES;
-            cx.ova = ova0 + b * OVA_BYTES;
-            cx.ovb = ovb0 + b * OVB_BYTES;
 #pragma unroll 1
             for (int kk = 0; kk < KC; ++kk) {
                 const int t = t0 + kk;
                 if (t > nz + 2) break;
                 if (t >= 3 && t < nz)
-                    hot_step(cx, stage, t, kk, fld, any_derived, st, acc_lane);
+                    hot_step(sctx, rec0 + b * REC_BYTES, stage, t, kk, b, w, fld, any_derived, st, acc_lane);
                 else
-                    general_step(cx, stage, t, kk, fld, any_derived, st, acc_lane);
+                    end_step(sctx, stage, t, kk, b, w, nz, fld, any_derived, st);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(bars + 8 * (NSTAGE + b));
