@@ -588,10 +588,23 @@ struct State {
     u64 A[4], B[4], dq[4], dc[4], xp[4], run[4];
 };
 
+// the second coarse interface of a layer (interior steps), inline; more than two go out of line
+__device__ __forceinline__ float second_event(uint32_t ova, uint32_t ovb, uint32_t sctx, int t, int kcb, int w, int info,
+                                              float q, float x, float y, float r, uint32_t acc_lane)
+{
+    if (info != 2) return apply_extras(sctx, t, kcb, info, q, x, y, r);
+    const int kk = kcb & 15, xc = 8 * w + ((kcb >> 4) & 15);
+    const float4 ev = lds128(ova + (kk * NCOL + xc) * (MAXE * 16));
+    const int off = ldsi32(ovb + (kk * NCOL + xc) * (MAXE * 4));
+    const float I = ev.x * q + ev.y * x + ev.z * y;
+    flush(acc_lane, off, r + I);
+    return ev.w * I;                                                        // stored negated
+}
+
 // One step of the tandem walk for the 8 columns of a row: level t arrives, layer t-2 is finished.
 // Interior levels: straight line, two columns per arithmetic instruction; the min/max, compare and
 // select parts run on the halves; further events of a layer out of line behind warp-uniform branches.
-__device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t stage, int t, int kk, int b, int w,
+__device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t ova, uint32_t ovb, uint32_t stage, int t, int kk, int b, int w,
                                          const Field &f, int any_derived, State &s, uint32_t acc_lane)
 {
     u64 q[4];
@@ -611,6 +624,9 @@ __device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t s
             lds2x64(rn, E1n, E2n);        lds2x64(rn + 16, Fmn, Gn);    lds2x64(rn + 32, NHn, DPWn);
             lds2x64(rn + 48, EXn, EYn);   lds2x64(rn + 64, EZn, NWn);   oin = lds128i(rn + 80);
         }
+        // the accumulator slots of the pair's first events: loaded now, stored once the sums are known
+        const uint32_t aa = acc_lane + oi.x, ab = acc_lane + oi.y;
+        const float va = lds32(aa), vb = lds32(ab);
         const u64 qn = q[p], dq1 = s.dq[p];
         const u64 dqn = sub2(qn, s.A[p]);                                   // delq(t)
         const u64 df2 = fma2(E1, dqn, mul2(E2, dq1));                       // layer t-1, mappm.f90:661
@@ -631,12 +647,19 @@ __device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t s
         xa = ca == 0.f ? 0.f : xa;  ya = ca == 0.f ? 0.f : ya;
         xb = cb == 0.f ? 0.f : xb;  yb = cb == 0.f ? 0.f : yb;
         const u64 xl = pk(xa, xb), yl = pk(ya, yb), qB = s.B[p];
-        // the first event of each column: close a target level, restart the next
+        // the first event of each column: close a target level (NaN-skipping block sum, coarsen.py:211), restart the next
         const u64 I = fma2(EZ, yl, fma2(EY, xl, mul2(EX, qB)));
         const u64 tot = add2(s.run[p], I);
         float tota, totb;
         upk(tot, tota, totb);
-        flush2(acc_lane, oi.x, oi.y, tota, totb);
+        tota = tota == tota ? tota : 0.f;
+        totb = totb == totb ? totb : 0.f;
+        if (oi.x == oi.y) {                                                 // warp-uniform
+            sts32(aa, va + (tota + totb));
+        } else {
+            sts32(aa, va + tota);
+            sts32(ab, vb + totb);
+        }
         float ra, rb_, na, nb;
         upk(s.run[p], ra, rb_);
         upk(mul2(NW, I), na, nb);
@@ -645,8 +668,8 @@ __device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t s
         if ((oi.z | oi.w) > 1) {                                            // layers cut by several coarse interfaces
             float qa, qb;
             upk(qB, qa, qb);
-            if (oi.z > 1) ra = apply_extras(sctx, t, kk | (2 * p) << 4 | b << 8, oi.z, qa, xa, ya, ra);
-            if (oi.w > 1) rb_ = apply_extras(sctx, t, kk | (2 * p + 1) << 4 | b << 8, oi.w, qb, xb, yb, rb_);
+            if (oi.z > 1) ra = second_event(ova, ovb, sctx, t, kk | (2 * p) << 4 | b << 8, w, oi.z, qa, xa, ya, ra, acc_lane);
+            if (oi.w > 1) rb_ = second_event(ova, ovb, sctx, t, kk | (2 * p + 1) << 4 | b << 8, w, oi.w, qb, xb, yb, rb_, acc_lane);
         }
         s.run[p] = fma2(DPW, qB, pk(ra, rb_));
         s.B[p] = s.A[p]; s.A[p] = qn; s.dq[p] = dqn; s.dc[p] = dcn; s.xp[p] = xn;
@@ -687,7 +710,9 @@ plevel_stream_kernel(const __grid_constant__ Params p)
     const Layout lay = make_layout(nsrc, nz);
     const uint32_t sbase = smem_u32(smem);
     const uint32_t ring = sbase + lay.ring;
-    // barriers: full[NSTAGE], empty[NSTAGE] (field ring + geometry buffers), gfull[2] (geometry buffers)
+    // mbarriers: full[NSTAGE] (field ring), gfull[2] (geometry buffers); stage / buffer b is handed back to the
+    // geometry warps through named barrier 2 + b (bar.arrive by the field warps, bar.sync by the geometry warps:
+    // a blocked warp does not poll)
     const uint32_t bars = sbase + lay.bars;
     const uint32_t gfull = bars + 8 * 2 * NSTAGE;
     const uint32_t sctx = sbase + lay.ctx;
@@ -703,7 +728,6 @@ plevel_stream_kernel(const __grid_constant__ Params p)
     if (tid == 0) {
         for (int s = 0; s < NSTAGE; ++s) {
             mbar_init(bars + 8 * s, NCELL);                 // full: one expect_tx arrival per geometry warp
-            mbar_init(bars + 8 * (NSTAGE + s), NCELL);      // empty: one arrival per field warp
             mbar_init(gfull + 8 * s, NCELL);                // geometry buffer: one arrival per geometry warp
         }
         asm volatile("fence.mbarrier_init.release.cluster;");
@@ -797,7 +821,7 @@ plevel_stream_kernel(const __grid_constant__ Params p)
                 if (chunk + 1 < nch) load_delp(row, chunk + 1);
                 else if (row + 1 < 8) load_delp(row + 1, 0);
                 // stage b of the field ring and geometry buffer b are released together by the field warps
-                if (it >= 2) mbar_wait(bars + 8 * (NSTAGE + b), ((it >> 1) - 1) & 1);
+                if (it >= 2) asm volatile("bar.sync %0, 256;" ::"r"(2 + b) : "memory");
                 if (lane == 0) mbar_expect_tx(bars + 8 * b, mine * KC * 128);
                 __syncwarp();
                 for (int l = lane; l < mine; l += 32) {
@@ -845,13 +869,14 @@ plevel_stream_kernel(const __grid_constant__ Params p)
             for (int kk = 0; kk < KC; ++kk) {
                 const int t = t0 + kk;
                 if (t > nz + 2) break;
-                if (t >= 3 && t < nz)
-                    hot_step(sctx, rec0 + b * REC_BYTES, stage, t, kk, b, w, fld, any_derived, st, acc_lane);
+                if (t != 2 && t < nz)        // (t = 0, 1: all-zero records, nothing is finished)
+                    hot_step(sctx, rec0 + b * REC_BYTES, ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, stage, t, kk, b, w, fld, any_derived,
+                             st, acc_lane);
                 else
                     end_step(sctx, stage, t, kk, b, w, nz, fld, any_derived, st);
             }
             __syncwarp();
-            if (lane == 0) mbar_arrive(bars + 8 * (NSTAGE + b));
+            if (it + 2 < 8 * nch) asm volatile("bar.arrive %0, 256;" ::"r"(2 + b) : "memory");
         }
     }
 
