@@ -228,6 +228,13 @@ __device__ __forceinline__ int4 lds128i(uint32_t addr)
     asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
     return v;
 }
+// a value the compiler must keep in a register instead of recomputing it where it is used
+__device__ __forceinline__ uint32_t opaque(uint32_t v)
+{
+    uint32_t r;
+    asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(v));
+    return r;
+}
 __device__ __forceinline__ int ldsi32(uint32_t addr)
 {
     int v;
@@ -588,17 +595,25 @@ struct State {
     u64 A[4], B[4], dq[4], dc[4], xp[4], run[4];
 };
 
-// the second coarse interface of a layer (interior steps), inline; more than two go out of line
-__device__ __forceinline__ float second_event(uint32_t ova, uint32_t ovb, uint32_t sctx, int t, int kcb, int w, int info,
-                                              float q, float x, float y, float r, uint32_t acc_lane)
+// Further coarse interfaces of a layer at an interior step.  oa / ob: the column's entries in the lists.
+// Out of line (one small body instead of eight inline copies): about a quarter of the layers have a second one.
+__device__ __noinline__ float further_events(uint32_t oa, uint32_t ob, int info, float q, float x, float y, float r,
+                                             uint32_t acc_lane, uint32_t sctx, int t, int kcb)
 {
-    if (info != 2) return apply_extras(sctx, t, kcb, info, q, x, y, r);
-    const int kk = kcb & 15, xc = 8 * w + ((kcb >> 4) & 15);
-    const float4 ev = lds128(ova + (kk * NCOL + xc) * (MAXE * 16));
-    const int off = ldsi32(ovb + (kk * NCOL + xc) * (MAXE * 4));
-    const float I = ev.x * q + ev.y * x + ev.z * y;
+    if (info > MAXE + 1) return apply_extras(sctx, t, kcb, info, q, x, y, r);      // INFO_SLOW
+    const float4 ev = lds128(oa);
+    const int off = ldsi32(ob);
+    float I = ev.x * q + ev.y * x + ev.z * y;
     flush(acc_lane, off, r + I);
-    return ev.w * I;                                                        // stored negated
+    r = ev.w * I;                                                           // stored negated
+    if (info > 2) {
+        const float4 e2 = lds128(oa + 16);
+        const int o2 = ldsi32(ob + 4);
+        I = e2.x * q + e2.y * x + e2.z * y;
+        flush(acc_lane, o2, r + I);
+        r = e2.w * I;
+    }
+    return r;
 }
 
 // One step of the tandem walk for the 8 columns of a row: level t arrives, layer t-2 is finished.
@@ -609,7 +624,7 @@ __device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t o
 {
     u64 q[4];
     load_row(q, stage, kk, w, f, any_derived);
-    const uint32_t rb = rec + (kk * (NCOL / 2) + 4 * w) * REC_BLOCK;
+    const uint32_t rb = rec;
     const u64 third = pk(1.f / 3.f, 1.f / 3.f), neg2 = pk(-2.f, -2.f);
     u64 E1, E2, Fm, G, NH, DPW, EX, EY, EZ, NW;
     int4 oi;
@@ -668,8 +683,11 @@ __device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t o
         if ((oi.z | oi.w) > 1) {                                            // layers cut by several coarse interfaces
             float qa, qb;
             upk(qB, qa, qb);
-            if (oi.z > 1) ra = second_event(ova, ovb, sctx, t, kk | (2 * p) << 4 | b << 8, w, oi.z, qa, xa, ya, ra, acc_lane);
-            if (oi.w > 1) rb_ = second_event(ova, ovb, sctx, t, kk | (2 * p + 1) << 4 | b << 8, w, oi.w, qb, xb, yb, rb_, acc_lane);
+            const uint32_t oa = ova + (2 * p) * (MAXE * 16), ob = ovb + (2 * p) * (MAXE * 4);
+            if (oi.z > 1) ra = further_events(oa, ob, oi.z, qa, xa, ya, ra, acc_lane, sctx, t, kk | (2 * p) << 4 | b << 8);
+            if (oi.w > 1)
+                rb_ = further_events(oa + MAXE * 16, ob + MAXE * 4, oi.w, qb, xb, yb, rb_, acc_lane, sctx, t,
+                                     kk | (2 * p + 1) << 4 | b << 8);
         }
         s.run[p] = fma2(DPW, qB, pk(ra, rb_));
         s.B[p] = s.A[p]; s.A[p] = qn; s.dq[p] = dqn; s.dc[p] = dcn; s.xp[p] = xn;
@@ -844,7 +862,12 @@ plevel_stream_kernel(const __grid_constant__ Params p)
     const uint32_t cb = sbase + lay.cell0 + w * lay.cell_bytes;
     const int cx_ = NCELL * bx + w;
     const bool active = lane < V;
-    const uint32_t acc_lane = cb + lay.acc + 4 * lane;          // every lane owns a column of the accumulator
+    // (opaque(): keep these in registers; otherwise the layout arithmetic is redone inside the step loop)
+    const uint32_t acc_lane = opaque(cb + lay.acc + 4 * lane);  // every lane owns a column of the accumulator
+    const uint32_t rec_w = opaque(rec0 + 4 * w * REC_BLOCK), ova_w = opaque(ova0 + 8 * w * (MAXE * 16)),
+                   ovb_w = opaque(ovb0 + 8 * w * (MAXE * 4));
+    const uint32_t ring_r = opaque(ring);
+    const int stage_bytes_r = (int)opaque((uint32_t)stage_bytes), nz_r = (int)opaque((uint32_t)nz);
     for (int i = lane; i < (nz + 1) * 32; i += 32) sts32(cb + lay.acc + 4 * i, 0.f);
     __syncwarp();
     Field fld;
@@ -864,16 +887,16 @@ plevel_stream_kernel(const __grid_constant__ Params p)
             const int it = row * nch + chunk, b = it & 1, t0 = chunk * KC;
             mbar_wait(gfull + 8 * b, (it >> 1) & 1);
             mbar_wait(bars + 8 * b, (it >> 1) & 1);
-            const uint32_t stage = ring + b * stage_bytes;
+            const uint32_t stage = ring_r + b * stage_bytes_r;
 #pragma unroll 1
             for (int kk = 0; kk < KC; ++kk) {
                 const int t = t0 + kk;
-                if (t > nz + 2) break;
-                if (t != 2 && t < nz)        // (t = 0, 1: all-zero records, nothing is finished)
-                    hot_step(sctx, rec0 + b * REC_BYTES, ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, stage, t, kk, b, w, fld, any_derived,
-                             st, acc_lane);
+                if (t > nz_r + 2) break;
+                if (t != 2 && t < nz_r)        // (t = 0, 1: all-zero records, nothing is finished)
+                    hot_step(sctx, rec_w + b * REC_BYTES + kk * ((NCOL / 2) * REC_BLOCK), ova_w + b * OVA_BYTES + kk * (NCOL * MAXE * 16),
+                             ovb_w + b * OVB_BYTES + kk * (NCOL * MAXE * 4), stage, t, kk, b, w, fld, any_derived, st, acc_lane);
                 else
-                    end_step(sctx, stage, t, kk, b, w, nz, fld, any_derived, st);
+                    end_step(sctx, stage, t, kk, b, w, nz_r, fld, any_derived, st);
             }
             __syncwarp();
             if (it + 2 < 8 * nch) asm volatile("bar.arrive %0, 256;" ::"r"(2 + b) : "memory");
