@@ -30,7 +30,7 @@ int stream_supported(int nfields, int nz, int ny, int nx, int f);
 long stream_workspace_bytes(long n_outer, int nz, int ny, int nx);
 int launch_surface_pressure_seq(const float *delp, float *ps, float toa, long n_outer, int nz, long h, cudaStream_t st);
 int launch_plevel_stream(const cg_field *fields, float *const *outs, int nfields, const float *delp,
-                         const float *area, const float *delp_coarse, const float *psurf, long n_outer,
+                         const float *area, const float *delp_coarse, const float *psurf, int *flags, long n_outer,
                          int nz, int ny, int nx, int mask_below, float toa, cudaStream_t st);
 
 // masked[o,k,y,x] = pe_c[o,k+1,y/f,x/f] < pe_f[o,nz,y,x] ? area[o,y,x] : 0   (regridz.py:150-161)
@@ -203,13 +203,14 @@ static int stream_path(const cg_field *fields, float *const *outs, int nfields, 
     char *w = (char *)workspace;
     float *dc = delp_coarse ? delp_coarse : (float *)w;
     float *ps = (float *)(w + align256(4 * n_outer * nz * hc));
+    int *flags = (int *)(w + align256(4 * n_outer * nz * hc) + align256(4 * n_outer * h));
     const void *in[1] = {delp};
     void *out[1] = {dc};
     int rc = cg_weighted_block_average(in, out, 1, nullptr, area, CG_W2D, n_outer, nz, ny, nx, 8, 8, 8, 8,
                                        nyc, nxc, CG_F32, CG_F32, st);
     if (rc) return rc;
     if (mask_below && (rc = launch_surface_pressure_seq(delp, ps, toa, n_outer, nz, h, st))) return rc;
-    return launch_plevel_stream(fields, outs, nfields, delp, area, dc, mask_below ? ps : nullptr, n_outer, nz,
+    return launch_plevel_stream(fields, outs, nfields, delp, area, dc, mask_below ? ps : nullptr, flags, n_outer, nz,
                                 ny, nx, mask_below, toa, st);
 }
 

@@ -26,6 +26,7 @@
 #include "common.cuh"
 #include <cuda.h>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -79,6 +80,7 @@ struct Params {
     int nsrc;                        // TMA sources (field parents)
     int nfields, nz, ny, nx, mask_below;
     float toa;
+    int *flags;                      // per CTA: the fast variant met a non-finite field value (NaN-safe variant reruns the CTA)
 };
 
 // ---- shared-memory carve-up --------------------------------------------------------------------
@@ -316,6 +318,7 @@ __device__ __forceinline__ Event make_event(const CellG &g, const ColG &col, flo
 //   E1, E2, F-1, G, H: PPM stencil of layer t-1 (mappm.f90:651-683, delp-only factors)
 //   dpw: weight of the whole layer t-2 in the target level open at its bottom
 //   ex, ey, ez, ew, off: the first event of layer t-2 (a no-op when it has none); further events go to the lists
+template <bool NS>
 __device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, float pm1, float p0, float pp1,
                                               const CellG &g, const ColG &col, int t, int kk, int x, uint32_t rec,
                                               uint32_t ova, uint32_t ovb, uint32_t tail, uint32_t edge, int nz,
@@ -357,7 +360,7 @@ __device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, f
     // (mappm.f90:70-75 keeps k0 the same way); L == nz is everything below the surface
     const int L = t - 2, kn = nz;
     const float pt = pm2, pb = pm1;
-    int i0 = icnt, i1 = icnt;
+    int i0 = icnt, i1 = icnt, open_slot = DUMMY_SLOT;
     float dpw = 0.f;
     if (L >= 0 && L <= nz) {
         if (L == 0) i0 = 0;
@@ -366,7 +369,10 @@ __device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, f
         if (L < nz) {
             while (i1 <= kn && lds32(g.pe2 + 4 * i1) <= pb) ++i1;
             const int ko = i1 - 1;                                      // level open at the bottom of L
-            if (ko >= 0 && ko < kn && lds32(g.pe2 + 4 * ko) > toa) dpw = level_scale(g, col, ko, mask_below) * (pb - pt);
+            if (ko >= 0 && ko < kn && lds32(g.pe2 + 4 * ko) > toa) {
+                dpw = level_scale(g, col, ko, mask_below) * (pb - pt);
+                open_slot = ko + 1;
+            }
         } else {
             i1 = kn + 1;
         }
@@ -376,7 +382,9 @@ __device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, f
     const bool below = L == nz;
     const int cap = below ? TAILMAX : MAXE;
     const uint32_t oa = ova + (kk * NCOL + x) * (MAXE * 16), ob = ovb + (kk * NCOL + x) * (MAXE * 4);
-    Event e0 = {0.f, 0.f, 0.f, 0.f, DUMMY_SLOT};
+    // no coarse interface in the layer: the record is a no-op that keeps the running sum (info = 0); the fast
+    // variant has no such select and instead moves the running sum to the open level's slot early (I = 0)
+    Event e0 = {0.f, 0.f, 0.f, 0.f, (!NS && n == 0) ? open_slot : DUMMY_SLOT};
     int info = n;
     const int nlist = n - 1 <= cap ? n : 1;
     for (int e = 0; e < nlist; ++e) {
@@ -410,30 +418,17 @@ __device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, f
 // ---- per-field work -----------------------------------------------------------------------------
 // close a target level with `tot` (NaN-skipping block sum, coarsen.py:211).  acc_lane = &acc[0][lane];
 // slot 0 collects what belongs to no level.
+template <bool NS>
 __device__ __forceinline__ void flush(uint32_t acc_lane, int off, float tot)
 {
     const uint32_t a = acc_lane + off;
-    sts32(a, lds32(a) + (tot == tot ? tot : 0.f));
+    sts32(a, lds32(a) + ((!NS || tot == tot) ? tot : 0.f));
 }
-// ... for two columns at once: their loads do not wait for each other's stores
-__device__ __forceinline__ void flush2(uint32_t acc_lane, int offa, int offb, float ta, float tb)
-{
-    ta = ta == ta ? ta : 0.f;
-    tb = tb == tb ? tb : 0.f;
-    const uint32_t a = acc_lane + offa, b = acc_lane + offb;
-    if (offa == offb) {                                                 // warp-uniform
-        sts32(a, lds32(a) + (ta + tb));
-    } else {
-        const float va = lds32(a), vb = lds32(b);
-        sts32(a, va + ta);
-        sts32(b, vb + tb);
-    }
-}
-
 __device__ __forceinline__ uint32_t ctx_u32(uint32_t sctx, int i) { return (uint32_t)ldsi32(sctx + 4 * i); }
 
 // Events 1 .. n-1 of column c of the warp's cell at step t (kcb = kk | c << 4 | buffer << 8); r = restart value
 // left by event 0.  Out of line: a layer cut by several coarse interfaces is the less common case.
+template <bool NS>
 __device__ __noinline__ float apply_extras(uint32_t sctx, int t, int kcb, int info, float q, float x, float y, float r)
 {
     const int kk = kcb & 15, c = (kcb >> 4) & 15, b = kcb >> 8;
@@ -446,7 +441,7 @@ __device__ __noinline__ float apply_extras(uint32_t sctx, int t, int kcb, int in
         const uint32_t a = ctx_u32(sctx, CTX_TAIL) + xc * (TAILMAX * 8);
         for (int e = 0; e + 2 <= info; ++e) {
             const float I = lds32(a + 8 * e) * q;
-            flush(acc_lane, ldsi32(a + 8 * e + 4), r + I);
+            flush<NS>(acc_lane, ldsi32(a + 8 * e + 4), r + I);
             r = 0.f * I;
         }
         return r;
@@ -457,7 +452,7 @@ __device__ __noinline__ float apply_extras(uint32_t sctx, int t, int kcb, int in
         for (int e = 0; e + 2 <= info; ++e) {
             const float4 ev = lds128(oa + 16 * e);
             const float I = ev.x * q + ev.y * x + ev.z * y;
-            flush(acc_lane, ldsi32(ob + 4 * e), r + I);
+            flush<NS>(acc_lane, ldsi32(ob + 4 * e), r + I);
             r = ev.w * I;                                               // stored negated
         }
         return r;
@@ -476,7 +471,7 @@ __device__ __noinline__ float apply_extras(uint32_t sctx, int t, int kcb, int in
     for (int e = 1; e < n; ++e) {
         const Event ev = make_event(g, col, pp.x, pp.y, t - 2, i0 + e, nz, mask_below, toa);
         const float I = ev.x * q + ev.y * x + ev.z * y;
-        flush(acc_lane, ev.slot * ACC_STRIDE, r + I);
+        flush<NS>(acc_lane, ev.slot * ACC_STRIDE, r + I);
         r = -(ev.w * I);
     }
     return r;
@@ -493,6 +488,7 @@ __device__ __forceinline__ float limited_slope(float df2, float dq_lo, float dq_
 // mappm.f90:689-707; t >= nz: one-sided cubic at the bottom, :729-747, and the layer below the surface).
 // State of the column: A = q(t-1), B = q(t-2), dq1 = delq(t-1), dcp = dc(t-2), xp = AL(t-2) - q(t-2), run.
 // Returns (delq(t), dc(t-1), AL(t-1) - q(t-1), run).  Out of line: 6 of nz + 3 steps.
+template <bool NS>
 __device__ __noinline__ float4 end_column(uint32_t sctx, int t, int kcb, float qn, float q3, float A, float B, float dq1,
                                           float dcp, float xp, float run)
 {
@@ -558,9 +554,9 @@ __device__ __noinline__ float4 end_column(uint32_t sctx, int t, int kcb, float q
     const int off = ldsi32(rb + 80), info = ldsi32(rb + 88);
     const uint32_t acc_lane = ctx_u32(sctx, CTX_CELL0) + w * ctx_u32(sctx, CTX_CELLB) + ctx_u32(sctx, CTX_ACC) + 4 * lane;
     const float I = ex * q + ey * x + ez * y;
-    flush(acc_lane, off, run + I);
-    float rs = info == 0 ? run : nw * I;                                    // -w is what the record holds
-    if (info > 1) rs = apply_extras(sctx, t, kcb, info, q, x, y, rs);
+    flush<NS>(acc_lane, off, run + I);
+    float rs = (NS && info == 0) ? run : nw * I;                            // -w is what the record holds
+    if (info > 1) rs = apply_extras<NS>(sctx, t, kcb, info, q, x, y, rs);
     run = fmaf(dpw, q, rs);
     return make_float4(dqn, dcn, xn, run);
 }
@@ -593,24 +589,26 @@ __device__ __forceinline__ void load_row(u64 (&q)[4], uint32_t stage, int kk, in
 // dc = dc(t-2), xp = AL(t-2) - q(t-2), run = running integral of the target level that is open
 struct State {
     u64 A[4], B[4], dq[4], dc[4], xp[4], run[4];
+    u64 chk;                         // fast variant: 0 * every field value; NaN once a non-finite value went by
 };
 
 // Further coarse interfaces of a layer at an interior step.  oa / ob: the column's entries in the lists.
 // Out of line (one small body instead of eight inline copies): about a quarter of the layers have a second one.
+template <bool NS>
 __device__ __noinline__ float further_events(uint32_t oa, uint32_t ob, int info, float q, float x, float y, float r,
                                              uint32_t acc_lane, uint32_t sctx, int t, int kcb)
 {
-    if (info > MAXE + 1) return apply_extras(sctx, t, kcb, info, q, x, y, r);      // INFO_SLOW
+    if (info > MAXE + 1) return apply_extras<NS>(sctx, t, kcb, info, q, x, y, r);      // INFO_SLOW
     const float4 ev = lds128(oa);
     const int off = ldsi32(ob);
     float I = ev.x * q + ev.y * x + ev.z * y;
-    flush(acc_lane, off, r + I);
+    flush<NS>(acc_lane, off, r + I);
     r = ev.w * I;                                                           // stored negated
     if (info > 2) {
         const float4 e2 = lds128(oa + 16);
         const int o2 = ldsi32(ob + 4);
         I = e2.x * q + e2.y * x + e2.z * y;
-        flush(acc_lane, o2, r + I);
+        flush<NS>(acc_lane, o2, r + I);
         r = e2.w * I;
     }
     return r;
@@ -619,6 +617,7 @@ __device__ __noinline__ float further_events(uint32_t oa, uint32_t ob, int info,
 // One step of the tandem walk for the 8 columns of a row: level t arrives, layer t-2 is finished.
 // Interior levels: straight line, two columns per arithmetic instruction; the min/max, compare and
 // select parts run on the halves; further events of a layer out of line behind warp-uniform branches.
+template <bool NS>
 __device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t ova, uint32_t ovb, uint32_t stage, int t, int kk, int b, int w,
                                          const Field &f, int any_derived, State &s, uint32_t acc_lane)
 {
@@ -651,45 +650,74 @@ __device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t o
         const u64 xn = fma2(NH, dcn, fma2(G, s.dc[p], mul2(Fm, dq1)));      // AL(t-1) - q(t-1), :674-683
         // layer t-2: limiter in deviation form (ppm_limiters lmt = 0)
         const u64 x = s.xp[p], y = add2(xn, dq1);
-        const u64 da1 = sub2(y, x), sm = add2(x, y);
-        const u64 tt = mul2(sm, da1), da2 = mul2(da1, mul2(da1, third));
-        const u64 m2x = mul2(x, neg2), m2y = mul2(y, neg2);
-        float xa, xb, ya, yb, ta, tb, ga, gb, mxa, mxb, mya, myb, ca, cb;
-        upk(x, xa, xb); upk(y, ya, yb); upk(tt, ta, tb); upk(da2, ga, gb);
-        upk(m2x, mxa, mxb); upk(m2y, mya, myb); upk(s.dc[p], ca, cb);
-        ya = ta > ga ? mxa : ya;    xa = -ta > ga ? mya : xa;
-        yb = tb > gb ? mxb : yb;    xb = -tb > gb ? myb : xb;
-        xa = ca == 0.f ? 0.f : xa;  ya = ca == 0.f ? 0.f : ya;
-        xb = cb == 0.f ? 0.f : xb;  yb = cb == 0.f ? 0.f : yb;
+        const u64 da1 = sub2(y, x);
+        float xa, xb, ya, yb, ca, cb;
+        upk(s.dc[p], ca, cb);
+        if (NS) {
+            const u64 sm = add2(x, y);
+            const u64 tt = mul2(sm, da1), da2 = mul2(da1, mul2(da1, third));
+            const u64 m2x = mul2(x, neg2), m2y = mul2(y, neg2);
+            float ta, tb, ga, gb, mxa, mxb, mya, myb;
+            upk(x, xa, xb); upk(y, ya, yb); upk(tt, ta, tb); upk(da2, ga, gb);
+            upk(m2x, mxa, mxb); upk(m2y, mya, myb);
+            ya = ta > ga ? mxa : ya;    xa = -ta > ga ? mya : xa;
+            yb = tb > gb ? mxb : yb;    xb = -tb > gb ? myb : xb;
+            xa = ca == 0.f ? 0.f : xa;  ya = ca == 0.f ? 0.f : ya;
+            xb = cb == 0.f ? 0.f : xb;  yb = cb == 0.f ? 0.f : yb;
+        } else {
+            // the same limiter without compares: with X = sg x, Y = sg y, sg = sign(y - x), the two cases
+            // a6da < -da2, a6da > da2 are (Y - X)(Y + 2X) > 0 and (X - Y)(X + 2Y) > 0 with Y >= X, i.e.
+            // Y' = min(Y, -2X), X' = max(X, -2Y) (they exclude each other); flat layers through a 0 / 1 factor
+            float da, db;
+            upk(da1, da, db);
+            const float sga = __int_as_float((__float_as_int(da) & 0x80000000) | 0x3f800000);
+            const float sgb = __int_as_float((__float_as_int(db) & 0x80000000) | 0x3f800000);
+            const u64 sg = pk(sga, sgb), sgm = mul2(sg, pk(ca != 0.f ? 1.f : 0.f, cb != 0.f ? 1.f : 0.f));
+            const u64 X = mul2(sg, x), Y = mul2(sg, y);
+            const u64 m2X = mul2(X, neg2), m2Y = mul2(Y, neg2);
+            float Xa, Xb, Ya, Yb, mXa, mXb, mYa, mYb;
+            upk(X, Xa, Xb); upk(Y, Ya, Yb); upk(m2X, mXa, mXb); upk(m2Y, mYa, mYb);
+            const u64 Xl = pk(fmaxf(Xa, mYa), fmaxf(Xb, mYb)), Yl = pk(fminf(Ya, mXa), fminf(Yb, mXb));
+            upk(mul2(sgm, Xl), xa, xb);
+            upk(mul2(sgm, Yl), ya, yb);
+        }
         const u64 xl = pk(xa, xb), yl = pk(ya, yb), qB = s.B[p];
         // the first event of each column: close a target level (NaN-skipping block sum, coarsen.py:211), restart the next
         const u64 I = fma2(EZ, yl, fma2(EY, xl, mul2(EX, qB)));
         const u64 tot = add2(s.run[p], I);
         float tota, totb;
         upk(tot, tota, totb);
-        tota = tota == tota ? tota : 0.f;
-        totb = totb == totb ? totb : 0.f;
+        if (NS) {
+            tota = tota == tota ? tota : 0.f;
+            totb = totb == totb ? totb : 0.f;
+        }
         if (oi.x == oi.y) {                                                 // warp-uniform
             sts32(aa, va + (tota + totb));
         } else {
             sts32(aa, va + tota);
             sts32(ab, vb + totb);
         }
-        float ra, rb_, na, nb;
-        upk(s.run[p], ra, rb_);
-        upk(mul2(NW, I), na, nb);
-        ra = oi.z == 0 ? ra : na;
-        rb_ = oi.w == 0 ? rb_ : nb;
-        if ((oi.z | oi.w) > 1) {                                            // layers cut by several coarse interfaces
-            float qa, qb;
-            upk(qB, qa, qb);
-            const uint32_t oa = ova + (2 * p) * (MAXE * 16), ob = ovb + (2 * p) * (MAXE * 4);
-            if (oi.z > 1) ra = further_events(oa, ob, oi.z, qa, xa, ya, ra, acc_lane, sctx, t, kk | (2 * p) << 4 | b << 8);
-            if (oi.w > 1)
-                rb_ = further_events(oa + MAXE * 16, ob + MAXE * 4, oi.w, qb, xb, yb, rb_, acc_lane, sctx, t,
-                                     kk | (2 * p + 1) << 4 | b << 8);
+        u64 rs = mul2(NW, I);                                               // restart of the next level
+        if (NS) {                                                           // no event: the running sum is kept
+            float ra, rb_, na, nb;
+            upk(s.run[p], ra, rb_);
+            upk(rs, na, nb);
+            rs = pk(oi.z == 0 ? ra : na, oi.w == 0 ? rb_ : nb);
+        } else {
+            s.chk = fma2(qn, 0ull, s.chk);
         }
-        s.run[p] = fma2(DPW, qB, pk(ra, rb_));
+        if ((oi.z | oi.w) > 1) {                                            // layers cut by several coarse interfaces
+            float qa, qb, ra, rb_;
+            upk(qB, qa, qb);
+            upk(rs, ra, rb_);
+            const uint32_t oa = ova + (2 * p) * (MAXE * 16), ob = ovb + (2 * p) * (MAXE * 4);
+            if (oi.z > 1) ra = further_events<NS>(oa, ob, oi.z, qa, xa, ya, ra, acc_lane, sctx, t, kk | (2 * p) << 4 | b << 8);
+            if (oi.w > 1)
+                rb_ = further_events<NS>(oa + MAXE * 16, ob + MAXE * 4, oi.w, qb, xb, yb, rb_, acc_lane, sctx, t,
+                                         kk | (2 * p + 1) << 4 | b << 8);
+            rs = pk(ra, rb_);
+        }
+        s.run[p] = fma2(DPW, qB, rs);
         s.B[p] = s.A[p]; s.A[p] = qn; s.dq[p] = dqn; s.dc[p] = dcn; s.xp[p] = xn;
         E1 = E1n; E2 = E2n; Fm = Fmn; G = Gn; NH = NHn; DPW = DPWn; EX = EXn; EY = EYn; EZ = EZn; NW = NWn;
         oi = oin;
@@ -697,6 +725,7 @@ __device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t o
 }
 
 // The same step at the ends of the column: column by column through end_column
+template <bool NS>
 __device__ __forceinline__ void end_step(uint32_t sctx, uint32_t stage, int t, int kk, int b, int w, int nz, const Field &f,
                                          int any_derived, State &s)
 {
@@ -705,13 +734,17 @@ __device__ __forceinline__ void end_step(uint32_t sctx, uint32_t stage, int t, i
     for (int p = 0; p < 4; ++p) { q[p] = s.A[p]; q3[p] = 0; }
     if (t < nz) load_row(q, stage, kk, w, f, any_derived);
     if (t == 2) load_row(q3, stage, 3, w, f, any_derived);          // level 3 is in the same stage (KC = 4)
+    if (!NS && t < nz) {
+#pragma unroll
+        for (int p = 0; p < 4; ++p) s.chk = fma2(q[p], 0ull, s.chk);
+    }
 #pragma unroll
     for (int p = 0; p < 4; ++p) {
         float qa, qb, ta, tb, Aa, Ab, Ba, Bb, da, db, ca, cb, xa, xb, ra, rb;
         upk(q[p], qa, qb);      upk(q3[p], ta, tb);     upk(s.A[p], Aa, Ab);    upk(s.B[p], Ba, Bb);
         upk(s.dq[p], da, db);   upk(s.dc[p], ca, cb);   upk(s.xp[p], xa, xb);   upk(s.run[p], ra, rb);
-        const float4 va = end_column(sctx, t, kk | (2 * p) << 4 | b << 8, qa, ta, Aa, Ba, da, ca, xa, ra);
-        const float4 vb = end_column(sctx, t, kk | (2 * p + 1) << 4 | b << 8, qb, tb, Ab, Bb, db, cb, xb, rb);
+        const float4 va = end_column<NS>(sctx, t, kk | (2 * p) << 4 | b << 8, qa, ta, Aa, Ba, da, ca, xa, ra);
+        const float4 vb = end_column<NS>(sctx, t, kk | (2 * p + 1) << 4 | b << 8, qb, tb, Ab, Bb, db, cb, xb, rb);
         s.B[p] = s.A[p]; s.A[p] = q[p];
         s.dq[p] = pk(va.x, vb.x); s.dc[p] = pk(va.y, vb.y); s.xp[p] = pk(va.z, vb.z); s.run[p] = pk(va.w, vb.w);
     }
@@ -719,9 +752,16 @@ __device__ __forceinline__ void end_step(uint32_t sctx, uint32_t stage, int t, i
 
 // 128 registers at launch (2 CTAs of 256 threads per SM); the field warpgroup then takes 184 and the
 // geometry warpgroup drops to 72 (setmaxnreg).
+// Two variants.  NS = false (fast): assumes every field value is finite, which lets the block sums drop their
+// NaN tests and selects; it checks that assumption (0 * q summed over everything it reads) and flags the CTA
+// otherwise.  NS = true: NaN-skipping sums exactly like the reference's nansum; launched after the fast one, its
+// CTAs return at once unless flagged (p.flags == nullptr: runs everywhere, CG_PLEVEL_NANSAFE=1).
+template <bool NS>
 __global__ void __maxnreg__(128)
 plevel_stream_kernel(const __grid_constant__ Params p)
 {
+    const int cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    if (NS && p.flags && p.flags[cta] == 0) return;
     extern __shared__ __align__(1024) unsigned char smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int nz = p.nz, V = p.nfields, nsrc = p.nsrc;
@@ -744,6 +784,7 @@ plevel_stream_kernel(const __grid_constant__ Params p)
     const uint32_t tail = sbase + lay.tail;
 
     if (tid == 0) {
+        if (!NS) p.flags[cta] = 0;
         for (int s = 0; s < NSTAGE; ++s) {
             mbar_init(bars + 8 * s, NCELL);                 // full: one expect_tx arrival per geometry warp
             mbar_init(gfull + 8 * s, NCELL);                // geometry buffer: one arrival per geometry warp
@@ -847,7 +888,7 @@ plevel_stream_kernel(const __grid_constant__ Params p)
                     tma_load_3d(ring + b * stage_bytes + src * BOX_BYTES, &p.maps[src], NCOL * bx, 8 * by + row,
                                 (int)(o * nz) + chunk * KC, bars + 8 * b);
                 }
-                geometry_step(icnt, pm3, pm2, pm1, p0, pp1, g, col, chunk * KC + gw, gw, x, rec0 + b * REC_BYTES,
+                geometry_step<NS>(icnt, pm3, pm2, pm1, p0, pp1, g, col, chunk * KC + gw, gw, x, rec0 + b * REC_BYTES,
                               ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, tail, edge, nz, mask_below, toa);
                 __syncwarp();
                 if (lane == 0) mbar_arrive(gfull + 8 * b);
@@ -878,10 +919,12 @@ plevel_stream_kernel(const __grid_constant__ Params p)
     fld.c3 = active ? p.fc3[lane] : 1.f;
     const int any_derived = p.any_derived;
 
+    u64 chk = 0;
     for (int row = 0; row < 8; ++row) {
         State st;
 #pragma unroll
         for (int i = 0; i < 4; ++i) { st.A[i] = 0; st.B[i] = 0; st.dq[i] = 0; st.dc[i] = 0; st.xp[i] = 0; st.run[i] = 0; }
+        st.chk = chk;
 
         for (int chunk = 0; chunk < nch; ++chunk) {
             const int it = row * nch + chunk, b = it & 1, t0 = chunk * KC;
@@ -893,14 +936,20 @@ plevel_stream_kernel(const __grid_constant__ Params p)
                 const int t = t0 + kk;
                 if (t > nz_r + 2) break;
                 if (t != 2 && t < nz_r)        // (t = 0, 1: all-zero records, nothing is finished)
-                    hot_step(sctx, rec_w + b * REC_BYTES + kk * ((NCOL / 2) * REC_BLOCK), ova_w + b * OVA_BYTES + kk * (NCOL * MAXE * 16),
+                    hot_step<NS>(sctx, rec_w + b * REC_BYTES + kk * ((NCOL / 2) * REC_BLOCK), ova_w + b * OVA_BYTES + kk * (NCOL * MAXE * 16),
                              ovb_w + b * OVB_BYTES + kk * (NCOL * MAXE * 4), stage, t, kk, b, w, fld, any_derived, st, acc_lane);
                 else
-                    end_step(sctx, stage, t, kk, b, w, nz_r, fld, any_derived, st);
+                    end_step<NS>(sctx, stage, t, kk, b, w, nz_r, fld, any_derived, st);
             }
             __syncwarp();
             if (it + 2 < 8 * nch) asm volatile("bar.arrive %0, 256;" ::"r"(2 + b) : "memory");
         }
+        chk = st.chk;
+    }
+    if (!NS) {
+        float c0, c1;
+        upk(chk, c0, c1);
+        if (__any_sync(0xffffffffu, c0 != c0 || c1 != c1) && lane == 0) p.flags[cta] = 1;
     }
 
     // coarse outputs: block sum / weight sum (coarsen.py:213); 0/0 -> NaN like the reference
@@ -991,7 +1040,7 @@ int stream_supported(int nfields, int nz, int ny, int nx, int f)
 long stream_workspace_bytes(long n_outer, int nz, int ny, int nx)
 {
     const long h = (long)ny * nx, hc = (long)(ny / 8) * (nx / 8);
-    return 4 * n_outer * nz * hc + 256 + 4 * n_outer * h + 256;
+    return 4 * n_outer * nz * hc + 256 + 4 * n_outer * h + 256 + 4 * n_outer * (ny / 8) * (nx / 32) + 256;
 }
 
 int launch_surface_pressure_seq(const float *delp, float *ps, float toa, long n_outer, int nz, long h, cudaStream_t st)
@@ -1005,7 +1054,7 @@ int launch_surface_pressure_seq(const float *delp, float *ps, float toa, long n_
 
 // fields/outs as in cg_pressure_level_average; delp_coarse (and psurf when mask_below) already computed
 int launch_plevel_stream(const cg_field *fields, float *const *outs, int nfields, const float *delp,
-                         const float *area, const float *delp_coarse, const float *psurf, long n_outer,
+                         const float *area, const float *delp_coarse, const float *psurf, int *flags, long n_outer,
                          int nz, int ny, int nx, int mask_below, float toa, cudaStream_t st)
 {
     using namespace stream;
@@ -1043,15 +1092,28 @@ int launch_plevel_stream(const cg_field *fields, float *const *outs, int nfields
     p.nsrc = nsrc; p.nfields = nfields; p.nz = nz; p.ny = ny; p.nx = nx; p.mask_below = mask_below; p.toa = toa;
     static int max_set = 0;
     if (lay.total > max_set) {
-        cudaError_t e = cudaFuncSetAttribute(plevel_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
-        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(plevel_stream)");
-        e = cudaFuncSetAttribute(plevel_stream_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(carveout)");
+        for (int v = 0; v < 2; ++v) {
+            const void *fn = v ? (const void *)plevel_stream_kernel<true> : (const void *)plevel_stream_kernel<false>;
+            cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
+            if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(plevel_stream)");
+            e = cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+            if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(carveout)");
+        }
         max_set = 227 * 1024 - 1024;
     }
     dim3 grid(nx / 32, ny / 8, (unsigned)n_outer);
-    plevel_stream_kernel<<<grid, NTHREADS, lay.total, st>>>(p);
-    CG_LAUNCH_CHECK("cg_pressure_level_average(stream)");
+    // CG_PLEVEL_NANSAFE=1: the NaN-safe variant alone (tests); default: the fast variant, then the NaN-safe one
+    // over the CTAs that met a non-finite field value
+    const char *env = getenv("CG_PLEVEL_NANSAFE");
+    const bool nansafe_only = env && env[0] == '1';
+    if (!nansafe_only) {
+        p.flags = flags;
+        plevel_stream_kernel<false><<<grid, NTHREADS, lay.total, st>>>(p);
+        CG_LAUNCH_CHECK("cg_pressure_level_average(stream)");
+    }
+    p.flags = nansafe_only ? nullptr : flags;
+    plevel_stream_kernel<true><<<grid, NTHREADS, lay.total, st>>>(p);
+    CG_LAUNCH_CHECK("cg_pressure_level_average(stream, NaN-safe pass)");
     return CG_OK;
 }
 

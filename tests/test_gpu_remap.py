@@ -121,13 +121,17 @@ def _plevel_case(nt, nc, f, seed, nfields=3):
 def _pin_impl(monkeypatch, impl):
     """composed | fused | stream pin one implementation where its shape constraints hold
     (otherwise the next one runs); default = the library's own choice."""
+    monkeypatch.delenv("CG_PLEVEL_NANSAFE", raising=False)
     if impl == "default":
         monkeypatch.delenv("CG_PLEVEL_IMPL", raising=False)
+    elif impl == "stream_nansafe":      # the streaming kernel's NaN-skipping variant alone (no fast first pass)
+        monkeypatch.setenv("CG_PLEVEL_IMPL", "stream")
+        monkeypatch.setenv("CG_PLEVEL_NANSAFE", "1")
     else:
         monkeypatch.setenv("CG_PLEVEL_IMPL", impl)
 
 
-@pytest.mark.parametrize("impl", ["composed", "fused", "stream", "default"])
+@pytest.mark.parametrize("impl", ["composed", "fused", "stream", "stream_nansafe", "default"])
 @pytest.mark.parametrize("mask_below", [False, True])
 @pytest.mark.parametrize("f,nc", [(8, 4), (2, 4), (16, 2)])  # even coarse sizes: odd = staggered in the reference
 def test_pressure_level_average_vs_oracle(ops, monkeypatch, impl, mask_below, f, nc):
@@ -179,7 +183,7 @@ def _check_plevel(ops, fields, delp, area, f, mask_below, descr=None, tol=3e-5):
         assert np.abs(g[ok] - e[ok]).max() <= tol * scale
 
 
-@pytest.mark.parametrize("impl", ["fused", "stream"])
+@pytest.mark.parametrize("impl", ["fused", "stream", "stream_nansafe"])
 @pytest.mark.parametrize("mask_below", [False, True])
 def test_pressure_level_budget_shaped_fields(ops, monkeypatch, impl, mask_below):
     """26 output fields like a fine_res_budget timestep: 22 first moments, 2 products and 2
@@ -198,7 +202,7 @@ def test_pressure_level_budget_shaped_fields(ops, monkeypatch, impl, mask_below)
     _check_plevel(ops, fields, delp, area, f, mask_below, descr)
 
 
-@pytest.mark.parametrize("impl", ["composed", "stream"])
+@pytest.mark.parametrize("impl", ["composed", "stream", "stream_nansafe"])
 @pytest.mark.parametrize("mask_below", [False, True])
 @pytest.mark.parametrize("case", ["rough", "steep", "shifted_top"])
 def test_pressure_level_hard_columns(ops, monkeypatch, impl, mask_below, case):
@@ -226,7 +230,7 @@ def test_pressure_level_hard_columns(ops, monkeypatch, impl, mask_below, case):
     _check_plevel(ops, fields, delp, area, f, mask_below, tol=1e-4)
 
 
-@pytest.mark.parametrize("impl", ["composed", "stream"])
+@pytest.mark.parametrize("impl", ["composed", "stream", "stream_nansafe"])
 def test_pressure_level_nan_columns_are_skipped(ops, monkeypatch, impl):
     """NaN in a fine column: the block sum skips it where the remapped value is NaN
     (xarray's coarsen().sum() is nansum, coarsen.py:211), other levels keep the column."""
@@ -240,6 +244,34 @@ def test_pressure_level_nan_columns_are_skipped(ops, monkeypatch, impl):
     fld[0, 10:14, 9, 17] = np.nan
     area[0, 20, 20] = np.nan
     _check_plevel(ops, [fld], delp, area, f, False)
+
+
+@pytest.mark.parametrize("mask_below", [False, True])
+def test_pressure_level_nonfinite_values_rerun_only_their_blocks(ops, monkeypatch, mask_below):
+    """The streaming kernel's fast pass assumes finite field values and hands the CTAs that saw
+    a NaN or an infinity to the NaN-skipping pass: results must equal the NaN-skipping pass alone,
+    bit for bit where no CTA was rerun and everywhere else too (same arithmetic)."""
+    nt, nc, f = 1, 8, 8
+    ny = nx = nc * f
+    delp = syn.delp_from_ps(syn.surface_pressure((nt, ny, nx), seed=16))
+    area = syn.area((nt, ny, nx), seed=17)
+    flds = [syn.field((nt, syn.NZ, ny, nx), 95 + i) for i in range(3)]
+    flds[0][0, 2, 1, 2] = np.nan           # level 2 is read by the end step
+    flds[1][0, 78, 40, 40] = np.nan
+    flds[2][0, 30:33, 63, 63] = np.inf
+    res = {}
+    for impl in ("stream", "stream_nansafe"):
+        _pin_impl(monkeypatch, impl)
+        outs, _ = ops.pressure_level_average([dev(x) for x in flds], dev(delp), dev(area), f, mask_below=mask_below)
+        res[impl] = [host(o) for o in outs]
+    for a, b in zip(res["stream"], res["stream_nansafe"]):
+        fin = np.isfinite(b)
+        assert np.array_equal(np.isfinite(a), fin)
+        touched = np.zeros(a.shape, bool)      # CTAs = 4 coarse cells along x: the rerun ones must match exactly
+        for (y, x) in ((0, 0), (5, 5), (7, 7)):
+            touched[:, :, y, 4 * (x // 4):4 * (x // 4) + 4] = True
+        np.testing.assert_array_equal(a[touched & fin], b[touched & fin])
+        np.testing.assert_allclose(a[~touched & fin], b[~touched & fin], rtol=0, atol=3e-5 * 5)
 
 
 def test_pressure_level_golden_restart_T(ops):
