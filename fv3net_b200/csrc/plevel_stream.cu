@@ -615,113 +615,140 @@ __device__ __noinline__ float further_events(uint32_t oa, uint32_t ob, int info,
 }
 
 // One step of the tandem walk for the 8 columns of a row: level t arrives, layer t-2 is finished.
-// Interior levels: straight line, two columns per arithmetic instruction; the min/max, compare and
-// select parts run on the halves; further events of a layer out of line behind warp-uniform branches.
+// Interior levels: two columns per arithmetic instruction; the min/max parts run on the halves; further events of a
+// layer out of line behind warp-uniform branches.  The work of a column pair is split into a front half
+// (pure arithmetic on the record and the rolling state) and a back half (accumulator update, further events,
+// state rotation); the fronts of two pairs are written next to each other so that the compiler can interleave
+// their dependency chains (the branches of the back halves end basic blocks).
+struct PairRec {
+    u64 E1, E2, Fm, G, NH, DPW, EX, EY, EZ, NW;
+    int4 oi;
+};
+__device__ __forceinline__ void load_pair_rec(PairRec &r, uint32_t rb)
+{
+    lds2x64(rb, r.E1, r.E2);        lds2x64(rb + 16, r.Fm, r.G);    lds2x64(rb + 32, r.NH, r.DPW);
+    lds2x64(rb + 48, r.EX, r.EY);   lds2x64(rb + 64, r.EZ, r.NW);   r.oi = lds128i(rb + 80);
+}
+struct PairFront {
+    u64 dqn, dcn, xn, xl, yl, tot, rs;
+};
+
+template <bool NS>
+__device__ __forceinline__ void pair_front(PairFront &o, const PairRec &r, const State &s, int p, u64 qn)
+{
+    const u64 third = pk(1.f / 3.f, 1.f / 3.f), neg2 = pk(-2.f, -2.f);
+    const u64 dq1 = s.dq[p];
+    const u64 dqn = sub2(qn, s.A[p]);                                   // delq(t)
+    const u64 df2 = fma2(r.E1, dqn, mul2(r.E2, dq1));                   // layer t-1, mappm.f90:661
+    float dfa, dfb, d1a, d1b, dna, dnb;
+    upk(df2, dfa, dfb); upk(dq1, d1a, d1b); upk(dqn, dna, dnb);
+    const u64 dcn = pk(limited_slope(dfa, d1a, dna), limited_slope(dfb, d1b, dnb));    // dc(t-1)
+    const u64 xn = fma2(r.NH, dcn, fma2(r.G, s.dc[p], mul2(r.Fm, dq1)));    // AL(t-1) - q(t-1), :674-683
+    // layer t-2: limiter in deviation form (ppm_limiters lmt = 0)
+    const u64 x = s.xp[p], y = add2(xn, dq1);
+    const u64 da1 = sub2(y, x);
+    float xa, xb, ya, yb, ca, cb;
+    upk(s.dc[p], ca, cb);
+    if (NS) {
+        const u64 sm = add2(x, y);
+        const u64 tt = mul2(sm, da1), da2 = mul2(da1, mul2(da1, third));
+        const u64 m2x = mul2(x, neg2), m2y = mul2(y, neg2);
+        float ta, tb, ga, gb, mxa, mxb, mya, myb;
+        upk(x, xa, xb); upk(y, ya, yb); upk(tt, ta, tb); upk(da2, ga, gb);
+        upk(m2x, mxa, mxb); upk(m2y, mya, myb);
+        ya = ta > ga ? mxa : ya;    xa = -ta > ga ? mya : xa;
+        yb = tb > gb ? mxb : yb;    xb = -tb > gb ? myb : xb;
+        xa = ca == 0.f ? 0.f : xa;  ya = ca == 0.f ? 0.f : ya;
+        xb = cb == 0.f ? 0.f : xb;  yb = cb == 0.f ? 0.f : yb;
+        o.xl = pk(xa, xb); o.yl = pk(ya, yb);
+    } else {
+        // the same limiter without compares: with X = sg x, Y = sg y, sg = sign(y - x), the two cases
+        // a6da < -da2, a6da > da2 are (Y - X)(Y + 2X) > 0 and (X - Y)(X + 2Y) > 0 with Y >= X, i.e.
+        // Y' = min(Y, -2X), X' = max(X, -2Y) (they exclude each other); flat layers through a 0 / 1 factor
+        float da, db;
+        upk(da1, da, db);
+        const float sga = __int_as_float((__float_as_int(da) & 0x80000000) | 0x3f800000);
+        const float sgb = __int_as_float((__float_as_int(db) & 0x80000000) | 0x3f800000);
+        const u64 sg = pk(sga, sgb), sgm = mul2(sg, pk(ca != 0.f ? 1.f : 0.f, cb != 0.f ? 1.f : 0.f));
+        const u64 X = mul2(sg, x), Y = mul2(sg, y);
+        const u64 m2X = mul2(X, neg2), m2Y = mul2(Y, neg2);
+        float Xa, Xb, Ya, Yb, mXa, mXb, mYa, mYb;
+        upk(X, Xa, Xb); upk(Y, Ya, Yb); upk(m2X, mXa, mXb); upk(m2Y, mYa, mYb);
+        const u64 Xl = pk(fmaxf(Xa, mYa), fmaxf(Xb, mYb)), Yl = pk(fminf(Ya, mXa), fminf(Yb, mXb));
+        o.xl = mul2(sgm, Xl);
+        o.yl = mul2(sgm, Yl);
+    }
+    // the first event of each column: close a target level, restart the next
+    const u64 I = fma2(r.EZ, o.yl, fma2(r.EY, o.xl, mul2(r.EX, s.B[p])));
+    o.tot = add2(s.run[p], I);
+    o.rs = mul2(r.NW, I);                                               // restart of the next level
+    if (NS) {                                                           // no event: the running sum is kept
+        float ra, rb_, na, nb;
+        upk(s.run[p], ra, rb_);
+        upk(o.rs, na, nb);
+        o.rs = pk(r.oi.z == 0 ? ra : na, r.oi.w == 0 ? rb_ : nb);
+    }
+    o.dqn = dqn; o.dcn = dcn; o.xn = xn;
+}
+
+template <bool NS>
+__device__ __forceinline__ void pair_back(const PairFront &o, const PairRec &r, State &s, int p, u64 qn, uint32_t acc_lane,
+                                          uint32_t ova, uint32_t ovb, uint32_t sctx, int t, int kk, int b)
+{
+    // close the levels (NaN-skipping block sum, coarsen.py:211); both loads before the stores
+    const int4 oi = r.oi;
+    const uint32_t aa = acc_lane + oi.x, ab = acc_lane + oi.y;
+    const float va = lds32(aa), vb = lds32(ab);
+    float tota, totb;
+    upk(o.tot, tota, totb);
+    if (NS) {
+        tota = tota == tota ? tota : 0.f;
+        totb = totb == totb ? totb : 0.f;
+    }
+    if (oi.x == oi.y) {                                                 // warp-uniform
+        sts32(aa, va + (tota + totb));
+    } else {
+        sts32(aa, va + tota);
+        sts32(ab, vb + totb);
+    }
+    u64 rs = o.rs;
+    const u64 qB = s.B[p];
+    if ((oi.z | oi.w) > 1) {                                            // layers cut by several coarse interfaces
+        float qa, qb, ra, rb_, xa, xb, ya, yb;
+        upk(qB, qa, qb); upk(rs, ra, rb_); upk(o.xl, xa, xb); upk(o.yl, ya, yb);
+        const uint32_t oa = ova + (2 * p) * (MAXE * 16), ob = ovb + (2 * p) * (MAXE * 4);
+        if (oi.z > 1) ra = further_events<NS>(oa, ob, oi.z, qa, xa, ya, ra, acc_lane, sctx, t, kk | (2 * p) << 4 | b << 8);
+        if (oi.w > 1)
+            rb_ = further_events<NS>(oa + MAXE * 16, ob + MAXE * 4, oi.w, qb, xb, yb, rb_, acc_lane, sctx, t,
+                                     kk | (2 * p + 1) << 4 | b << 8);
+        rs = pk(ra, rb_);
+    }
+    s.run[p] = fma2(r.DPW, qB, rs);
+    if (!NS) s.chk = fma2(qn, 0ull, s.chk);
+    s.B[p] = s.A[p]; s.A[p] = qn; s.dq[p] = o.dqn; s.dc[p] = o.dcn; s.xp[p] = o.xn;
+}
+
 template <bool NS>
 __device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t ova, uint32_t ovb, uint32_t stage, int t, int kk, int b, int w,
                                          const Field &f, int any_derived, State &s, uint32_t acc_lane)
 {
     u64 q[4];
     load_row(q, stage, kk, w, f, any_derived);
-    const uint32_t rb = rec;
-    const u64 third = pk(1.f / 3.f, 1.f / 3.f), neg2 = pk(-2.f, -2.f);
-    u64 E1, E2, Fm, G, NH, DPW, EX, EY, EZ, NW;
-    int4 oi;
-    lds2x64(rb, E1, E2);        lds2x64(rb + 16, Fm, G);    lds2x64(rb + 32, NH, DPW);
-    lds2x64(rb + 48, EX, EY);   lds2x64(rb + 64, EZ, NW);   oi = lds128i(rb + 80);
-#pragma unroll
-    for (int p = 0; p < 4; ++p) {
-        u64 E1n = E1, E2n = E2, Fmn = Fm, Gn = G, NHn = NH, DPWn = DPW, EXn = EX, EYn = EY, EZn = EZ, NWn = NW;
-        int4 oin = oi;
-        if (p + 1 < 4) {
-            const uint32_t rn = rb + (p + 1) * REC_BLOCK;
-            lds2x64(rn, E1n, E2n);        lds2x64(rn + 16, Fmn, Gn);    lds2x64(rn + 32, NHn, DPWn);
-            lds2x64(rn + 48, EXn, EYn);   lds2x64(rn + 64, EZn, NWn);   oin = lds128i(rn + 80);
-        }
-        // the accumulator slots of the pair's first events: loaded now, stored once the sums are known
-        const uint32_t aa = acc_lane + oi.x, ab = acc_lane + oi.y;
-        const float va = lds32(aa), vb = lds32(ab);
-        const u64 qn = q[p], dq1 = s.dq[p];
-        const u64 dqn = sub2(qn, s.A[p]);                                   // delq(t)
-        const u64 df2 = fma2(E1, dqn, mul2(E2, dq1));                       // layer t-1, mappm.f90:661
-        float dfa, dfb, d1a, d1b, dna, dnb;
-        upk(df2, dfa, dfb); upk(dq1, d1a, d1b); upk(dqn, dna, dnb);
-        const u64 dcn = pk(limited_slope(dfa, d1a, dna), limited_slope(dfb, d1b, dnb));    // dc(t-1)
-        const u64 xn = fma2(NH, dcn, fma2(G, s.dc[p], mul2(Fm, dq1)));      // AL(t-1) - q(t-1), :674-683
-        // layer t-2: limiter in deviation form (ppm_limiters lmt = 0)
-        const u64 x = s.xp[p], y = add2(xn, dq1);
-        const u64 da1 = sub2(y, x);
-        float xa, xb, ya, yb, ca, cb;
-        upk(s.dc[p], ca, cb);
-        if (NS) {
-            const u64 sm = add2(x, y);
-            const u64 tt = mul2(sm, da1), da2 = mul2(da1, mul2(da1, third));
-            const u64 m2x = mul2(x, neg2), m2y = mul2(y, neg2);
-            float ta, tb, ga, gb, mxa, mxb, mya, myb;
-            upk(x, xa, xb); upk(y, ya, yb); upk(tt, ta, tb); upk(da2, ga, gb);
-            upk(m2x, mxa, mxb); upk(m2y, mya, myb);
-            ya = ta > ga ? mxa : ya;    xa = -ta > ga ? mya : xa;
-            yb = tb > gb ? mxb : yb;    xb = -tb > gb ? myb : xb;
-            xa = ca == 0.f ? 0.f : xa;  ya = ca == 0.f ? 0.f : ya;
-            xb = cb == 0.f ? 0.f : xb;  yb = cb == 0.f ? 0.f : yb;
-        } else {
-            // the same limiter without compares: with X = sg x, Y = sg y, sg = sign(y - x), the two cases
-            // a6da < -da2, a6da > da2 are (Y - X)(Y + 2X) > 0 and (X - Y)(X + 2Y) > 0 with Y >= X, i.e.
-            // Y' = min(Y, -2X), X' = max(X, -2Y) (they exclude each other); flat layers through a 0 / 1 factor
-            float da, db;
-            upk(da1, da, db);
-            const float sga = __int_as_float((__float_as_int(da) & 0x80000000) | 0x3f800000);
-            const float sgb = __int_as_float((__float_as_int(db) & 0x80000000) | 0x3f800000);
-            const u64 sg = pk(sga, sgb), sgm = mul2(sg, pk(ca != 0.f ? 1.f : 0.f, cb != 0.f ? 1.f : 0.f));
-            const u64 X = mul2(sg, x), Y = mul2(sg, y);
-            const u64 m2X = mul2(X, neg2), m2Y = mul2(Y, neg2);
-            float Xa, Xb, Ya, Yb, mXa, mXb, mYa, mYb;
-            upk(X, Xa, Xb); upk(Y, Ya, Yb); upk(m2X, mXa, mXb); upk(m2Y, mYa, mYb);
-            const u64 Xl = pk(fmaxf(Xa, mYa), fmaxf(Xb, mYb)), Yl = pk(fminf(Ya, mXa), fminf(Yb, mXb));
-            upk(mul2(sgm, Xl), xa, xb);
-            upk(mul2(sgm, Yl), ya, yb);
-        }
-        const u64 xl = pk(xa, xb), yl = pk(ya, yb), qB = s.B[p];
-        // the first event of each column: close a target level (NaN-skipping block sum, coarsen.py:211), restart the next
-        const u64 I = fma2(EZ, yl, fma2(EY, xl, mul2(EX, qB)));
-        const u64 tot = add2(s.run[p], I);
-        float tota, totb;
-        upk(tot, tota, totb);
-        if (NS) {
-            tota = tota == tota ? tota : 0.f;
-            totb = totb == totb ? totb : 0.f;
-        }
-        if (oi.x == oi.y) {                                                 // warp-uniform
-            sts32(aa, va + (tota + totb));
-        } else {
-            sts32(aa, va + tota);
-            sts32(ab, vb + totb);
-        }
-        u64 rs = mul2(NW, I);                                               // restart of the next level
-        if (NS) {                                                           // no event: the running sum is kept
-            float ra, rb_, na, nb;
-            upk(s.run[p], ra, rb_);
-            upk(rs, na, nb);
-            rs = pk(oi.z == 0 ? ra : na, oi.w == 0 ? rb_ : nb);
-        } else {
-            s.chk = fma2(qn, 0ull, s.chk);
-        }
-        if ((oi.z | oi.w) > 1) {                                            // layers cut by several coarse interfaces
-            float qa, qb, ra, rb_;
-            upk(qB, qa, qb);
-            upk(rs, ra, rb_);
-            const uint32_t oa = ova + (2 * p) * (MAXE * 16), ob = ovb + (2 * p) * (MAXE * 4);
-            if (oi.z > 1) ra = further_events<NS>(oa, ob, oi.z, qa, xa, ya, ra, acc_lane, sctx, t, kk | (2 * p) << 4 | b << 8);
-            if (oi.w > 1)
-                rb_ = further_events<NS>(oa + MAXE * 16, ob + MAXE * 4, oi.w, qb, xb, yb, rb_, acc_lane, sctx, t,
-                                         kk | (2 * p + 1) << 4 | b << 8);
-            rs = pk(ra, rb_);
-        }
-        s.run[p] = fma2(DPW, qB, rs);
-        s.B[p] = s.A[p]; s.A[p] = qn; s.dq[p] = dqn; s.dc[p] = dcn; s.xp[p] = xn;
-        E1 = E1n; E2 = E2n; Fm = Fmn; G = Gn; NH = NHn; DPW = DPWn; EX = EXn; EY = EYn; EZ = EZn; NW = NWn;
-        oi = oin;
-    }
+    PairRec r0, r1;
+    PairFront f0, f1;
+    load_pair_rec(r0, rec);
+    load_pair_rec(r1, rec + REC_BLOCK);
+    pair_front<NS>(f0, r0, s, 0, q[0]);
+    pair_front<NS>(f1, r1, s, 1, q[1]);
+    PairRec r2, r3;
+    load_pair_rec(r2, rec + 2 * REC_BLOCK);
+    load_pair_rec(r3, rec + 3 * REC_BLOCK);
+    pair_back<NS>(f0, r0, s, 0, q[0], acc_lane, ova, ovb, sctx, t, kk, b);
+    pair_back<NS>(f1, r1, s, 1, q[1], acc_lane, ova, ovb, sctx, t, kk, b);
+    pair_front<NS>(f0, r2, s, 2, q[2]);
+    pair_front<NS>(f1, r3, s, 3, q[3]);
+    pair_back<NS>(f0, r2, s, 2, q[2], acc_lane, ova, ovb, sctx, t, kk, b);
+    pair_back<NS>(f1, r3, s, 3, q[3], acc_lane, ova, ovb, sctx, t, kk, b);
 }
 
 // The same step at the ends of the column: column by column through end_column
