@@ -364,7 +364,12 @@ __device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, f
     float dpw = 0.f;
     if (L >= 0 && L <= nz) {
         if (L == 0) i0 = 0;
-        else while (i0 <= kn && lds32(g.pe2 + 4 * i0) <= pt) ++i0;
+        else {      // this warp last stood at the bottom of layer L - 4: usually three more interfaces since
+            const int lo = i0;
+            i0 = min(i0 + 3, kn + 1);
+            while (i0 > lo && !(lds32(g.pe2 + 4 * (i0 - 1)) <= pt)) --i0;
+            while (i0 <= kn && lds32(g.pe2 + 4 * i0) <= pt) ++i0;
+        }
         i1 = i0;
         if (L < nz) {
             while (i1 <= kn && lds32(g.pe2 + 4 * i1) <= pb) ++i1;
@@ -598,7 +603,7 @@ template <bool NS>
 __device__ __noinline__ float further_events(uint32_t oa, uint32_t ob, int info, float q, float x, float y, float r,
                                              uint32_t acc_lane, uint32_t sctx, int t, int kcb)
 {
-    if (info > MAXE + 1) return apply_extras<NS>(sctx, t, kcb, info, q, x, y, r);      // INFO_SLOW
+    if (info > MAXE + 1) return apply_extras<NS>(sctx, t, kcb, info & 1023, q, x, y, r);    // INFO_SLOW, or the tail
     const float4 ev = lds128(oa);
     const int off = ldsi32(ob);
     float I = ev.x * q + ev.y * x + ev.z * y;
@@ -693,7 +698,7 @@ __device__ __forceinline__ void pair_front(PairFront &o, const PairRec &r, const
 
 template <bool NS>
 __device__ __forceinline__ void pair_back(const PairFront &o, const PairRec &r, State &s, int p, u64 qn, uint32_t acc_lane,
-                                          uint32_t ova, uint32_t ovb, uint32_t sctx, int t, int kk, int b)
+                                          uint32_t ova, uint32_t ovb, uint32_t sctx, int t, int nz, int kk, int b)
 {
     // close the levels (NaN-skipping block sum, coarsen.py:211); both loads before the stores
     const int4 oi = r.oi;
@@ -717,9 +722,11 @@ __device__ __forceinline__ void pair_back(const PairFront &o, const PairRec &r, 
         float qa, qb, ra, rb_, xa, xb, ya, yb;
         upk(qB, qa, qb); upk(rs, ra, rb_); upk(o.xl, xa, xb); upk(o.yl, ya, yb);
         const uint32_t oa = ova + (2 * p) * (MAXE * 16), ob = ovb + (2 * p) * (MAXE * 4);
-        if (oi.z > 1) ra = further_events<NS>(oa, ob, oi.z, qa, xa, ya, ra, acc_lane, sctx, t, kk | (2 * p) << 4 | b << 8);
+        // (t > nz: the layer below the surface, whose further events sit in the tail list: info beyond MAXE + 1 routes there)
+        const int big = t > nz ? 1024 : 0;
+        if (oi.z > 1) ra = further_events<NS>(oa, ob, oi.z + big, qa, xa, ya, ra, acc_lane, sctx, t, kk | (2 * p) << 4 | b << 8);
         if (oi.w > 1)
-            rb_ = further_events<NS>(oa + MAXE * 16, ob + MAXE * 4, oi.w, qb, xb, yb, rb_, acc_lane, sctx, t,
+            rb_ = further_events<NS>(oa + MAXE * 16, ob + MAXE * 4, oi.w + big, qb, xb, yb, rb_, acc_lane, sctx, t,
                                      kk | (2 * p + 1) << 4 | b << 8);
         rs = pk(ra, rb_);
     }
@@ -729,11 +736,15 @@ __device__ __forceinline__ void pair_back(const PairFront &o, const PairRec &r, 
 }
 
 template <bool NS>
-__device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t ova, uint32_t ovb, uint32_t stage, int t, int kk, int b, int w,
-                                         const Field &f, int any_derived, State &s, uint32_t acc_lane)
+__device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t ova, uint32_t ovb, uint32_t stage, int t, int nz, int kk, int b,
+                                         int w, const Field &f, int any_derived, State &s, uint32_t acc_lane)
 {
     u64 q[4];
     load_row(q, stage, kk, w, f, any_derived);
+    if (t >= nz) {                      // below the last level (t = nz + 1, nz + 2): q(nz - 1) again; the records' zero
+#pragma unroll                          // stencils then give y = delq, x = y = dc = 0 as mappm.f90:729-747, :115-120 want
+        for (int p = 0; p < 4; ++p) q[p] = s.A[p];
+    }
     PairRec r0, r1;
     PairFront f0, f1;
     load_pair_rec(r0, rec);
@@ -743,12 +754,12 @@ __device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t o
     PairRec r2, r3;
     load_pair_rec(r2, rec + 2 * REC_BLOCK);
     load_pair_rec(r3, rec + 3 * REC_BLOCK);
-    pair_back<NS>(f0, r0, s, 0, q[0], acc_lane, ova, ovb, sctx, t, kk, b);
-    pair_back<NS>(f1, r1, s, 1, q[1], acc_lane, ova, ovb, sctx, t, kk, b);
+    pair_back<NS>(f0, r0, s, 0, q[0], acc_lane, ova, ovb, sctx, t, nz, kk, b);
+    pair_back<NS>(f1, r1, s, 1, q[1], acc_lane, ova, ovb, sctx, t, nz, kk, b);
     pair_front<NS>(f0, r2, s, 2, q[2]);
     pair_front<NS>(f1, r3, s, 3, q[3]);
-    pair_back<NS>(f0, r2, s, 2, q[2], acc_lane, ova, ovb, sctx, t, kk, b);
-    pair_back<NS>(f1, r3, s, 3, q[3], acc_lane, ova, ovb, sctx, t, kk, b);
+    pair_back<NS>(f0, r2, s, 2, q[2], acc_lane, ova, ovb, sctx, t, nz, kk, b);
+    pair_back<NS>(f1, r3, s, 3, q[3], acc_lane, ova, ovb, sctx, t, nz, kk, b);
 }
 
 // The same step at the ends of the column: column by column through end_column
@@ -883,15 +894,21 @@ plevel_stream_kernel(const __grid_constant__ Params p)
         g.rdp2 = sbase + lay.cell0 + cell * lay.cell_bytes + lay.rdp2;
         const float *dcol = p.delp + o * nz * h + (long)(8 * by) * nx + NCOL * bx + x;
         float dn[KC];
-        auto load_delp = [&](int row, int chunk) {                   // thicknesses of levels t-3 .. t, t = 4 chunk + gw
+        const float *dptr = dcol + (long)(gw - 3) * h;               // level t - 3 of the chunk to load, t = 4 chunk + gw
+        int dlvl = gw - 3;
+        auto load_delp = [&]() {                                     // thicknesses of levels t-3 .. t, then on to the next chunk
 #pragma unroll
             for (int i = 0; i < KC; ++i) {
-                const int lvl = chunk * KC + gw - 3 + i;
-                dn[i] = (lvl >= 0 && lvl < nz) ? ldg_stream(dcol + (long)lvl * h + (long)row * nx) : 0.f;
+                const int lvl = dlvl + i;
+                dn[i] = (lvl >= 0 && lvl < nz) ? ldg_stream(dptr + i * h) : 0.f;
             }
+            dptr += KC * h;
+            dlvl += KC;
         };
-        load_delp(0, 0);
-        const int mine = (nsrc - gw + NCELL - 1) / NCELL;            // this warp's share of the TMA boxes: gw, gw + 4, ...
+        load_delp();
+        const int mine = (nsrc - gw + NCELL - 1) / NCELL;            // this warp's share of the TMA boxes: gw, gw + 4, ... (<= 16)
+        const CUtensorMap *mymap = &p.maps[gw + NCELL * (lane < mine ? lane : 0)];
+        const uint32_t mydst = ring + (gw + NCELL * lane) * BOX_BYTES;
         for (int row = 0; row < 8; ++row) {
             ColG col;
             col.w = lds32(colw + 4 * (row * NCOL + x));
@@ -904,17 +921,17 @@ plevel_stream_kernel(const __grid_constant__ Params p)
                 // every warp carries the running sum of its own column walk, same order of additions
                 const float pm3 = plast, pm2 = pm3 + dn[0], pm1 = pm2 + dn[1], p0 = pm1 + dn[2], pp1 = p0 + dn[3];
                 plast = pp1;
-                if (chunk + 1 < nch) load_delp(row, chunk + 1);
-                else if (row + 1 < 8) load_delp(row + 1, 0);
+                if (chunk + 1 == nch) {                              // on to the next row
+                    dptr = dcol + (long)(gw - 3) * h + (long)(row + 1) * nx;
+                    dlvl = gw - 3;
+                }
+                if (chunk + 1 < nch || row + 1 < 8) load_delp();
                 // stage b of the field ring and geometry buffer b are released together by the field warps
                 if (it >= 2) asm volatile("bar.sync %0, 256;" ::"r"(2 + b) : "memory");
                 if (lane == 0) mbar_expect_tx(bars + 8 * b, mine * KC * 128);
                 __syncwarp();
-                for (int l = lane; l < mine; l += 32) {
-                    const int src = gw + NCELL * l;
-                    tma_load_3d(ring + b * stage_bytes + src * BOX_BYTES, &p.maps[src], NCOL * bx, 8 * by + row,
-                                (int)(o * nz) + chunk * KC, bars + 8 * b);
-                }
+                if (lane < mine)
+                    tma_load_3d(mydst + b * stage_bytes, mymap, NCOL * bx, 8 * by + row, (int)(o * nz) + chunk * KC, bars + 8 * b);
                 geometry_step<NS>(icnt, pm3, pm2, pm1, p0, pp1, g, col, chunk * KC + gw, gw, x, rec0 + b * REC_BYTES,
                               ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, tail, edge, nz, mask_below, toa);
                 __syncwarp();
@@ -962,9 +979,9 @@ plevel_stream_kernel(const __grid_constant__ Params p)
             for (int kk = 0; kk < KC; ++kk) {
                 const int t = t0 + kk;
                 if (t > nz_r + 2) break;
-                if (t != 2 && t < nz_r)        // (t = 0, 1: all-zero records, nothing is finished)
+                if (t != 2 && t != nz_r)       // (t = 0, 1: all-zero records, nothing is finished)
                     hot_step<NS>(sctx, rec_w + b * REC_BYTES + kk * ((NCOL / 2) * REC_BLOCK), ova_w + b * OVA_BYTES + kk * (NCOL * MAXE * 16),
-                             ovb_w + b * OVB_BYTES + kk * (NCOL * MAXE * 4), stage, t, kk, b, w, fld, any_derived, st, acc_lane);
+                             ovb_w + b * OVB_BYTES + kk * (NCOL * MAXE * 4), stage, t, nz_r, kk, b, w, fld, any_derived, st, acc_lane);
                 else
                     end_step<NS>(sctx, stage, t, kk, b, w, nz_r, fld, any_derived, st);
             }
