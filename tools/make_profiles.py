@@ -1,0 +1,63 @@
+"""Summarise gpurun_out/ (launch list + full ncu capture of the streaming kernel + bench lines) into profiles/.
+    python tools/make_profiles.py r01b          # tag of the files written
+Only reads gpurun_out/; run after tools/gpu_round.sh came back."""
+import collections, csv, io, json, os, shutil, subprocess, sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+G = os.path.join(ROOT, "gpurun_out"); P = os.path.join(ROOT, "profiles")
+tag = sys.argv[1] if len(sys.argv) > 1 else "r01"
+
+# ---- launch list -----------------------------------------------------------------------------
+rows = [r for r in csv.reader(open(os.path.join(G, "launches.csv"))) if r and not r[0].startswith("==")]
+hdr = rows[0]; ik = hdr.index("Kernel Name"); iv = hdr.index("Metric Value"); iu = hdr.index("Metric Unit")
+lib = collections.OrderedDict(); other = collections.OrderedDict()
+for r in rows[1:]:
+    if len(r) <= iv: continue
+    us = float(r[iv].replace(",", "")) * {"ns": 1e-3, "us": 1.0, "ms": 1e3, "usecond": 1.0, "nsecond": 1e-3, "msecond": 1e3}.get(r[iu], 1.0)
+    name = r[ik]
+    d = lib if ("cg::" in name or "stream::" in name) else other
+    n, t = d.get(name, (0, 0.0)); d[name] = (n + 1, t + us)
+tot = sum(t for _, t in lib.values())
+with open(os.path.join(P, f"{tag}_launches_summary.txt"), "w") as f:
+    f.write("# ncu --metrics gpu__time_duration.sum --clock-control none -c 400: python bench.py --steps 2 --warmup 3 --no-cpu --e2e-steps 0\n")
+    f.write("# Cold-cache, serialised launches: compare SHARES, not absolutes.  The capture holds torch's synthetic input\n")
+    f.write("# generation first, then 5 steps (3 warm-up + 2 timed).\n")
+    f.write(f"# library kernels: {sum(n for n, _ in lib.values())} launches, {tot/1e3:.3f} ms total\n")
+    f.write(f"{'kernel':92s} {'launches':>8s} {'total_us':>12s} {'us_each':>10s} {'share_of_step':>14s}\n")
+    for k, (n, t) in sorted(lib.items(), key=lambda kv: -kv[1][1]):
+        f.write(f"{k[:92]:92s} {n:8d} {t:12.1f} {t/n:10.1f} {100*t/tot:13.2f}%\n")
+    f.write("# torch kernels in the same capture (synthetic input generation, outside the steps):\n")
+    for k, (n, t) in sorted(other.items(), key=lambda kv: -kv[1][1])[:8]:
+        f.write(f"{k[:92]:92s} {n:8d} {t:12.1f}\n")
+
+# ---- full capture ----------------------------------------------------------------------------
+rep = os.path.join(G, "prof_stream.ncu-rep")
+raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+r = list(csv.reader(io.StringIO(raw))); h, u, v = r[0], r[1], r[2]
+keep = ["dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "gpu__time_duration.sum", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
+        "launch__block_size", "launch__grid_size", "launch__occupancy_limit_registers", "launch__occupancy_limit_shared_mem",
+        "launch__registers_per_thread", "launch__shared_mem_per_block_dynamic", "lts__t_sectors_srcunit_tex_op_read.sum",
+        "sm__cycles_elapsed.avg.per_second", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_tma.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active"]
+keep += [k for k in h if k.startswith("smsp__average_warps_issue_stalled_") and k.endswith("_per_issue_active.ratio")]
+with open(os.path.join(P, f"{tag}_ncu_plevel_stream.txt"), "w") as f:
+    f.write("# ncu --set full --clock-control none --import-source on -k regex:plevel_stream -s 2 -c 1: python bench.py --steps 1 --warmup 3 --no-cpu --e2e-steps 0\n")
+    f.write(f"# kernel: {v[h.index('Kernel Name')]}, C384 budget timestep (26 fields, 6 tiles x 79 levels)\n")
+    for k in sorted(set(keep)):
+        if k in h: f.write(f"{k:100s} {v[h.index(k)]:>20s} {u[h.index(k)]}\n")
+    reg = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_regions.py"), rep], capture_output=True, text=True).stdout
+    f.write("# warp-state samples and executed instructions by role (tools/ncu_regions.py):\n")
+    for line in reg.strip().splitlines(): f.write("#   " + line + "\n")
+def val(k):
+    x = float(v[h.index(k)].replace(",", "")); un = u[h.index(k)]
+    return x * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}.get(un, 1.0)
+json.dump({"kernel": v[h.index("Kernel Name")], "dram_bytes_read": val("dram__bytes_read.sum"),
+           "dram_bytes_write": val("dram__bytes_write.sum"), "plevel_cells": 1817247744,
+           "source": f"profiles/{tag}_ncu_plevel_stream.txt (ncu --set full, one launch, C384 budget timestep)"},
+          open(os.path.join(P, "traffic.json"), "w"), indent=1)
+for src, dst in (("bench.json", f"{tag}_bench.json"), ("bench_reference.json", f"{tag}_bench_reference.json")):
+    if os.path.exists(os.path.join(G, src)): shutil.copy(os.path.join(G, src), os.path.join(P, dst))
+print(open(os.path.join(P, f"{tag}_launches_summary.txt")).read()[:1800])
