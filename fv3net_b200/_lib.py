@@ -42,7 +42,13 @@ SIGNATURES = {
     "cg_pressure_level_average": (_i, [_vp, _pp, _i, _vp, _vp, _vp, _l, _i, _i, _i, _i, _i, _d,
                                        _vp, _l, _vp]),
     "cg_area_above_fine_surface": (_i, [_vp, _vp, _vp, _vp, _l, _i, _i, _i, _i, _d, _vp]),
+    "cg_elementwise": (_i, [_i, _vp, _vp, _vp, _d, _vp, _l, _i, _vp]),
+    "cg_surface_pressure": (_i, [_vp, _vp, _d, _l, _i, _l, _i, _vp]),
+    "cg_blending_weights": (_i, [_vp, _vp, _vp, _d, _d, _l, _i, _l, _i, _vp]),
+    "cg_hydrostatic_balance": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _d, _l, _i, _l, _i, _vp]),
 }
+(CG_EW_MUL, CG_EW_ISCLOSE, CG_EW_AND, CG_EW_WHERE, CG_EW_GT, CG_EW_LT, CG_EW_BLEND,
+ CG_EW_FILLNA, CG_EW_SUB, CG_EW_DIV) = range(10)
 
 CG_FIELD_PLAIN, CG_FIELD_PRODUCT, CG_FIELD_DIFF = 0, 1, 2
 

@@ -22,4 +22,9 @@ from .regridz import (  # noqa: F401
     regrid_to_edge_weighted_pressure,
     regrid_vertical,
 )
+from .coarsen_restarts import (  # noqa: F401
+    coarsen_restarts_on_pressure,
+    coarsen_restarts_on_sigma,
+    coarsen_restarts_via_blended_method,
+)
 from .constants import *  # noqa: F401,F403

@@ -92,6 +92,17 @@ def _canonical4(da, lead, z_dim, y_dim, x_dim):
                      da.sizes[x_dim])
 
 
+def _weights3(weights, delp, lead, y_dim, x_dim):
+    """2-D weights as a contiguous (lead..., y, x) tensor; leading dims the weights lack (the
+    grid's area has no Time) are broadcast by name, like xarray does."""
+    order = list(lead) + [y_dim, x_dim]
+    if any(d not in order for d in weights.dims) or y_dim not in weights.dims or x_dim not in weights.dims:
+        raise ValueError(f"weights dims {weights.dims} must be among {tuple(order)} and hold {y_dim!r}, {x_dim!r}")
+    if set(weights.dims) == set(order):
+        return lay.device_tensor(weights, order)
+    return lay.broadcast_to(weights, order, delp.sizes).contiguous()
+
+
 def _mask_weights(weights, phalf_coarse_on_fine, phalf_fine, dim_center=RESTART_Z_CENTER,
                   dim_outer=RESTART_Z_OUTER):
     """Weights zeroed where the coarse layer's bottom interface is not above the fine surface:
@@ -134,6 +145,7 @@ def _regrid_given_delp(ds, delp_fine, delp_coarse, weights, x_dim=FV_CORE_X_CENT
     pf = ops.pressure_at_interface(df, TOA_PRESSURE)
     h = ny * nx
     s_p, s_q = ((nz + 1) * h, 1, h), (nz * h, 1, h)
+    pf32, pc32 = pf.to(torch.float32), pc.to(torch.float32)    # f2py hands mappm Fortran `real`s
     arrays, names = _as_list(ds)
     lead_shape = [delp_fine.sizes[d] for d in lead]
     out = OrderedDict()
@@ -142,15 +154,12 @@ def _regrid_given_delp(ds, delp_fine, delp_coarse, weights, x_dim=FV_CORE_X_CENT
             raise ValueError(f"variable {da.name!r} has dims {da.dims}; expected {dims} in any order")
         q = _canonical4(da, lead, z_dim, y_dim, x_dim).to(torch.float32)
         res = torch.empty_like(q)
-        ops.mappm(pf, q, pc, n_outer, h, nz, nz, s_p, s_q, s_p, s_q, res)
+        ops.mappm(pf32, q, pc32, n_outer, h, nz, nz, s_p, s_q, s_p, s_q, res)
         data = lay.finish(res.reshape(lead_shape + [nz, ny, nx]), dims, da.dims, da)
         coords = OrderedDict((k, c) for k, c in da.coords.items())
         out[da.name] = DataArray(data, da.dims, coords, da.name, da.attrs)
     ds_regrid = Dataset(out, attrs=ds.attrs) if names is not None else out[arrays[0].name]
-    w_lead = [d for d in weights.dims if d not in (y_dim, x_dim)]
-    if w_lead != lead:
-        raise ValueError(f"weights dims {weights.dims} must be {tuple(lead) + (y_dim, x_dim)}")
-    tw = lay.device_tensor(weights, lead + [y_dim, x_dim]).reshape(n_outer, ny, nx)
+    tw = _weights3(weights, delp_fine, lead, y_dim, x_dim).reshape(n_outer, ny, nx)
     mw = ops.mask_weights(tw, pc, pf)
     coords = OrderedDict((k, c) for k, c in weights.coords.items())
     masked = DataArray(lay.finish(mw.reshape(lead_shape + [nz, ny, nx]), dims, dims, weights), dims,
@@ -191,6 +200,25 @@ def _edge_delp(delp, edge, lead, x_dim, y_dim, z_dim, tile_dim="tile"):
     return out.reshape(shape), dims, interp_axis
 
 
+def staggered_delp(delp, edge, x_dim=FV_CORE_X_CENTER, y_dim=FV_CORE_Y_OUTER, z_dim=RESTART_Z_CENTER):
+    """`delp` on the cell edges the winds of `edge` live on (regridz.py:85-100, the same steps as
+    coarsen_restarts.py:762-790 compute_edge_delp): interpolated across the six faces along the
+    other axis; the staggered dim takes the winds' name and the coordinate 1..n+1 (float32)."""
+    hor_dims = {"x": x_dim, "y": y_dim}
+    centre = {"x": FV_CORE_X_CENTER, "y": FV_CORE_Y_CENTER}
+    lead = [d for d in delp.dims if d not in (z_dim, centre["x"], centre["y"])]
+    t, dims, interp_axis = _edge_delp(delp, edge, lead, centre["x"], centre["y"], z_dim)
+    rename = {centre[interp_axis]: hor_dims[interp_axis], centre[edge]: hor_dims[edge]}
+    dims = [rename.get(d, d) for d in dims]
+    n = delp.sizes[centre[edge]]
+    coords = OrderedDict((k, c) for k, c in delp.coords.items()
+                         if not any(d in (centre["x"], centre["y"]) for d in c.dims))
+    if centre[edge] in delp.coords and hor_dims[edge] == centre[edge]:
+        coords[centre[edge]] = delp.coords[centre[edge]]
+    coords[hor_dims[interp_axis]] = ((hor_dims[interp_axis],), np.arange(1, n + 2, dtype=np.float32))
+    return DataArray(lay.finish(t, dims, dims, delp), dims, coords, delp.name, None)
+
+
 def regrid_to_edge_weighted_pressure(ds, delp, length, coarsening_factor, x_dim=FV_CORE_X_CENTER,
                                      y_dim=FV_CORE_Y_OUTER, z_dim=RESTART_Z_CENTER, edge="x"):
     """Regrid edge-valued quantities (u with dx, v with dy) to the pressure levels of the
@@ -201,17 +229,7 @@ def regrid_to_edge_weighted_pressure(ds, delp, length, coarsening_factor, x_dim=
     ds, delp, length = lab.adapt(ds), lab.adapt(delp), lab.adapt(length)
     from .coarsen import edge_weighted_block_average
 
-    hor_dims = {"x": x_dim, "y": y_dim}
-    centre = {"x": FV_CORE_X_CENTER, "y": FV_CORE_Y_CENTER}
-    lead = [d for d in delp.dims if d not in (z_dim, centre["x"], centre["y"])]
-    t, dims, interp_axis = _edge_delp(delp, edge, lead, centre["x"], centre["y"], z_dim)
-    rename = {centre[interp_axis]: hor_dims[interp_axis], centre[edge]: hor_dims[edge]}
-    dims = [rename.get(d, d) for d in dims]
-    n = delp.sizes[centre[edge]]
-    coords = OrderedDict((k, c) for k, c in delp.coords.items()
-                         if not any(d in (centre["x"], centre["y"]) for d in c.dims))
-    coords[hor_dims[interp_axis]] = ((hor_dims[interp_axis],), np.arange(1, n + 2, dtype=np.float32))
-    delp_staggered = DataArray(lay.finish(t, dims, dims, delp), dims, coords, delp.name, None)
+    delp_staggered = staggered_delp(delp, edge, x_dim=x_dim, y_dim=y_dim, z_dim=z_dim)
     delp_staggered_coarse = edge_weighted_block_average(
         delp_staggered, length, coarsening_factor, x_dim=x_dim, y_dim=y_dim, edge=edge)
     regridded, masked = _regrid_given_delp(ds, delp_staggered, delp_staggered_coarse, length,
@@ -244,12 +262,10 @@ def pressure_level_average(ds, delp, area, coarsening_factor, x_dim=FV_CORE_X_CE
         lay.check_exact(delp.sizes[d], f, d)
     lead = [d for d in delp.dims if d not in (z_dim, y_dim, x_dim)]
     dims = tuple(lead) + (z_dim, y_dim, x_dim)
-    if [d for d in area.dims if d not in (y_dim, x_dim)] != lead:
-        raise ValueError(f"area dims {area.dims} must be {tuple(lead) + (y_dim, x_dim)}")
     arrays, names = _as_list(ds)
     df = _canonical4(delp, lead, z_dim, y_dim, x_dim).to(torch.float32)
     n_outer, nz, ny, nx = df.shape
-    ta = lay.device_tensor(area, lead + [y_dim, x_dim]).reshape(n_outer, ny, nx).to(torch.float32)
+    ta = _weights3(area, delp, lead, y_dim, x_dim).reshape(n_outer, ny, nx).to(torch.float32)
     fields = []
     for da in arrays:
         if set(da.dims) != set(dims):

@@ -280,3 +280,70 @@ def area_above_fine_surface(delp, delp_coarse, area, f, toa=300.0):
     L.check(L.lib().cg_area_above_fine_surface(_p(delp), _p(delp_coarse), _p(area), _p(out), n_outer,
                                                nz, ny, nx, f, float(toa), _stream()))
     return out
+
+
+# ---- restart-coarsening recipes (coarsen_restarts.py): element-wise steps and column thermodynamics
+_EW = {"mul": L.CG_EW_MUL, "isclose": L.CG_EW_ISCLOSE, "and": L.CG_EW_AND, "where": L.CG_EW_WHERE,
+       "gt": L.CG_EW_GT, "lt": L.CG_EW_LT, "blend": L.CG_EW_BLEND, "fillna": L.CG_EW_FILLNA, "sub": L.CG_EW_SUB, "div": L.CG_EW_DIV}
+
+
+def elementwise(op, a, b=None, c=None):
+    """out = op(a, b, c) on same-shape tensors of one dtype; `b` may be a Python scalar.
+    Masks are 0 / 1 in the data dtype.  op: mul, isclose, and, where (c ? a : b), gt, lt,
+    blend (a*b + (1-a)*c), fillna."""
+    scalar = 0.0
+    tb = b
+    if not isinstance(b, torch.Tensor):
+        scalar, tb = (0.0 if b is None else float(b)), None
+    for t in (tb, c):
+        if t is not None and (t.dtype != a.dtype or tuple(t.shape) != tuple(a.shape)):
+            raise ValueError("elementwise operands must share shape and dtype")
+    a = a.contiguous()
+    tb = tb.contiguous() if tb is not None else None
+    c = c.contiguous() if c is not None else None
+    out = torch.empty_like(a)
+    L.check(L.lib().cg_elementwise(_EW[op], _p(a), _p(tb), _p(c), scalar, _p(out), a.numel(),
+                                   _DT[a.dtype], _stream()))
+    return out
+
+
+def _column_shape(t):
+    n_outer, nz = t.shape[:2]
+    return n_outer, nz, int(np.prod(t.shape[2:], dtype=np.int64))
+
+
+def surface_pressure(delp, toa=300.0):
+    """(n_outer, nz, *h) -> (n_outer, *h): sum over z + toa (vertically_dependent.py:189-208)."""
+    n_outer, nz, h = _column_shape(delp)
+    out = torch.empty((n_outer,) + tuple(delp.shape[2:]), dtype=delp.dtype, device=delp.device)
+    L.check(L.lib().cg_surface_pressure(_p(delp), _p(out), float(toa), n_outer, nz, h,
+                                        _DT[delp.dtype], _stream()))
+    return out
+
+
+def blending_weights(delp_coarse, ps_min, toa=300.0, sigma=0.9):
+    """coarsen_restarts.py:519-581: delp_coarse (n_outer, nz, *h), ps_min (n_outer, *h) the block
+    minimum of the fine surface pressure -> weights (n_outer, nz, *h)."""
+    n_outer, nz, h = _column_shape(delp_coarse)
+    if ps_min.dtype != delp_coarse.dtype or ps_min.numel() != n_outer * h:
+        raise ValueError("ps_min must be (n_outer, *h) in the dtype of delp_coarse")
+    out = torch.empty_like(delp_coarse)
+    L.check(L.lib().cg_blending_weights(_p(delp_coarse), _p(ps_min), _p(out), float(toa), float(sigma),
+                                        n_outer, nz, h, _DT[delp_coarse.dtype], _stream()))
+    return out
+
+
+def hydrostatic_balance(dz, phis, temp, sphum, delp, toa=300.0):
+    """coarsen_restarts.py:916-938: returns (hydrostatic DZ, adjusted phis) keeping the model-top
+    height.  3-D arguments (n_outer, nz, *h), phis (n_outer, *h), one dtype."""
+    n_outer, nz, h = _column_shape(dz)
+    for t in (temp, sphum, delp):
+        if t.dtype != dz.dtype or tuple(t.shape) != tuple(dz.shape):
+            raise ValueError("hydrostatic_balance operands must share shape and dtype")
+    if phis.dtype != dz.dtype or phis.numel() != n_outer * h:
+        raise ValueError("phis must be (n_outer, *h) in the dtype of DZ")
+    dz_out, phis_out = torch.empty_like(dz), torch.empty_like(phis)
+    L.check(L.lib().cg_hydrostatic_balance(_p(dz), _p(phis), _p(temp), _p(sphum), _p(delp), _p(dz_out),
+                                           _p(phis_out), float(toa), n_outer, nz, h, _DT[dz.dtype],
+                                           _stream()))
+    return dz_out, phis_out

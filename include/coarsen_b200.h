@@ -161,6 +161,50 @@ int cg_area_above_fine_surface(const float *delp, const float *delp_coarse, cons
                                float *out, long n_outer, int nz, int ny, int nx, int f,
                                double toa, void *stream);
 
+/* ---- restart-coarsening recipes (external/vcm/vcm/cubedsphere/coarsen_restarts.py) ----------- */
+
+/* Element-wise steps between the block kernels, on same-shape dense arrays of one dtype
+ * (masks are 0 / 1 in that dtype).  `b` may be NULL: the scalar takes its place.
+ *   CG_EW_MUL      out = a * b                  delp * area (:374), area * vfrac (:1160)
+ *   CG_EW_ISCLOSE  out = np.isclose(a, b)       xarray_utils.isclose (:1097, :1107, :1109, :1352)
+ *   CG_EW_AND      out = a && b                 is_dominant_surface_type & is_dominant_vtype (:1156)
+ *   CG_EW_WHERE    out = c ? a : b              DataArray.where(mask) with b = NaN, xr.where (:1176, :1352)
+ *   CG_EW_GT / LT  out = a > b, a < b           :1176, :1360, :1394
+ *   CG_EW_BLEND    out = a*b + (1 - a)*c        blend (:624-639)
+ *   CG_EW_FILLNA   out = isnan(a) ? b : a       .fillna(0.0) (:1242, :1254)
+ *   CG_EW_SUB / DIV out = a - b, a / b          compute_blending_weights (:519-536) */
+#define CG_EW_MUL 0
+#define CG_EW_ISCLOSE 1
+#define CG_EW_AND 2
+#define CG_EW_WHERE 3
+#define CG_EW_GT 4
+#define CG_EW_LT 5
+#define CG_EW_BLEND 6
+#define CG_EW_FILLNA 7
+#define CG_EW_SUB 8
+#define CG_EW_DIV 9
+int cg_elementwise(int op, const void *a, const void *b, const void *c, double scalar, void *out,
+                   long n, int dtype, void *stream);
+
+/* calc/thermo/vertically_dependent.py:189-208 surface_pressure_from_delp:
+ * (n_outer, nz, h) -> (n_outer, h), sum over z (top-down) + toa. */
+int cg_surface_pressure(const void *delp, void *out, double toa, long n_outer, int nz, long h,
+                        int dtype, void *stream);
+
+/* coarsen_restarts.py:519-581 (compute_blending_weights with pressure_at_midpoint_log and
+ * surface_pressure_from_delp of the coarse delp): delp_coarse (n_outer, nz, h), ps_min
+ * (n_outer, h) = block minimum of the fine surface pressure; out (n_outer, nz, h):
+ *   w = pfull > sigma*ps_min ? (ps - pfull) / (ps - sigma*ps_min) : 1 */
+int cg_blending_weights(const void *delp_coarse, const void *ps_min, void *out, double toa,
+                        double sigma, long n_outer, int nz, long h, int dtype, void *stream);
+
+/* coarsen_restarts.py:916-938 _impose_hydrostatic_balance (height_at_interface, hydrostatic_dz,
+ * dz_and_top_to_phis of vertically_dependent.py:69-100, 211-232, 182-186) per coarse column:
+ * dz, temp, sphum, delp, dz_out (n_outer, nz, h); phis, phis_out (n_outer, h). */
+int cg_hydrostatic_balance(const void *dz, const void *phis, const void *temp, const void *sphum,
+                           const void *delp, void *dz_out, void *phis_out, double toa,
+                           long n_outer, int nz, long h, int dtype, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

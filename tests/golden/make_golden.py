@@ -9,7 +9,9 @@ What is extracted (data only, no reference source):
     data variable of the 24 JSON files under
     external/vcm/tests/_coarsen_restarts_regression_tests/reference/
     (key "<tag>/<category>/<var>", plus "<...>@dims" with the dim names).
-  * restart_schemas.json — name/dims/shape/dtype of every input variable from
+  * coarsen_restarts_meta.json — per golden file the coordinates (dims, values) and the
+    attrs of every output variable, for checking the labelled results' metadata.
+  * restart_schemas.json — name/dims/shape/dtype/attrs of every input variable from
     .../schemas/*.json, enough to regenerate the synthetic inputs the way
     external/synth/synth/core.py:63-67 does
     (np.random.seed(0); np.random.uniform(lo, hi, shape).astype(dtype)).
@@ -33,7 +35,7 @@ def main(ref="/root/reference"):
     tests = os.path.join(ref, "external/vcm/tests")
     reg = os.path.join(tests, "_coarsen_restarts_regression_tests")
 
-    out = {}
+    out, meta = {}, {}
     for path in sorted(glob.glob(os.path.join(reg, "reference", "*.json"))):
         base = os.path.basename(path)[: -len(".json")]
         for cat in ("fv_core.res", "fv_srf_wnd.res", "fv_tracer.res", "sfc_data"):
@@ -48,6 +50,12 @@ def main(ref="/root/reference"):
             arr = np.array(v["data"], dtype=np.float64)
             out[f"{tag}/{cat}/{var}"] = arr
             out[f"{tag}/{cat}/{var}@dims"] = np.array(v["dims"])
+        meta[f"{tag}/{cat}"] = {
+            "coords": {k: {"dims": c["dims"], "data": c["data"]} for k, c in d["coords"].items()},
+            "attrs": {k: v["attrs"] for k, v in d["data_vars"].items()},
+        }
+    with open(os.path.join(HERE, "coarsen_restarts_meta.json"), "w") as f:
+        json.dump(meta, f, indent=0, sort_keys=True)
     np.savez_compressed(os.path.join(HERE, "coarsen_restarts_reference.npz"), **out)
 
     schemas = {}
@@ -57,11 +65,12 @@ def main(ref="/root/reference"):
             s = json.load(f)["schema"]
         schemas[cat] = {
             "variables": {
-                k: {"dims": v["dims"], "shape": v["array"]["shape"], "dtype": v["array"]["dtype"]}
+                k: {"dims": v["dims"], "shape": v["array"]["shape"], "dtype": v["array"]["dtype"],
+                    "attrs": v.get("attrs", {})}
                 for k, v in s["variables"].items()
             },
-            "coords": {k: {"dims": v["dims"], "value": v["value"]} for k, v in s["coords"].items()
-                       if k != "time"},
+            "coords": {k: {"dims": v["dims"], "value": v["value"], "attrs": v.get("attrs", {})}
+                       for k, v in s["coords"].items() if k != "time"},
         }
     with open(os.path.join(HERE, "restart_schemas.json"), "w") as f:
         json.dump(schemas, f, indent=0, sort_keys=True)

@@ -44,3 +44,27 @@ def golden(tag, category, var, squeeze_time=True):
         a = np.squeeze(a, axis=ax)
         dims.pop(ax)
     return a, dims
+
+
+def dataset(category):
+    """The synthetic Dataset of one restart category (or "grid") as the reference's test
+    builds it (synth.generate: variables with their attrs, coordinates from the schema's
+    values), as an fv3net_b200.labeled.Dataset on the host."""
+    from fv3net_b200.labeled import DataArray, Dataset
+
+    schema = load_schemas()[category]
+    coords = {}
+    for k, c in schema["coords"].items():
+        v = np.asarray(c["value"])
+        coords[k] = DataArray(v, tuple(c["dims"]), None, k, c.get("attrs", {}))
+    out = Dataset(coords=coords)
+    for var, v in schema["variables"].items():
+        a, dims = generate(category, var, squeeze_time=False)
+        own = {k: c for k, c in coords.items() if all(d in dims for d in c.dims)}
+        out[var] = DataArray(a, tuple(dims), own, var, v.get("attrs", {}))
+    return out
+
+
+def golden_meta(tag, category):
+    with open(os.path.join(_HERE, "golden", "coarsen_restarts_meta.json")) as f:
+        return json.load(f)[f"{tag}/{category}"]
