@@ -1,6 +1,6 @@
-// cg_mappm — general PPM vertical remap (mappm.f90:10-126, ppm_profile :614-851,
-// ppm_limiters :854-931 of the reference), any iv, kord <= 7, any km/kn, strided
-// columns.  This is the drop-in for the f2py entry point the reference calls from
+// cg_mappm — general PPM vertical remap (mappm.f90:10-126; ppm_profile :614-851 and
+// ppm_limiters :854-931 for kord <= 7, cs_profile :132-532 and cs_limiters :535-611 for
+// kord > 7), any iv, any km/kn, strided columns.  This is the drop-in for the f2py entry point the reference calls from
 // regridz.py:273; the fused pressure-level kernel (plevel_fused.cu) is the fast
 // path for the iv=1/kord=1 coarse-graining case.
 //
@@ -190,6 +190,232 @@ __device__ void ppm_column(const ColumnViews &c, int km, int iv, int kord)
     }
 }
 
+// ---- kord > 7: cs_profile (mappm.f90:132-532) and cs_limiters (:535-611) -----------------------------
+// Cubic-spline edge values from a tridiagonal solve along the column, then the kord 8..16 constraint
+// variants.  1-based accessors below keep each statement next to its Fortran line.  Edge values live in
+// H2 (km + 1 entries), gam in DC, the three extremum flags as bits of FL.
+// cs_limiters for one layer; `mode` is its `iv` argument (0: positive definite, 1, else: standard PPM)
+__device__ __forceinline__ void cs_limit(bool extm, float q, float &al, float &ar, float &a6, int mode)
+{
+    const float r12 = 1.f / 12.f;
+    if (mode == 0) {
+        if (q <= 0.f) {
+            al = q; ar = q; a6 = 0.f;
+        } else if (fabsf(ar - al) < -a6) {
+            const float d = ar - al;
+            if ((q + 0.25f * (d * d) / a6 + a6 * r12) < 0.f) {
+                if (q < ar && q < al) {
+                    ar = q; al = q; a6 = 0.f;
+                } else if (ar > al) {
+                    a6 = 3.f * (al - q);
+                    ar = al - a6;
+                } else {
+                    a6 = 3.f * (ar - q);
+                    al = ar - a6;
+                }
+            }
+        }
+        return;
+    }
+    const bool flat = mode == 1 ? ((q - al) * (q - ar) >= 0.f) : extm;
+    if (flat) {
+        al = q; ar = q; a6 = 0.f;
+    } else {
+        const float da1 = ar - al;
+        const float da2 = da1 * da1;
+        const float a6da = a6 * da1;
+        if (a6da < -da2) {
+            a6 = 3.f * (al - q);
+            ar = al - a6;
+        } else if (a6da > da2) {
+            a6 = 3.f * (ar - q);
+            al = ar - a6;
+        }
+    }
+}
+
+struct CsColumn {
+    const ColumnViews &c;
+    float *fl;
+    __device__ __forceinline__ float A1(int k) const { return c.Q(k - 1); }
+    __device__ __forceinline__ float DELP(int k) const { return c.DP(k - 1); }
+    __device__ __forceinline__ float &AL(int k) const { return c.AL(k - 1); }
+    __device__ __forceinline__ float &AR(int k) const { return c.AR(k - 1); }
+    __device__ __forceinline__ float &A6(int k) const { return c.A6(k - 1); }
+    __device__ __forceinline__ float &QE(int k) const { return c.H2(k - 1); }
+    __device__ __forceinline__ float &GAM(int k) const { return c.DC(k - 1); }
+    __device__ __forceinline__ int FLAGS(int k) const { return __float_as_int(fl[(k - 1) * TPB + c.tid]); }
+    __device__ __forceinline__ void set_flags(int k, int v) const { fl[(k - 1) * TPB + c.tid] = __int_as_float(v); }
+    __device__ __forceinline__ bool extm(int k) const { return FLAGS(k) & 1; }
+    __device__ __forceinline__ bool ext5(int k) const { return FLAGS(k) & 2; }
+    __device__ __forceinline__ bool ext6(int k) const { return FLAGS(k) & 4; }
+    __device__ __forceinline__ float curvature(int k) const { return 3.f * (2.f * A1(k) - (AL(k) + AR(k))); }
+    __device__ __forceinline__ void flatten(int k) const { AL(k) = A1(k); AR(k) = A1(k); }
+    // Huynh's 2nd constraint on both edges (:331-340 and its repeats)
+    __device__ __forceinline__ void huynh(int k) const
+    {
+        const float a = A1(k);
+        const float pmp_1 = a - 2.f * GAM(k + 1);
+        const float lac_1 = pmp_1 + 1.5f * GAM(k + 2);
+        AL(k) = fminf(fmaxf(AL(k), min3f(a, pmp_1, lac_1)), max3f(a, pmp_1, lac_1));
+        const float pmp_2 = a + 2.f * GAM(k);
+        const float lac_2 = pmp_2 - 1.5f * GAM(k - 1);
+        AR(k) = fminf(fmaxf(AR(k), min3f(a, pmp_2, lac_2)), max3f(a, pmp_2, lac_2));
+    }
+    __device__ __forceinline__ void limit(int k, int mode) const
+    {
+        float al = AL(k), ar = AR(k), a6 = A6(k);
+        cs_limit(extm(k), A1(k), al, ar, a6, mode);
+        AL(k) = al; AR(k) = ar; A6(k) = a6;
+    }
+};
+
+__device__ void cs_column(const ColumnViews &cv, float *fl, int km, int iv, int kord)
+{
+    const CsColumn c{cv, fl};
+    const int ak = kord < 0 ? -kord : kord;
+    float d4 = 0.f;
+    {                                                                     // :175-201 spline solve
+        const float grat = c.DELP(2) / c.DELP(1);
+        float bet = grat * (grat + 0.5f);
+        c.QE(1) = ((grat + grat) * (grat + 1.f) * c.A1(1) + c.A1(2)) / bet;
+        c.GAM(1) = (1.f + grat * (grat + 1.5f)) / bet;
+        for (int k = 2; k <= km; ++k) {
+            d4 = c.DELP(k - 1) / c.DELP(k);
+            bet = 2.f + d4 + d4 - c.GAM(k - 1);
+            c.QE(k) = (3.f * (c.A1(k - 1) + d4 * c.A1(k)) - c.QE(k - 1)) / bet;
+            c.GAM(k) = d4 / bet;
+        }
+        const float a_bot = 1.f + d4 * (d4 + 1.5f);
+        c.QE(km + 1) = (2.f * d4 * (d4 + 1.f) * c.A1(km) + c.A1(km - 1) - a_bot * c.QE(km)) /
+                       (d4 * (d4 + 0.5f) - a_bot * c.GAM(km));
+        for (int k = km; k >= 1; --k) c.QE(k) = c.QE(k) - c.GAM(k) * c.QE(k + 1);
+    }
+    if (ak > 16) {                                                        // :204-213
+        for (int k = 1; k <= km; ++k) {
+            c.AL(k) = c.QE(k);
+            c.AR(k) = c.QE(k + 1);
+            c.A6(k) = c.curvature(k);
+        }
+        return;
+    }
+    // large-scale constraints :222-258
+    c.QE(2) = fminf(c.QE(2), fmaxf(c.A1(1), c.A1(2)));
+    c.QE(2) = fmaxf(c.QE(2), fminf(c.A1(1), c.A1(2)));
+    for (int k = 2; k <= km; ++k) c.GAM(k) = c.A1(k) - c.A1(k - 1);
+    for (int k = 3; k <= km - 1; ++k) {
+        const float lo = fminf(c.A1(k - 1), c.A1(k)), hi = fmaxf(c.A1(k - 1), c.A1(k));
+        float q = c.QE(k);
+        if (c.GAM(k - 1) * c.GAM(k + 1) > 0.f) {
+            q = fminf(q, hi);
+            q = fmaxf(q, lo);
+        } else if (c.GAM(k - 1) > 0.f) {
+            q = fmaxf(q, lo);
+        } else {
+            q = fminf(q, hi);
+            if (iv == 0) q = fmaxf(0.f, q);
+        }
+        c.QE(k) = q;
+    }
+    c.QE(km) = fminf(c.QE(km), fmaxf(c.A1(km - 1), c.A1(km)));
+    c.QE(km) = fmaxf(c.QE(km), fminf(c.A1(km - 1), c.A1(km)));
+    for (int k = 1; k <= km; ++k) {                                       // :260-287
+        c.AL(k) = c.QE(k);
+        c.AR(k) = c.QE(k + 1);
+    }
+    for (int k = 1; k <= km; ++k) {
+        int f;
+        if (k == 1 || k == km)
+            f = (c.AL(k) - c.A1(k)) * (c.AR(k) - c.A1(k)) > 0.f;
+        else
+            f = c.GAM(k) * c.GAM(k + 1) < 0.f;
+        if (ak > 9) {
+            const float x0 = 2.f * c.A1(k) - (c.AL(k) + c.AR(k));
+            const float x1 = fabsf(c.AL(k) - c.AR(k));
+            c.A6(k) = 3.f * x0;
+            f |= (fabsf(x0) > x1) ? 2 : 0;
+            f |= (fabsf(c.A6(k)) > x1) ? 4 : 0;
+        }
+        c.set_flags(k, f);
+    }
+    // top two layers :296-324
+    if (iv == 0) {
+        c.AL(1) = fmaxf(0.f, c.AL(1));
+    } else if (iv == -1) {
+        if (c.AL(1) * c.A1(1) <= 0.f) c.AL(1) = 0.f;
+    } else if (iv == 2) {
+        c.AL(1) = c.A1(1); c.AR(1) = c.A1(1); c.A6(1) = 0.f;
+    }
+    if (iv != 2) {
+        c.A6(1) = c.curvature(1);
+        c.limit(1, 1);
+    }
+    c.A6(2) = c.curvature(2);
+    c.limit(2, 2);
+    for (int k = 3; k <= km - 2; ++k) {                                   // interior :329-497
+        if (ak < 9) {
+            c.huynh(k);
+            c.A6(k) = c.curvature(k);
+        } else if (ak == 9 || ak == 12) {
+            const bool wave = ak == 12 ? c.extm(k) : ((c.extm(k) && c.extm(k - 1)) || (c.extm(k) && c.extm(k + 1)));
+            if (wave) {
+                c.flatten(k);
+                c.A6(k) = 0.f;
+            } else {
+                c.A6(k) = 6.f * c.A1(k) - 3.f * (c.AL(k) + c.AR(k));
+                if (fabsf(c.A6(k)) > fabsf(c.AL(k) - c.AR(k))) {
+                    c.huynh(k);
+                    c.A6(k) = 6.f * c.A1(k) - 3.f * (c.AL(k) + c.AR(k));
+                }
+            }
+        } else if (ak == 10) {
+            if (c.ext5(k)) {
+                if (c.ext5(k - 1) || c.ext5(k + 1)) c.flatten(k);
+                else if (c.ext6(k - 1) || c.ext6(k + 1)) c.huynh(k);
+            } else if (c.ext6(k)) {
+                if (c.ext5(k - 1) || c.ext5(k + 1)) c.huynh(k);
+            }
+            c.A6(k) = c.curvature(k);
+        } else if (ak == 13) {
+            if (c.ext6(k) && c.ext6(k - 1) && c.ext6(k + 1)) c.flatten(k);
+            c.A6(k) = c.curvature(k);
+        } else if (ak == 14) {
+            c.A6(k) = c.curvature(k);
+        } else if (ak == 15) {
+            if (c.ext5(k)) {
+                if (c.ext5(k - 1) || c.ext5(k + 1)) c.flatten(k);
+            } else if (c.ext6(k)) {
+                c.huynh(k);
+            }
+            c.A6(k) = c.curvature(k);
+        } else if (ak == 16) {
+            if (c.ext5(k)) {
+                if (c.ext5(k - 1) || c.ext5(k + 1)) c.flatten(k);
+                else if (c.ext6(k - 1) || c.ext6(k + 1)) c.huynh(k);
+            }
+            c.A6(k) = c.curvature(k);
+        } else {                                                          // kord = 11
+            if (c.ext5(k) && (c.ext5(k - 1) || c.ext5(k + 1))) {
+                c.flatten(k);
+                c.A6(k) = 0.f;
+            } else {
+                c.A6(k) = c.curvature(k);
+            }
+        }
+        if (iv == 0) c.limit(k, 0);
+    }
+    // bottom two layers :502-519
+    if (iv == 0) {
+        c.AR(km) = fmaxf(0.f, c.AR(km));
+    } else if (iv == -1) {
+        if (c.AR(km) * c.A1(km) <= 0.f) c.AR(km) = 0.f;
+    }
+    c.A6(km - 1) = c.curvature(km - 1);
+    c.limit(km - 1, 2);
+    c.A6(km) = c.curvature(km);
+    c.limit(km, 1);
+}
+
 struct Strides { long v[12]; };
 // f > 0: target pressures live on the coarse grid; fine column i = (y, x) of a
 // (ny, nx) tile reads coarse column (y/f, x/f) of a (ny/f, nx/f) tile.
@@ -213,6 +439,7 @@ mappm_generic_kernel(const float *__restrict__ pe1, const float *__restrict__ q1
     c.a6 = c.ar + km * TPB;
     c.dc = c.a6 + km * TPB;
     c.h2 = c.dc + km * TPB;
+    float *fl = c.h2 + (km + 1) * TPB;                                    // kord > 7 only
 
     const long o = col / n_inner, i = col % n_inner;
     const float *p1 = pe1 + o * s.v[0] + i * s.v[1];
@@ -225,7 +452,10 @@ mappm_generic_kernel(const float *__restrict__ pe1, const float *__restrict__ q1
 
     for (int k = 0; k <= km; ++k) c.PE(k) = p1[k * l_pe1];
     for (int k = 0; k < km; ++k) c.Q(k) = f1[k * l_q1];
-    ppm_column(c, km, iv, kord);
+    if (kord > 7)
+        cs_column(c, fl, km, iv, kord);
+    else
+        ppm_column(c, km, iv, kord);
 
     const float r3 = 1.f / 3.f, r23 = 2.f / 3.f;
     const float pe_top = c.PE(0), pe_bot = c.PE(km), q_top = c.Q(0), q_bot = c.Q(km - 1);
@@ -307,8 +537,8 @@ int launch_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,
     CG_REQUIRE(n_outer >= 0 && n_inner >= 0, "bad column counts");
     CG_REQUIRE(km >= 4 && kn >= 1, "mappm needs km >= 4 and kn >= 1 (got %d, %d)", km, kn);
     CG_REQUIRE(iv >= -2 && iv <= 2, "iv must be in [-2, 2]");
-    if (kord > 7) {
-        set_error("kord=%d (cs_profile, mappm.f90:132) is not built yet", kord);
+    if (kord > 7 && iv == -2) {
+        set_error("kord=%d with iv=-2: cs_profile reads an array mappm never sets (mappm.f90:35, :163)", kord);
         return CG_ENOTSUP;
     }
     const long ncol = n_outer * n_inner;
@@ -316,7 +546,7 @@ int launch_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,
     Strides s;
     for (int i = 0; i < 12; ++i) s.v[i] = strides[i];
     Pe2Block pb{pe2_f, pe2_nx, pe2_nxc};
-    const size_t smem = sizeof(float) * TPB * (size_t)(7 * km + 1);
+    const size_t smem = sizeof(float) * TPB * (size_t)(kord > 7 ? 8 * km + 2 : 7 * km + 1);
     CG_REQUIRE(smem <= 227 * 1024, "km=%d needs %zu B of shared memory per block", km, smem);
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(mappm_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

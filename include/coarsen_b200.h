@@ -29,7 +29,7 @@ extern "C" {
 
 #define CG_OK 0
 #define CG_EINVAL (-1)   /* bad shape / factor / enum */
-#define CG_ENOTSUP (-2)  /* valid in the reference but not built yet (e.g. kord > 7) */
+#define CG_ENOTSUP (-2)  /* outside what the kernels take (see each entry point) */
 #define CG_ECUDA (-3)    /* CUDA runtime error; see cg_last_error() */
 
 #define CG_F32 0
@@ -109,12 +109,13 @@ int cg_mask_weights(const void *w2d, const void *pc, const void *pf, void *out,
 int cg_interp_to_edges(const void *c, void *out, int nz, int n, int axis,
                        int dtype, void *stream);
 
-/* mappm.f90:10-126 (ppm_profile :614, ppm_limiters :854): conservative PPM remap,
+/* mappm.f90:10-126 (ppm_profile :614, ppm_limiters :854, cs_profile :132): conservative PPM remap,
  * fp32 arithmetic like the Fortran `real`.  Strided columns: column (o,i) level k
  * of array A is A[o*os_A + i*cs_A + k*ls_A]; (ncol,nz) z-last and (tile,z,y,x)
  * layouts both work without a transpose; cs_pe2 = 0 shares target pressures.
  * strides: {os,cs,ls} for pe1, q1, pe2, q2 in that order (12 longs, elements).
- * kord <= 7; kord > 7 (cs_profile) -> CG_ENOTSUP. km >= 4.
+ * kord <= 7: ppm_profile; kord > 7: cs_profile (:132-532) / cs_limiters (:535-611); km >= 4.
+ * (iv = -2 with kord > 7 -> CG_ENOTSUP: cs_profile reads mappm's never-set `qs` there.)
  * A target layer no source layer brackets (NaN / non-monotone pressure: undefined
  * behaviour in the Fortran) yields NaN. */
 int cg_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,

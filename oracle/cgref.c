@@ -68,11 +68,11 @@
                           int iv, int kord, int nthreads)                                 \
     {                                                                                     \
         if (km < 4 || kn < 1) return CG_EINVAL;                                           \
-        if (kord > 7) return CG_ENOTSUP;                                                  \
+        if (kord > 7 && iv == -2) return CG_ENOTSUP; /* reads an uninitialised qs there */ \
         long ncol = n_outer * n_inner;                                                    \
         (void)nthreads; /* threading is done by the caller (ctypes releases the GIL) */  \
         {                                                                                 \
-            T *buf = (T *)malloc(sizeof(T) * (size_t)(2 * (km + 1) + 2 * (kn + 1) + 9 * km)); \
+            T *buf = (T *)malloc(sizeof(T) * (size_t)(2 * (km + 1) + 2 * (kn + 1) + 9 * km + 8)); \
             T *cpe1 = buf, *cq1 = cpe1 + km + 1, *cpe2 = cq1 + km + 1;                    \
             T *cq2 = cpe2 + kn + 1, *wk = cq2 + kn + 1;                                   \
             for (long c = 0; c < ncol; ++c) {                                             \
@@ -97,9 +97,12 @@ int cgref_ppm_profile_f32(const float *q, const float *dp, int km, int iv, int k
                           float *al, float *ar, float *a6)
 {
     if (km < 4) return CG_EINVAL;
-    if (kord > 7) return CG_ENOTSUP;
-    float *wk = (float *)malloc(sizeof(float) * (size_t)(5 * km));
-    ppm_column_f32(km, q, dp, al, ar, a6, iv, kord, wk);
+    if (kord > 7 && iv == -2) return CG_ENOTSUP;
+    float *wk = (float *)malloc(sizeof(float) * (size_t)(5 * km + 8));
+    if (kord > 7)
+        cs_column_f32(km, q, dp, al, ar, a6, iv, kord, wk);
+    else
+        ppm_column_f32(km, q, dp, al, ar, a6, iv, kord, wk);
     free(wk);
     return CG_OK;
 }

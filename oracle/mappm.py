@@ -55,7 +55,7 @@ def _check(rc):
     if rc == -1:
         raise ValueError("cgref: invalid argument (km >= 4 and kn >= 1 required)")
     if rc == -2:
-        raise NotImplementedError("cgref: kord > 7 (cs_profile) is not restated yet")
+        raise NotImplementedError("cgref: kord > 7 with iv = -2 reads an uninitialised array in the reference (mappm.f90:35, :163)")
     if rc != 0:
         raise RuntimeError(f"cgref: error {rc}")
 

@@ -82,6 +82,19 @@ def test_mappm_bit_exact_vs_oracle(ops, km, kn, iv, kord):
     np.testing.assert_array_equal(got, exp)
 
 
+@pytest.mark.parametrize("km,kn", [(79, 79), (4, 3), (6, 9), (32, 79)])
+@pytest.mark.parametrize("kord", [8, 9, 10, 11, 12, 13, 14, 15, 16, 17])
+@pytest.mark.parametrize("iv", [1, 0, -1, 2])
+def test_mappm_cs_profile_bit_exact_vs_oracle(ops, km, kn, iv, kord):
+    """kord > 7: cs_profile / cs_limiters (mappm.f90:132-611).  The oracle for these orders is
+    pinned only by properties (tests/test_oracle_golden.py): no reference test exists."""
+    rng = np.random.RandomState(km * 100 + kn + kord)
+    pe1, q, pe2 = _random_columns(rng, 129, km, kn)
+    got = gpu_mappm_zlast(ops, pe1, q, pe2, iv, kord)
+    exp = oracle.mappm(pe1, q, pe2, iv=iv, kord=kord)
+    np.testing.assert_array_equal(got, exp)
+
+
 def test_mappm_tile_layout_and_shared_target(ops):
     """(tile, z, y, x) layout addressed by strides; cs_pe2 = 0 shares one target column."""
     rng = np.random.RandomState(3)
@@ -104,8 +117,8 @@ def test_mappm_errors(ops):
     z = torch.zeros((1, 4), dtype=torch.float32, device="cuda")
     with pytest.raises(ValueError, match="km >= 4"):
         ops.mappm(z, z, z, 1, 1, 3, 3, (0, 4, 1), (0, 3, 1), (0, 4, 1), (0, 3, 1), z)
-    with pytest.raises(NotImplementedError, match="kord"):
-        ops.mappm(z, z, z, 1, 1, 4, 3, (0, 5, 1), (0, 4, 1), (0, 4, 1), (0, 3, 1), z, kord=9)
+    with pytest.raises(NotImplementedError, match="kord"):       # cs_profile would read mappm's unset `qs`
+        ops.mappm(z, z, z, 1, 1, 4, 3, (0, 5, 1), (0, 4, 1), (0, 4, 1), (0, 3, 1), z, iv=-2, kord=9)
 
 
 # ---- pressure-level coarse-graining --------------------------------------------------------

@@ -41,6 +41,62 @@ def test_mappm_f64_close_to_f32():
     assert np.abs(a - b).max() < 3e-5 * 1000 * 10
 
 
+# ---- kord > 7 (cs_profile): no reference test exists -> properties only ("parity unpinned")
+def _two_grids(n, km, kn, seed):
+    rng = np.random.RandomState(seed)
+    dp = rng.uniform(1, 1.5, (n, km))
+    pe1 = np.concatenate([np.full((n, 1), 3.0), 3 + np.cumsum(dp, 1)], 1)
+    w = rng.uniform(1, 1.5, (n, kn))
+    w = w / w.sum(1, keepdims=True) * (pe1[:, -1:] - 3)
+    pe2 = np.concatenate([np.full((n, 1), 3.0), 3 + np.cumsum(w, 1)], 1)
+    pe2[:, -1] = pe1[:, -1]
+    pe2[:, 0] = 3.000001             # a target interface AT the source top takes q1(1) (mappm.f90:62-64)
+    return pe1, pe2
+
+
+@pytest.mark.parametrize("kord", [8, 9, 10, 11, 12, 13, 14, 15, 16, 17])
+@pytest.mark.parametrize("iv", [-1, 0, 1, 2])
+def test_cs_profile_properties(kord, iv):
+    pe1, pe2 = _two_grids(64, 24, 19, kord)
+    rng = np.random.RandomState(iv + 5)
+    q = rng.uniform(-1, 1, (64, 24))
+    if iv == 0:
+        q = np.abs(q)
+    out = oracle.mappm(pe1, q, pe2, iv=iv, kord=kord, dtype=np.float64)
+    assert not np.isnan(out).any()
+    # conservative: the column integral is kept (up to the 1e-6 sliver cut off the top)
+    m1, m2 = (q * np.diff(pe1, axis=1)).sum(1), (out * np.diff(pe2, axis=1)).sum(1)
+    np.testing.assert_allclose(m2, m1, atol=2e-5)
+    # constants are reproduced
+    c = oracle.mappm(pe1, np.full_like(q, 2.5), pe2, iv=iv, kord=kord, dtype=np.float64)
+    np.testing.assert_allclose(c, 2.5, rtol=1e-12)
+    if iv == 0 and kord <= 16:       # positive definite (kord > 16 is the unconstrained spline, :204-213)
+        assert out.min() >= 0.0
+
+
+@pytest.mark.parametrize("kord", [8, 9, 10, 11, 13, 14, 15, 16, 17])
+def test_cs_profile_is_a_spline_on_smooth_data(kord):
+    """Layer means of sin(p / L) remapped to another grid stay close to that grid's layer means:
+    the tridiagonal solve of mappm.f90:175-201 is 4th-order, an order better than the PPM edges
+    of kord <= 7 (kord = 12 flattens every extremum and is left out)."""
+    pe1, pe2 = _two_grids(32, 40, 37, 3)
+    L = 25.0
+
+    def mean(pe):
+        return (-L * np.cos(pe[:, 1:] / L) + L * np.cos(pe[:, :-1] / L)) / np.diff(pe, axis=1) + 2.0
+
+    out = oracle.mappm(pe1, mean(pe1), pe2, iv=1, kord=kord, dtype=np.float64)
+    ppm = oracle.mappm(pe1, mean(pe1), pe2, iv=1, kord=1, dtype=np.float64)
+    err, err_ppm = np.abs(out - mean(pe2))[:, 3:-3].max(), np.abs(ppm - mean(pe2))[:, 3:-3].max()
+    assert err < 2e-5 and err < 0.1 * err_ppm
+
+
+def test_cs_profile_iv_minus2_is_refused():
+    pe1, pe2 = _two_grids(2, 8, 8, 0)
+    with pytest.raises(NotImplementedError):
+        oracle.mappm(pe1, np.zeros((2, 8)), pe2, iv=-2, kord=9)
+
+
 # ---- unit values of external/vcm/tests/test_cubedsphere.py ---------------------------
 def test_weighted_block_average_unit():           # :206-236  -> 3.0
     data = np.array([[2.0, 6.0], [6.0, 2.0]], np.float32)
