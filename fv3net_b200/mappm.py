@@ -37,3 +37,16 @@ def mappm(pe1, q1, pe2, i1, i2, iv, kord, ptop=0.0):
     q2 = np.zeros((n, kn), dtype=np.float32)
     q2[lo:lo + cnt] = out.cpu().numpy()
     return q2
+
+
+def interpolate_2d(xp, x, y, fill_value):
+    """`mappm.interpolate_2d(xp[m, n_out], x[m, n_in], y[m, n_in], fill_value) -> y_out[m, n_out]`
+    float64 (interpolate_2d.f90:1-29; called by vcm/interpolate.py:176-180 with
+    fill_value=np.nan).  Host arrays in, host array out, any input dtype (f2py casts to real(8))."""
+    xp, x, y = (np.ascontiguousarray(a, dtype=np.float64) for a in (xp, x, y))
+    if xp.ndim != 2 or x.ndim != 2 or y.ndim != 2:
+        raise ValueError("interpolate_2d expects 2-D arrays (rows, levels)")
+    if x.shape != y.shape or xp.shape[0] != x.shape[0]:
+        raise ValueError(f"shape mismatch: xp {xp.shape}, x {x.shape}, y {y.shape}")
+    out = ops.interpolate_2d(ops.to_device(xp), ops.to_device(x), ops.to_device(y), float(fill_value))
+    return out.cpu().numpy()

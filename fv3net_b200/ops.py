@@ -347,3 +347,23 @@ def hydrostatic_balance(dz, phis, temp, sphum, delp, toa=300.0):
                                            _p(phis_out), float(toa), n_outer, nz, h, _DT[dz.dtype],
                                            _stream()))
     return dz_out, phis_out
+
+
+def interpolate_2d(xp, x, y, fill_value=float("nan"), strides=None):
+    """interpolate_2d.f90: rows of y given at x, linearly interpolated to xp; float64 tensors
+    (m, n_out), (m, n_in), (m, n_in) -> (m, n_out).  `strides` = ((row, level) element strides of
+    xp, x, y, out) for layouts other than row-major."""
+    for t in (xp, x, y):
+        if t.dtype != torch.float64:
+            raise ValueError("interpolate_2d runs in float64 (the Fortran's real(8))")
+    m, n_out = xp.shape
+    n_in = x.shape[1]
+    if tuple(x.shape) != (m, n_in) or tuple(y.shape) != (m, n_in):
+        raise ValueError(f"shape mismatch: xp {tuple(xp.shape)}, x {tuple(x.shape)}, y {tuple(y.shape)}")
+    out = torch.empty((m, n_out), dtype=torch.float64, device=xp.device)
+    if strides is None:
+        strides = tuple(t.stride() for t in (xp, x, y, out))
+    flat = (ctypes.c_long * 8)(*[int(v) for pair in strides for v in pair])
+    L.check(L.lib().cg_interpolate_2d(_p(xp), _p(x), _p(y), _p(out), float(fill_value), m, n_in, n_out,
+                                      flat, _stream()))
+    return out

@@ -122,6 +122,16 @@ int cg_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,
              long n_outer, long n_inner, int km, int kn, const long *strides,
              int iv, int kord, void *stream);
 
+/* external/mappm/mappm/interpolate_2d.f90:1-29, the f2py module's second entry point
+ * (mappm.interpolate_2d(xp, x, y, fill_value) -> y_out, vcm/interpolate.py:176-180): for every
+ * row i, y(i, :) given at x(i, :) linearly interpolated to xp(i, :); float64; targets outside
+ * every source interval keep fill_value; the last matching interval wins, as in the Fortran.
+ * Element (i, k) of an array lives at A[i*rs + k*ls]; strides = {rs, ls} for xp, x, y, y_out
+ * (8 longs, elements). */
+int cg_interpolate_2d(const double *xp, const double *x, const double *y, double *y_out,
+                      double fill_value, long m, int n_in, int n_out, const long *strides,
+                      void *stream);
+
 /* Fused pressure-level coarse-graining (iv=1, kord=1, the only combination the
  * reference's callers use: regridz.py:168-169, budgets.py:45):
  *   regridz.py:115-147 (+ coarsen.py:183 with the masked weights)  mask_below=1

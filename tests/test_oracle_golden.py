@@ -229,3 +229,32 @@ def test_golden_pressure_level_staggered():       # regridz.py:58-112 incl. xgcm
     ev, _ = S.golden(tag, "fv_core.res", "v")
     assert np.abs(gu - eu).max() < 3e-5 * 1000
     assert np.abs(gv - ev).max() < 3e-5 * 1000
+
+
+# ---- external/vcm/tests/test_interpolate.py:109-132 (mappm.interpolate_2d) ----------------
+def test_interpolate_2d_matches_reference_test():
+    import scipy.interpolate
+
+    x = np.arange(10).reshape((1, 10))
+    y = (x ** 2).reshape((1, 10))
+    xp = np.arange(12).reshape((1, 12))
+    expected = np.zeros_like(xp, dtype=np.float64)
+    for i in range(xp.shape[0]):
+        expected[i] = scipy.interpolate.interp1d(x[i], y[i], bounds_error=False)(xp[i])
+    assert np.isnan(expected[:, -2:]).all()
+    np.testing.assert_allclose(expected, oracle.interpolate_2d(xp, x, y))
+
+
+def test_interpolate_2d_random_rows_match_scipy():
+    import scipy.interpolate
+
+    rng = np.random.RandomState(0)
+    x = np.cumsum(rng.uniform(0.1, 1, (20, 30)), axis=1)
+    y = rng.uniform(-5, 5, (20, 30))
+    xp = rng.uniform(-1, x.max() + 1, (20, 17))
+    xp[:, 3] = x[:, 7]                                       # exact hits
+    xp[:, 4] = x[:, -1]                                      # the last point is included (:23-24)
+    got = oracle.interpolate_2d(xp, x, y, fill_value=-99.0)
+    for i in range(20):
+        exp = scipy.interpolate.interp1d(x[i], y[i], bounds_error=False, fill_value=-99.0)(xp[i])
+        np.testing.assert_allclose(got[i], exp, rtol=1e-12, atol=1e-12)
