@@ -34,6 +34,15 @@
 namespace cg {
 namespace stream {
 
+#ifndef STREAM_UNROLL
+#define STREAM_UNROLL 1
+#endif
+#ifndef CG_STEP1
+#define HOT_STEP hot_step2
+#else
+#define HOT_STEP hot_step
+#endif
+constexpr int STEP_UNROLL = STREAM_UNROLL;   // steps of the walk per loop body
 constexpr int C = 8;                 // fine columns per thread (one row of a coarse cell)
 constexpr int NCELL = 4;             // coarse cells per CTA = field warps
 constexpr int NCOL = NCELL * C;      // fine columns per CTA row = lanes of the geometry warp
@@ -178,6 +187,13 @@ __device__ __forceinline__ uint32_t swz(uint32_t row, int chunk)
 __device__ __forceinline__ void sts32(uint32_t addr, float v)
 {
     asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+// acc[slot][lane] += v.  (red.shared.add.f32 compiles to a compare-and-swap loop on sm_100a: 9.2 ms against 6.7 ms.)
+__device__ __forceinline__ void red_add(uint32_t addr, float v)
+{
+    float o;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(o) : "r"(addr));
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(o + v) : "memory");
 }
 __device__ __forceinline__ void sts128(uint32_t addr, float4 v)
 {
@@ -426,8 +442,7 @@ __device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, f
 template <bool NS>
 __device__ __forceinline__ void flush(uint32_t acc_lane, int off, float tot)
 {
-    const uint32_t a = acc_lane + off;
-    sts32(a, lds32(a) + ((!NS || tot == tot) ? tot : 0.f));
+    red_add(acc_lane + off, (!NS || tot == tot) ? tot : 0.f);
 }
 __device__ __forceinline__ uint32_t ctx_u32(uint32_t sctx, int i) { return (uint32_t)ldsi32(sctx + 4 * i); }
 
@@ -619,6 +634,31 @@ __device__ __noinline__ float further_events(uint32_t oa, uint32_t ob, int info,
     return r;
 }
 
+// Both columns of pair p at step t when some column has more than one further event, or below the surface.
+// code = kk | p << 2 | buffer << 4 | t << 5 | info_a << 13 | info_b << 21.  Out of line, rare: everything the
+// events need is recomputed from the context block so that the call site stays a handful of instructions.
+template <bool NS>
+__device__ __noinline__ u64 rare_pair(uint32_t sctx, int code, u64 q, u64 x, u64 y, u64 r)
+{
+    const int kk = code & 3, p = (code >> 2) & 3, b = (code >> 4) & 1, t = (code >> 5) & 255;
+    const int info[2] = {(code >> 13) & 255, (code >> 21) & 255};
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nz = ldsi32(sctx + 4 * CTX_NZ);
+    const uint32_t acc_lane = ctx_u32(sctx, CTX_CELL0) + w * ctx_u32(sctx, CTX_CELLB) + ctx_u32(sctx, CTX_ACC) + 4 * lane;
+    const int big = t > nz ? 1024 : 0;
+    float qv[2], xv[2], yv[2], rv[2];
+    upk(q, qv[0], qv[1]); upk(x, xv[0], xv[1]); upk(y, yv[0], yv[1]); upk(r, rv[0], rv[1]);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        if (info[h] <= 1) continue;
+        const int c = 2 * p + h, xc = 8 * w + c;
+        const uint32_t oa = ctx_u32(sctx, CTX_OVA) + b * OVA_BYTES + (kk * NCOL + xc) * (MAXE * 16);
+        const uint32_t ob = ctx_u32(sctx, CTX_OVB) + b * OVB_BYTES + (kk * NCOL + xc) * (MAXE * 4);
+        rv[h] = further_events<NS>(oa, ob, info[h] + big, qv[h], xv[h], yv[h], rv[h], acc_lane, sctx, t, kk | c << 4 | b << 8);
+    }
+    return pk(rv[0], rv[1]);
+}
+
 // One step of the tandem walk for the 8 columns of a row: level t arrives, layer t-2 is finished.
 // Interior levels: two columns per arithmetic instruction; the min/max parts run on the halves; further events of a
 // layer out of line behind warp-uniform branches.  The work of a column pair is split into a front half
@@ -719,19 +759,33 @@ __device__ __forceinline__ void pair_back(const PairFront &o, const PairRec &r, 
     u64 rs = o.rs;
     const u64 qB = s.B[p];
     if ((oi.z | oi.w) > 1) {                                            // layers cut by several coarse interfaces
-        float qa, qb, ra, rb_, xa, xb, ya, yb;
-        upk(qB, qa, qb); upk(rs, ra, rb_); upk(o.xl, xa, xb); upk(o.yl, ya, yb);
         const uint32_t oa = ova + (2 * p) * (MAXE * 16), ob = ovb + (2 * p) * (MAXE * 4);
-        // (t > nz: the layer below the surface, whose further events sit in the tail list: info beyond MAXE + 1 routes there)
-        const int big = t > nz ? 1024 : 0;
-        if (oi.z > 1) ra = further_events<NS>(oa, ob, oi.z + big, qa, xa, ya, ra, acc_lane, sctx, t, kk | (2 * p) << 4 | b << 8);
-        if (oi.w > 1)
-            rb_ = further_events<NS>(oa + MAXE * 16, ob + MAXE * 4, oi.w + big, qb, xb, yb, rb_, acc_lane, sctx, t,
-                                     kk | (2 * p + 1) << 4 | b << 8);
-        rs = pk(ra, rb_);
+        if (max(oi.z, oi.w) == 2 && t <= nz) {
+            // at most one further event per column (a sixth of the layers): in line
+            float qa, qb, ra, rb_, xa, xb, ya, yb;
+            upk(qB, qa, qb); upk(rs, ra, rb_); upk(o.xl, xa, xb); upk(o.yl, ya, yb);
+            if (oi.z == 2) {
+                const float4 ev = lds128(oa);
+                const float I = ev.x * qa + ev.y * xa + ev.z * ya;
+                flush<NS>(acc_lane, ldsi32(ob), ra + I);
+                ra = ev.w * I;                                              // stored negated
+            }
+            if (oi.w == 2) {
+                const float4 ev = lds128(oa + MAXE * 16);
+                const float I = ev.x * qb + ev.y * xb + ev.z * yb;
+                flush<NS>(acc_lane, ldsi32(ob + MAXE * 4), rb_ + I);
+                rb_ = ev.w * I;
+            }
+            rs = pk(ra, rb_);
+        } else {
+            // more of them, or the layer below the surface: one compact call per pair
+            rs = rare_pair<NS>(sctx, kk | p << 2 | b << 4 | t << 5 | oi.z << 13 | oi.w << 21, qB, o.xl, o.yl, rs);
+        }
     }
     s.run[p] = fma2(r.DPW, qB, rs);
+#ifndef CG_EXP_NOCHK
     if (!NS) s.chk = fma2(qn, 0ull, s.chk);
+#endif
     s.B[p] = s.A[p]; s.A[p] = qn; s.dq[p] = o.dqn; s.dc[p] = o.dcn; s.xp[p] = o.xn;
 }
 
@@ -741,7 +795,12 @@ __device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t o
 {
     u64 q[4];
     load_row(q, stage, kk, w, f, any_derived);
-    if (t >= nz) {                      // below the last level (t = nz + 1, nz + 2): q(nz - 1) again; the records' zero
+#ifndef CG_EXP_NOSEL
+    if (t >= nz)
+#else
+    if (t >= 1000)
+#endif
+    {                                   // below the last level (t = nz + 1, nz + 2): q(nz - 1) again; the records' zero
 #pragma unroll                          // stencils then give y = delq, x = y = dc = 0 as mappm.f90:729-747, :115-120 want
         for (int p = 0; p < 4; ++p) q[p] = s.A[p];
     }
@@ -760,6 +819,93 @@ __device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t o
     pair_front<NS>(f1, r3, s, 3, q[3]);
     pair_back<NS>(f0, r2, s, 2, q[2], acc_lane, ova, ovb, sctx, t, nz, kk, b);
     pair_back<NS>(f1, r3, s, 3, q[3], acc_lane, ova, ovb, sctx, t, nz, kk, b);
+}
+
+// The same step as one straight-line block: fronts and accumulator updates of the four pairs without a branch
+// (two columns closing the same level are added one after the other), then the further events of all pairs behind
+// ONE warp-uniform branch, then the running sums.  Branches end scheduling regions: this leaves the compiler one long
+// region to interleave the four dependency chains in.
+template <bool NS>
+__device__ __forceinline__ void close_levels(const PairFront &o, const int4 &oi, uint32_t acc_lane)
+{
+    float tota, totb;
+    upk(o.tot, tota, totb);
+    if (NS) {
+        tota = tota == tota ? tota : 0.f;
+        totb = totb == totb ? totb : 0.f;
+    }
+    const uint32_t aa = acc_lane + oi.x, ab = acc_lane + oi.y;
+    red_add(aa, tota);
+    red_add(ab, totb);
+}
+template <bool NS>
+__device__ __forceinline__ u64 pair_extras(const PairFront &o, const int4 &oi, u64 qB, int p, uint32_t acc_lane, uint32_t ova,
+                                           uint32_t ovb, uint32_t sctx, int t, int nz, int kk, int b)
+{
+    u64 rs = o.rs;
+    if ((oi.z | oi.w) > 1) {
+        const uint32_t oa = ova + (2 * p) * (MAXE * 16), ob = ovb + (2 * p) * (MAXE * 4);
+        if (max(oi.z, oi.w) == 2 && t <= nz) {
+            float qa, qb, ra, rb_, xa, xb, ya, yb;
+            upk(qB, qa, qb); upk(rs, ra, rb_); upk(o.xl, xa, xb); upk(o.yl, ya, yb);
+            if (oi.z == 2) {
+                const float4 ev = lds128(oa);
+                const float I = ev.x * qa + ev.y * xa + ev.z * ya;
+                flush<NS>(acc_lane, ldsi32(ob), ra + I);
+                ra = ev.w * I;                                              // stored negated
+            }
+            if (oi.w == 2) {
+                const float4 ev = lds128(oa + MAXE * 16);
+                const float I = ev.x * qb + ev.y * xb + ev.z * yb;
+                flush<NS>(acc_lane, ldsi32(ob + MAXE * 4), rb_ + I);
+                rb_ = ev.w * I;
+            }
+            rs = pk(ra, rb_);
+        } else {
+            rs = rare_pair<NS>(sctx, kk | p << 2 | b << 4 | t << 5 | oi.z << 13 | oi.w << 21, qB, o.xl, o.yl, rs);
+        }
+    }
+    return rs;
+}
+template <bool NS>
+__device__ __forceinline__ void hot_step2(uint32_t sctx, uint32_t rec, uint32_t ova, uint32_t ovb, uint32_t stage, int t, int nz, int kk, int b,
+                                          int w, const Field &f, int any_derived, State &s, uint32_t acc_lane)
+{
+    u64 q[4];
+    load_row(q, stage, kk, w, f, any_derived);
+    if (t >= nz) {
+#pragma unroll
+        for (int p = 0; p < 4; ++p) q[p] = s.A[p];
+    }
+    PairRec r0, r1, r2, r3;
+    PairFront f0, f1, f2, f3;
+    load_pair_rec(r0, rec);
+    load_pair_rec(r1, rec + REC_BLOCK);
+    pair_front<NS>(f0, r0, s, 0, q[0]);
+    pair_front<NS>(f1, r1, s, 1, q[1]);
+    load_pair_rec(r2, rec + 2 * REC_BLOCK);
+    load_pair_rec(r3, rec + 3 * REC_BLOCK);
+    close_levels<NS>(f0, r0.oi, acc_lane);
+    close_levels<NS>(f1, r1.oi, acc_lane);
+    pair_front<NS>(f2, r2, s, 2, q[2]);
+    pair_front<NS>(f3, r3, s, 3, q[3]);
+    close_levels<NS>(f2, r2.oi, acc_lane);
+    close_levels<NS>(f3, r3.oi, acc_lane);
+    u64 rs0 = f0.rs, rs1 = f1.rs, rs2 = f2.rs, rs3 = f3.rs;
+    if ((r0.oi.z | r0.oi.w | r1.oi.z | r1.oi.w | r2.oi.z | r2.oi.w | r3.oi.z | r3.oi.w) > 1) {
+        rs0 = pair_extras<NS>(f0, r0.oi, s.B[0], 0, acc_lane, ova, ovb, sctx, t, nz, kk, b);
+        rs1 = pair_extras<NS>(f1, r1.oi, s.B[1], 1, acc_lane, ova, ovb, sctx, t, nz, kk, b);
+        rs2 = pair_extras<NS>(f2, r2.oi, s.B[2], 2, acc_lane, ova, ovb, sctx, t, nz, kk, b);
+        rs3 = pair_extras<NS>(f3, r3.oi, s.B[3], 3, acc_lane, ova, ovb, sctx, t, nz, kk, b);
+    }
+    s.run[0] = fma2(r0.DPW, s.B[0], rs0);   s.run[1] = fma2(r1.DPW, s.B[1], rs1);
+    s.run[2] = fma2(r2.DPW, s.B[2], rs2);   s.run[3] = fma2(r3.DPW, s.B[3], rs3);
+    const PairFront *fr[4] = {&f0, &f1, &f2, &f3};
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        if (!NS) s.chk = fma2(q[p], 0ull, s.chk);
+        s.B[p] = s.A[p]; s.A[p] = q[p]; s.dq[p] = fr[p]->dqn; s.dc[p] = fr[p]->dcn; s.xp[p] = fr[p]->xn;
+    }
 }
 
 // The same step at the ends of the column: column by column through end_column
@@ -975,12 +1121,16 @@ plevel_stream_kernel(const __grid_constant__ Params p)
             mbar_wait(gfull + 8 * b, (it >> 1) & 1);
             mbar_wait(bars + 8 * b, (it >> 1) & 1);
             const uint32_t stage = ring_r + b * stage_bytes_r;
-#pragma unroll 1
+#pragma unroll STEP_UNROLL
             for (int kk = 0; kk < KC; ++kk) {
                 const int t = t0 + kk;
                 if (t > nz_r + 2) break;
+#ifdef CG_EXP_NOEND
+                if (true)
+#else
                 if (t != 2 && t != nz_r)       // (t = 0, 1: all-zero records, nothing is finished)
-                    hot_step<NS>(sctx, rec_w + b * REC_BYTES + kk * ((NCOL / 2) * REC_BLOCK), ova_w + b * OVA_BYTES + kk * (NCOL * MAXE * 16),
+#endif
+                    HOT_STEP<NS>(sctx, rec_w + b * REC_BYTES + kk * ((NCOL / 2) * REC_BLOCK), ova_w + b * OVA_BYTES + kk * (NCOL * MAXE * 16),
                              ovb_w + b * OVB_BYTES + kk * (NCOL * MAXE * 4), stage, t, nz_r, kk, b, w, fld, any_derived, st, acc_lane);
                 else
                     end_step<NS>(sctx, stage, t, kk, b, w, nz_r, fld, any_derived, st);
