@@ -54,19 +54,32 @@ block_reduce_kernel(const T *__restrict__ in, T *__restrict__ out, long n_outer,
 }
 
 // coarsen.py:843-897: out[y,x] = in[min(y/fy, nyc-1), min(x/fx, nxc-1)]
+// Write-bound: a warp owns an output row (8 rows per block), a lane four consecutive x written as one 16-B
+// store where the row base is aligned; the coarse row it repeats stays in L1.  No 64-bit index arithmetic
+// per element.
 template <typename T>
 __global__ void __launch_bounds__(256)
-upsample_kernel(const T *__restrict__ in, T *__restrict__ out, long n_outer, int nyc, int nxc,
-                int fy, int fx, int ny, int nx)
+upsample_kernel(const T *__restrict__ in, T *__restrict__ out, long n_rows, int nyc, int nxc,
+                int fy, int fx, int ny, int nx, int vec_ok)
 {
-    const long total = n_outer * (long)ny * nx;
-    for (long idx = blockIdx.x * (long)blockDim.x + threadIdx.x; idx < total;
-         idx += (long)gridDim.x * blockDim.x) {
-        const int x = (int)(idx % nx);
-        const int y = (int)((idx / nx) % ny);
-        const long o = idx / ((long)nx * ny);
-        const int J = min(y / fy, nyc - 1), I = min(x / fx, nxc - 1);
-        out[idx] = in[o * (long)nyc * nxc + (long)J * nxc + I];
+    constexpr int V = 16 / sizeof(T);
+    struct alignas(16) Vec { T v[V]; };
+    const int lane = threadIdx.x & 31;
+    for (long row = (long)blockIdx.x * 8 + (threadIdx.x >> 5); row < n_rows; row += (long)gridDim.x * 8) {
+        const long o = row / ny;
+        const int y = (int)(row - o * ny);
+        const T *src = in + (o * nyc + min(y / fy, nyc - 1)) * (long)nxc;
+        T *dst = out + row * nx;
+        if (vec_ok) {
+            for (int x0 = V * lane; x0 < nx; x0 += V * 32) {
+                Vec r;
+#pragma unroll
+                for (int j = 0; j < V; ++j) r.v[j] = src[min((x0 + j) / fx, nxc - 1)];
+                *reinterpret_cast<Vec *>(dst + x0) = r;
+            }
+        } else {
+            for (int x = lane; x < nx; x += 32) dst[x] = src[min(x / fx, nxc - 1)];
+        }
     }
 }
 
@@ -204,9 +217,13 @@ extern "C" int cg_block_upsample(const void *in, void *out, long n_outer, int ny
     const long total = n_outer * (long)ny * nx;
     if (total == 0) return CG_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    const unsigned g = grid_for(total, 256);
-    if (dtype == CG_F32) upsample_kernel<float><<<g, 256, 0, st>>>((const float *)in, (float *)out, n_outer, nyc, nxc, fy, fx, ny, nx);
-    else upsample_kernel<double><<<g, 256, 0, st>>>((const double *)in, (double *)out, n_outer, nyc, nxc, fy, fx, ny, nx);
+    const long n_rows = n_outer * ny;
+    const long blocks = (n_rows + 7) / 8;
+    const unsigned g = (unsigned)(blocks < 0x7fffffffL ? blocks : 0x7fffffffL);
+    const int per16 = dtype == CG_F32 ? 4 : 2;
+    const int vec_ok = nx % per16 == 0 && ((uintptr_t)out & 15) == 0;
+    if (dtype == CG_F32) upsample_kernel<float><<<g, 256, 0, st>>>((const float *)in, (float *)out, n_rows, nyc, nxc, fy, fx, ny, nx, vec_ok);
+    else upsample_kernel<double><<<g, 256, 0, st>>>((const double *)in, (double *)out, n_rows, nyc, nxc, fy, fx, ny, nx, vec_ok);
     CG_LAUNCH_CHECK("cg_block_upsample");
     return CG_OK;
 }

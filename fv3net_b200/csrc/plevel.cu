@@ -85,6 +85,62 @@ exposed_area_kernel(const float *__restrict__ pe_c, const float *__restrict__ de
     }
 }
 
+// The same in one pass without temporaries: a warp owns a coarse cell.  Lanes over the cell's f x f fine
+// columns sum delp top-down into the fine surface pressures (every fine value read once, whole 32-B sectors);
+// lanes over levels then form the coarse log-midpoint pressures from the sequential cumsum of delp_coarse and
+// add the areas of the exposed columns in the order of the loop above (y, then x), so both kernels agree bitwise.
+constexpr int EXPOSED_WARPS = 8;
+__global__ void __launch_bounds__(32 * EXPOSED_WARPS)
+exposed_area_fused_kernel(const float *__restrict__ delp, const float *__restrict__ delp_c,
+                          const float *__restrict__ area, float *__restrict__ out, long n_outer, int nz,
+                          int ny, int nx, int f, float toa)
+{
+    extern __shared__ float sm_exposed[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nyc = ny / f, nxc = nx / f, ncol = f * f;
+    const long hc = (long)nyc * nxc, h = (long)ny * nx;
+    float *ps = sm_exposed + warp * (2 * ncol + nz + 1), *ar = ps + ncol, *pe = ar + ncol;
+    const long cells = n_outer * hc;
+    for (long cell = (long)blockIdx.x * EXPOSED_WARPS + warp; cell < cells; cell += (long)gridDim.x * EXPOSED_WARPS) {
+        const long o = cell / hc, ic = cell - o * hc;
+        const int J = (int)(ic / nxc), I = (int)(ic - (long)J * nxc);
+        const float *d0 = delp + o * nz * h + (long)(J * f) * nx + I * f;
+        for (int c0 = 0; c0 < ncol; c0 += 64) {                       // two columns per lane and sweep
+            const int ca = c0 + lane, cb = c0 + 32 + lane;
+            const bool va = ca < ncol, vb = cb < ncol;
+            const long ia = va ? (long)(ca / f) * nx + ca % f : 0, ib = vb ? (long)(cb / f) * nx + cb % f : 0;
+            float sa = 0.f, sb = 0.f;
+#pragma unroll 4
+            for (int k = 0; k < nz; ++k) {
+                const float a = ldg_stream(d0 + (long)k * h + ia), b = ldg_stream(d0 + (long)k * h + ib);
+                sa += (a == a) ? a : 0.f;
+                sb += (b == b) ? b : 0.f;
+            }
+            if (va) { ps[ca] = sa + toa; ar[ca] = area[o * h + (long)(J * f) * nx + I * f + ia]; }
+            if (vb) { ps[cb] = sb + toa; ar[cb] = area[o * h + (long)(J * f) * nx + I * f + ib]; }
+        }
+        for (int k = lane; k < nz; k += 32) pe[k + 1] = delp_c[(o * nz + k) * hc + ic];
+        __syncwarp();
+        if (lane == 0) {                                              // vertically_dependent.py:61-63, same order of additions
+            float acc = toa;
+            pe[0] = acc;
+            for (int k = 0; k < nz; ++k) { acc = acc + pe[k + 1]; pe[k + 1] = acc; }
+        }
+        __syncwarp();
+        for (int k = lane; k < nz; k += 32) {
+            const float p0 = pe[k], p1 = pe[k + 1];
+            const float pmid = delp_c[(o * nz + k) * hc + ic] / (logf(p1) - logf(p0));
+            float acc = 0.f;
+            for (int c = 0; c < ncol; ++c) {
+                const float a = (pmid <= ps[c]) ? ar[c] : 0.f;
+                acc += (a == a) ? a : 0.f;
+            }
+            out[(o * nz + k) * hc + ic] = acc;
+        }
+        __syncwarp();
+    }
+}
+
 __global__ void __launch_bounds__(256)
 surface_pressure_kernel(const float *__restrict__ delp, float *__restrict__ ps, float toa,
                         long n_outer, int nz, long h)
@@ -267,6 +323,15 @@ extern "C" int cg_area_above_fine_surface(const float *delp, const float *delp_c
     if (n_outer == 0) return CG_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const long h = (long)ny * nx, hc = (long)(ny / f) * (nx / f);
+    const size_t smem = (size_t)EXPOSED_WARPS * (2 * f * f + nz + 1) * sizeof(float);
+    if (smem <= 48 * 1024) {
+        const long blocks = (n_outer * hc + EXPOSED_WARPS - 1) / EXPOSED_WARPS;
+        exposed_area_fused_kernel<<<(unsigned)(blocks < 0x7fffffffL ? blocks : 0x7fffffffL), 32 * EXPOSED_WARPS, smem, st>>>(
+            delp, delp_coarse, area, out, n_outer, nz, ny, nx, f, (float)toa);
+        CG_LAUNCH_CHECK("cg_area_above_fine_surface");
+        return CG_OK;
+    }
+    // very large blocks or columns: the three-kernel form with temporaries
     float *ps = nullptr, *pe_c = nullptr;
     cudaError_t e = cudaMallocAsync((void **)&ps, 4 * n_outer * h, st);
     if (e != cudaSuccess) return cuda_fail(e, "cudaMallocAsync(ps)");
