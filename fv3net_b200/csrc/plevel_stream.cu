@@ -37,11 +37,6 @@ namespace stream {
 #ifndef STREAM_UNROLL
 #define STREAM_UNROLL 1
 #endif
-#ifndef CG_STEP1
-#define HOT_STEP hot_step2
-#else
-#define HOT_STEP hot_step
-#endif
 constexpr int STEP_UNROLL = STREAM_UNROLL;   // steps of the walk per loop body
 constexpr int C = 8;                 // fine columns per thread (one row of a coarse cell)
 constexpr int NCELL = 4;             // coarse cells per CTA = field warps
@@ -367,10 +362,14 @@ __device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, f
         const float Pq = d2 * (5.f * d1 + d2) - 3.f * d1 * d1;
         const float Rr = d1 * d2 * (d2 + 3.f * d1);
         const float r12 = 1.f / (d1 + d2);
-        const uint32_t e = edge + 4 * (x * EDGE_WORDS + (top ? 0 : 12));
-        sts128(e, make_float4(d2 * r12, d1 * r12, 2.f * r12, (top ? 4.f : 1.f) / D));
-        sts128(e + 16, make_float4(d2, (top ? 0.5f : 2.f) * Pq, (top ? 0.25f : 1.f) * Rr, (top ? 2.f : 8.f) * d1 * d1 * d1));
-        sts32(e + 32, d1);
+        // pair-interleaved like the records: word i of column x sits at pair base + 8 i + 4 (x & 1)
+        const uint32_t e = edge + 4 * ((x >> 1) * (2 * EDGE_WORDS) + (x & 1)) + 8 * (top ? 0 : 12);
+        sts32(e, d2 * r12);             sts32(e + 8, d1 * r12);             sts32(e + 16, 2.f * r12);
+        sts32(e + 24, (top ? 4.f : 1.f) / D);
+        sts32(e + 32, d2);              sts32(e + 40, (top ? 0.5f : 2.f) * Pq);
+        sts32(e + 48, (top ? 0.25f : 1.f) * Rr);
+        sts32(e + 56, (top ? 2.f : 8.f) * d1 * d1 * d1);
+        sts32(e + 64, d1);
     }
     // events of layer L = t - 2: the coarse interfaces in (top, bottom] of the layer, by the two-pointer merge
     // (mappm.f90:70-75 keeps k0 the same way); L == nz is everything below the surface
@@ -504,83 +503,6 @@ __device__ __forceinline__ float limited_slope(float df2, float dq_lo, float dq_
     return max3(min3(df2, hi3, -nlo), -hi3, nlo);
 }
 
-// One column at one of the end steps of the walk (t < 3: nothing to finish yet / one-sided cubic at the top,
-// mappm.f90:689-707; t >= nz: one-sided cubic at the bottom, :729-747, and the layer below the surface).
-// State of the column: A = q(t-1), B = q(t-2), dq1 = delq(t-1), dcp = dc(t-2), xp = AL(t-2) - q(t-2), run.
-// Returns (delq(t), dc(t-1), AL(t-1) - q(t-1), run).  Out of line: 6 of nz + 3 steps.
-template <bool NS>
-__device__ __noinline__ float4 end_column(uint32_t sctx, int t, int kcb, float qn, float q3, float A, float B, float dq1,
-                                          float dcp, float xp, float run)
-{
-    const int kk = kcb & 15, c = (kcb >> 4) & 15, b = kcb >> 8;
-    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int nz = ldsi32(sctx + 4 * CTX_NZ);
-    const uint32_t rec = ctx_u32(sctx, CTX_REC) + b * REC_BYTES;
-    const uint32_t rb = rec + (kk * (NCOL / 2) + 4 * w + (c >> 1)) * REC_BLOCK + 4 * (c & 1);
-    const float E1 = lds32(rb), E2 = lds32(rb + 8), Fm = lds32(rb + 16), G = lds32(rb + 24), nH = lds32(rb + 32);
-    float dqn = qn - A;                                                     // delq(t)
-    const float df2 = E1 * dqn + E2 * dq1;                                  // layer t-1, mappm.f90:661
-    float dcn = limited_slope(df2, dq1, dqn);                               // dc(t-1)
-    float xn = Fm * dq1 + G * dcp + nH * dcn;                               // AL(t-1) - q(t-1), :674-683
-    float x = xp, y = xn + dq1, dc = dcp;                                   // layer t-2
-    const uint32_t edge = ctx_u32(sctx, CTX_EDGE) + 4 * ((8 * w + c) * EDGE_WORDS);
-    if (t == 2) {
-        // level 3 is visible (same stage): AL of layer 2 from the record of step 3, then the cubic through
-        // the top two layers and that edge
-        const uint32_t r3 = rec + (3 * (NCOL / 2) + 4 * w + (c >> 1)) * REC_BLOCK + 4 * (c & 1);
-        const float e1 = lds32(r3), e2 = lds32(r3 + 8), fm = lds32(r3 + 16), gg = lds32(r3 + 24), nh = lds32(r3 + 32);
-        const float dq3 = q3 - qn;
-        const float dc2 = limited_slope(e1 * dq3 + e2 * dqn, dqn, dq3);
-        const float al2 = qn + (fm * dqn + gg * dcn + nh * dc2);
-        const float4 ea = lds128(edge), eb = lds128(edge + 16);
-        const float sd1 = lds32(edge + 32);
-        const float q0 = B, q1 = A;
-        const float qm = ea.x * q0 + ea.y * q1, dq = ea.z * (q1 - q0);
-        const float c1 = (al2 - qm - eb.x * dq) * ea.w;
-        const float c3 = dq - c1 * eb.y;
-        const float inner = qm - c1 * eb.z;
-        const float top = c1 * eb.w - c3 * sd1 + inner;
-        const float al1 = fminf(fmaxf(inner, fminf(q0, q1)), fmaxf(q0, q1));
-        x = top - q0; y = al1 - q0; dc = 0.5f * (al1 - q0); xn = al1 - q1;
-    } else if (t == nz) {
-        const float4 ea = lds128(edge + 48), eb = lds128(edge + 64);
-        const float sd1 = lds32(edge + 80);
-        const float qe = A, qi = B;
-        const float ali = qi + xp;
-        const float qm = ea.x * qe + ea.y * qi, dq = ea.z * (qi - qe);
-        const float c1 = (ali - qm - eb.x * dq) * ea.w;
-        const float c3 = dq - c1 * eb.y;
-        const float inner = qm - c1 * eb.z;
-        const float bot = c1 * eb.w - c3 * sd1 + inner;
-        const float alb = fminf(fmaxf(inner, fminf(qe, qi)), fmaxf(qe, qi));
-        y = alb - qi; xn = alb - qe; dcn = 0.5f * (qe - alb); dqn = bot - qe;   // layer nz-1 is finished next step
-    } else if (t == nz + 1) {
-        y = dq1;
-    } else if (t > nz + 1) {                                                // below the surface
-        x = 0.f; y = 0.f; dc = 0.f;
-    }
-    // limited parabola of layer t-2 in deviation form, x = AL - q, y = AR - q, A6 = -3 (x + y)
-    // (ppm_limiters lmt = 0, mappm.f90:875-894), then the events of the layer and its whole-layer term
-    const float q = B;
-    const float da1 = y - x, s = x + y;
-    const float tt = s * da1, da2 = da1 * (da1 * (1.f / 3.f));
-    const float m2x = -2.f * x, m2y = -2.f * y;
-    const bool k1 = tt > da2, k2 = -tt > da2, flat = dc == 0.f;            // k1 and k2 exclude each other (da2 >= 0)
-    y = k1 ? m2x : y;                  // a6da < -da2: AR = AL - 3 (AL - q)
-    x = k2 ? m2y : x;                  // a6da >  da2: AL = AR - 3 (AR - q)
-    x = flat ? 0.f : x;
-    y = flat ? 0.f : y;
-    const float ex = lds32(rb + 48), ey = lds32(rb + 56), ez = lds32(rb + 64), nw = lds32(rb + 72), dpw = lds32(rb + 40);
-    const int off = ldsi32(rb + 80), info = ldsi32(rb + 88);
-    const uint32_t acc_lane = ctx_u32(sctx, CTX_CELL0) + w * ctx_u32(sctx, CTX_CELLB) + ctx_u32(sctx, CTX_ACC) + 4 * lane;
-    const float I = ex * q + ey * x + ez * y;
-    flush<NS>(acc_lane, off, run + I);
-    float rs = (NS && info == 0) ? run : nw * I;                            // -w is what the record holds
-    if (info > 1) rs = apply_extras<NS>(sctx, t, kcb, info, q, x, y, rs);
-    run = fmaf(dpw, q, rs);
-    return make_float4(dqn, dcn, xn, run);
-}
-
 // the per-lane description of a field: parents' boxes and q = (a - c1 b) (c2 b + c3)
 struct Field {
     int fa, fb;
@@ -660,11 +582,7 @@ __device__ __noinline__ u64 rare_pair(uint32_t sctx, int code, u64 q, u64 x, u64
 }
 
 // One step of the tandem walk for the 8 columns of a row: level t arrives, layer t-2 is finished.
-// Interior levels: two columns per arithmetic instruction; the min/max parts run on the halves; further events of a
-// layer out of line behind warp-uniform branches.  The work of a column pair is split into a front half
-// (pure arithmetic on the record and the rolling state) and a back half (accumulator update, further events,
-// state rotation); the fronts of two pairs are written next to each other so that the compiler can interleave
-// their dependency chains (the branches of the back halves end basic blocks).
+// Interior levels: two columns per arithmetic instruction; the min/max parts run on the halves.
 struct PairRec {
     u64 E1, E2, Fm, G, NH, DPW, EX, EY, EZ, NW;
     int4 oi;
@@ -736,89 +654,111 @@ __device__ __forceinline__ void pair_front(PairFront &o, const PairRec &r, const
     o.dqn = dqn; o.dcn = dcn; o.xn = xn;
 }
 
-template <bool NS>
-__device__ __forceinline__ void pair_back(const PairFront &o, const PairRec &r, State &s, int p, u64 qn, uint32_t acc_lane,
-                                          uint32_t ova, uint32_t ovb, uint32_t sctx, int t, int nz, int kk, int b)
+// Both columns of pair p at one of the end steps of the walk (t < 3: nothing to finish yet / one-sided cubic at the
+// top, mappm.f90:689-707; t >= nz: one-sided cubic at the bottom, :729-747, and the layer below the surface), packed
+// like the hot step.  State of the pair: A = q(t-1), B = q(t-2), dq1 = delq(t-1), dcp = dc(t-2), xp = AL(t-2) - q(t-2),
+// run.  Returns (delq(t), dc(t-1), AL(t-1) - q(t-1), run).  Out of line: 3 of nz + 3 steps.
+struct EndOut { u64 dq, dc, x, run; };
+__device__ __forceinline__ u64 clamp2(u64 v, u64 a, u64 b)            // v between a and b, per half
 {
-    // close the levels (NaN-skipping block sum, coarsen.py:211); both loads before the stores
-    const int4 oi = r.oi;
-    const uint32_t aa = acc_lane + oi.x, ab = acc_lane + oi.y;
-    const float va = lds32(aa), vb = lds32(ab);
-    float tota, totb;
-    upk(o.tot, tota, totb);
-    if (NS) {
-        tota = tota == tota ? tota : 0.f;
-        totb = totb == totb ? totb : 0.f;
-    }
-    if (oi.x == oi.y) {                                                 // warp-uniform
-        sts32(aa, va + (tota + totb));
-    } else {
-        sts32(aa, va + tota);
-        sts32(ab, vb + totb);
-    }
-    u64 rs = o.rs;
-    const u64 qB = s.B[p];
-    if ((oi.z | oi.w) > 1) {                                            // layers cut by several coarse interfaces
-        const uint32_t oa = ova + (2 * p) * (MAXE * 16), ob = ovb + (2 * p) * (MAXE * 4);
-        if (max(oi.z, oi.w) == 2 && t <= nz) {
-            // at most one further event per column (a sixth of the layers): in line
-            float qa, qb, ra, rb_, xa, xb, ya, yb;
-            upk(qB, qa, qb); upk(rs, ra, rb_); upk(o.xl, xa, xb); upk(o.yl, ya, yb);
-            if (oi.z == 2) {
-                const float4 ev = lds128(oa);
-                const float I = ev.x * qa + ev.y * xa + ev.z * ya;
-                flush<NS>(acc_lane, ldsi32(ob), ra + I);
-                ra = ev.w * I;                                              // stored negated
-            }
-            if (oi.w == 2) {
-                const float4 ev = lds128(oa + MAXE * 16);
-                const float I = ev.x * qb + ev.y * xb + ev.z * yb;
-                flush<NS>(acc_lane, ldsi32(ob + MAXE * 4), rb_ + I);
-                rb_ = ev.w * I;
-            }
-            rs = pk(ra, rb_);
-        } else {
-            // more of them, or the layer below the surface: one compact call per pair
-            rs = rare_pair<NS>(sctx, kk | p << 2 | b << 4 | t << 5 | oi.z << 13 | oi.w << 21, qB, o.xl, o.yl, rs);
-        }
-    }
-    s.run[p] = fma2(r.DPW, qB, rs);
-#ifndef CG_EXP_NOCHK
-    if (!NS) s.chk = fma2(qn, 0ull, s.chk);
-#endif
-    s.B[p] = s.A[p]; s.A[p] = qn; s.dq[p] = o.dqn; s.dc[p] = o.dcn; s.xp[p] = o.xn;
+    float va, vb, aa, ab, ba, bb;
+    upk(v, va, vb); upk(a, aa, ab); upk(b, ba, bb);
+    return pk(fminf(fmaxf(va, fminf(aa, ba)), fmaxf(aa, ba)), fminf(fmaxf(vb, fminf(ab, bb)), fmaxf(ab, bb)));
 }
-
-template <bool NS>
-__device__ __forceinline__ void hot_step(uint32_t sctx, uint32_t rec, uint32_t ova, uint32_t ovb, uint32_t stage, int t, int nz, int kk, int b,
-                                         int w, const Field &f, int any_derived, State &s, uint32_t acc_lane)
+__device__ __forceinline__ u64 slope2(u64 df2, u64 dlo, u64 dhi)
 {
-    u64 q[4];
-    load_row(q, stage, kk, w, f, any_derived);
-#ifndef CG_EXP_NOSEL
-    if (t >= nz)
-#else
-    if (t >= 1000)
-#endif
-    {                                   // below the last level (t = nz + 1, nz + 2): q(nz - 1) again; the records' zero
-#pragma unroll                          // stencils then give y = delq, x = y = dc = 0 as mappm.f90:729-747, :115-120 want
-        for (int p = 0; p < 4; ++p) q[p] = s.A[p];
+    float fa, fb, la, lb, ha, hb;
+    upk(df2, fa, fb); upk(dlo, la, lb); upk(dhi, ha, hb);
+    return pk(limited_slope(fa, la, ha), limited_slope(fb, lb, hb));
+}
+template <bool NS>
+__device__ __noinline__ EndOut end_pair(uint32_t sctx, int t, int kpb, u64 qn, u64 q3, u64 A, u64 B, u64 dq1, u64 dcp, u64 xp,
+                                        u64 run)
+{
+    const int kk = kpb & 15, p = (kpb >> 4) & 3, b = kpb >> 8;
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nz = ldsi32(sctx + 4 * CTX_NZ);
+    const uint32_t rec = ctx_u32(sctx, CTX_REC) + b * REC_BYTES;
+    PairRec r;
+    load_pair_rec(r, rec + (kk * (NCOL / 2) + 4 * w + p) * REC_BLOCK);
+    const u64 half = pk(0.5f, 0.5f);
+    u64 dqn = sub2(qn, A);                                                  // delq(t)
+    const u64 df2 = fma2(r.E1, dqn, mul2(r.E2, dq1));                       // layer t-1, mappm.f90:661
+    u64 dcn = slope2(df2, dq1, dqn);                                        // dc(t-1)
+    u64 xn = fma2(r.NH, dcn, fma2(r.G, dcp, mul2(r.Fm, dq1)));              // AL(t-1) - q(t-1), :674-683
+    u64 x = xp, y = add2(xn, dq1), dc = dcp;                                // layer t-2
+    const uint32_t edge = ctx_u32(sctx, CTX_EDGE) + 4 * ((4 * w + p) * (2 * EDGE_WORDS));
+    if (t == 2) {
+        // level 3 is visible (same stage): AL of layer 2 from the record of step 3, then the cubic through
+        // the top two layers and that edge
+        const uint32_t r3 = rec + (3 * (NCOL / 2) + 4 * w + p) * REC_BLOCK;
+        u64 e1, e2, fm, gg, nh, unused;
+        lds2x64(r3, e1, e2); lds2x64(r3 + 16, fm, gg); lds2x64(r3 + 32, nh, unused);
+        const u64 dq3 = sub2(q3, qn);
+        const u64 dc2 = slope2(fma2(e1, dq3, mul2(e2, dqn)), dqn, dq3);
+        const u64 al2 = add2(qn, fma2(nh, dc2, fma2(gg, dcn, mul2(fm, dqn))));
+        u64 c0, c1_, c2, c3_, c4, c5, c6, c7, c8, pad;
+        lds2x64(edge, c0, c1_); lds2x64(edge + 16, c2, c3_); lds2x64(edge + 32, c4, c5); lds2x64(edge + 48, c6, c7);
+        lds2x64(edge + 64, c8, pad);
+        const u64 q0 = B, q1 = A;
+        const u64 qm = fma2(c0, q0, mul2(c1_, q1)), dq = mul2(c2, sub2(q1, q0));
+        const u64 cc = mul2(sub2(sub2(al2, qm), mul2(c4, dq)), c3_);
+        const u64 c3 = sub2(dq, mul2(cc, c5));
+        const u64 inner = sub2(qm, mul2(cc, c6));
+        const u64 top = add2(sub2(mul2(cc, c7), mul2(c3, c8)), inner);
+        const u64 al1 = clamp2(inner, q0, q1);
+        x = sub2(top, q0); y = sub2(al1, q0); dc = mul2(half, sub2(al1, q0)); xn = sub2(al1, q1);
+    } else if (t == nz) {
+        const uint32_t eb = edge + 8 * 12;
+        u64 c0, c1_, c2, c3_, c4, c5, c6, c7, c8, pad;
+        lds2x64(eb, c0, c1_); lds2x64(eb + 16, c2, c3_); lds2x64(eb + 32, c4, c5); lds2x64(eb + 48, c6, c7);
+        lds2x64(eb + 64, c8, pad);
+        const u64 qe = A, qi = B;
+        const u64 ali = add2(qi, xp);
+        const u64 qm = fma2(c0, qe, mul2(c1_, qi)), dq = mul2(c2, sub2(qi, qe));
+        const u64 cc = mul2(sub2(sub2(ali, qm), mul2(c4, dq)), c3_);
+        const u64 c3 = sub2(dq, mul2(cc, c5));
+        const u64 inner = sub2(qm, mul2(cc, c6));
+        const u64 bot = add2(sub2(mul2(cc, c7), mul2(c3, c8)), inner);
+        const u64 alb = clamp2(inner, qe, qi);
+        y = sub2(alb, qi); xn = sub2(alb, qe); dcn = mul2(half, sub2(qe, alb)); dqn = sub2(bot, qe);   // layer nz-1 is finished next step
+    } else if (t == nz + 1) {
+        y = dq1;
+    } else if (t > nz + 1) {                                                // below the surface
+        x = 0; y = 0; dc = 0;
     }
-    PairRec r0, r1;
-    PairFront f0, f1;
-    load_pair_rec(r0, rec);
-    load_pair_rec(r1, rec + REC_BLOCK);
-    pair_front<NS>(f0, r0, s, 0, q[0]);
-    pair_front<NS>(f1, r1, s, 1, q[1]);
-    PairRec r2, r3;
-    load_pair_rec(r2, rec + 2 * REC_BLOCK);
-    load_pair_rec(r3, rec + 3 * REC_BLOCK);
-    pair_back<NS>(f0, r0, s, 0, q[0], acc_lane, ova, ovb, sctx, t, nz, kk, b);
-    pair_back<NS>(f1, r1, s, 1, q[1], acc_lane, ova, ovb, sctx, t, nz, kk, b);
-    pair_front<NS>(f0, r2, s, 2, q[2]);
-    pair_front<NS>(f1, r3, s, 3, q[3]);
-    pair_back<NS>(f0, r2, s, 2, q[2], acc_lane, ova, ovb, sctx, t, nz, kk, b);
-    pair_back<NS>(f1, r3, s, 3, q[3], acc_lane, ova, ovb, sctx, t, nz, kk, b);
+    // limited parabola of layer t-2 in deviation form, x = AL - q, y = AR - q, A6 = -3 (x + y)
+    // (ppm_limiters lmt = 0, mappm.f90:875-894), then the events of the layer and its whole-layer term
+    const u64 q = B;
+    {
+        const u64 da1 = sub2(y, x), sm = add2(x, y);
+        const u64 tt = mul2(sm, da1), da2 = mul2(da1, mul2(da1, pk(1.f / 3.f, 1.f / 3.f)));
+        float xa, xb, ya, yb, ta, tb, ga, gb, ca, cb;
+        upk(x, xa, xb); upk(y, ya, yb); upk(tt, ta, tb); upk(da2, ga, gb); upk(dc, ca, cb);
+        const float mxa = -2.f * xa, mxb = -2.f * xb, mya = -2.f * ya, myb = -2.f * yb;
+        const bool k1a = ta > ga, k2a = -ta > ga, k1b = tb > gb, k2b = -tb > gb;    // k1 and k2 exclude each other (da2 >= 0)
+        ya = k1a ? mxa : ya;    xa = k2a ? mya : xa;                    // a6da < -da2: AR = AL - 3 (AL - q); > da2: AL = AR - 3 (AR - q)
+        yb = k1b ? mxb : yb;    xb = k2b ? myb : xb;
+        xa = ca == 0.f ? 0.f : xa;  ya = ca == 0.f ? 0.f : ya;
+        xb = cb == 0.f ? 0.f : xb;  yb = cb == 0.f ? 0.f : yb;
+        x = pk(xa, xb); y = pk(ya, yb);
+    }
+    const uint32_t acc_lane = ctx_u32(sctx, CTX_CELL0) + w * ctx_u32(sctx, CTX_CELLB) + ctx_u32(sctx, CTX_ACC) + 4 * lane;
+    const u64 I = fma2(r.EZ, y, fma2(r.EY, x, mul2(r.EX, q)));
+    float ta_, tb_, ra, rb_, na, nb, qa, qb, xa, xb, ya, yb;
+    upk(add2(run, I), ta_, tb_); upk(run, ra, rb_); upk(mul2(r.NW, I), na, nb);     // -w is what the record holds
+    flush<NS>(acc_lane, r.oi.x, ta_);
+    flush<NS>(acc_lane, r.oi.y, tb_);
+    float rsa = (NS && r.oi.z == 0) ? ra : na, rsb = (NS && r.oi.w == 0) ? rb_ : nb;
+    if ((r.oi.z | r.oi.w) > 1) {
+        upk(q, qa, qb); upk(x, xa, xb); upk(y, ya, yb);
+        if (r.oi.z > 1) rsa = apply_extras<NS>(sctx, t, kk | (2 * p) << 4 | b << 8, r.oi.z, qa, xa, ya, rsa);
+        if (r.oi.w > 1) rsb = apply_extras<NS>(sctx, t, kk | (2 * p + 1) << 4 | b << 8, r.oi.w, qb, xb, yb, rsb);
+    }
+    EndOut o;
+    o.dq = dqn; o.dc = dcn; o.x = xn;
+    o.run = fma2(r.DPW, q, pk(rsa, rsb));
+    return o;
 }
 
 // The same step as one straight-line block: fronts and accumulator updates of the four pairs without a branch
@@ -908,7 +848,7 @@ __device__ __forceinline__ void hot_step2(uint32_t sctx, uint32_t rec, uint32_t 
     }
 }
 
-// The same step at the ends of the column: column by column through end_column
+// The same step at the ends of the column: pair by pair through end_pair
 template <bool NS>
 __device__ __forceinline__ void end_step(uint32_t sctx, uint32_t stage, int t, int kk, int b, int w, int nz, const Field &f,
                                          int any_derived, State &s)
@@ -924,13 +864,9 @@ __device__ __forceinline__ void end_step(uint32_t sctx, uint32_t stage, int t, i
     }
 #pragma unroll
     for (int p = 0; p < 4; ++p) {
-        float qa, qb, ta, tb, Aa, Ab, Ba, Bb, da, db, ca, cb, xa, xb, ra, rb;
-        upk(q[p], qa, qb);      upk(q3[p], ta, tb);     upk(s.A[p], Aa, Ab);    upk(s.B[p], Ba, Bb);
-        upk(s.dq[p], da, db);   upk(s.dc[p], ca, cb);   upk(s.xp[p], xa, xb);   upk(s.run[p], ra, rb);
-        const float4 va = end_column<NS>(sctx, t, kk | (2 * p) << 4 | b << 8, qa, ta, Aa, Ba, da, ca, xa, ra);
-        const float4 vb = end_column<NS>(sctx, t, kk | (2 * p + 1) << 4 | b << 8, qb, tb, Ab, Bb, db, cb, xb, rb);
+        const EndOut v = end_pair<NS>(sctx, t, kk | p << 4 | b << 8, q[p], q3[p], s.A[p], s.B[p], s.dq[p], s.dc[p], s.xp[p], s.run[p]);
         s.B[p] = s.A[p]; s.A[p] = q[p];
-        s.dq[p] = pk(va.x, vb.x); s.dc[p] = pk(va.y, vb.y); s.xp[p] = pk(va.z, vb.z); s.run[p] = pk(va.w, vb.w);
+        s.dq[p] = v.dq; s.dc[p] = v.dc; s.xp[p] = v.x; s.run[p] = v.run;
     }
 }
 
@@ -1125,12 +1061,8 @@ plevel_stream_kernel(const __grid_constant__ Params p)
             for (int kk = 0; kk < KC; ++kk) {
                 const int t = t0 + kk;
                 if (t > nz_r + 2) break;
-#ifdef CG_EXP_NOEND
-                if (true)
-#else
                 if (t != 2 && t != nz_r)       // (t = 0, 1: all-zero records, nothing is finished)
-#endif
-                    HOT_STEP<NS>(sctx, rec_w + b * REC_BYTES + kk * ((NCOL / 2) * REC_BLOCK), ova_w + b * OVA_BYTES + kk * (NCOL * MAXE * 16),
+                    hot_step2<NS>(sctx, rec_w + b * REC_BYTES + kk * ((NCOL / 2) * REC_BLOCK), ova_w + b * OVA_BYTES + kk * (NCOL * MAXE * 16),
                              ovb_w + b * OVB_BYTES + kk * (NCOL * MAXE * 4), stage, t, nz_r, kk, b, w, fld, any_derived, st, acc_lane);
                 else
                     end_step<NS>(sctx, stage, t, kk, b, w, nz_r, fld, any_derived, st);
