@@ -215,3 +215,21 @@ def test_config5_c3072_row_band(ops):
         gg = host(g[:, :, 40:42])
         assert np.array_equal(np.isfinite(gg), ok)
         assert np.abs(gg[ok] - e[ok]).max() <= 3e-5 * np.abs(x).max()
+
+
+# ---- N > 1 on one box: shards by tile / row band, one NCCL gather of the coarse outputs ----
+def test_nccl_gather_matches_unsharded():
+    """Runs tools/multi_gpu_gather.py on every GPU of the box (skipped on a one-GPU box; the gloo world-2 twin of
+    the host logic is tests/test_sharding.py)."""
+    import os
+    import subprocess
+    import sys
+    n = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    if n < 2:
+        pytest.skip("needs at least two GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+                        "--master-addr", "127.0.0.1", "--master-port", "29533", os.path.join(root, "tools", "multi_gpu_gather.py")],
+                       capture_output=True, text=True, timeout=600, cwd=root)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert '"bit_identical_to_unsharded": true' in r.stdout
