@@ -11,22 +11,25 @@
 // and rounding, so results are bit-identical to the CPU oracle (gcc
 // -ffp-contract=off), which is what gfortran produces without FMA contraction.
 #include "common.cuh"
+#include <cstdlib>
 #include <cmath>
 
 namespace cg {
 
-constexpr int TPB = 32;
+constexpr int TPB = 32;            // shared-memory variant: columns per block
+constexpr int TPB_LOCAL = 128;     // local-memory variant
+constexpr int KMAX_LOCAL = 96;     // deepest column the local-memory variant takes
 
 struct ColumnViews {
     float *pe, *q, *al, *ar, *a6, *dc, *h2;
-    int tid;
-    __device__ __forceinline__ float &PE(int k) const { return pe[k * TPB + tid]; }
-    __device__ __forceinline__ float &Q(int k) const { return q[k * TPB + tid]; }
-    __device__ __forceinline__ float &AL(int k) const { return al[k * TPB + tid]; }
-    __device__ __forceinline__ float &AR(int k) const { return ar[k * TPB + tid]; }
-    __device__ __forceinline__ float &A6(int k) const { return a6[k * TPB + tid]; }
-    __device__ __forceinline__ float &DC(int k) const { return dc[k * TPB + tid]; }
-    __device__ __forceinline__ float &H2(int k) const { return h2[k * TPB + tid]; }
+    int tid, stride;                 // element k of an array sits at k * stride + tid
+    __device__ __forceinline__ float &PE(int k) const { return pe[k * stride + tid]; }
+    __device__ __forceinline__ float &Q(int k) const { return q[k * stride + tid]; }
+    __device__ __forceinline__ float &AL(int k) const { return al[k * stride + tid]; }
+    __device__ __forceinline__ float &AR(int k) const { return ar[k * stride + tid]; }
+    __device__ __forceinline__ float &A6(int k) const { return a6[k * stride + tid]; }
+    __device__ __forceinline__ float &DC(int k) const { return dc[k * stride + tid]; }
+    __device__ __forceinline__ float &H2(int k) const { return h2[k * stride + tid]; }
     __device__ __forceinline__ float DP(int k) const { return PE(k + 1) - PE(k); }
     __device__ __forceinline__ float D4(int k) const { return DP(k - 1) + DP(k); }
     __device__ __forceinline__ float DELQ(int k) const { return Q(k + 1) - Q(k); }
@@ -244,8 +247,8 @@ struct CsColumn {
     __device__ __forceinline__ float &A6(int k) const { return c.A6(k - 1); }
     __device__ __forceinline__ float &QE(int k) const { return c.H2(k - 1); }
     __device__ __forceinline__ float &GAM(int k) const { return c.DC(k - 1); }
-    __device__ __forceinline__ int FLAGS(int k) const { return __float_as_int(fl[(k - 1) * TPB + c.tid]); }
-    __device__ __forceinline__ void set_flags(int k, int v) const { fl[(k - 1) * TPB + c.tid] = __int_as_float(v); }
+    __device__ __forceinline__ int FLAGS(int k) const { return __float_as_int(fl[(k - 1) * c.stride + c.tid]); }
+    __device__ __forceinline__ void set_flags(int k, int v) const { fl[(k - 1) * c.stride + c.tid] = __int_as_float(v); }
     __device__ __forceinline__ bool extm(int k) const { return FLAGS(k) & 1; }
     __device__ __forceinline__ bool ext5(int k) const { return FLAGS(k) & 2; }
     __device__ __forceinline__ bool ext6(int k) const { return FLAGS(k) & 4; }
@@ -421,25 +424,33 @@ struct Strides { long v[12]; };
 // (ny, nx) tile reads coarse column (y/f, x/f) of a (ny/f, nx/f) tile.
 struct Pe2Block { int f, nx, nxc; };
 
-__global__ void __launch_bounds__(TPB)
+// Two homes for the column's work arrays (pe, q, AL, AR, A6, dc, h2 [, flags]: 7-8 values per level).  SHARED:
+// interleaved in shared memory, 32 columns per block - 71 KB per warp at km = 79, i.e. 3 warps per SM, for any
+// km that fits 227 KB.  LOCAL (km <= KMAX_LOCAL): thread-private arrays in local memory, which the hardware
+// interleaves across the lanes the same way and serves from L1 / L2; occupancy is then bounded by registers only
+// (one C384 field: 7.5 ms shared, see DESIGN.md for the local figure).
+template <bool LOCAL>
+__global__ void __launch_bounds__(LOCAL ? TPB_LOCAL : TPB)
 mappm_generic_kernel(const float *__restrict__ pe1, const float *__restrict__ q1,
                      const float *__restrict__ pe2, float *__restrict__ q2,
                      long ncol, long n_inner, int km, int kn, Strides s, Pe2Block pb,
                      int iv, int kord)
 {
     extern __shared__ float smem[];
-    const long col = blockIdx.x * (long)TPB + threadIdx.x;
+    float local_buf[LOCAL ? 8 * KMAX_LOCAL + 2 : 1];
+    const long col = blockIdx.x * (long)(LOCAL ? TPB_LOCAL : TPB) + threadIdx.x;
     if (col >= ncol) return;  // no block-level synchronisation below
     ColumnViews c;
-    c.tid = threadIdx.x;
-    c.pe = smem;
-    c.q = c.pe + (km + 1) * TPB;
-    c.al = c.q + km * TPB;
-    c.ar = c.al + km * TPB;
-    c.a6 = c.ar + km * TPB;
-    c.dc = c.a6 + km * TPB;
-    c.h2 = c.dc + km * TPB;
-    float *fl = c.h2 + (km + 1) * TPB;                                    // kord > 7 only
+    c.tid = LOCAL ? 0 : threadIdx.x;
+    c.stride = LOCAL ? 1 : TPB;
+    c.pe = LOCAL ? local_buf : smem;
+    c.q = c.pe + (km + 1) * c.stride;
+    c.al = c.q + km * c.stride;
+    c.ar = c.al + km * c.stride;
+    c.a6 = c.ar + km * c.stride;
+    c.dc = c.a6 + km * c.stride;
+    c.h2 = c.dc + km * c.stride;
+    float *fl = c.h2 + (km + 1) * c.stride;                               // kord > 7 only
 
     const long o = col / n_inner, i = col % n_inner;
     const float *p1 = pe1 + o * s.v[0] + i * s.v[1];
@@ -546,13 +557,19 @@ int launch_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,
     Strides s;
     for (int i = 0; i < 12; ++i) s.v[i] = strides[i];
     Pe2Block pb{pe2_f, pe2_nx, pe2_nxc};
+    const char *home = getenv("CG_MAPPM_ARRAYS");                        // "shared" forces the shared-memory variant (tests)
+    if (km <= KMAX_LOCAL && !(home && home[0] == 's')) {
+        mappm_generic_kernel<true><<<cdiv(ncol, TPB_LOCAL), TPB_LOCAL, 0, st>>>(pe1, q1, pe2, q2, ncol, n_inner, km, kn, s, pb, iv, kord);
+        CG_LAUNCH_CHECK("cg_mappm");
+        return CG_OK;
+    }
     const size_t smem = sizeof(float) * TPB * (size_t)(kord > 7 ? 8 * km + 2 : 7 * km + 1);
     CG_REQUIRE(smem <= 227 * 1024, "km=%d needs %zu B of shared memory per block", km, smem);
     if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(mappm_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(mappm_generic_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(mappm)");
     }
-    mappm_generic_kernel<<<cdiv(ncol, TPB), TPB, smem, st>>>(pe1, q1, pe2, q2, ncol, n_inner, km, kn, s, pb, iv, kord);
+    mappm_generic_kernel<false><<<cdiv(ncol, TPB), TPB, smem, st>>>(pe1, q1, pe2, q2, ncol, n_inner, km, kn, s, pb, iv, kord);
     CG_LAUNCH_CHECK("cg_mappm");
     return CG_OK;
 }

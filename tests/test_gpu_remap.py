@@ -95,6 +95,19 @@ def test_mappm_cs_profile_bit_exact_vs_oracle(ops, km, kn, iv, kord):
     np.testing.assert_array_equal(got, exp)
 
 
+@pytest.mark.parametrize("kord", [1, 7, 9, 13])
+def test_mappm_shared_memory_variant(ops, monkeypatch, kord):
+    """km <= 96 keeps the column's work arrays in local memory; deeper columns (and CG_MAPPM_ARRAYS=shared)
+    use the shared-memory variant.  Both are the same code over two array homes: same bits."""
+    rng = np.random.RandomState(40 + kord)
+    pe1, q, pe2 = _random_columns(rng, 200, 79, 79)
+    local = gpu_mappm_zlast(ops, pe1, q, pe2, 1, kord)
+    monkeypatch.setenv("CG_MAPPM_ARRAYS", "shared")
+    shared = gpu_mappm_zlast(ops, pe1, q, pe2, 1, kord)
+    np.testing.assert_array_equal(local, shared)
+    np.testing.assert_array_equal(shared, oracle.mappm(pe1, q, pe2, iv=1, kord=kord))
+
+
 def test_mappm_tile_layout_and_shared_target(ops):
     """(tile, z, y, x) layout addressed by strides; cs_pe2 = 0 shares one target column."""
     rng = np.random.RandomState(3)
