@@ -128,6 +128,47 @@ median_small_kernel(const T *__restrict__ in, T *__restrict__ out, long n_cells,
     out[idx] = has_nan ? T(NAN) : (a[N / 2 - 1] + a[N / 2]) / T(2);
 }
 
+// Mode of small power-of-two blocks: the same register sort, then the longest run of the sorted keys (the
+// smallest value among equally long runs, like scipy.stats.mode).  NaNs sort last as +inf and are counted apart.
+// MODE: 1 = propagate NaN, 2 = omit NaN (see select_generic_kernel for the rules).
+template <typename T, int F, int MODE>
+__global__ void __launch_bounds__(128)
+mode_small_kernel(const T *__restrict__ in, T *__restrict__ out, long n_cells, int ny, int nx)
+{
+    constexpr int N = F * F;
+    const int nxo = nx / F, nyo = ny / F;
+    const long idx = blockIdx.x * (long)blockDim.x + threadIdx.x;
+    if (idx >= n_cells) return;
+    const int I = (int)(idx % nxo);
+    const int J = (int)((idx / nxo) % nyo);
+    const long o = idx / ((long)nxo * nyo);
+    const T *p = in + o * (long)ny * nx + (long)(J * F) * nx + I * F;
+    T a[N];
+    int nan_cnt = 0;
+#pragma unroll
+    for (int y = 0; y < F; ++y)
+#pragma unroll
+        for (int x = 0; x < F; ++x) {
+            T v = p[(long)y * nx + x];
+            if (v != v) { ++nan_cnt; v = T(INFINITY); }
+            a[y * F + x] = v;
+        }
+    sort_network<T, N>(a);
+    const int m = N - nan_cnt;
+    T best = a[0];
+    int best_len = 0, run = 0;
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        if (i < m) {
+            run = (i > 0 && a[i] == a[i > 0 ? i - 1 : 0]) ? run + 1 : 1;
+            if (run > best_len) { best_len = run; best = a[i]; }
+        }
+    }
+    T r = best;
+    if (m == 0 || (MODE == 1 && nan_cnt > best_len)) r = T(NAN);
+    out[idx] = r;
+}
+
 // ---------------------------------------------------------------------------------
 // Generic: one warp per block, n = f*f <= 1024 values sorted in shared memory
 // (bitonic, padded with +inf; NaNs are counted apart and sort as +inf).
@@ -266,6 +307,21 @@ extern "C" int cg_block_mode(const void *in, void *out, long n_outer, int ny, in
     const long n_cells = n_outer * (long)(ny / f) * (nx / f);
     if (n_cells == 0) return CG_OK;
     cudaStream_t st = (cudaStream_t)stream;
+    // small power-of-two blocks: thread per block, register sort (f = 8 fp32 is the sfc_data shape)
+    const unsigned g = cdiv(n_cells, 128);
+#define CG_MODE_SMALL(T, F)                                                                                          \
+    do {                                                                                                             \
+        if (nan_omit) mode_small_kernel<T, F, 2><<<g, 128, 0, st>>>((const T *)in, (T *)out, n_cells, ny, nx);       \
+        else mode_small_kernel<T, F, 1><<<g, 128, 0, st>>>((const T *)in, (T *)out, n_cells, ny, nx);                \
+        CG_LAUNCH_CHECK("cg_block_mode");                                                                            \
+        return CG_OK;                                                                                                \
+    } while (0)
+    if (dtype == CG_F32 && f == 8) CG_MODE_SMALL(float, 8);
+    if (dtype == CG_F32 && f == 4) CG_MODE_SMALL(float, 4);
+    if (dtype == CG_F32 && f == 2) CG_MODE_SMALL(float, 2);
+    if (dtype == CG_F64 && f == 4) CG_MODE_SMALL(double, 4);
+    if (dtype == CG_F64 && f == 2) CG_MODE_SMALL(double, 2);
+#undef CG_MODE_SMALL
     if (dtype == CG_F32)
         return nan_omit ? launch_generic_select<float, 2>(in, out, n_cells, ny, nx, f, st, "cg_block_mode")
                         : launch_generic_select<float, 1>(in, out, n_cells, ny, nx, f, st, "cg_block_mode");

@@ -191,6 +191,25 @@ def test_block_mode(ops, policy, f):
     np.testing.assert_array_equal(got, exp)
 
 
+@pytest.mark.parametrize("policy", ["propagate", "omit"])
+@pytest.mark.parametrize("f,dt", [(2, "f4"), (4, "f4"), (8, "f4"), (2, "f8"), (4, "f8"), (3, "f4"), (8, "f8"), (16, "f4")])
+def test_block_mode_ties_nans_infs(ops, policy, f, dt):
+    """Register-sort kernel (f = 2, 4, 8) and the warp-per-block one (other sizes, f = 8 fp64): ties go to the smallest
+    value, NaN wins under 'propagate' only when strictly most frequent, +inf is an ordinary value."""
+    rng = np.random.RandomState(80 + f)
+    a = rng.randint(-2, 3, (5, 6 * f, 5 * f)).astype(dt)
+    a[rng.uniform(size=a.shape) < 0.15] = np.nan
+    a[rng.uniform(size=a.shape) < 0.10] = np.inf
+    a[0, :f, :f] = np.nan                               # all NaN
+    a[0, :f, f:2 * f] = np.inf                          # all +inf
+    a[1, :f, :f] = np.nan
+    a[1, 0, 0] = 1.0                                    # NaN strictly most frequent
+    a[2, :f, :f] = np.where(np.arange(f * f).reshape(f, f) % 2 == 0, np.nan, 7.0)   # NaN ties with a value
+    got = host(ops.block_mode(dev(a), f, policy))
+    exp = oracle.block_mode(a, f, policy)
+    np.testing.assert_array_equal(got, exp)
+
+
 @pytest.mark.parametrize("stag_y,stag_x", [(False, False), (True, False), (False, True), (True, True)])
 @pytest.mark.parametrize("dt", ["f4", "f8"])
 def test_block_upsample(ops, stag_y, stag_x, dt):
