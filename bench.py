@@ -328,9 +328,11 @@ def e2e_run(args, spec, inp, device, world, barrier):
     back to the host.  All of it inside the timed region."""
     import torch
 
+    prev_cpus = os.sched_getaffinity(0) if hasattr(os, "sched_getaffinity") else None
     try:
         from fv3net_b200 import staging
 
+        staging.bind_host_thread(device)                # pinned buffers on the GPU's own NUMA node (matters at N = 8)
         # every input in pinned host memory; the device copies in `inp` are not used below
         host = staging.pin({k: ({n: t.cpu() for n, t in v.items()} if isinstance(v, dict) else v.cpu())
                             for k, v in inp.items()})
@@ -361,6 +363,9 @@ def e2e_run(args, spec, inp, device, world, barrier):
     except RuntimeError as e:  # e.g. pinned allocation refused
         return {"value": None, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                 "error": str(e)[:200]}
+    finally:
+        if prev_cpus is not None:
+            os.sched_setaffinity(0, prev_cpus)          # the CPU baseline below uses every host core again
 
 
 def main():

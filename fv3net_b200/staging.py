@@ -45,6 +45,41 @@ def _unflatten(flat):
     return out
 
 
+def bind_host_thread(device=None):
+    """Run the calling process on the CPUs next to `device` (NVML's affinity mask) so that the pinned buffers it
+    allocates afterwards, and the copies it enqueues, stay on the GPU's own NUMA node and PCIe root.  With one
+    process per GPU on an 8-GPU box the host -> device streams otherwise meet in one socket's memory.  Returns the
+    CPU set, or None when NVML or the affinity call is not available (nothing is changed then)."""
+    import os
+
+    try:
+        import pynvml
+
+        index = torch.cuda.current_device() if device is None else torch.device(device).index
+        pynvml.nvmlInit()
+        # NVML enumerates physical devices; honour CUDA_VISIBLE_DEVICES through the PCI bus id
+        bus = torch.cuda.get_device_properties(index).pci_bus_id if hasattr(torch.cuda.get_device_properties(index), "pci_bus_id") else None
+        handle = None
+        if bus is not None:
+            for i in range(pynvml.nvmlDeviceGetCount()):
+                h = pynvml.nvmlDeviceGetHandleByIndex(i)
+                if pynvml.nvmlDeviceGetPciInfo(h).bus == bus:
+                    handle = h
+                    break
+        if handle is None:
+            handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+        ncpu = os.cpu_count() or 1
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (ncpu + 63) // 64)
+        cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return cpus
+    except Exception:                       # no NVML, no permission, not Linux: leave the process where it is
+        return None
+
+
 def pin(inputs):
     """The same nested dict with every array in pinned host memory (numpy or CPU tensors in)."""
     flat = _flatten(inputs)
