@@ -857,7 +857,19 @@ __device__ __forceinline__ void end_step(uint32_t sctx, uint32_t stage, int t, i
 #pragma unroll
     for (int p = 0; p < 4; ++p) { q[p] = s.A[p]; q3[p] = 0; }
     if (t < nz) load_row(q, stage, kk, w, f, any_derived);
-    if (t == 2) load_row(q3, stage, 3, w, f, any_derived);          // level 3 is in the same stage (KC = 4)
+    if (t == 2) {
+        // the walk starts here: levels 0 and 1 (same stage) only seed the rolling state - B = q(0), A = q(1),
+        // delq(1), everything else zero - so steps 0 and 1 are not run; level 3 is visible too (KC = 4)
+        u64 l0[4], l1[4];
+        load_row(l0, stage, 0, w, f, any_derived);
+        load_row(l1, stage, 1, w, f, any_derived);
+        load_row(q3, stage, 3, w, f, any_derived);
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            s.B[p] = l0[p]; s.A[p] = l1[p]; s.dq[p] = sub2(l1[p], l0[p]);
+            if (!NS) s.chk = fma2(l1[p], 0ull, fma2(l0[p], 0ull, s.chk));
+        }
+    }
     if (!NS && t < nz) {
 #pragma unroll
         for (int p = 0; p < 4; ++p) s.chk = fma2(q[p], 0ull, s.chk);
@@ -1058,10 +1070,10 @@ plevel_stream_kernel(const __grid_constant__ Params p)
             mbar_wait(bars + 8 * b, (it >> 1) & 1);
             const uint32_t stage = ring_r + b * stage_bytes_r;
 #pragma unroll STEP_UNROLL
-            for (int kk = 0; kk < KC; ++kk) {
+            for (int kk = t0 == 0 ? 2 : 0; kk < KC; ++kk) {     // (t = 0, 1 finish nothing: the end step at t = 2 seeds the state)
                 const int t = t0 + kk;
                 if (t > nz_r + 2) break;
-                if (t != 2 && t != nz_r)       // (t = 0, 1: all-zero records, nothing is finished)
+                if (t != 2 && t != nz_r)
                     hot_step2<NS>(sctx, rec_w + b * REC_BYTES + kk * ((NCOL / 2) * REC_BLOCK), ova_w + b * OVA_BYTES + kk * (NCOL * MAXE * 16),
                              ovb_w + b * OVB_BYTES + kk * (NCOL * MAXE * 4), stage, t, nz_r, kk, b, w, fld, any_derived, st, acc_lane);
                 else

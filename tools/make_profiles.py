@@ -61,3 +61,22 @@ json.dump({"kernel": v[h.index("Kernel Name")], "dram_bytes_read": val("dram__by
 for src, dst in (("bench.json", f"{tag}_bench.json"), ("bench_reference.json", f"{tag}_bench_reference.json")):
     if os.path.exists(os.path.join(G, src)): shutil.copy(os.path.join(G, src), os.path.join(P, dst))
 print(open(os.path.join(P, f"{tag}_launches_summary.txt")).read()[:1800])
+
+# ---- the other kernels (tools/kernel_rooflines.py under ncu): average duration per kernel --------------
+kn = os.path.join(G, "kernels_ncu.csv")
+if os.path.exists(kn):
+    rows = [r for r in csv.reader(open(kn)) if r and not r[0].startswith("==")]
+    hdr = rows[0]; ik = hdr.index("Kernel Name"); iv = hdr.index("Metric Value"); iu = hdr.index("Metric Unit")
+    agg = collections.OrderedDict()
+    for r in rows[1:]:
+        if len(r) <= iv or not ("cg::" in r[ik] or "stream::" in r[ik]): continue
+        us = float(r[iv].replace(",", "")) * {"ns": 1e-3, "us": 1.0, "ms": 1e3, "usecond": 1.0, "nsecond": 1e-3, "msecond": 1e3}.get(r[iu], 1.0)
+        n, t, lo = agg.get(r[ik], (0, 0.0, 1e30)); agg[r[ik]] = (n + 1, t + us, min(lo, us))
+    with open(os.path.join(P, f"{tag}_kernels_ncu.txt"), "w") as f:
+        f.write("# ncu --metrics gpu__time_duration.sum --clock-control none: python tools/kernel_rooflines.py\n")
+        f.write("# (cold-cache, serialised launches; 23 launches per case: 3 warm-up + 20 timed)\n")
+        f.write(f"{'kernel':100s} {'launches':>8s} {'avg_us':>10s} {'min_us':>10s}\n")
+        for k, (n, t, lo) in agg.items():
+            f.write(f"{k[:100]:100s} {n:8d} {t/n:10.1f} {lo:10.1f}\n")
+    if os.path.exists(os.path.join(G, "kernel_rooflines.txt")):
+        shutil.copy(os.path.join(G, "kernel_rooflines.txt"), os.path.join(P, f"{tag}_kernel_rooflines.txt"))
