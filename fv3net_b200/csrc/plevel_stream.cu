@@ -1026,6 +1026,7 @@ plevel_stream_kernel(const __grid_constant__ Params p)
                 __syncwarp();
                 if (lane < mine)
                     tma_load_3d(mydst + b * stage_bytes, mymap, NCOL * bx, 8 * by + row, (int)(o * nz) + chunk * KC, bars + 8 * b);
+                if (chunk * KC + gw >= 2)                            // (the records of steps 0 and 1 are not read)
                 geometry_step<NS>(icnt, pm3, pm2, pm1, p0, pp1, g, col, chunk * KC + gw, gw, x, rec0 + b * REC_BYTES,
                               ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, tail, edge, nz, mask_below, toa);
                 __syncwarp();
