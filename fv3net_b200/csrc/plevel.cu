@@ -90,6 +90,7 @@ exposed_area_kernel(const float *__restrict__ pe_c, const float *__restrict__ de
 // lanes over levels then form the coarse log-midpoint pressures from the sequential cumsum of delp_coarse and
 // add the areas of the exposed columns in the order of the loop above (y, then x), so both kernels agree bitwise.
 constexpr int EXPOSED_WARPS = 8;
+template <bool F8>
 __global__ void __launch_bounds__(32 * EXPOSED_WARPS)
 exposed_area_fused_kernel(const float *__restrict__ delp, const float *__restrict__ delp_c,
                           const float *__restrict__ area, float *__restrict__ out, long n_outer, int nz,
@@ -105,6 +106,28 @@ exposed_area_fused_kernel(const float *__restrict__ delp, const float *__restric
         const long o = cell / hc, ic = cell - o * hc;
         const int J = (int)(ic / nxc), I = (int)(ic - (long)J * nxc);
         const float *d0 = delp + o * nz * h + (long)(J * f) * nx + I * f;
+        if (F8) {
+            // f = 8: lane = (row lane / 8 and that row + 4, column lane % 8); eight levels = 16 loads in flight per lane,
+            // added in level order per column (the order of surface_pressure_kernel)
+            const float *pa = d0 + (long)(lane >> 3) * nx + (lane & 7), *pb = pa + 4L * nx;
+            float sa = 0.f, sb = 0.f;
+            int k = 0;
+            for (; k + 8 <= nz; k += 8) {
+                float a[8], b[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { a[j] = ldg_stream(pa + (long)(k + j) * h); b[j] = ldg_stream(pb + (long)(k + j) * h); }
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { sa += (a[j] == a[j]) ? a[j] : 0.f; sb += (b[j] == b[j]) ? b[j] : 0.f; }
+            }
+            for (; k < nz; ++k) {
+                const float a = ldg_stream(pa + (long)k * h), b = ldg_stream(pb + (long)k * h);
+                sa += (a == a) ? a : 0.f;
+                sb += (b == b) ? b : 0.f;
+            }
+            const long ia = (long)(lane >> 3) * nx + (lane & 7), ib = ia + 4L * nx;
+            ps[lane] = sa + toa;        ar[lane] = area[o * h + (long)(J * 8) * nx + I * 8 + ia];
+            ps[lane + 32] = sb + toa;   ar[lane + 32] = area[o * h + (long)(J * 8) * nx + I * 8 + ib];
+        } else
         for (int c0 = 0; c0 < ncol; c0 += 64) {                       // two columns per lane and sweep
             const int ca = c0 + lane, cb = c0 + 32 + lane;
             const bool va = ca < ncol, vb = cb < ncol;
@@ -136,6 +159,89 @@ exposed_area_fused_kernel(const float *__restrict__ delp, const float *__restric
                 acc += (a == a) ? a : 0.f;
             }
             out[(o * nz + k) * hc + ic] = acc;
+        }
+        __syncwarp();
+    }
+}
+
+// f = 8 and a coarse row that is a multiple of 4 cells: a warp owns a strip of 4 adjacent cells, so that every
+// load is one whole 128-B line (lane = fine column of the strip; rows and levels in registers).  The warp-per-cell
+// form above asks DRAM for 32-B pieces of four lines per instruction: 125 us against this form's time in DESIGN.md.
+__global__ void __launch_bounds__(32 * EXPOSED_WARPS, 3)         // 24 warps per SM: the C384 strips fit one wave
+exposed_area_strip_kernel(const float *__restrict__ delp, const float *__restrict__ delp_c,
+                          const float *__restrict__ area, float *__restrict__ out, long n_outer, int nz,
+                          int ny, int nx, float toa)
+{
+    extern __shared__ float sm_exposed[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nyc = ny >> 3, nxc = nx >> 3, nstrip = nxc >> 2;
+    const long hc = (long)nyc * nxc, h = (long)ny * nx;
+    float *ps = sm_exposed + warp * (512 + nz + 1), *ar = ps + 256, *pe = ar + 256;
+    const long strips = n_outer * nyc * nstrip;
+    for (long sidx = (long)blockIdx.x * EXPOSED_WARPS + warp; sidx < strips; sidx += (long)gridDim.x * EXPOSED_WARPS) {
+        const long o = sidx / ((long)nyc * nstrip), rem = sidx - o * ((long)nyc * nstrip);
+        const int J = (int)(rem / nstrip), I4 = (int)(rem - (long)J * nstrip);
+        const float *base = delp + o * nz * h + (long)(J * 8) * nx + I4 * 32 + lane;
+        float s[8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) s[r] = 0.f;
+        int k = 0;
+        for (; k + 4 <= nz; k += 4) {                                   // 32 whole lines in flight per warp
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = ldg_stream(base + (long)(k + (j >> 3)) * h + (long)(j & 7) * nx);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) s[j & 7] += (v[j] == v[j]) ? v[j] : 0.f;      // level order per column
+        }
+        for (; k < nz; ++k) {
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                const float v = ldg_stream(base + (long)k * h + (long)r * nx);
+                s[r] += (v == v) ? v : 0.f;
+            }
+        }
+        const int cell = lane >> 3, x = lane & 7;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            ps[cell * 64 + r * 8 + x] = s[r] + toa;
+            ar[cell * 64 + r * 8 + x] = area[o * h + (long)(J * 8 + r) * nx + I4 * 32 + lane];
+        }
+        for (int c4 = 0; c4 < 4; ++c4) {
+            const long ic = (long)J * nxc + I4 * 4 + c4;
+            __syncwarp();
+            for (int kk = lane; kk < nz; kk += 32) pe[kk] = delp_c[(o * nz + kk) * hc + ic];
+            __syncwarp();
+            // vertically_dependent.py:61-63: the sequential sum from toa, carried by every lane in a register (broadcast
+            // reads, no store-to-load chain); a lane keeps the interfaces of its own levels lane, lane + 32, ...
+            float pl[4][2];
+            {
+                float acc = toa;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {                           // (nz <= 128: checked by the host)
+                    pl[q][0] = 0.f; pl[q][1] = 0.f;
+                    const int n = min(32, nz - 32 * q);
+                    for (int j = 0; j < n; ++j) {
+                        const float nxt = acc + pe[32 * q + j];
+                        if (j == lane) { pl[q][0] = acc; pl[q][1] = nxt; }
+                        acc = nxt;
+                    }
+                }
+            }
+            const float *psc = ps + c4 * 64, *arc = ar + c4 * 64;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int kk = 32 * q + lane;
+                if (kk >= nz) break;
+                const float p0 = pl[q][0], p1 = pl[q][1];
+                const float pmid = pe[kk] / (logf(p1) - logf(p0));
+                float acc = 0.f;
+#pragma unroll 8
+                for (int c = 0; c < 64; ++c) {
+                    const float a = (pmid <= psc[c]) ? arc[c] : 0.f;
+                    acc += (a == a) ? a : 0.f;
+                }
+                out[(o * nz + kk) * hc + ic] = acc;
+            }
         }
         __syncwarp();
     }
@@ -323,11 +429,20 @@ extern "C" int cg_area_above_fine_surface(const float *delp, const float *delp_c
     if (n_outer == 0) return CG_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const long h = (long)ny * nx, hc = (long)(ny / f) * (nx / f);
+    if (f == 8 && nz <= 128 && (nx / 8) % 4 == 0 && (size_t)EXPOSED_WARPS * (512 + nz + 1) * sizeof(float) <= 48 * 1024) {
+        const long blocks = (n_outer * (ny / 8) * (nx / 32) + EXPOSED_WARPS - 1) / EXPOSED_WARPS;
+        exposed_area_strip_kernel<<<(unsigned)(blocks < 0x7fffffffL ? blocks : 0x7fffffffL), 32 * EXPOSED_WARPS,
+                                    (size_t)EXPOSED_WARPS * (512 + nz + 1) * sizeof(float), st>>>(
+            delp, delp_coarse, area, out, n_outer, nz, ny, nx, (float)toa);
+        CG_LAUNCH_CHECK("cg_area_above_fine_surface");
+        return CG_OK;
+    }
     const size_t smem = (size_t)EXPOSED_WARPS * (2 * f * f + nz + 1) * sizeof(float);
     if (smem <= 48 * 1024) {
         const long blocks = (n_outer * hc + EXPOSED_WARPS - 1) / EXPOSED_WARPS;
-        exposed_area_fused_kernel<<<(unsigned)(blocks < 0x7fffffffL ? blocks : 0x7fffffffL), 32 * EXPOSED_WARPS, smem, st>>>(
-            delp, delp_coarse, area, out, n_outer, nz, ny, nx, f, (float)toa);
+        const unsigned g = (unsigned)(blocks < 0x7fffffffL ? blocks : 0x7fffffffL);
+        if (f == 8) exposed_area_fused_kernel<true><<<g, 32 * EXPOSED_WARPS, smem, st>>>(delp, delp_coarse, area, out, n_outer, nz, ny, nx, f, (float)toa);
+        else exposed_area_fused_kernel<false><<<g, 32 * EXPOSED_WARPS, smem, st>>>(delp, delp_coarse, area, out, n_outer, nz, ny, nx, f, (float)toa);
         CG_LAUNCH_CHECK("cg_area_above_fine_surface");
         return CG_OK;
     }

@@ -319,15 +319,19 @@ def test_pressure_level_golden_restart_T(ops):
     np.testing.assert_allclose(host(dcoarse), dexp, rtol=1e-5)
 
 
-def test_area_above_fine_surface(ops):
-    fields, delp, area = _plevel_case(2, 4, 8, seed=9, nfields=0)
-    dc = oracle.weighted_block_average(delp, area[:, None], 8)
-    got = host(ops.area_above_fine_surface(dev(delp), dev(dc), dev(area), 8))
-    exp = recipes.area_above_fine_surface(delp, dc, area, 8)
+@pytest.mark.parametrize("nc,f", [(4, 8), (6, 8), (8, 4)])
+def test_area_above_fine_surface(ops, nc, f):
+    """(4, 8): warp per strip of four cells (whole-line loads); (6, 8), (8, 4): warp per cell, any factor.
+    NaN areas are skipped by both like the reference's nansum."""
+    fields, delp, area = _plevel_case(2, nc, f, seed=9, nfields=0)
+    area[0, 3, 5] = np.nan
+    dc = oracle.weighted_block_average(delp, np.nan_to_num(area)[:, None], f)
+    got = host(ops.area_above_fine_surface(dev(delp), dev(dc), dev(area), f))
+    exp = recipes.area_above_fine_surface(delp, dc, area, f)
     # p_mid = delp / (log p[k+1] - log p[k]) cancels: a 1-ulp difference between libm's and
     # CUDA's logf moves p_mid by ~eps*log(p)/dlog(p) ~ 5e-4 relative, so a fine column whose
     # surface pressure sits that close to a coarse mid-level may flip.  Allow a few single
     # columns; everything else must agree to summation-order precision.
     bad = ~np.isclose(got, exp, rtol=2e-6, atol=0)
     assert bad.mean() < 1e-2
-    assert np.abs(got - exp)[bad].max(initial=0.0) <= 3 * area.max()
+    assert np.abs(got - exp)[bad].max(initial=0.0) <= 3 * np.nanmax(area)
