@@ -435,6 +435,31 @@ __device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, f
     stsi32(r + 88, info);
 }
 
+// Integral weights times (q, x, y) of one event.  Events that use the layer mean alone - a target interface at or
+// above the column top (mappm.f90:62-64), everything below the surface (:115-120), the empty record - carry
+// z = +0; an event inside a layer always carries z = -(a s (1 - s)) with the sign bit set, even when it is zero
+// (make_event).  The NaN-safe variant drops the edge terms of the former, so that a NaN edge value (e.g. from a NaN
+// two levels down, through the one-sided cubic) does not reach a level the Fortran fills from q alone, and keeps
+// them for the latter, where the Fortran evaluates the parabola and returns NaN.
+template <bool NS>
+__device__ __forceinline__ float event_sum(float ex, float ey, float ez, float q, float x, float y)
+{
+    if (NS && __float_as_int(ez) == 0) return ex * q;
+    return ex * q + ey * x + ez * y;
+}
+template <bool NS>
+__device__ __forceinline__ u64 event_sum2(u64 EX, u64 EY, u64 EZ, u64 q, u64 x, u64 y)
+{
+    if (NS) {
+        float eza, ezb, xa, xb, ya, yb;
+        upk(EZ, eza, ezb); upk(x, xa, xb); upk(y, ya, yb);
+        const bool ma = __float_as_int(eza) == 0, mb = __float_as_int(ezb) == 0;
+        x = pk(ma ? 0.f : xa, mb ? 0.f : xb);
+        y = pk(ma ? 0.f : ya, mb ? 0.f : yb);
+    }
+    return fma2(EZ, y, fma2(EY, x, mul2(EX, q)));
+}
+
 // ---- per-field work -----------------------------------------------------------------------------
 // close a target level with `tot` (NaN-skipping block sum, coarsen.py:211).  acc_lane = &acc[0][lane];
 // slot 0 collects what belongs to no level.
@@ -470,7 +495,7 @@ __device__ __noinline__ float apply_extras(uint32_t sctx, int t, int kcb, int in
     if (info != INFO_SLOW) {
         for (int e = 0; e + 2 <= info; ++e) {
             const float4 ev = lds128(oa + 16 * e);
-            const float I = ev.x * q + ev.y * x + ev.z * y;
+            const float I = event_sum<NS>(ev.x, ev.y, ev.z, q, x, y);
             flush<NS>(acc_lane, ldsi32(ob + 4 * e), r + I);
             r = ev.w * I;                                               // stored negated
         }
@@ -489,7 +514,7 @@ __device__ __noinline__ float apply_extras(uint32_t sctx, int t, int kcb, int in
     col.ps = pp.w;
     for (int e = 1; e < n; ++e) {
         const Event ev = make_event(g, col, pp.x, pp.y, t - 2, i0 + e, nz, mask_below, toa);
-        const float I = ev.x * q + ev.y * x + ev.z * y;
+        const float I = event_sum<NS>(ev.x, ev.y, ev.z, q, x, y);
         flush<NS>(acc_lane, ev.slot * ACC_STRIDE, r + I);
         r = -(ev.w * I);
     }
@@ -543,13 +568,13 @@ __device__ __noinline__ float further_events(uint32_t oa, uint32_t ob, int info,
     if (info > MAXE + 1) return apply_extras<NS>(sctx, t, kcb, info & 1023, q, x, y, r);    // INFO_SLOW, or the tail
     const float4 ev = lds128(oa);
     const int off = ldsi32(ob);
-    float I = ev.x * q + ev.y * x + ev.z * y;
+    float I = event_sum<NS>(ev.x, ev.y, ev.z, q, x, y);
     flush<NS>(acc_lane, off, r + I);
     r = ev.w * I;                                                           // stored negated
     if (info > 2) {
         const float4 e2 = lds128(oa + 16);
         const int o2 = ldsi32(ob + 4);
-        I = e2.x * q + e2.y * x + e2.z * y;
+        I = event_sum<NS>(e2.x, e2.y, e2.z, q, x, y);
         flush<NS>(acc_lane, o2, r + I);
         r = e2.w * I;
     }
@@ -642,7 +667,7 @@ __device__ __forceinline__ void pair_front(PairFront &o, const PairRec &r, const
         o.yl = mul2(sgm, Yl);
     }
     // the first event of each column: close a target level, restart the next
-    const u64 I = fma2(r.EZ, o.yl, fma2(r.EY, o.xl, mul2(r.EX, s.B[p])));
+    const u64 I = event_sum2<NS>(r.EX, r.EY, r.EZ, s.B[p], o.xl, o.yl);
     o.tot = add2(s.run[p], I);
     o.rs = mul2(r.NW, I);                                               // restart of the next level
     if (NS) {                                                           // no event: the running sum is kept
@@ -744,7 +769,7 @@ __device__ __noinline__ EndOut end_pair(uint32_t sctx, int t, int kpb, u64 qn, u
         x = pk(xa, xb); y = pk(ya, yb);
     }
     const uint32_t acc_lane = ctx_u32(sctx, CTX_CELL0) + w * ctx_u32(sctx, CTX_CELLB) + ctx_u32(sctx, CTX_ACC) + 4 * lane;
-    const u64 I = fma2(r.EZ, y, fma2(r.EY, x, mul2(r.EX, q)));
+    const u64 I = event_sum2<NS>(r.EX, r.EY, r.EZ, q, x, y);
     float ta_, tb_, ra, rb_, na, nb, qa, qb, xa, xb, ya, yb;
     upk(add2(run, I), ta_, tb_); upk(run, ra, rb_); upk(mul2(r.NW, I), na, nb);     // -w is what the record holds
     flush<NS>(acc_lane, r.oi.x, ta_);
@@ -790,13 +815,13 @@ __device__ __forceinline__ u64 pair_extras(const PairFront &o, const int4 &oi, u
             upk(qB, qa, qb); upk(rs, ra, rb_); upk(o.xl, xa, xb); upk(o.yl, ya, yb);
             if (oi.z == 2) {
                 const float4 ev = lds128(oa);
-                const float I = ev.x * qa + ev.y * xa + ev.z * ya;
+                const float I = event_sum<NS>(ev.x, ev.y, ev.z, qa, xa, ya);
                 flush<NS>(acc_lane, ldsi32(ob), ra + I);
                 ra = ev.w * I;                                              // stored negated
             }
             if (oi.w == 2) {
                 const float4 ev = lds128(oa + MAXE * 16);
-                const float I = ev.x * qb + ev.y * xb + ev.z * yb;
+                const float I = event_sum<NS>(ev.x, ev.y, ev.z, qb, xb, yb);
                 flush<NS>(acc_lane, ldsi32(ob + MAXE * 4), rb_ + I);
                 rb_ = ev.w * I;
             }

@@ -272,6 +272,37 @@ def test_pressure_level_nan_columns_are_skipped(ops, monkeypatch, impl):
     _check_plevel(ops, [fld], delp, area, f, False)
 
 
+@pytest.mark.parametrize("impl", ["composed", "stream", "stream_nansafe"])
+@pytest.mark.parametrize("mask_below", [False, True])
+def test_pressure_level_nan_at_the_column_ends(ops, monkeypatch, impl, mask_below):
+    """NaN in the top two levels (which only seed the streaming walk), in levels 2 and 3 (read ahead by the top end
+    step; through the one-sided cubic they make the edge values of layers 0 and 1 NaN, while the top target level is
+    filled from q alone, mappm.f90:62-64) and in the bottom two (one-sided cubic, extension below the surface).
+    Near the model top the hybrid levels are pure pressure levels: fine and coarse interfaces coincide up to
+    rounding, so whether a NaN layer touches the neighbouring target level hangs on the last bit of delp_coarse -
+    the oracle is therefore given the GPU's own delp_coarse (itself checked to 2e-6)."""
+    _pin_impl(monkeypatch, impl)
+    nt, nc, f = 1, 4, 8
+    ny = nx = nc * f
+    delp = syn.delp_from_ps(syn.surface_pressure((nt, ny, nx), seed=16))
+    area = syn.area((nt, ny, nx), seed=17)
+    fld = syn.field((nt, syn.NZ, ny, nx), 91)
+    for k, y, x in ((0, 1, 1), (1, 2, 9), (2, 11, 3), (3, 12, 20), (-1, 20, 5), (-2, 25, 30), (0, 30, 14), (1, 30, 14)):
+        fld[0, k, y, x] = np.nan
+    outs, dcoarse = ops.pressure_level_average([dev(fld)], dev(delp), dev(area), f, mask_below=mask_below)
+    dc = host(dcoarse)
+    np.testing.assert_allclose(dc, oracle.weighted_block_average(delp, area[:, None], f), rtol=2e-6)
+    if mask_below:
+        remapped, masked = recipes.regrid_given_delp([fld], delp, dc, area)
+        exp = oracle.weighted_block_average(remapped[0], masked, f)
+    else:
+        exp = recipes.pressure_level_average(fld, delp, dc, area, f)
+    g = host(outs[0])
+    ok = np.isfinite(exp)
+    assert np.array_equal(np.isfinite(g), ok)
+    assert np.abs(g[ok] - exp[ok]).max() <= 3e-5 * np.nanmax(np.abs(fld))
+
+
 @pytest.mark.parametrize("mask_below", [False, True])
 def test_pressure_level_nonfinite_values_rerun_only_their_blocks(ops, monkeypatch, mask_below):
     """The streaming kernel's fast pass assumes finite field values and hands the CTAs that saw
