@@ -70,7 +70,15 @@ upsample_kernel(const T *__restrict__ in, T *__restrict__ out, long n_rows, int 
         const int y = (int)(row - o * ny);
         const T *src = in + (o * nyc + min(y / fy, nyc - 1)) * (long)nxc;
         T *dst = out + row * nx;
-        if (vec_ok) {
+        if (vec_ok == 2) {                           // fx a multiple of the vector width: one coarse value per 16-B store
+            for (int x0 = V * lane; x0 < nx; x0 += V * 32) {
+                const T c = src[min(x0 / fx, nxc - 1)];
+                Vec r;
+#pragma unroll
+                for (int j = 0; j < V; ++j) r.v[j] = c;
+                *reinterpret_cast<Vec *>(dst + x0) = r;
+            }
+        } else if (vec_ok) {
             for (int x0 = V * lane; x0 < nx; x0 += V * 32) {
                 Vec r;
 #pragma unroll
@@ -221,7 +229,8 @@ extern "C" int cg_block_upsample(const void *in, void *out, long n_outer, int ny
     const long blocks = (n_rows + 7) / 8;
     const unsigned g = (unsigned)(blocks < 0x7fffffffL ? blocks : 0x7fffffffL);
     const int per16 = dtype == CG_F32 ? 4 : 2;
-    const int vec_ok = nx % per16 == 0 && ((uintptr_t)out & 15) == 0;
+    int vec_ok = nx % per16 == 0 && ((uintptr_t)out & 15) == 0;
+    if (vec_ok && fx % per16 == 0) vec_ok = 2;
     if (dtype == CG_F32) upsample_kernel<float><<<g, 256, 0, st>>>((const float *)in, (float *)out, n_rows, nyc, nxc, fy, fx, ny, nx, vec_ok);
     else upsample_kernel<double><<<g, 256, 0, st>>>((const double *)in, (double *)out, n_rows, nyc, nxc, fy, fx, ny, nx, vec_ok);
     CG_LAUNCH_CHECK("cg_block_upsample");
