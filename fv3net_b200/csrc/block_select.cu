@@ -29,6 +29,27 @@ template <> __device__ __forceinline__ void cswap<float>(float &a, float &b)
     a = lo;
     b = hi;
 }
+// min / max that return NaN when either operand is NaN (FMNMX.NAN): a comparator network built from them carries a
+// NaN input to every output it can reach, so the block's "any NaN -> NaN" rule needs no separate test
+__device__ __forceinline__ float min_nan(float a, float b)
+{
+    float r;
+    asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ float max_nan(float a, float b)
+{
+    float r;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+struct NanF { float v; };                                   // float whose compare-exchange propagates NaN
+__device__ __forceinline__ void cswap(NanF &a, NanF &b)
+{
+    const float lo = min_nan(a.v, b.v), hi = max_nan(a.v, b.v);
+    a.v = lo;
+    b.v = hi;
+}
 
 // Batcher's odd-even merge sort on a register array; N a power of two.  Written as
 // template recursion so every index is a compile-time constant (the array must
@@ -75,31 +96,29 @@ median_f8_f32_kernel(const float *__restrict__ in, float *__restrict__ out, long
     const long o = idx / ((long)nxo * nyo);
     const float *p = in + o * (long)ny * nx + (long)(J * 8) * nx + I * 8;
 
-    float a[32], b[32];
+    NanF a[32], b[32];
 #pragma unroll
     for (int y = 0; y < 4; ++y)
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const float4 v = ldg_stream4(p + (long)y * nx + 4 * h);
             const float4 u = ldg_stream4(p + (long)(y + 4) * nx + 4 * h);
-            a[y * 8 + h * 4 + 0] = v.x; a[y * 8 + h * 4 + 1] = v.y;
-            a[y * 8 + h * 4 + 2] = v.z; a[y * 8 + h * 4 + 3] = v.w;
-            b[y * 8 + h * 4 + 0] = u.x; b[y * 8 + h * 4 + 1] = u.y;
-            b[y * 8 + h * 4 + 2] = u.z; b[y * 8 + h * 4 + 3] = u.w;
+            a[y * 8 + h * 4 + 0].v = v.x; a[y * 8 + h * 4 + 1].v = v.y;
+            a[y * 8 + h * 4 + 2].v = v.z; a[y * 8 + h * 4 + 3].v = v.w;
+            b[y * 8 + h * 4 + 0].v = u.x; b[y * 8 + h * 4 + 1].v = u.y;
+            b[y * 8 + h * 4 + 2].v = u.z; b[y * 8 + h * 4 + 3].v = u.w;
         }
-    bool has_nan = false;
-#pragma unroll
-    for (int i = 0; i < 32; ++i) has_nan = has_nan || (a[i] != a[i]) || (b[i] != b[i]);
-
-    sort_network<float, 32>(a);
-    sort_network<float, 32>(b);
+    // every wire of both halves enters lo or hi below, and a NaN stays on a wire through every comparator: any NaN
+    // in the block makes lo and hi NaN (numpy's median propagates NaN the same way)
+    sort_network<NanF, 32>(a);
+    sort_network<NanF, 32>(b);
     float lo = -INFINITY, hi = INFINITY;
 #pragma unroll
     for (int i = 0; i < 32; ++i) {
-        lo = fmaxf(lo, fminf(a[i], b[31 - i]));
-        hi = fminf(hi, fmaxf(a[i], b[31 - i]));
+        lo = max_nan(lo, min_nan(a[i].v, b[31 - i].v));
+        hi = min_nan(hi, max_nan(a[i].v, b[31 - i].v));
     }
-    out[idx] = has_nan ? NAN : (lo + hi) / 2.0f;
+    out[idx] = (lo + hi) / 2.0f;
 }
 
 // Small power-of-two blocks (N = f*f in {4, 16, 64}), any dtype: full sort in registers.
