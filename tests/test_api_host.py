@@ -224,3 +224,28 @@ def test_compute_without_cuda_fails_loudly():
     da = DataArray(np.ones((4, 4), np.float32), ["x", "y"], name="foo")
     with pytest.raises((CoarsenLibraryError, RuntimeError, AssertionError)):
         C.weighted_block_average(da, da, 2, x_dim="x", y_dim="y")
+
+
+def test_staging_host_helpers_without_a_gpu():
+    """The host-side pieces of the staging layer: binding is a no-op (None, affinity untouched) where NVML or a
+    CUDA device is missing, and the input tree flattens / unflattens losslessly."""
+    import os
+
+    from fv3net_b200 import staging
+
+    before = os.sched_getaffinity(0) if hasattr(os, "sched_getaffinity") else None
+    import torch
+    if not torch.cuda.is_available():
+        assert staging.bind_host_thread(0) is None
+        if before is not None:
+            assert os.sched_getaffinity(0) == before
+    tree = {"middle3d": {"T": np.zeros((1, 2, 8, 8), "f4")}, "middle2d": {"LHTFLsfc": np.ones((1, 8, 8), "f4")},
+            "begin": {"T": np.zeros((1, 2, 8, 8), "f4")}, "end": {"T": np.ones((1, 2, 8, 8), "f4")},
+            "delp": np.full((1, 2, 8, 8), 5.0, "f4"), "area": np.ones((1, 8, 8), "f4"),
+            "exposed_area_fine": np.ones((1, 8, 8), "f4")}
+    flat = staging._flatten(tree)
+    assert list(flat)[-3:] == [("delp", None), ("area", None), ("exposed_area_fine", None)]
+    back = staging._unflatten(flat)
+    assert back["delp"] is tree["delp"] and back["end"]["T"] is tree["end"]["T"]
+    with pytest.raises(Exception):
+        staging.BudgetPipeline().run(tree)              # no CUDA device, no CPU fallback
