@@ -48,7 +48,12 @@ constexpr int NSTAGE = 2;            // == geometry buffers: both are released b
 constexpr int MAXF = CG_MAX_FIELDS;  // output fields per launch (lanes)
 constexpr int MAXSRC = 2 * MAXF;     // distinct parent arrays
 constexpr int NTHREADS = 2 * NCELL * 32;         // field warpgroup + helper warpgroup (its first warp builds the geometry)
-constexpr int CONSUMER_REGS = 184, HELPER_REGS = 72;   // setmaxnreg targets; launch value 128 x 256 threads
+// setmaxnreg targets (launch value 128 x 256 threads; multiples of 8, sum 256).  Measured: 184 / 72 6.50 ms,
+// 176 / 80 and 168 / 88 6.37, 160 / 96 6.49, 192 / 64 6.53 - the geometry warps' code wants its 80 registers
+#ifndef CG_FIELD_REGS
+#define CG_FIELD_REGS 176
+#endif
+constexpr int CONSUMER_REGS = CG_FIELD_REGS, HELPER_REGS = 256 - CG_FIELD_REGS;   // setmaxnreg targets; launch value 128 x 256 threads
 // geometry record of one step and one PAIR of adjacent columns (a, b): 6 x 16 B, pair-interleaved so that
 // the field warps load every coefficient as an f32x2 operand
 //   +0  E1a E1b E2a E2b | +16 Fa Fb Ga Gb | +32 -Ha -Hb dpwa dpwb | +48 exa exb eya eyb
@@ -907,8 +912,8 @@ __device__ __forceinline__ void end_step(uint32_t sctx, uint32_t stage, int t, i
     }
 }
 
-// 128 registers at launch (2 CTAs of 256 threads per SM); the field warpgroup then takes 184 and the
-// geometry warpgroup drops to 72 (setmaxnreg).
+// 128 registers at launch (2 CTAs of 256 threads per SM); the field warpgroup then takes 176 and the
+// geometry warpgroup drops to 80 (setmaxnreg).
 // Two variants.  NS = false (fast): assumes every field value is finite, which lets the block sums drop their
 // NaN tests and selects; it checks that assumption (0 * q summed over everything it reads) and flags the CTA
 // otherwise.  NS = true: NaN-skipping sums exactly like the reference's nansum; launched after the fast one, its
