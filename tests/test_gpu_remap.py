@@ -272,6 +272,24 @@ def test_pressure_level_nan_columns_are_skipped(ops, monkeypatch, impl):
     _check_plevel(ops, [fld], delp, area, f, False)
 
 
+@pytest.mark.parametrize("impl", ["stream", "stream_nansafe", "fused"])
+@pytest.mark.parametrize("nz", [6, 7, 9, 12, 33, 126])
+def test_pressure_level_other_level_counts(ops, monkeypatch, impl, nz):
+    """Shallow and deep columns: the end steps of the streaming walk (t = 2, t = nz, the two steps below the last
+    level) sit in other places of the 4-level stages than at nz = 79, down to a single stage between them."""
+    _pin_impl(monkeypatch, impl)
+    nt, nc, f = 1, 4, 8
+    ny = nx = nc * f
+    rng = np.random.RandomState(100 + nz)
+    ps = syn.surface_pressure((nt, ny, nx), seed=nz)
+    frac = rng.uniform(0.5, 1.5, nz)
+    frac /= frac.sum()
+    delp = ((ps[:, None] - 300.0) * frac[None, :, None, None]).astype(np.float32)
+    area = syn.area((nt, ny, nx), seed=nz + 1)
+    fields = [syn.field((nt, nz, ny, nx), 300 + nz + i, scale=10.0 ** i) for i in range(2)]
+    _check_plevel(ops, fields, delp, area, f, mask_below=bool(nz % 2))
+
+
 @pytest.mark.parametrize("impl", ["composed", "stream", "stream_nansafe"])
 @pytest.mark.parametrize("mask_below", [False, True])
 def test_pressure_level_nan_at_the_column_ends(ops, monkeypatch, impl, mask_below):
