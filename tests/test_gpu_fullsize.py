@@ -138,6 +138,39 @@ def test_config3_pressure_level_c384(ops, mask_below):
     assert (c[fin] + 3.5).abs().max().item() <= 3.5 * 32 * np.finfo("f4").eps
 
 
+@pytest.mark.parametrize("mask_below", [False, True])
+def test_config3_deterministic_under_load(ops, mask_below):
+    """The streaming kernel hands buffers between warps through mbarriers and named barriers; a missed hand-over
+    would show as run-to-run differences.  Twelve runs of a 26-field timestep with a rough surface (many layers cut by
+    several coarse interfaces, many coarse levels below the fine surface: the rare paths), while a second stream keeps
+    the memory system busy, must agree bit for bit."""
+    nt, n = 6, 384
+    dev = torch.device("cuda")
+    g = torch.Generator(device=dev).manual_seed(77)
+    base = syn.torch_delp(nt, n, n, 7, dev)
+    rough = 1.0 + 0.25 * (torch.rand((nt, 1, n, n), generator=g, device=dev) * 2 - 1) * (
+        torch.rand((nt, 1, n, n), generator=g, device=dev) < 0.3)
+    delp = (base * rough).contiguous()
+    area = syn.torch_area((nt, n, n), 8, dev)
+    fields = _budget_fields(nt, n, 22, 90)
+    args = fields + [ops.product(fields[0], fields[1]), ops.product(fields[2], fields[1]),
+                     ops.storage(fields[3], fields[4], 900.0), ops.storage(fields[5], fields[6], 900.0)]
+    ref, dc = ops.pressure_level_average(args, delp, area, F, mask_below=mask_below)
+    ref = [t.clone() for t in ref]
+    noise_a = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    noise_b = torch.empty_like(noise_a)
+    side = torch.cuda.Stream()
+    for i in range(12):
+        if i % 2:
+            with torch.cuda.stream(side):
+                for _ in range(8):
+                    noise_b.copy_(noise_a)
+        outs, _ = ops.pressure_level_average(args, delp, area, F, mask_below=mask_below, want_delp_coarse=False)
+        for a, b in zip(outs, ref):
+            assert torch.equal(torch.nan_to_num(a), torch.nan_to_num(b)) and torch.equal(torch.isnan(a), torch.isnan(b)), i
+    torch.cuda.synchronize()
+
+
 def test_config3_exposed_area_c384(ops):
     nt, n = 6, 384
     dev = torch.device("cuda")
