@@ -169,6 +169,24 @@ def test_config3_deterministic_under_load(ops, mask_below):
         for a, b in zip(outs, ref):
             assert torch.equal(torch.nan_to_num(a), torch.nan_to_num(b)) and torch.equal(torch.isnan(a), torch.isnan(b)), i
     torch.cuda.synchronize()
+    # the rare paths against the oracle on a slab of this rough timestep (ill-conditioned columns: 1e-4 as in
+    # test_gpu_remap.test_pressure_level_hard_columns), with the GPU's own delp_coarse as the target pressures
+    tile, r0 = 5, 192
+    rows = slice(r0, r0 + 2 * F)
+    d_h, a_h = host(delp[tile:tile + 1, :, rows]), host(area[tile:tile + 1, rows])
+    dc_h = host(dc[tile:tile + 1, :, r0 // F:r0 // F + 2])
+    np.testing.assert_allclose(dc_h, oracle.weighted_block_average(d_h, a_h[:, None], F), rtol=2e-6)
+    for v in (0, 7, 21):
+        x = host(fields[v][tile:tile + 1, :, rows])
+        if mask_below:
+            remapped, masked = recipes.regrid_given_delp([x], d_h, dc_h, a_h, threads=8)
+            e = oracle.weighted_block_average(remapped[0], masked, F)
+        else:
+            e = recipes.pressure_level_average(x, d_h, dc_h, a_h, F, threads=8)
+        gg = host(ref[v][tile:tile + 1, :, r0 // F:r0 // F + 2])
+        ok = np.isfinite(e)
+        assert np.array_equal(np.isfinite(gg), ok)
+        assert np.abs(gg[ok] - e[ok]).max() <= 1e-4 * np.abs(x).max()
 
 
 def test_config3_exposed_area_c384(ops):
