@@ -42,6 +42,8 @@ SIGNATURES = {
     "cg_pressure_level_average": (_i, [_vp, _pp, _i, _vp, _vp, _vp, _l, _i, _i, _i, _i, _i, _d,
                                        _vp, _l, _vp]),
     "cg_area_above_fine_surface": (_i, [_vp, _vp, _vp, _vp, _l, _i, _i, _i, _i, _d, _vp]),
+    "cg_static_scratch_bytes": (_l, []),
+    "cg_area_above_fine_surface_static": (_i, [_vp, _vp, _vp, _vp, _l, _i, _i, _i, _i, _d, _vp]),
     "cg_interpolate_2d": (_i, [_vp, _vp, _vp, _vp, _d, _l, _i, _i, _c.POINTER(_l), _vp]),
     "cg_elementwise": (_i, [_i, _vp, _vp, _vp, _d, _vp, _l, _i, _vp]),
     "cg_surface_pressure": (_i, [_vp, _vp, _d, _l, _i, _l, _i, _vp]),

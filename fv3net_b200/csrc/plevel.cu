@@ -13,6 +13,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 namespace cg {
 
@@ -465,5 +466,67 @@ extern "C" int cg_area_above_fine_surface(const float *delp, const float *delp_c
     cudaFreeAsync(pe_c, st);
     if (rc) return rc;
     if (le != cudaSuccess) return cuda_fail(le, "cg_area_above_fine_surface");
+    return CG_OK;
+}
+
+// ---- allocation-free variant (no counterpart in the reference) ----
+// cg_area_above_fine_surface's general form needs two temporaries (fine surface pressure, coarse interface
+// pressures) which it takes from cudaMallocAsync.  Callers that may not allocate (CUDA graph capture, serving
+// loops, harnesses that forbid it) get the same three kernels over a file-scope device array instead.
+// Every GPU that loads the library holds the array until exit.  All calls share it and it keeps the last call's
+// contents: both temporaries are fully overwritten before they are read, so nothing has to be cleared, but
+// calls that overlap on the GPU (different streams, no ordering) race on it.
+namespace cg {
+constexpr long STATIC_SCRATCH_BYTES = 16L << 20;       // 16 MiB: a 6-tile C384 timestep needs 8.0 MiB
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_SCRATCH_BYTES];
+
+// Device address of the array on the current device.  In host code the array's name is only a stand-in for
+// the symbol, not a device pointer: the address comes from cudaGetSymbolAddress, once per device.
+static int static_scratch_ptr(unsigned char **out)
+{
+    constexpr int MAXDEV = 64;
+    static std::mutex mu;
+    static unsigned char *ptrs[MAXDEV] = {nullptr};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+    if (dev < 0 || dev >= MAXDEV) { set_error("device index %d out of range", dev); return CG_ENOTSUP; }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        void *p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_static_scratch)");
+        ptrs[dev] = (unsigned char *)p;
+    }
+    *out = ptrs[dev];
+    return CG_OK;
+}
+}  // namespace cg
+
+extern "C" long cg_static_scratch_bytes(void) { return cg::STATIC_SCRATCH_BYTES; }
+
+extern "C" int cg_area_above_fine_surface_static(const float *delp, const float *delp_coarse, const float *area,
+                                                 float *out, long n_outer, int nz, int ny, int nx, int f,
+                                                 double toa, void *stream)
+{
+    CG_REQUIRE(delp && delp_coarse && area && out, "null pointer");
+    CG_REQUIRE(n_outer >= 0 && nz >= 1 && ny >= 1 && nx >= 1 && f >= 1, "bad shape");
+    CG_REQUIRE(ny % f == 0 && nx % f == 0, "dimension sizes (%d, %d) are not multiples of the factor %d", ny, nx, f);
+    if (n_outer == 0) return CG_OK;
+    const long h = (long)ny * nx, hc = (long)(ny / f) * (nx / f);
+    const long ps_bytes = align256(4 * n_outer * h), pe_bytes = align256(4 * n_outer * (nz + 1) * hc);
+    CG_REQUIRE(ps_bytes + pe_bytes <= STATIC_SCRATCH_BYTES,
+               "cg_area_above_fine_surface_static: needs %ld bytes of scratch, the static array holds %ld; "
+               "use cg_area_above_fine_surface for this size", ps_bytes + pe_bytes, STATIC_SCRATCH_BYTES);
+    unsigned char *scratch = nullptr;
+    int rc = static_scratch_ptr(&scratch);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    float *ps = (float *)scratch, *pe_c = (float *)(scratch + ps_bytes);
+    surface_pressure_kernel<<<grid_for(n_outer * h), 256, 0, st>>>(delp, ps, (float)toa, n_outer, nz, h);
+    CG_LAUNCH_CHECK("cg_area_above_fine_surface_static(surface pressure)");
+    if ((rc = cg_pressure_at_interface(delp_coarse, pe_c, toa, n_outer, nz, hc, CG_F32, st))) return rc;
+    exposed_area_kernel<<<grid_for(n_outer * nz * hc), 256, 0, st>>>(pe_c, delp_coarse, ps, area, out, n_outer, nz, ny, nx, f);
+    CG_LAUNCH_CHECK("cg_area_above_fine_surface_static");
     return CG_OK;
 }

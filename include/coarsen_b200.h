@@ -172,6 +172,19 @@ int cg_area_above_fine_surface(const float *delp, const float *delp_coarse, cons
                                float *out, long n_outer, int nz, int ny, int nx, int f,
                                double toa, void *stream);
 
+/* No counterpart in the reference.
+ * cg_area_above_fine_surface without any allocation, for callers that may not allocate
+ * (CUDA graph capture, serving loops).  Same arguments and result; its two temporaries live
+ * in a file-scope device array of cg_static_scratch_bytes() = 16 MiB that every GPU loading
+ * the library holds until exit.  CG_EINVAL when
+ *   align256(4 n_outer ny nx) + align256(4 n_outer (nz + 1) (ny/f) (nx/f)) exceeds it
+ * (a 6-tile C384 timestep needs 8.0 MiB).  All calls share the array (it keeps the last
+ * call's contents, which are overwritten before use): calls that overlap on the GPU race. */
+long cg_static_scratch_bytes(void);
+int cg_area_above_fine_surface_static(const float *delp, const float *delp_coarse,
+                                      const float *area, float *out, long n_outer, int nz,
+                                      int ny, int nx, int f, double toa, void *stream);
+
 /* ---- restart-coarsening recipes (external/vcm/vcm/cubedsphere/coarsen_restarts.py) ----------- */
 
 /* Element-wise steps between the block kernels, on same-shape dense arrays of one dtype
