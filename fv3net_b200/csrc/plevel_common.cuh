@@ -121,3 +121,152 @@ __device__ __forceinline__ uint32_t opaque(uint32_t v)
     asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"(v));
     return r;
 }
+
+// ---- f32x2: two adjacent columns per instruction ---------------------------------------------------
+__device__ __forceinline__ u64 pk(float lo, float hi)
+{
+    u64 r;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void upk(u64 v, float &lo, float &hi)
+{
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c)
+{
+    u64 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ u64 add2(u64 a, u64 b)
+{
+    u64 r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ u64 sub2(u64 a, u64 b)
+{
+    u64 r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ u64 mul2(u64 a, u64 b)
+{
+    u64 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
+// ---- geometry: what all fields share -----------------------------------------------------------
+constexpr int DUMMY_SLOT = 0;        // accumulator slot k + 1 belongs to target level k; slot 0 collects the rest
+
+struct CellG {                       // shared-window byte addresses of one coarse cell's arrays
+    uint32_t pe2, rdp2;              // coarse interfaces (nz + 1), 1 / thickness of every coarse level
+};
+struct ColG {                        // one fine column
+    float w, ps;                     // block-average weight (NaN -> 0); fine surface pressure (mask_below)
+};
+
+// weight of a fine column in target level k (regridz.py:150-161 when mask_below)
+__device__ __forceinline__ float level_weight(const CellG &g, const ColG &col, int k, int mask_below)
+{
+    if (!mask_below) return col.w;
+    return lds32(g.pe2 + 4 * (k + 1)) < col.ps ? col.w : 0.f;
+}
+// ... times 1 / thickness of that level
+__device__ __forceinline__ float level_scale(const CellG &g, const ColG &col, int k, int mask_below)
+{
+    return level_weight(g, col, k, mask_below) * lds32(g.rdp2 + 4 * k);
+}
+
+// Event of target interface i met in source layer L = [pt, pb] of a column (L == nz: below the
+// surface, pt = surface pressure).  I = x*q + y*x' + z*y' closes a target level: run + I goes to
+// accumulator slot `slot`; the running sum of the next level restarts at -w * I.
+struct Event {
+    float x, y, z, w;
+    int slot;
+};
+__device__ __forceinline__ Event make_event(const CellG &g, const ColG &col, float pt, float pb, int L, int i, int nz,
+                                            int mask_below, float toa)
+{
+    const int kn = nz;
+    Event e = {0.f, 0.f, 0.f, 0.f, DUMMY_SLOT};
+    if (L < nz) {
+        const float pi = lds32(g.pe2 + 4 * i);
+        if (pi <= toa) {                                                // mappm.f90:62-64, only met in L == 0
+            if (i < kn) { e.x = level_weight(g, col, i, mask_below); e.slot = i + 1; }
+        } else {
+            const float dpl = pb - pt;
+            const float s = __fdividef(pi - pt, dpl);
+            const int ke = i - 1;
+            const bool end_ok = ke >= 0 && lds32(g.pe2 + 4 * (ke < 0 ? 0 : ke)) > toa;
+            const bool start_ok = i < kn;
+            const float sc_e = end_ok ? level_scale(g, col, ke, mask_below) : 0.f;
+            const float sc_s = start_ok ? level_scale(g, col, i, mask_below) : 0.f;
+            const float sc = end_ok ? sc_e : sc_s;
+            const float a = sc * dpl * s, oms = 1.f - s;
+            e.x = a;
+            e.y = a * oms * oms;
+            e.z = -a * s * oms;
+            e.w = end_ok ? (sc_e != 0.f ? __fdividef(sc_s, sc_e) : 0.f) : 1.f;
+            e.slot = end_ok ? ke + 1 : DUMMY_SLOT;
+        }
+    } else {                                                            // mappm.f90:65-67, :115-120
+        const float psf = pt;
+        const int ke = i - 1;                                           // level whose bottom is interface i
+        if (ke >= 0 && ke < kn) {
+            const float top = lds32(g.pe2 + 4 * ke);
+            if (top >= psf) { e.x = level_weight(g, col, ke, mask_below); e.slot = ke + 1; }
+            else if (top > toa) { e.x = level_scale(g, col, ke, mask_below) * (lds32(g.pe2 + 4 * i) - psf); e.slot = ke + 1; }
+        }
+    }
+    return e;
+}
+
+// Integral weights times (q, x, y) of one event.  Events that use the layer mean alone - a target interface at or
+// above the column top (mappm.f90:62-64), everything below the surface (:115-120), the empty record - carry
+// z = +0; an event inside a layer always carries z = -(a s (1 - s)) with the sign bit set, even when it is zero
+// (make_event).  The NaN-safe variant drops the edge terms of the former, so that a NaN edge value does not reach
+// a level the Fortran fills from q alone, and keeps them for the latter, where the Fortran evaluates the parabola.
+template <bool NS>
+__device__ __forceinline__ float event_sum(float ex, float ey, float ez, float q, float x, float y)
+{
+    if (NS && __float_as_int(ez) == 0) return ex * q;
+    return ex * q + ey * x + ez * y;
+}
+template <bool NS>
+__device__ __forceinline__ u64 event_sum2(u64 EX, u64 EY, u64 EZ, u64 q, u64 x, u64 y)
+{
+    if (NS) {
+        float eza, ezb, xa, xb, ya, yb;
+        upk(EZ, eza, ezb); upk(x, xa, xb); upk(y, ya, yb);
+        const bool ma = __float_as_int(eza) == 0, mb = __float_as_int(ezb) == 0;
+        x = pk(ma ? 0.f : xa, mb ? 0.f : xb);
+        y = pk(ma ? 0.f : ya, mb ? 0.f : yb);
+    }
+    return fma2(EZ, y, fma2(EY, x, mul2(EX, q)));
+}
+
+// mappm.f90:663-665: sign(min(|df2|, max(q-,q,q+) - q, q - min(q-,q,q+)), df2), by min / max alone
+__device__ __forceinline__ float limited_slope(float df2, float dq_lo, float dq_hi)
+{
+    const float na = -dq_lo;
+    const float hi3 = max3(na, dq_hi, 0.f), nlo = min3(na, dq_hi, 0.f);
+    return max3(min3(df2, hi3, -nlo), -hi3, nlo);
+}
+__device__ __forceinline__ u64 slope2(u64 df2, u64 dlo, u64 dhi)
+{
+    float fa, fb, la, lb, ha, hb;
+    upk(df2, fa, fb); upk(dlo, la, lb); upk(dhi, ha, hb);
+    return pk(limited_slope(fa, la, ha), limited_slope(fb, lb, hb));
+}
+__device__ __forceinline__ u64 clamp2(u64 v, u64 a, u64 b)            // v between a and b, per half
+{
+    float va, vb, aa, ab, ba, bb;
+    upk(v, va, vb); upk(a, aa, ab); upk(b, ba, bb);
+    return pk(fminf(fmaxf(va, fminf(aa, ba)), fmaxf(aa, ba)), fminf(fmaxf(vb, fminf(ab, bb)), fmaxf(ab, bb)));
+}
+
+}  // namespace plv
+}  // namespace cg
