@@ -106,3 +106,117 @@ __host__ __device__ inline Layout make_layout(int nsrc, int nz, int nfw)
     return L;
 }
 
+// ---- geometry warps ---------------------------------------------------------------------------------
+// Step t of column x (geometry warp g handles t = 3 chunk + g): level t arrives.  P(t-3) .. P(t+1) are the
+// column's interface pressures, icnt the coarse interfaces met up to this warp's previous step (3 layers above).
+// Writes the column's half of the pair record:
+//   E1, E2, F-1, G, H: PPM stencil of layer t-1 (mappm.f90:651-683, delp-only factors)
+//   dpw: weight of the whole layer t-2 in the target level open at its bottom
+//   ex, ey, ez, ew, off: the first event of layer t-2 (a no-op when it has none); further events go to the lists
+template <bool NS>
+__device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, float pm1, float p0, float pp1,
+                                              const CellG &g, const ColG &col, int t, int kk, int x, uint32_t rec,
+                                              uint32_t ova, uint32_t ovb, uint32_t tail, uint32_t edge, int nz,
+                                              int mask_below, float toa, int astride)
+{
+    // (approximate division, 2 ulp: these factors multiply differences of q)
+    float E1 = 0.f, E2 = 0.f, Fm = 0.f, G = 0.f, H = 0.f;
+    const int j = t - 1;
+    if (j >= 1 && j <= nz - 2) {
+        const float dm1 = pm1 - pm2, d0 = p0 - pm1, dp1 = pp1 - p0;     // mappm.f90:43 (from the rounded sums)
+        const float d4 = dm1 + d0, d4p = d0 + dp1;
+        const float r4 = __fdividef(1.f, d4), inv = __fdividef(d0, d4 + dp1);
+        E1 = __fdividef(dm1 + 0.5f * d0, d4p) * inv;
+        E2 = (dp1 + 0.5f * d0) * r4 * inv;
+        if (j >= 2) {
+            const float dm2 = pm2 - pm3, d4m = dm2 + dm1;
+            const float cq = dm1 * r4, a1 = __fdividef(d4m, d4 + dm1), a2 = __fdividef(d4p, d4 + d0);
+            const float gg = __fdividef(2.f, d4m + d4p);
+            Fm = cq * (1.f + gg * d0 * (a1 - a2)) - 1.f;
+            G = gg * d0 * a2;
+            H = gg * dm1 * a1;
+        }
+    }
+    // one-sided cubics at the column ends (mappm.f90:689-747), once per column
+    if (t == 2 || t == nz) {
+        const bool top = (t == 2);
+        const float q0 = pm2, q1 = pm1, q2 = p0;                        // P(m), P(m+1), P(m+2), m = 0 or nz - 2
+        const float d1 = top ? q1 - q0 : q2 - q1, d2 = top ? q2 - q1 : q1 - q0;
+        const float D = d2 * (2.f * d2 * d2 + d1 * (d2 + 3.f * d1));
+        const float Pq = d2 * (5.f * d1 + d2) - 3.f * d1 * d1;
+        const float Rr = d1 * d2 * (d2 + 3.f * d1);
+        const float r12 = 1.f / (d1 + d2);
+        // pair-interleaved like the records: word i of column x sits at pair base + 8 i + 4 (x & 1)
+        const uint32_t e = edge + 4 * ((x >> 1) * (2 * EDGE_WORDS) + (x & 1)) + 8 * (top ? 0 : 12);
+        sts32(e, d2 * r12);             sts32(e + 8, d1 * r12);             sts32(e + 16, 2.f * r12);
+        sts32(e + 24, (top ? 4.f : 1.f) / D);
+        sts32(e + 32, d2);              sts32(e + 40, (top ? 0.5f : 2.f) * Pq);
+        sts32(e + 48, (top ? 0.25f : 1.f) * Rr);
+        sts32(e + 56, (top ? 2.f : 8.f) * d1 * d1 * d1);
+        sts32(e + 64, d1);
+    }
+    // events of layer L = t - 2: the coarse interfaces in (top, bottom] of the layer, by the two-pointer merge
+    // (mappm.f90:70-75 keeps k0 the same way); L == nz is everything below the surface
+    const int L = t - 2, kn = nz;
+    const float pt = pm2, pb = pm1;
+    int i0 = icnt, i1 = icnt, open_slot = DUMMY_SLOT;
+    float dpw = 0.f;
+    if (L >= 0 && L <= nz) {
+        if (L == 0) i0 = 0;
+        else {      // this warp last stood at the bottom of layer L - 3: usually two more interfaces since
+            const int lo = i0;
+            i0 = min(i0 + 2, kn + 1);
+            while (i0 > lo && !(lds32(g.pe2 + 4 * (i0 - 1)) <= pt)) --i0;
+            while (i0 <= kn && lds32(g.pe2 + 4 * i0) <= pt) ++i0;
+        }
+        i1 = i0;
+        if (L < nz) {
+            while (i1 <= kn && lds32(g.pe2 + 4 * i1) <= pb) ++i1;
+            const int ko = i1 - 1;                                      // level open at the bottom of L
+            if (ko >= 0 && ko < kn && lds32(g.pe2 + 4 * ko) > toa) {
+                dpw = level_scale(g, col, ko, mask_below) * (pb - pt);
+                open_slot = ko + 1;
+            }
+        } else {
+            i1 = kn + 1;
+        }
+        icnt = i1;
+    }
+    const int n = i1 - i0;
+    const bool below = L == nz;
+    const int cap = below ? TAILMAX : MAXE;
+    const uint32_t oa = ova + (kk * NCOL + x) * (MAXE * 16), ob = ovb + (kk * NCOL + x) * (MAXE * 4);
+    // no coarse interface in the layer: the record is a no-op that keeps the running sum (info = 0); the fast
+    // variant has no such select and instead moves the running sum to the open level's slot early (I = 0)
+    Event e0 = {0.f, 0.f, 0.f, 0.f, (!NS && n == 0) ? open_slot : DUMMY_SLOT};
+    int info = n;
+    const int nlist = n - 1 <= cap ? n : 1;
+    for (int e = 0; e < nlist; ++e) {
+        const Event ev = make_event(g, col, pt, pb, L, i0 + e, nz, mask_below, toa);
+        if (e == 0) e0 = ev;
+        else if (below) {
+            const uint32_t a = tail + (x * TAILMAX + e - 1) * 8;
+            sts32(a, ev.x);
+            stsi32(a + 4, ev.slot * astride);
+        } else {
+            sts128(oa + 16 * (e - 1), make_float4(ev.x, ev.y, ev.z, -ev.w));
+            stsi32(ob + 4 * (e - 1), ev.slot * astride);
+        }
+    }
+    if (n - 1 > cap) {                                                  // park what the field threads need to form them
+        sts128(oa, make_float4(pt, pb, col.w, col.ps));
+        stsi32(ob, i0);
+        stsi32(ob + 4, n);
+        info = INFO_SLOW;
+    }
+    const int other = __shfl_xor_sync(0xffffffffu, info, 1);
+    const uint32_t r = rec + kk * REC_LEVEL + (x >> 1) * 16 + 4 * (x & 1);
+    sts32(r, E1);                           sts32(r + 8, E2);
+    sts32(r + GROUP_BYTES, Fm);             sts32(r + GROUP_BYTES + 8, G);
+    sts32(r + 2 * GROUP_BYTES, -H);         sts32(r + 2 * GROUP_BYTES + 8, dpw);
+    sts32(r + 3 * GROUP_BYTES, e0.x);       sts32(r + 3 * GROUP_BYTES + 8, e0.y);
+    sts32(r + 4 * GROUP_BYTES, e0.z);       sts32(r + 4 * GROUP_BYTES + 8, -e0.w);
+    stsi32(r + 5 * GROUP_BYTES, e0.slot * astride);
+    stsi32(r + 5 * GROUP_BYTES + 8, (x & 1) ? ((info > 1 || other > 1) ? 1 : 0) : (info | other << 8));
+}
+
