@@ -220,3 +220,77 @@ __device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, f
     stsi32(r + 5 * GROUP_BYTES + 8, (x & 1) ? ((info > 1 || other > 1) ? 1 : 0) : (info | other << 8));
 }
 
+// ---- field threads: rare paths (out of line) -------------------------------------------------------
+__device__ __forceinline__ uint32_t ctx_u32(uint32_t sctx, int i) { return (uint32_t)ldsi32(sctx + 4 * i); }
+
+// close a target level with `tot` (NaN-skipping block sum, coarsen.py:211)
+template <bool NS>
+__device__ __forceinline__ void flush(uint32_t acc_item, int off, float tot)
+{
+    red_add(acc_item + off, (!NS || tot == tot) ? tot : 0.f);
+}
+
+// Events 1 .. n-1 of both columns of pair p at step t; r2 = restart values left by the first events.
+// code = kk | buffer << 2 | p << 4 | t << 8 | infos << 16.  Everything the events need is recomputed from the
+// context block so that the call site stays a handful of instructions (3 % of the pair steps of a budget timestep).
+template <bool NS>
+__device__ __noinline__ u64 extras_pair(uint32_t sctx, int code, u64 q2, u64 x2, u64 y2, u64 r2)
+{
+    const int kk = code & 3, b = (code >> 2) & 3, p = (code >> 4) & 15, t = (code >> 8) & 255;
+    const int info2[2] = {(code >> 16) & 255, (code >> 24) & 255};
+    const int nz = ldsi32(sctx + 4 * CTX_NZ);
+    const uint32_t acc_item = ctx_u32(sctx, CTX_ACC) + 4 * threadIdx.x;
+    float qv[2], xv[2], yv[2], rv[2];
+    upk(q2, qv[0], qv[1]); upk(x2, xv[0], xv[1]); upk(y2, yv[0], yv[1]); upk(r2, rv[0], rv[1]);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int info = info2[h];
+        if (info <= 1) continue;
+        const int xc = 2 * p + h;
+        const float q = qv[h], x = xv[h], y = yv[h];
+        float r = rv[h];
+        if (info != INFO_SLOW && t == nz + 2) {                         // below the surface: I = x * q, restart at 0
+            const uint32_t a = ctx_u32(sctx, CTX_TAIL) + xc * (TAILMAX * 8);
+            for (int e = 0; e + 2 <= info; ++e) {
+                const float I = lds32(a + 8 * e) * q;
+                flush<NS>(acc_item, ldsi32(a + 8 * e + 4), r + I);
+                r = 0.f * I;
+            }
+            rv[h] = r;
+            continue;
+        }
+        const uint32_t oa = ctx_u32(sctx, CTX_OVA) + b * OVA_BYTES + (kk * NCOL + xc) * (MAXE * 16);
+        const uint32_t ob = ctx_u32(sctx, CTX_OVB) + b * OVB_BYTES + (kk * NCOL + xc) * (MAXE * 4);
+        if (info != INFO_SLOW) {
+            for (int e = 0; e + 2 <= info; ++e) {
+                const float4 ev = lds128(oa + 16 * e);
+                const float I = event_sum<NS>(ev.x, ev.y, ev.z, q, x, y);
+                flush<NS>(acc_item, ldsi32(ob + 4 * e), r + I);
+                r = ev.w * I;                                           // stored negated
+            }
+            rv[h] = r;
+            continue;
+        }
+        // more than the lists hold (rare): formed on the fly from the column's pressures parked in the list
+        const float4 pp = lds128(oa);                                   // pt, pb, weight, surface pressure
+        const int i0 = ldsi32(ob), n = ldsi32(ob + 4);
+        const int mask_below = ldsi32(sctx + 4 * CTX_MASK), astride = ldsi32(sctx + 4 * CTX_ASTRIDE);
+        const float toa = lds32(sctx + 4 * CTX_TOA);
+        const uint32_t cb = ctx_u32(sctx, CTX_CELL0) + (p >> 2) * ctx_u32(sctx, CTX_CELLB);
+        CellG g;
+        g.pe2 = cb + ctx_u32(sctx, CTX_PE2);
+        g.rdp2 = cb + ctx_u32(sctx, CTX_RDP2);
+        ColG col;
+        col.w = pp.z;
+        col.ps = pp.w;
+        for (int e = 1; e < n; ++e) {
+            const Event ev = make_event(g, col, pp.x, pp.y, t - 2, i0 + e, nz, mask_below, toa);
+            const float I = event_sum<NS>(ev.x, ev.y, ev.z, q, x, y);
+            flush<NS>(acc_item, ev.slot * astride, r + I);
+            r = -(ev.w * I);
+        }
+        rv[h] = r;
+    }
+    return pk(rv[0], rv[1]);
+}
+
