@@ -294,3 +294,115 @@ __device__ __noinline__ u64 extras_pair(uint32_t sctx, int code, u64 q2, u64 x2,
     return pk(rv[0], rv[1]);
 }
 
+// one pair's record of one step
+struct PairRec {
+    u64 E1, E2, Fm, G, NH, DPW, EX, EY, EZ, NW;
+    int4 oi;                         // offa, offb, infos, flag
+};
+__device__ __forceinline__ void load_pair_rec(PairRec &r, uint32_t rb)      // rb = record of the level + 16 p
+{
+    lds2x64(rb, r.E1, r.E2);
+    lds2x64(rb + GROUP_BYTES, r.Fm, r.G);
+    lds2x64(rb + 2 * GROUP_BYTES, r.NH, r.DPW);
+    lds2x64(rb + 3 * GROUP_BYTES, r.EX, r.EY);
+    lds2x64(rb + 4 * GROUP_BYTES, r.EZ, r.NW);
+    r.oi = lds128i(rb + 5 * GROUP_BYTES);
+}
+
+// Both columns of a pair at one of the end steps of the walk (t == 2: nothing above / one-sided cubic at the top,
+// mappm.f90:689-707; t >= nz: one-sided cubic at the bottom, :729-747, the bottom layer, the layer below the
+// surface).  State of the pair: A = q(t-1), B = q(t-2), dq1 = delq(t-1), dcp = dc(t-2), xp = AL(t-2) - q(t-2), run.
+// Returns delq(t), dc(t-1), AL(t-1) - q(t-1), run and the 0 / 1 mask "layer t-1 is not flat".
+// The parabola limiter is the compare form of ppm_limiters lmt = 0 (:875-894): the edges of the top and bottom
+// layers may lie on the same side of the mean, which the sign-splice form of the hot step does not cover.
+// code = kk | buffer << 2 | p << 4.  Out of line: 4 of nz + 1 steps.
+struct EndOut { u64 dq, dc, x, run, mk; };
+template <bool NS>
+__device__ __noinline__ EndOut end_pair(uint32_t sctx, int t, int code, u64 qn, u64 q3, u64 A, u64 B, u64 dq1, u64 dcp,
+                                        u64 xp, u64 run)
+{
+    const int kk = code & 3, b = (code >> 2) & 3, p = (code >> 4) & 15;
+    const int nz = ldsi32(sctx + 4 * CTX_NZ);
+    const uint32_t rec = ctx_u32(sctx, CTX_REC) + b * REC_BYTES;
+    PairRec r;
+    load_pair_rec(r, rec + kk * REC_LEVEL + 16 * p);
+    const u64 half = pk(0.5f, 0.5f);
+    u64 dqn = sub2(qn, A);                                                  // delq(t)
+    const u64 df2 = fma2(r.E1, dqn, mul2(r.E2, dq1));                       // layer t-1, mappm.f90:661
+    u64 dcn = slope2(df2, dq1, dqn);                                        // dc(t-1)
+    u64 xn = fma2(r.NH, dcn, fma2(r.G, dcp, mul2(r.Fm, dq1)));              // AL(t-1) - q(t-1), :674-683
+    u64 x = xp, y = add2(xn, dq1), dc = dcp;                                // layer t-2
+    const uint32_t edge = ctx_u32(sctx, CTX_EDGE) + 4 * (p * (2 * EDGE_WORDS));
+    if (t == 2) {
+        // level 3 is visible (q3; same or next stage): AL of layer 2 from the record of step 3, then the cubic
+        // through the top two layers and that edge.  Step 3 is level 0 of the next stage's records.
+        const uint32_t r3 = ctx_u32(sctx, CTX_REC) + ((b + 1) % NSTAGE) * REC_BYTES + 16 * p;
+        u64 e1, e2, fm, gg, nh, unused;
+        lds2x64(r3, e1, e2); lds2x64(r3 + GROUP_BYTES, fm, gg); lds2x64(r3 + 2 * GROUP_BYTES, nh, unused);
+        const u64 dq3 = sub2(q3, qn);
+        const u64 dc2 = slope2(fma2(e1, dq3, mul2(e2, dqn)), dqn, dq3);
+        const u64 al2 = add2(qn, fma2(nh, dc2, fma2(gg, dcn, mul2(fm, dqn))));
+        u64 c0, c1_, c2, c3_, c4, c5, c6, c7, c8, pad;
+        lds2x64(edge, c0, c1_); lds2x64(edge + 16, c2, c3_); lds2x64(edge + 32, c4, c5); lds2x64(edge + 48, c6, c7);
+        lds2x64(edge + 64, c8, pad);
+        const u64 q0 = B, q1 = A;
+        const u64 qm = fma2(c0, q0, mul2(c1_, q1)), dq = mul2(c2, sub2(q1, q0));
+        const u64 cc = mul2(sub2(sub2(al2, qm), mul2(c4, dq)), c3_);
+        const u64 c3 = sub2(dq, mul2(cc, c5));
+        const u64 inner = sub2(qm, mul2(cc, c6));
+        const u64 top = add2(sub2(mul2(cc, c7), mul2(c3, c8)), inner);
+        const u64 al1 = clamp2(inner, q0, q1);
+        x = sub2(top, q0); y = sub2(al1, q0); dc = mul2(half, sub2(al1, q0)); xn = sub2(al1, q1);
+    } else if (t == nz) {
+        const uint32_t eb = edge + 8 * 12;
+        u64 c0, c1_, c2, c3_, c4, c5, c6, c7, c8, pad;
+        lds2x64(eb, c0, c1_); lds2x64(eb + 16, c2, c3_); lds2x64(eb + 32, c4, c5); lds2x64(eb + 48, c6, c7);
+        lds2x64(eb + 64, c8, pad);
+        const u64 qe = A, qi = B;
+        const u64 ali = add2(qi, xp);
+        const u64 qm = fma2(c0, qe, mul2(c1_, qi)), dq = mul2(c2, sub2(qi, qe));
+        const u64 cc = mul2(sub2(sub2(ali, qm), mul2(c4, dq)), c3_);
+        const u64 c3 = sub2(dq, mul2(cc, c5));
+        const u64 inner = sub2(qm, mul2(cc, c6));
+        const u64 bot = add2(sub2(mul2(cc, c7), mul2(c3, c8)), inner);
+        const u64 alb = clamp2(inner, qe, qi);
+        y = sub2(alb, qi); xn = sub2(alb, qe); dcn = mul2(half, sub2(qe, alb)); dqn = sub2(bot, qe);   // layer nz-1 is finished next step
+    } else if (t == nz + 1) {
+        y = dq1;                                                            // (dq1 holds bottom edge - q(nz-1))
+    } else if (t > nz + 1) {                                                // below the surface
+        x = 0; y = 0; dc = 0;
+    }
+    // limited parabola of layer t-2 in deviation form, x = AL - q, y = AR - q, A6 = -3 (x + y)
+    // (ppm_limiters lmt = 0, mappm.f90:875-894), then the events of the layer and its whole-layer term
+    const u64 q = B;
+    {
+        const u64 da1 = sub2(y, x), sm = add2(x, y);
+        const u64 tt = mul2(sm, da1), da2 = mul2(da1, mul2(da1, pk(1.f / 3.f, 1.f / 3.f)));
+        float xa, xb, ya, yb, ta, tb, ga, gb, ca, cb;
+        upk(x, xa, xb); upk(y, ya, yb); upk(tt, ta, tb); upk(da2, ga, gb); upk(dc, ca, cb);
+        const float mxa = -2.f * xa, mxb = -2.f * xb, mya = -2.f * ya, myb = -2.f * yb;
+        const bool k1a = ta > ga, k2a = -ta > ga, k1b = tb > gb, k2b = -tb > gb;    // k1 and k2 exclude each other (da2 >= 0)
+        ya = k1a ? mxa : ya;    xa = k2a ? mya : xa;                    // a6da < -da2: AR = AL - 3 (AL - q); > da2: AL = AR - 3 (AR - q)
+        yb = k1b ? mxb : yb;    xb = k2b ? myb : xb;
+        xa = ca == 0.f ? 0.f : xa;  ya = ca == 0.f ? 0.f : ya;
+        xb = cb == 0.f ? 0.f : xb;  yb = cb == 0.f ? 0.f : yb;
+        x = pk(xa, xb); y = pk(ya, yb);
+    }
+    const uint32_t acc_item = ctx_u32(sctx, CTX_ACC) + 4 * threadIdx.x;
+    const u64 I = event_sum2<NS>(r.EX, r.EY, r.EZ, q, x, y);
+    float ta_, tb_, ra, rb_, na, nb;
+    upk(add2(run, I), ta_, tb_); upk(run, ra, rb_); upk(mul2(r.NW, I), na, nb);     // -w is what the record holds
+    flush<NS>(acc_item, r.oi.x, ta_);
+    flush<NS>(acc_item, r.oi.y, tb_);
+    const int ia = r.oi.z & 255, ib = (r.oi.z >> 8) & 255;
+    u64 rs = pk((NS && ia == 0) ? ra : na, (NS && ib == 0) ? rb_ : nb);
+    if (r.oi.w) rs = extras_pair<NS>(sctx, kk | b << 2 | p << 4 | t << 8 | r.oi.z << 16, q, x, y, rs);
+    float ca, cb;
+    upk(dcn, ca, cb);
+    EndOut o;
+    o.dq = dqn; o.dc = dcn; o.x = xn;
+    o.mk = pk(ca != 0.f ? 1.f : 0.f, cb != 0.f ? 1.f : 0.f);
+    o.run = fma2(r.DPW, q, rs);
+    return o;
+}
+
