@@ -82,7 +82,7 @@ __host__ __device__ inline Layout make_layout(int nsrc, int nz, int nfw)
 {
     Layout L;
     int o = 0;
-    L.stage_bytes = nsrc * BOX_BYTES;
+    L.stage_bytes = (nsrc * BOX_BYTES + 1023) & ~1023;       // stage bases keep the swizzle phase of a row
     L.ring = o;  o += NSTAGE * L.stage_bytes;    o = (o + 127) & ~127;
     L.bars = o;  o += 128;
     L.cell0 = o;
@@ -404,5 +404,103 @@ __device__ __noinline__ EndOut end_pair(uint32_t sctx, int t, int code, u64 qn, 
     o.mk = pk(ca != 0.f ? 1.f : 0.f, cb != 0.f ? 1.f : 0.f);
     o.run = fma2(r.DPW, q, rs);
     return o;
+}
+
+// ---- field threads: the hot step -----------------------------------------------------------------
+// Rolling state of a work item (two adjacent columns, one field): q(t-1), q(t-2) in a 3-slot ring indexed by
+// t mod 3 = level within the stage (compile time), delq(t-1), dc(t-2), AL(t-2) - q(t-2), the mask "layer t-2 is
+// not flat", the running integral of the target level that is open.
+struct Pair {
+    u64 q[3], dq, dc, xp, mk, run;
+};
+// the per-thread description of a field: byte offsets of its two columns in the parents' boxes for the three
+// levels of a stage (128-B swizzle folded in: stage bases are multiples of 1024), q = (a - c1 b) (c2 b + c3)
+struct Field {
+    int offa[KC], offb[KC];
+    u64 n1, m2, a3;
+};
+template <int KK>
+__device__ __forceinline__ u64 load_q(uint32_t stage, const Field &f, int any_derived)
+{
+    u64 q = lds64(stage + f.offa[KK]);
+    if (any_derived) {                                   // uniform across the launch (budgets.py:80, :151)
+        const u64 b = lds64(stage + f.offb[KK]);
+        q = mul2(fma2(b, f.n1, q), fma2(b, f.m2, f.a3));
+    }
+    return q;
+}
+__device__ __forceinline__ float absmin3_sign(float a, float b, float c, float s)
+{
+    return copysignf(fminf(fminf(fabsf(a), fabsf(b)), fabsf(c)), s);
+}
+__device__ __forceinline__ float absmin2_sign(float a, float b, float s) { return copysignf(fminf(fabsf(a), fabsf(b)), s); }
+
+// One step of the tandem walk for a pair: level t = 3 chunk + S arrives (qn), layer t-2 is finished.
+// recp = record of the step + 16 p; code = buffer << 2 | p << 4.
+// Fast variant (finite values):
+//   dc = sign(df2) min(|df2|, |delq(t-1)|, |delq(t)|) where the two differences agree in sign, else 0
+//        (mappm.f90:663-665: max(q-,q,q+) - q and q - min(q-,q,q+) are |delq(t)|, |delq(t-1)| or 0; df2 is a
+//        positive combination of the two differences, so its sign is theirs)
+//   limiter lmt = 0 (:875-894) in deviation form x = AL - q, y = AR - q: the edges of an interior layer that is
+//        not flat lie on opposite sides of the mean, where "a6da < -da2 -> AR = AL - 3 (AL - q)" and its mirror
+//        are y = sign(y) min(|y|, 2 |x|), x = sign(x) min(|x|, 2 |y|); flat layers through the 0 / 1 mask
+// NaN-safe variant: the compare forms, NaN behaving as in the Fortran.
+template <bool NS, int S>
+__device__ __forceinline__ void hot_step(Pair &s, uint32_t recp, u64 qn, uint32_t acc_item, uint32_t sctx, int code,
+                                         int t, u64 &chk)
+{
+    constexpr int a = (S + 2) % 3, b = (S + 1) % 3;                     // slots of q(t-1), q(t-2)
+    PairRec r;
+    load_pair_rec(r, recp);
+    const u64 A = s.q[a], B = s.q[b], dq1 = s.dq;
+    const u64 dqn = sub2(qn, A);                                        // delq(t)
+    const u64 df2 = fma2(r.E1, dqn, mul2(r.E2, dq1));                   // layer t-1, mappm.f90:661
+    u64 dcn, mkn, xl, yl;
+    if (!NS) {
+        float dfa, dfb, d1a, d1b, dna, dnb, saa, sab, sda, sdb;
+        upk(df2, dfa, dfb); upk(dq1, d1a, d1b); upk(dqn, dna, dnb);
+        upk(add2(dq1, dqn), saa, sab); upk(sub2(dq1, dqn), sda, sdb);
+        mkn = pk(gt01(fabsf(saa), fabsf(sda)), gt01(fabsf(sab), fabsf(sdb)));      // |a + b| > |a - b|  <=>  a b > 0
+        dcn = mul2(pk(absmin3_sign(dfa, d1a, dna, d1a), absmin3_sign(dfb, d1b, dnb, d1b)), mkn);
+    } else {
+        dcn = slope2(df2, dq1, dqn);
+        mkn = 0;
+    }
+    const u64 xn = fma2(r.NH, dcn, fma2(r.G, s.dc, mul2(r.Fm, dq1)));   // AL(t-1) - q(t-1), :674-683
+    if (!NS) {
+        const u64 x = s.xp, y = mul2(add2(xn, dq1), s.mk);
+        float xa, xb, ya, yb, x2a, x2b, y2a, y2b;
+        upk(x, xa, xb); upk(y, ya, yb); upk(add2(x, x), x2a, x2b); upk(add2(y, y), y2a, y2b);
+        xl = pk(absmin2_sign(xa, y2a, xa), absmin2_sign(xb, y2b, xb));
+        yl = pk(absmin2_sign(ya, x2a, ya), absmin2_sign(yb, x2b, yb));
+    } else {
+        const u64 x = s.xp, y = add2(xn, dq1);
+        const u64 da1 = sub2(y, x), sm = add2(x, y);
+        const u64 tt = mul2(sm, da1), da2 = mul2(da1, mul2(da1, pk(1.f / 3.f, 1.f / 3.f)));
+        float xa, xb, ya, yb, ta, tb, ga, gb, ca, cb;
+        upk(x, xa, xb); upk(y, ya, yb); upk(tt, ta, tb); upk(da2, ga, gb); upk(s.dc, ca, cb);
+        const float mxa = -2.f * xa, mxb = -2.f * xb, mya = -2.f * ya, myb = -2.f * yb;
+        ya = ta > ga ? mxa : ya;    xa = -ta > ga ? mya : xa;
+        yb = tb > gb ? mxb : yb;    xb = -tb > gb ? myb : xb;
+        xa = ca == 0.f ? 0.f : xa;  ya = ca == 0.f ? 0.f : ya;
+        xb = cb == 0.f ? 0.f : xb;  yb = cb == 0.f ? 0.f : yb;
+        xl = pk(xa, xb); yl = pk(ya, yb);
+    }
+    // the first event of each column closes a target level and restarts the next
+    const u64 I = event_sum2<NS>(r.EX, r.EY, r.EZ, B, xl, yl);
+    float ta_, tb_;
+    upk(add2(s.run, I), ta_, tb_);
+    flush<NS>(acc_item, r.oi.x, ta_);
+    flush<NS>(acc_item, r.oi.y, tb_);
+    u64 rs = mul2(r.NW, I);
+    if (NS) {                                                           // no event: the running sum is kept
+        float ra, rb_, na, nb;
+        upk(s.run, ra, rb_); upk(rs, na, nb);
+        rs = pk((r.oi.z & 255) == 0 ? ra : na, ((r.oi.z >> 8) & 255) == 0 ? rb_ : nb);
+    }
+    if (r.oi.w) rs = extras_pair<NS>(sctx, S | code | t << 8 | r.oi.z << 16, B, xl, yl, rs);
+    s.run = fma2(r.DPW, B, rs);
+    if (!NS) chk = fma2(qn, 0ull, chk);
+    s.q[S] = qn; s.dq = dqn; s.dc = dcn; s.xp = xn; s.mk = mkn;
 }
 
