@@ -504,3 +504,163 @@ __device__ __forceinline__ void hot_step(Pair &s, uint32_t recp, u64 qn, uint32_
     s.q[S] = qn; s.dq = dqn; s.dc = dcn; s.xp = xn; s.mk = mkn;
 }
 
+// ---- the kernel ------------------------------------------------------------------------------------
+// (nfw + 3) warps: field warps 0 .. nfw-1, then the geometry warps.  128 registers per thread at 512 threads.
+// Two variants.  NS = false (fast): assumes every field value is finite, which lets the block sums drop their
+// NaN tests and selects; it checks that assumption (0 * q summed over everything it reads) and flags the CTA
+// otherwise.  NS = true: NaN-skipping sums exactly like the reference's nansum; launched after the fast one, its
+// CTAs return at once unless flagged (p.flags == nullptr: runs everywhere).
+template <bool NS>
+__global__ void __launch_bounds__((MAXFW + NGW) * 32, 1)
+plevel_pair_kernel(const __grid_constant__ Params p)
+{
+    const int cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
+    if (NS && p.flags && p.flags[cta] == 0) return;
+    extern __shared__ __align__(1024) unsigned char smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int nz = p.nz, V = p.nfields, nsrc = p.nsrc, nfw = p.nfw;
+    const Layout lay = make_layout(nsrc, nz, nfw);
+    const uint32_t sbase = smem_u32(smem);
+    const uint32_t ring = sbase + lay.ring;
+    // mbarriers: full[NSTAGE] (field ring), gfull[NSTAGE] (geometry buffers); stage / buffer b is handed back to
+    // the geometry warps through named barrier 2 + b (bar.arrive by the field warps, bar.sync by the geometry
+    // warps: a blocked warp does not poll)
+    const uint32_t bars = sbase + lay.bars;
+    const uint32_t gfull = bars + 8 * NSTAGE;
+    const uint32_t sctx = sbase + lay.ctx;
+    const int nch = (nz + 3 + KC - 1) / KC;                     // steps t = 0 .. nz + 2
+    const int bx = blockIdx.x, by = blockIdx.y;
+    const long o = blockIdx.z;
+    const float toa = p.toa;
+    const int mask_below = p.mask_below;
+    const uint32_t rec0 = sbase + lay.rec, ova0 = sbase + lay.ova, ovb0 = sbase + lay.ovb, edge = sbase + lay.edge;
+    const uint32_t tail = sbase + lay.tail;
+    const int nthreads = (nfw + NGW) * 32;
+
+    if (tid == 0) {
+        if (!NS) p.flags[cta] = 0;
+        for (int s = 0; s < NSTAGE; ++s) {
+            mbar_init(bars + 8 * s, NGW);                   // full: one expect_tx arrival per geometry warp
+            mbar_init(gfull + 8 * s, NGW);                  // geometry buffer: one arrival per geometry warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;");
+        stsi32(sctx + 4 * CTX_NZ, nz);              stsi32(sctx + 4 * CTX_MASK, mask_below);
+        sts32(sctx + 4 * CTX_TOA, toa);             stsi32(sctx + 4 * CTX_REC, (int)rec0);
+        stsi32(sctx + 4 * CTX_OVA, (int)ova0);      stsi32(sctx + 4 * CTX_OVB, (int)ovb0);
+        stsi32(sctx + 4 * CTX_EDGE, (int)edge);     stsi32(sctx + 4 * CTX_TAIL, (int)tail);
+        stsi32(sctx + 4 * CTX_CELL0, (int)(sbase + lay.cell0));
+        stsi32(sctx + 4 * CTX_CELLB, lay.cell_bytes);
+        stsi32(sctx + 4 * CTX_ACC, (int)(sbase + lay.acc));
+        stsi32(sctx + 4 * CTX_PE2, lay.pe2);        stsi32(sctx + 4 * CTX_RDP2, lay.rdp2);
+        stsi32(sctx + 4 * CTX_ASTRIDE, lay.acc_stride);
+    }
+    __syncthreads();
+
+    const int ny = p.ny, nx = p.nx, nyc = ny >> 3, nxc = nx >> 3;
+    const long h = (long)ny * nx, hc = (long)nyc * nxc;
+
+    if (warp >= nfw) {
+        // ---------------- geometry warp gw: lane = fine column x of the CTA's 32, level 3 chunk + gw ----
+        const int gw = warp - nfw;
+        const int x = lane, cell = x >> 3;
+        const uint32_t colw = sbase + lay.colw, colps = sbase + lay.colps;
+        // CTA prologue: coarse interfaces (sequential cumsum, vertically_dependent.py:61-63), 1 / thickness,
+        // sum of the 64 columns' weights per target level (coarsen.py:212); cells and rows dealt over the warps
+        for (int r = gw; r < 8; r += NGW) {
+            const long col = o * h + (long)(8 * by + r) * nx + NCOL * bx + x;
+            const float a = p.area[col];
+            sts32(colw + 4 * (r * NCOL + x), (a == a) ? a : 0.f);
+            sts32(colps + 4 * (r * NCOL + x), mask_below ? p.psurf[col] : 0.f);
+        }
+        for (int c = gw; c < NCELL; c += NGW) {
+            const uint32_t cbw = sbase + lay.cell0 + c * lay.cell_bytes;
+            for (int k = lane; k < nz; k += 32)
+                sts32(cbw + lay.rdp2 + 4 * k, p.delp_coarse[(o * nz + k) * hc + (long)by * nxc + NCELL * bx + c]);
+            __syncwarp();
+            if (lane == 0) {
+                float pe = toa;
+                sts32(cbw + lay.pe2, pe);
+                for (int k = 0; k < nz; ++k) { pe = pe + lds32(cbw + lay.rdp2 + 4 * k); sts32(cbw + lay.pe2 + 4 * (k + 1), pe); }
+            }
+            __syncwarp();
+            for (int k = lane; k < nz; k += 32)
+                sts32(cbw + lay.rdp2 + 4 * k, 1.f / (lds32(cbw + lay.pe2 + 4 * (k + 1)) - lds32(cbw + lay.pe2 + 4 * k)));
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(NGW * 32) : "memory");     // the geometry warps: weights and cell arrays are in place
+        for (int c = gw; c < NCELL; c += NGW) {
+            const uint32_t cbw = sbase + lay.cell0 + c * lay.cell_bytes;
+            // the cell's 64 columns: rows lane / 8 and 4 + lane / 8, column lane % 8
+            const int xc = 8 * c + (lane & 7), r0 = lane >> 3;
+            const float w0 = lds32(colw + 4 * (r0 * NCOL + xc)), w1 = lds32(colw + 4 * ((r0 + 4) * NCOL + xc));
+            const float s0 = lds32(colps + 4 * (r0 * NCOL + xc)), s1 = lds32(colps + 4 * ((r0 + 4) * NCOL + xc));
+            if (!mask_below) {
+                float d = w0 + w1;
+#pragma unroll
+                for (int m = 1; m < 32; m <<= 1) d += __shfl_xor_sync(0xffffffffu, d, m);
+                for (int k = lane; k < nz; k += 32) sts32(cbw + lay.den + 4 * k, d);
+            } else {
+                for (int k = 0; k < nz; ++k) {
+                    const float lower = lds32(cbw + lay.pe2 + 4 * (k + 1));
+                    float d = (lower < s0 ? w0 : 0.f) + (lower < s1 ? w1 : 0.f);
+#pragma unroll
+                    for (int m = 1; m < 32; m <<= 1) d += __shfl_xor_sync(0xffffffffu, d, m);
+                    if (lane == 0) sts32(cbw + lay.den + 4 * k, d);
+                }
+            }
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(NGW * 32) : "memory");
+        CellG g;
+        g.pe2 = sbase + lay.cell0 + cell * lay.cell_bytes + lay.pe2;
+        g.rdp2 = sbase + lay.cell0 + cell * lay.cell_bytes + lay.rdp2;
+        const float *dcol = p.delp + o * nz * h + (long)(8 * by) * nx + NCOL * bx + x;
+        // thicknesses of levels t-2 .. t of the chunk to come, t = 3 chunk + gw (level t-3 is carried over)
+        float dn[KC];
+        const float *dptr = dcol + (long)(gw - 2) * h;
+        int dlvl = gw - 2;
+        auto load_delp = [&]() {
+#pragma unroll
+            for (int i = 0; i < KC; ++i) {
+                const int lvl = dlvl + i;
+                dn[i] = (lvl >= 0 && lvl < nz) ? ldg_stream(dptr + i * h) : 0.f;
+            }
+            dptr += KC * h;
+            dlvl += KC;
+        };
+        load_delp();
+        const int mine = (nsrc - gw + NGW - 1) / NGW;                // this warp's share of the TMA boxes: gw, gw + 3, ... (<= 18)
+        const CUtensorMap *mymap = &p.maps[gw + NGW * (lane < mine ? lane : 0)];
+        const uint32_t mydst = ring + (gw + NGW * lane) * BOX_BYTES;
+        for (int row = 0; row < 8; ++row) {
+            ColG col;
+            col.w = lds32(colw + 4 * (row * NCOL + x));
+            col.ps = lds32(colps + 4 * (row * NCOL + x));
+            float plast = toa, dcar = 0.f;                           // P(t-3) and the thickness of level t-3
+            int icnt = 0;
+            for (int chunk = 0; chunk < nch; ++chunk) {
+                const int it = row * nch + chunk, b = it % NSTAGE;
+                // interface pressures by the reference's sequential cumsum (vertically_dependent.py:61-63):
+                // every warp carries the running sum of its own column walk, same order of additions
+                const float pm3 = plast, pm2 = pm3 + dcar, pm1 = pm2 + dn[0], p0 = pm1 + dn[1], pp1 = p0 + dn[2];
+                plast = p0;
+                dcar = dn[2];
+                if (chunk + 1 == nch) {                              // on to the next row
+                    dptr = dcol + (long)(gw - 2) * h + (long)(row + 1) * nx;
+                    dlvl = gw - 2;
+                }
+                if (chunk + 1 < nch || row + 1 < 8) load_delp();
+                // stage b of the field ring and geometry buffer b are released together by the field warps
+                if (it >= NSTAGE) asm volatile("bar.sync %0, %1;" ::"r"(2 + b), "r"(nthreads) : "memory");
+                if (lane == 0) mbar_expect_tx(bars + 8 * b, mine * BOX_BYTES);
+                __syncwarp();
+                if (lane < mine)
+                    tma_load_3d(mydst + b * lay.stage_bytes, mymap, NCOL * bx, 8 * by + row, (int)(o * nz) + chunk * KC, bars + 8 * b);
+                if (chunk * KC + gw >= 2)                            // (the records of steps 0 and 1 are not read)
+                    geometry_step<NS>(icnt, pm3, pm2, pm1, p0, pp1, g, col, chunk * KC + gw, gw, x, rec0 + b * REC_BYTES,
+                                      ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, tail, edge, nz, mask_below, toa, lay.acc_stride);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(gfull + 8 * b);
+            }
+        }
+        return;
+    }
+
