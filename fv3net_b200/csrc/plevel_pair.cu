@@ -664,3 +664,101 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         return;
     }
 
+    // ---------------- field threads: work item = (column pair, field) ----------------------------------
+    const int item = tid, nitems = NPAIR * V;
+    const bool active = item < nitems;
+    const int pr = active ? item / V : NPAIR - 1;                    // pair of the CTA row (idle lanes shadow the last one)
+    const int v = active ? item - pr * V : 0;
+    const uint32_t acc_item = sbase + lay.acc + 4 * item;            // every thread owns a column of the accumulator
+    for (int k = 0; k <= nz; ++k) sts32(acc_item + k * lay.acc_stride, 0.f);
+    Field fld;
+    {
+        const int fa = p.fa[v], fb = p.fb[v];
+        const float c1 = p.fc1[v], c2 = p.fc2[v], c3 = p.fc3[v];
+#pragma unroll
+        for (int kk = 0; kk < KC; ++kk) {
+            fld.offa[kk] = fa * BOX_BYTES + kk * 128 + ((((fa * KC + kk) ^ (pr >> 1)) & 7) << 4) + 8 * (pr & 1);
+            fld.offb[kk] = fb * BOX_BYTES + kk * 128 + ((((fb * KC + kk) ^ (pr >> 1)) & 7) << 4) + 8 * (pr & 1);
+        }
+        fld.n1 = pk(-c1, -c1); fld.m2 = pk(c2, c2); fld.a3 = pk(c3, c3);
+    }
+    const int any_derived = p.any_derived;
+    const uint32_t recp = rec0 + 16 * pr;
+    const int hot_end = nz / KC;                                     // chunks 1 .. hot_end - 1 hold levels 3 .. nz - 1 only
+    const int total = 8 * nch;
+
+    u64 chk = 0;
+    for (int row = 0; row < 8; ++row) {
+        Pair st;
+        st.q[0] = st.q[1] = st.q[2] = 0; st.dq = 0; st.dc = 0; st.xp = 0; st.mk = 0; st.run = 0;
+        for (int chunk = 0; chunk < nch; ++chunk) {
+            const int it = row * nch + chunk, b = it % NSTAGE;
+            mbar_wait(gfull + 8 * b, (it / NSTAGE) & 1);
+            mbar_wait(bars + 8 * b, (it / NSTAGE) & 1);
+            const uint32_t stage = ring + b * lay.stage_bytes;
+            const uint32_t rec = recp + b * REC_BYTES;
+            const int code = b << 2 | pr << 4;
+            if (chunk == 0) {
+                // the walk starts at t = 2: levels 0 and 1 only seed the rolling state; the one-sided cubic at the
+                // top needs level 3 and the record of step 3, which are the head of the next stage
+                const int b1 = (it + 1) % NSTAGE;
+                mbar_wait(gfull + 8 * b1, ((it + 1) / NSTAGE) & 1);
+                mbar_wait(bars + 8 * b1, ((it + 1) / NSTAGE) & 1);
+                const u64 l0 = load_q<0>(stage, fld, any_derived), l1 = load_q<1>(stage, fld, any_derived);
+                const u64 l2 = load_q<2>(stage, fld, any_derived);
+                const u64 l3 = load_q<0>(ring + b1 * lay.stage_bytes, fld, any_derived);
+                if (!NS) chk = fma2(l2, 0ull, fma2(l1, 0ull, fma2(l0, 0ull, chk)));
+                const EndOut e = end_pair<NS>(sctx, 2, 2 | code, l2, l3, l1, l0, sub2(l1, l0), 0ull, 0ull, 0ull);
+                st.q[0] = l0; st.q[1] = l1; st.q[2] = l2;
+                st.dq = e.dq; st.dc = e.dc; st.xp = e.x; st.mk = e.mk; st.run = e.run;
+            } else if (chunk < hot_end) {
+                const int t0 = chunk * KC;
+                hot_step<NS, 0>(st, rec, load_q<0>(stage, fld, any_derived), acc_item, sctx, code, t0, chk);
+                hot_step<NS, 1>(st, rec + REC_LEVEL, load_q<1>(stage, fld, any_derived), acc_item, sctx, code, t0 + 1, chk);
+                hot_step<NS, 2>(st, rec + 2 * REC_LEVEL, load_q<2>(stage, fld, any_derived), acc_item, sctx, code, t0 + 2, chk);
+            } else {
+                // the last chunks: levels up to nz - 1, then t = nz, nz + 1 (the bottom layers) and nz + 2 (below the surface)
+#pragma unroll
+                for (int kk = 0; kk < KC; ++kk) {
+                    const int t = chunk * KC + kk;
+                    if (t > nz + 2) continue;
+                    const u64 A = st.q[(kk + 2) % 3], B = st.q[(kk + 1) % 3];
+                    u64 qn = A;
+                    if (t < nz) qn = kk == 0 ? load_q<0>(stage, fld, any_derived) : kk == 1 ? load_q<1>(stage, fld, any_derived) : load_q<2>(stage, fld, any_derived);
+                    if (t < nz) {
+                        if (kk == 0) hot_step<NS, 0>(st, rec, qn, acc_item, sctx, code, t, chk);
+                        else if (kk == 1) hot_step<NS, 1>(st, rec + REC_LEVEL, qn, acc_item, sctx, code, t, chk);
+                        else hot_step<NS, 2>(st, rec + 2 * REC_LEVEL, qn, acc_item, sctx, code, t, chk);
+                    } else {
+                        const EndOut e = end_pair<NS>(sctx, t, kk | code, qn, 0ull, A, B, st.dq, st.dc, st.xp, st.run);
+                        st.q[kk] = qn;
+                        st.dq = e.dq; st.dc = e.dc; st.xp = e.x; st.mk = e.mk; st.run = e.run;
+                    }
+                }
+            }
+            __syncwarp();
+            if (it + NSTAGE < total) asm volatile("bar.arrive %0, %1;" ::"r"(2 + b), "r"(nthreads) : "memory");
+        }
+    }
+    if (!NS) {
+        float c0, c1;
+        upk(chk, c0, c1);
+        if (active && (c0 != c0 || c1 != c1)) p.flags[cta] = 1;
+    }
+
+    // coarse outputs: the four pairs of a cell in a fixed order, block sum / weight sum (coarsen.py:213);
+    // 0/0 -> NaN like the reference
+    asm volatile("bar.sync 5, %0;" ::"r"(nfw * 32) : "memory");
+    const uint32_t acc0 = sbase + lay.acc;
+    for (int idx = tid; idx < nz * NCELL * V; idx += nfw * 32) {
+        const int c = idx % NCELL, vv = (idx / NCELL) % V, k = idx / (NCELL * V);
+        const uint32_t a = acc0 + (k + 1) * lay.acc_stride + 4 * ((NCELL * c) * V + vv);
+        float sum = lds32(a);
+        sum += lds32(a + 4 * V);
+        sum += lds32(a + 8 * V);
+        sum += lds32(a + 12 * V);
+        const float den = lds32(sbase + lay.cell0 + c * lay.cell_bytes + lay.den + 4 * k);
+        p.outs[vv][(o * nz + k) * hc + (long)by * nxc + NCELL * bx + c] = sum / den;
+    }
+}
+
