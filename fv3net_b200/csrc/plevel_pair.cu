@@ -762,3 +762,156 @@ plevel_pair_kernel(const __grid_constant__ Params p)
     }
 }
 
+// ---- host side ----------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn()
+{
+    static EncodeTiledFn fn = [] {
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess) f = nullptr;
+        return (EncodeTiledFn)f;
+    }();
+    return fn;
+}
+
+struct MapKey {
+    const void *ptr;
+    long n_outer;
+    int nz, ny, nx;
+    bool operator==(const MapKey &o) const
+    { return ptr == o.ptr && n_outer == o.n_outer && nz == o.nz && ny == o.ny && nx == o.nx; }
+};
+
+// (n_outer, nz, ny, nx) fp32 as a 3-D tensor (x, y, outer*z); box = [KC levels][1 row][32 columns], 128B swizzle
+static int tensor_map_for(CUtensorMap *out, const float *ptr, long n_outer, int nz, int ny, int nx)
+{
+    struct Entry { MapKey key; CUtensorMap map; };
+    static thread_local Entry cache[128];
+    static thread_local int ncache = 0, next = 0;
+    const MapKey key{ptr, n_outer, nz, ny, nx};
+    for (int i = 0; i < ncache; ++i)
+        if (cache[i].key == key) { *out = cache[i].map; return CG_OK; }
+    EncodeTiledFn enc = encode_fn();
+    if (!enc) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return CG_ECUDA; }
+    const cuuint64_t dims[3] = {(cuuint64_t)nx, (cuuint64_t)ny, (cuuint64_t)(n_outer * nz)};
+    const cuuint64_t strides[2] = {(cuuint64_t)nx * 4, (cuuint64_t)nx * ny * 4};
+    const cuuint32_t box[3] = {32, 1, KC};
+    const cuuint32_t es[3] = {1, 1, 1};
+    CUtensorMap m;
+    const CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void *)ptr, dims, strides, box, es,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return CG_ECUDA; }
+    cache[next].key = key;
+    cache[next].map = m;
+    next = (next + 1) % 128;
+    if (ncache < 128) ++ncache;
+    *out = m;
+    return CG_OK;
+}
+
+constexpr int SMEM_LIMIT = 227 * 1024 - 1024;
+
+// one launch: nfields <= MAXV output fields
+static int launch_group(const cg_field *fields, float *const *outs, int nfields, const float *delp, const float *area,
+                        const float *delp_coarse, const float *psurf, int *flags, long n_outer, int nz, int ny, int nx,
+                        int mask_below, float toa, int nansafe_only, cudaStream_t st)
+{
+    static Params p;                       // ~8 KB: keep it off the stack; filled under a lock
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
+    const float *srcs[MAXSRC];
+    int nsrc = 0, any_derived = 0;
+    auto source_index = [&](const float *ptr) {
+        for (int i = 0; i < nsrc; ++i)
+            if (srcs[i] == ptr) return i;
+        srcs[nsrc] = ptr;
+        return nsrc++;
+    };
+    for (int v = 0; v < nfields; ++v) {
+        p.fa[v] = source_index(fields[v].a);
+        p.fb[v] = fields[v].op != CG_FIELD_PLAIN ? source_index(fields[v].b) : p.fa[v];
+        p.fc1[v] = fields[v].op == CG_FIELD_DIFF ? 1.f : 0.f;
+        p.fc2[v] = fields[v].op == CG_FIELD_PRODUCT ? 1.f : 0.f;
+        p.fc3[v] = fields[v].op == CG_FIELD_DIFF ? 1.f / fields[v].scale : (fields[v].op == CG_FIELD_PRODUCT ? 0.f : 1.f);
+        any_derived |= fields[v].op != CG_FIELD_PLAIN;
+        p.outs[v] = outs[v];
+    }
+    p.any_derived = any_derived;
+    const int nfw = (NPAIR * nfields + 31) / 32;
+    const Layout lay = make_layout(nsrc, nz, nfw);
+    if (lay.total > SMEM_LIMIT) return CG_ENOTSUP;
+    for (int i = 0; i < nsrc; ++i) {
+        if (((uintptr_t)srcs[i]) & 15) return CG_ENOTSUP;
+        const int rc = tensor_map_for(&p.maps[i], srcs[i], n_outer, nz, ny, nx);
+        if (rc) return rc;
+    }
+    p.area = area; p.psurf = psurf; p.delp_coarse = delp_coarse; p.delp = delp;
+    p.nsrc = nsrc; p.nfields = nfields; p.nz = nz; p.ny = ny; p.nx = nx; p.mask_below = mask_below; p.toa = toa;
+    p.nfw = nfw;
+    // per device attributes: cheap, so set on every call (a process may drive several devices)
+    for (int v = 0; v < 2; ++v) {
+        const void *fn = v ? (const void *)plevel_pair_kernel<true> : (const void *)plevel_pair_kernel<false>;
+        cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_LIMIT);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(plevel_pair)");
+        e = cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(carveout)");
+    }
+    dim3 grid(nx / 32, ny / 8, (unsigned)n_outer);
+    const int nthreads = (nfw + NGW) * 32;
+    if (!nansafe_only) {
+        p.flags = flags;
+        plevel_pair_kernel<false><<<grid, nthreads, lay.total, st>>>(p);
+        CG_LAUNCH_CHECK("cg_pressure_level_average(pair)");
+    }
+    p.flags = nansafe_only ? nullptr : flags;
+    plevel_pair_kernel<true><<<grid, nthreads, lay.total, st>>>(p);
+    CG_LAUNCH_CHECK("cg_pressure_level_average(pair, NaN-safe pass)");
+    return CG_OK;
+}
+
+}  // namespace pairk
+
+// groups of at most 26 output fields, each as one launch of 16 V work items per CTA row
+static void pair_groups(int nfields, int &ngroups, int &per)
+{
+    ngroups = (nfields + pairk::MAXV - 1) / pairk::MAXV;
+    per = (nfields + ngroups - 1) / ngroups;
+}
+
+int pair_supported(int nfields, int nz, int ny, int nx, int f)
+{
+    if (!(f == 8 && nx % 32 == 0 && ny % 8 == 0 && nz >= 6 && nz <= 250 && nfields >= 1)) return 0;
+    int ng, per;
+    pair_groups(nfields, ng, per);
+    // worst case: every field has two parents
+    const pairk::Layout lay = pairk::make_layout(2 * per, nz, (pairk::NPAIR * per + 31) / 32);
+    return lay.total <= pairk::SMEM_LIMIT;
+}
+
+// fields/outs as in cg_pressure_level_average; delp_coarse (and psurf when mask_below) already computed
+int launch_plevel_pair(const cg_field *fields, float *const *outs, int nfields, const float *delp,
+                       const float *area, const float *delp_coarse, const float *psurf, int *flags, long n_outer,
+                       int nz, int ny, int nx, int mask_below, float toa, int nansafe_only, cudaStream_t st)
+{
+    if (n_outer > 65535 || n_outer * nz > 0x7fffffffL) return CG_ENOTSUP;
+    if (((uintptr_t)delp) & 3) return CG_ENOTSUP;
+    for (int v = 0; v < nfields; ++v)
+        if ((((uintptr_t)fields[v].a) & 15) || (fields[v].op != CG_FIELD_PLAIN && (((uintptr_t)fields[v].b) & 15))) return CG_ENOTSUP;
+    int ng, per;
+    pair_groups(nfields, ng, per);
+    for (int v0 = 0; v0 < nfields; v0 += per) {
+        const int n = nfields - v0 < per ? nfields - v0 : per;
+        const int rc = pairk::launch_group(fields + v0, outs + v0, n, delp, area, delp_coarse, psurf, flags, n_outer, nz, ny,
+                                           nx, mask_below, toa, nansafe_only, st);
+        if (rc) return rc;       // (CG_ENOTSUP can only come from the first group: the layout bound is the same for all)
+    }
+    return CG_OK;
+}
+
+}  // namespace cg
