@@ -30,6 +30,10 @@ long fused_workspace_bytes(int nfields, long n_outer, int nz, int ny, int nx, in
 int stream_supported(int nfields, int nz, int ny, int nx, int f);
 long stream_workspace_bytes(long n_outer, int nz, int ny, int nx);
 int launch_surface_pressure_seq(const float *delp, float *ps, float toa, long n_outer, int nz, long h, cudaStream_t st);
+int pair_supported(int nfields, int nz, int ny, int nx, int f);
+int launch_plevel_pair(const cg_field *fields, float *const *outs, int nfields, const float *delp,
+                       const float *area, const float *delp_coarse, const float *psurf, int *flags, long n_outer,
+                       int nz, int ny, int nx, int mask_below, float toa, int nansafe_only, cudaStream_t st);
 int launch_plevel_stream(const cg_field *fields, float *const *outs, int nfields, const float *delp,
                          const float *area, const float *delp_coarse, const float *psurf, int *flags, long n_outer,
                          int nz, int ny, int nx, int mask_below, float toa, cudaStream_t st);
@@ -373,6 +377,14 @@ static int stream_path(const cg_field *fields, float *const *outs, int nfields, 
                                        nyc, nxc, CG_F32, CG_F32, st);
     if (rc) return rc;
     if (mask_below && (rc = launch_surface_pressure_seq(delp, ps, toa, n_outer, nz, h, st))) return rc;
+    // the pair-thread kernel where its shared-memory layout fits (CG_PLEVEL_IMPL=stream pins the round-1 kernel)
+    if (!impl_is("stream") && pair_supported(nfields, nz, ny, nx, 8)) {
+        const char *env = getenv("CG_PLEVEL_NANSAFE");
+        rc = launch_plevel_pair(fields, outs, nfields, delp, area, dc, mask_below ? ps : nullptr, flags, n_outer, nz,
+                                ny, nx, mask_below, toa, env && env[0] == '1', st);
+        if (rc != CG_ENOTSUP) return rc;
+    }
+    if (!stream_supported(nfields, nz, ny, nx, 8)) return CG_ENOTSUP;
     return launch_plevel_stream(fields, outs, nfields, delp, area, dc, mask_below ? ps : nullptr, flags, n_outer, nz,
                                 ny, nx, mask_below, toa, st);
 }
@@ -406,7 +418,8 @@ extern "C" int cg_pressure_level_average(const cg_field *fields, float *const *o
     }
     if (n_outer == 0) return CG_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    if (!want_composed() && !impl_is("fused") && nfields > 0 && stream_supported(nfields, nz, ny, nx, f)) {
+    if (!want_composed() && !impl_is("fused") && nfields > 0 &&
+        (stream_supported(nfields, nz, ny, nx, f) || pair_supported(nfields, nz, ny, nx, f))) {
         const int rc = stream_path(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz, ny, nx,
                                    mask_below, (float)toa, workspace, workspace_bytes, st);
         if (rc != CG_ENOTSUP) return rc;        // misaligned pointers / no workspace: next implementation

@@ -150,14 +150,14 @@ def _pin_impl(monkeypatch, impl):
     monkeypatch.delenv("CG_PLEVEL_NANSAFE", raising=False)
     if impl == "default":
         monkeypatch.delenv("CG_PLEVEL_IMPL", raising=False)
-    elif impl == "stream_nansafe":      # the streaming kernel's NaN-skipping variant alone (no fast first pass)
-        monkeypatch.setenv("CG_PLEVEL_IMPL", "stream")
+    elif impl in ("stream_nansafe", "pair_nansafe"):    # the NaN-skipping variant alone (no fast first pass)
+        monkeypatch.setenv("CG_PLEVEL_IMPL", impl.split("_")[0])
         monkeypatch.setenv("CG_PLEVEL_NANSAFE", "1")
     else:
         monkeypatch.setenv("CG_PLEVEL_IMPL", impl)
 
 
-@pytest.mark.parametrize("impl", ["composed", "fused", "stream", "stream_nansafe", "default"])
+@pytest.mark.parametrize("impl", ["composed", "fused", "stream", "stream_nansafe", "pair", "pair_nansafe", "default"])
 @pytest.mark.parametrize("mask_below", [False, True])
 @pytest.mark.parametrize("f,nc", [(8, 4), (2, 4), (16, 2)])  # even coarse sizes: odd = staggered in the reference
 def test_pressure_level_average_vs_oracle(ops, monkeypatch, impl, mask_below, f, nc):
@@ -209,7 +209,7 @@ def _check_plevel(ops, fields, delp, area, f, mask_below, descr=None, tol=3e-5):
         assert np.abs(g[ok] - e[ok]).max() <= tol * scale
 
 
-@pytest.mark.parametrize("impl", ["fused", "stream", "stream_nansafe"])
+@pytest.mark.parametrize("impl", ["fused", "stream", "stream_nansafe", "pair", "pair_nansafe"])
 @pytest.mark.parametrize("mask_below", [False, True])
 def test_pressure_level_budget_shaped_fields(ops, monkeypatch, impl, mask_below):
     """26 output fields like a fine_res_budget timestep: 22 first moments, 2 products and 2
@@ -228,7 +228,7 @@ def test_pressure_level_budget_shaped_fields(ops, monkeypatch, impl, mask_below)
     _check_plevel(ops, fields, delp, area, f, mask_below, descr)
 
 
-@pytest.mark.parametrize("impl", ["composed", "stream", "stream_nansafe"])
+@pytest.mark.parametrize("impl", ["composed", "stream", "stream_nansafe", "pair", "pair_nansafe"])
 @pytest.mark.parametrize("mask_below", [False, True])
 @pytest.mark.parametrize("case", ["rough", "steep", "shifted_top"])
 def test_pressure_level_hard_columns(ops, monkeypatch, impl, mask_below, case):
@@ -256,7 +256,7 @@ def test_pressure_level_hard_columns(ops, monkeypatch, impl, mask_below, case):
     _check_plevel(ops, fields, delp, area, f, mask_below, tol=1e-4)
 
 
-@pytest.mark.parametrize("impl", ["composed", "stream", "stream_nansafe"])
+@pytest.mark.parametrize("impl", ["composed", "stream", "stream_nansafe", "pair", "pair_nansafe"])
 def test_pressure_level_nan_columns_are_skipped(ops, monkeypatch, impl):
     """NaN in a fine column: the block sum skips it where the remapped value is NaN
     (xarray's coarsen().sum() is nansum, coarsen.py:211), other levels keep the column."""
@@ -272,7 +272,7 @@ def test_pressure_level_nan_columns_are_skipped(ops, monkeypatch, impl):
     _check_plevel(ops, [fld], delp, area, f, False)
 
 
-@pytest.mark.parametrize("impl", ["stream", "stream_nansafe", "fused"])
+@pytest.mark.parametrize("impl", ["stream", "stream_nansafe", "pair", "pair_nansafe", "fused"])
 @pytest.mark.parametrize("nz", [6, 7, 9, 12, 33, 126])
 def test_pressure_level_other_level_counts(ops, monkeypatch, impl, nz):
     """Shallow and deep columns: the end steps of the streaming walk (t = 2, t = nz, the two steps below the last
@@ -290,7 +290,7 @@ def test_pressure_level_other_level_counts(ops, monkeypatch, impl, nz):
     _check_plevel(ops, fields, delp, area, f, mask_below=bool(nz % 2))
 
 
-@pytest.mark.parametrize("impl", ["composed", "stream", "stream_nansafe"])
+@pytest.mark.parametrize("impl", ["composed", "stream", "stream_nansafe", "pair", "pair_nansafe"])
 @pytest.mark.parametrize("mask_below", [False, True])
 def test_pressure_level_nan_at_the_column_ends(ops, monkeypatch, impl, mask_below):
     """NaN in the top two levels (which only seed the streaming walk), in levels 2 and 3 (read ahead by the top end
@@ -321,8 +321,9 @@ def test_pressure_level_nan_at_the_column_ends(ops, monkeypatch, impl, mask_belo
     assert np.abs(g[ok] - exp[ok]).max() <= 3e-5 * np.nanmax(np.abs(fld))
 
 
+@pytest.mark.parametrize("kernel", ["stream", "pair"])
 @pytest.mark.parametrize("mask_below", [False, True])
-def test_pressure_level_nonfinite_values_rerun_only_their_blocks(ops, monkeypatch, mask_below):
+def test_pressure_level_nonfinite_values_rerun_only_their_blocks(ops, monkeypatch, mask_below, kernel):
     """The streaming kernel's fast pass assumes finite field values and hands the CTAs that saw
     a NaN or an infinity to the NaN-skipping pass: results must equal the NaN-skipping pass alone,
     bit for bit where no CTA was rerun and everywhere else too (same arithmetic)."""
@@ -335,11 +336,11 @@ def test_pressure_level_nonfinite_values_rerun_only_their_blocks(ops, monkeypatc
     flds[1][0, 78, 40, 40] = np.nan
     flds[2][0, 30:33, 63, 63] = np.inf
     res = {}
-    for impl in ("stream", "stream_nansafe"):
+    for impl in (kernel, kernel + "_nansafe"):
         _pin_impl(monkeypatch, impl)
         outs, _ = ops.pressure_level_average([dev(x) for x in flds], dev(delp), dev(area), f, mask_below=mask_below)
         res[impl] = [host(o) for o in outs]
-    for a, b in zip(res["stream"], res["stream_nansafe"]):
+    for a, b in zip(res[kernel], res[kernel + "_nansafe"]):
         fin = np.isfinite(b)
         assert np.array_equal(np.isfinite(a), fin)
         touched = np.zeros(a.shape, bool)      # CTAs = 4 coarse cells along x: the rerun ones must match exactly
