@@ -38,6 +38,7 @@ SIGNATURES = {
     "cg_mask_weights": (_i, [_vp, _vp, _vp, _vp, _l, _i, _i, _l, _i, _i, _vp]),
     "cg_interp_to_edges": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     "cg_mappm": (_i, [_vp, _vp, _vp, _vp, _l, _l, _i, _i, _c.POINTER(_l), _i, _i, _vp]),
+    "cg_pressure_level_last_impl": (_c.c_char_p, []),
     "cg_pressure_level_workspace_bytes": (_l, [_i, _l, _i, _i, _i, _i]),
     "cg_pressure_level_average": (_i, [_vp, _pp, _i, _vp, _vp, _vp, _l, _i, _i, _i, _i, _i, _d,
                                        _vp, _l, _vp]),

@@ -359,6 +359,7 @@ static bool impl_is(const char *name)
     return e && strcmp(e, name) == 0;
 }
 static bool want_composed() { return impl_is("composed"); }
+static thread_local const char *g_last_impl = "none";
 
 static int stream_path(const cg_field *fields, float *const *outs, int nfields, const float *delp,
                        const float *area, float *delp_coarse, long n_outer, int nz, int ny, int nx,
@@ -382,9 +383,10 @@ static int stream_path(const cg_field *fields, float *const *outs, int nfields, 
         const char *env = getenv("CG_PLEVEL_NANSAFE");
         rc = launch_plevel_pair(fields, outs, nfields, delp, area, dc, mask_below ? ps : nullptr, flags, n_outer, nz,
                                 ny, nx, mask_below, toa, env && env[0] == '1', st);
-        if (rc != CG_ENOTSUP) return rc;
+        if (rc != CG_ENOTSUP) { g_last_impl = "pair"; return rc; }
     }
     if (!stream_supported(nfields, nz, ny, nx, 8)) return CG_ENOTSUP;
+    g_last_impl = "stream";
     return launch_plevel_stream(fields, outs, nfields, delp, area, dc, mask_below ? ps : nullptr, flags, n_outer, nz,
                                 ny, nx, mask_below, toa, st);
 }
@@ -392,6 +394,8 @@ static int stream_path(const cg_field *fields, float *const *outs, int nfields, 
 }  // namespace cg
 
 using namespace cg;
+
+extern "C" const char *cg_pressure_level_last_impl(void) { return g_last_impl; }
 
 extern "C" long cg_pressure_level_workspace_bytes(int nfields, long n_outer, int nz, int ny, int nx, int f)
 {
@@ -427,8 +431,9 @@ extern "C" int cg_pressure_level_average(const cg_field *fields, float *const *o
     if (!want_composed() && !impl_is("stream") && fused_supported(nz, ny, nx, f)) {
         const int rc = launch_plevel_fused(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz,
                                            ny, nx, f, mask_below, (float)toa, workspace, workspace_bytes, st);
-        if (rc != CG_ENOTSUP) return rc;        // misaligned pointers: use the composed path
+        if (rc != CG_ENOTSUP) { g_last_impl = "fused"; return rc; }     // misaligned pointers: use the composed path
     }
+    g_last_impl = "composed";
     return composed(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz, ny, nx, f, mask_below,
                     (float)toa, workspace, workspace_bytes, st);
 }

@@ -884,14 +884,28 @@ static void pair_groups(int nfields, int &ngroups, int &per)
     per = (nfields + ngroups - 1) / ngroups;
 }
 
+// shape constraints alone, with the smallest possible number of sources; launch_plevel_pair checks the real one
 int pair_supported(int nfields, int nz, int ny, int nx, int f)
 {
     if (!(f == 8 && nx % 32 == 0 && ny % 8 == 0 && nz >= 6 && nz <= 250 && nfields >= 1)) return 0;
     int ng, per;
     pair_groups(nfields, ng, per);
-    // worst case: every field has two parents
-    const pairk::Layout lay = pairk::make_layout(2 * per, nz, (pairk::NPAIR * per + 31) / 32);
+    const pairk::Layout lay = pairk::make_layout(1, nz, (pairk::NPAIR * per + 31) / 32);
     return lay.total <= pairk::SMEM_LIMIT;
+}
+
+static int distinct_sources(const cg_field *fields, int n)
+{
+    const float *srcs[pairk::MAXSRC];
+    int nsrc = 0;
+    for (int v = 0; v < n; ++v)
+        for (int h = 0; h < (fields[v].op != CG_FIELD_PLAIN ? 2 : 1); ++h) {
+            const float *ptr = h ? fields[v].b : fields[v].a;
+            int i = 0;
+            while (i < nsrc && srcs[i] != ptr) ++i;
+            if (i == nsrc) srcs[nsrc++] = ptr;
+        }
+    return nsrc;
 }
 
 // fields/outs as in cg_pressure_level_average; delp_coarse (and psurf when mask_below) already computed
@@ -905,11 +919,16 @@ int launch_plevel_pair(const cg_field *fields, float *const *outs, int nfields, 
         if ((((uintptr_t)fields[v].a) & 15) || (fields[v].op != CG_FIELD_PLAIN && (((uintptr_t)fields[v].b) & 15))) return CG_ENOTSUP;
     int ng, per;
     pair_groups(nfields, ng, per);
+    for (int v0 = 0; v0 < nfields; v0 += per) {          // every group must fit before anything is launched
+        const int n = nfields - v0 < per ? nfields - v0 : per;
+        const pairk::Layout lay = pairk::make_layout(distinct_sources(fields + v0, n), nz, (pairk::NPAIR * n + 31) / 32);
+        if (lay.total > pairk::SMEM_LIMIT) return CG_ENOTSUP;
+    }
     for (int v0 = 0; v0 < nfields; v0 += per) {
         const int n = nfields - v0 < per ? nfields - v0 : per;
         const int rc = pairk::launch_group(fields + v0, outs + v0, n, delp, area, delp_coarse, psurf, flags, n_outer, nz, ny,
                                            nx, mask_below, toa, nansafe_only, st);
-        if (rc) return rc;       // (CG_ENOTSUP can only come from the first group: the layout bound is the same for all)
+        if (rc) return rc;
     }
     return CG_OK;
 }

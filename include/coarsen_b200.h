@@ -160,6 +160,9 @@ typedef struct cg_field {
 } cg_field;
 
 long cg_pressure_level_workspace_bytes(int nfields, long n_outer, int nz, int ny, int nx, int f);
+/* which implementation the calling thread's last cg_pressure_level_average ran: "pair", "stream",
+ * "fused", "composed" ("none" before the first call) - for tests and bench records */
+const char *cg_pressure_level_last_impl(void);
 int cg_pressure_level_average(const cg_field *fields, float *const *outs, int nfields,
                               const float *delp, const float *area, float *delp_coarse,
                               long n_outer, int nz, int ny, int nx, int f,

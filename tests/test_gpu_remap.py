@@ -144,7 +144,24 @@ def _plevel_case(nt, nc, f, seed, nfields=3):
     return fields, delp, area
 
 
+_PINNED = {"impl": None}
+
+
+def _check_ran(f, nz):
+    """A pinned kernel must be the one that ran wherever its shape constraints hold (no silent fall-back)."""
+    from fv3net_b200 import _lib
+    impl = _PINNED["impl"]
+    ran = _lib.lib().cg_pressure_level_last_impl().decode()
+    if impl in ("pair", "pair_nansafe", "default") and f == 8 and nz <= 100:
+        assert ran == "pair", ran
+    elif impl in ("stream", "stream_nansafe") and f == 8:
+        assert ran == "stream", ran
+    elif impl == "composed":
+        assert ran == "composed", ran
+
+
 def _pin_impl(monkeypatch, impl):
+    _PINNED["impl"] = impl
     """composed | fused | stream pin one implementation where its shape constraints hold
     (otherwise the next one runs); default = the library's own choice."""
     monkeypatch.delenv("CG_PLEVEL_NANSAFE", raising=False)
@@ -165,6 +182,7 @@ def test_pressure_level_average_vs_oracle(ops, monkeypatch, impl, mask_below, f,
     fields, delp, area = _plevel_case(2, nc, f, seed=5)
     outs, dcoarse = ops.pressure_level_average([dev(x) for x in fields], dev(delp), dev(area), f,
                                                mask_below=mask_below)
+    _check_ran(f, delp.shape[1])
     dc_exp = oracle.weighted_block_average(delp, area[:, None], f)
     np.testing.assert_allclose(host(dcoarse), dc_exp, rtol=2e-6)
     if mask_below:
@@ -194,6 +212,7 @@ def _check_plevel(ops, fields, delp, area, f, mask_below, descr=None, tol=3e-5):
             args.append(ops.storage(d[e[1]], d[e[2]], e[3]))
             cpu.append(((fields[e[1]] - fields[e[2]]) / np.float32(e[3])).astype(np.float32))
     outs, dcoarse = ops.pressure_level_average(args, dev(delp), dev(area), f, mask_below=mask_below)
+    _check_ran(f, delp.shape[1])
     dc_exp = oracle.weighted_block_average(delp, area[:, None], f)
     np.testing.assert_allclose(host(dcoarse), dc_exp, rtol=2e-6)
     if mask_below:
