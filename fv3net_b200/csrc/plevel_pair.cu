@@ -75,7 +75,7 @@ struct Params {
 struct Layout {
     int ring, stage_bytes, bars, cell0, cell_bytes;
     int pe2, rdp2, den;              // within a cell block
-    int rec, ova, ovb, tail, ctx, edge, colw, colps, acc, acc_stride, total;
+    int rec, ova, ovb, tail, ctx, edge, colw, colps, cnt, cnt_bytes, acc, acc_stride, total;
 };
 
 __host__ __device__ inline Layout make_layout(int nsrc, int nz, int nfw)
@@ -100,21 +100,34 @@ __host__ __device__ inline Layout make_layout(int nsrc, int nz, int nfw)
     L.edge = o;  o += NCOL * EDGE_WORDS * 4;
     L.colw = o;  o += 8 * NCOL * 4;              // [row][column of the CTA]
     L.colps = o; o += 8 * NCOL * 4;
+    L.cnt_bytes = ((nz + 2) * NCOL + 127) & ~127;    // per row: coarse interfaces at or above every fine interface
+    L.cnt = o;   o += 2 * L.cnt_bytes;
     L.acc_stride = nfw * 32 * 4;                 // bytes per accumulator slot: one float per work item
     L.acc = o;   o += (nz + 1) * L.acc_stride;
     L.total = o;
     return L;
 }
 
+__device__ __forceinline__ int ldsu8(uint32_t addr)
+{
+    int v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ void stsu8(uint32_t addr, int v)
+{
+    asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
 // ---- geometry warps ---------------------------------------------------------------------------------
 // Step t of column x (geometry warp g handles t = 3 chunk + g): level t arrives.  P(t-3) .. P(t+1) are the
-// column's interface pressures, icnt the coarse interfaces met up to this warp's previous step (3 layers above).
+// column's interface pressures; cnt = the column's entry in the walker's table of the row.
 // Writes the column's half of the pair record:
 //   E1, E2, F-1, G, H: PPM stencil of layer t-1 (mappm.f90:651-683, delp-only factors)
 //   dpw: weight of the whole layer t-2 in the target level open at its bottom
 //   ex, ey, ez, ew, off: the first event of layer t-2 (a no-op when it has none); further events go to the lists
 template <bool NS>
-__device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, float pm1, float p0, float pp1,
+__device__ __forceinline__ void geometry_step(uint32_t cnt, float pm3, float pm2, float pm1, float p0, float pp1,
                                               const CellG &g, const ColG &col, int t, int kk, int x, uint32_t rec,
                                               uint32_t ova, uint32_t ovb, uint32_t tail, uint32_t edge, int nz,
                                               int mask_below, float toa, int astride)
@@ -155,23 +168,17 @@ __device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, f
         sts32(e + 56, (top ? 2.f : 8.f) * d1 * d1 * d1);
         sts32(e + 64, d1);
     }
-    // events of layer L = t - 2: the coarse interfaces in (top, bottom] of the layer, by the two-pointer merge
-    // (mappm.f90:70-75 keeps k0 the same way); L == nz is everything below the surface
+    // events of layer L = t - 2: the coarse interfaces in (top, bottom] of the layer (the two-pointer merge of
+    // mappm.f90:70-75 is the column walker's); L == nz is everything below the surface
     const int L = t - 2, kn = nz;
     const float pt = pm2, pb = pm1;
-    int i0 = icnt, i1 = icnt, open_slot = DUMMY_SLOT;
+    // cnt[L] = number of coarse interfaces at or above the top of layer L, left by the column walker
+    int i0 = 0, i1 = 0, open_slot = DUMMY_SLOT;
     float dpw = 0.f;
     if (L >= 0 && L <= nz) {
-        if (L == 0) i0 = 0;
-        else {      // this warp last stood at the bottom of layer L - 3: usually two more interfaces since
-            const int lo = i0;
-            i0 = min(i0 + 2, kn + 1);
-            while (i0 > lo && !(lds32(g.pe2 + 4 * (i0 - 1)) <= pt)) --i0;
-            while (i0 <= kn && lds32(g.pe2 + 4 * i0) <= pt) ++i0;
-        }
-        i1 = i0;
+        i0 = L == 0 ? 0 : ldsu8(cnt + NCOL * L);
         if (L < nz) {
-            while (i1 <= kn && lds32(g.pe2 + 4 * i1) <= pb) ++i1;
+            i1 = ldsu8(cnt + NCOL * (L + 1));
             const int ko = i1 - 1;                                      // level open at the bottom of L
             if (ko >= 0 && ko < kn && lds32(g.pe2 + 4 * ko) > toa) {
                 dpw = level_scale(g, col, ko, mask_below) * (pb - pt);
@@ -180,7 +187,6 @@ __device__ __forceinline__ void geometry_step(int &icnt, float pm3, float pm2, f
         } else {
             i1 = kn + 1;
         }
-        icnt = i1;
     }
     const int n = i1 - i0;
     const bool below = L == nz;
@@ -505,13 +511,14 @@ __device__ __forceinline__ void hot_step(Pair &s, uint32_t recp, u64 qn, uint32_
 }
 
 // ---- the kernel ------------------------------------------------------------------------------------
-// (nfw + 3) warps: field warps 0 .. nfw-1, then the geometry warps.  128 registers per thread at 512 threads.
+// (nfw + 4) warps: field warps 0 .. nfw-1, the three geometry warps, the column walker.  120 registers per
+// thread at 544 threads.
 // Two variants.  NS = false (fast): assumes every field value is finite, which lets the block sums drop their
 // NaN tests and selects; it checks that assumption (0 * q summed over everything it reads) and flags the CTA
 // otherwise.  NS = true: NaN-skipping sums exactly like the reference's nansum; launched after the fast one, its
 // CTAs return at once unless flagged (p.flags == nullptr: runs everywhere).
 template <bool NS>
-__global__ void __launch_bounds__((MAXFW + NGW) * 32, 1)
+__global__ void __launch_bounds__((MAXFW + NGW + 1) * 32, 1)
 plevel_pair_kernel(const __grid_constant__ Params p)
 {
     const int cta = (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
@@ -527,6 +534,8 @@ plevel_pair_kernel(const __grid_constant__ Params p)
     // warps: a blocked warp does not poll)
     const uint32_t bars = sbase + lay.bars;
     const uint32_t gfull = bars + 8 * NSTAGE;
+    // count tables of the column walker, one per row parity: cfull (walker -> geometry warps), cempty (back)
+    const uint32_t cfull = gfull + 8 * NSTAGE, cempty = cfull + 16;
     const uint32_t sctx = sbase + lay.ctx;
     const int nch = (nz + 3 + KC - 1) / KC;                     // steps t = 0 .. nz + 2
     const int bx = blockIdx.x, by = blockIdx.y;
@@ -542,6 +551,10 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         for (int s = 0; s < NSTAGE; ++s) {
             mbar_init(bars + 8 * s, NGW);                   // full: one expect_tx arrival per geometry warp
             mbar_init(gfull + 8 * s, NGW);                  // geometry buffer: one arrival per geometry warp
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(cfull + 8 * s, 1);
+            mbar_init(cempty + 8 * s, NGW);
         }
         asm volatile("fence.mbarrier_init.release.cluster;");
         stsi32(sctx + 4 * CTX_NZ, nz);              stsi32(sctx + 4 * CTX_MASK, mask_below);
@@ -559,6 +572,45 @@ plevel_pair_kernel(const __grid_constant__ Params p)
     const int ny = p.ny, nx = p.nx, nyc = ny >> 3, nxc = nx >> 3;
     const long h = (long)ny * nx, hc = (long)nyc * nxc;
 
+    if (warp == nfw + NGW) {
+        // ---------------- column walker: lane = fine column, one row ahead of the geometry warps ----------
+        // The two-pointer merge of mappm.f90:70-75: walking the column down with the reference's sequential
+        // cumsum of interface pressures (same additions as the geometry warps: bit-identical), count the coarse
+        // interfaces at or above every fine interface.  cnt[L][x] for L = 1 .. nz; one byte each.
+        const int x = lane;
+        const uint32_t pe2 = sbase + lay.cell0 + (x >> 3) * lay.cell_bytes + lay.pe2;
+        asm volatile("bar.sync 6, %0;" ::"n"((NGW + 1) * 32) : "memory");   // the cells' coarse interfaces are in place
+        const float *dcol = p.delp + o * nz * h + (long)(8 * by) * nx + NCOL * bx + x;
+        constexpr int WB = 8;                                            // levels per batch of loads
+        for (int row = 0; row < 8; ++row) {
+            const float *d = dcol + (long)row * nx;
+            float cur[WB], nxt[WB];
+#pragma unroll
+            for (int i = 0; i < WB; ++i) cur[i] = i < nz ? ldg_stream(d + (long)i * h) : 0.f;
+            if (row >= 2) mbar_wait(cempty + 8 * (row & 1), ((row >> 1) - 1) & 1);
+            const uint32_t crow = sbase + lay.cnt + (row & 1) * lay.cnt_bytes + x;
+            float P = toa, pnext = lds32(pe2);
+            int i = 0;
+            for (int l0 = 0; l0 < nz; l0 += WB) {
+#pragma unroll
+                for (int j = 0; j < WB; ++j) nxt[j] = l0 + WB + j < nz ? ldg_stream(d + (long)(l0 + WB + j) * h) : 0.f;
+#pragma unroll
+                for (int j = 0; j < WB; ++j) {
+                    const int L = l0 + j + 1;                            // interface below level l0 + j
+                    if (L <= nz) {
+                        P = P + cur[j];
+                        while (i <= nz && pnext <= P) { ++i; pnext = lds32(pe2 + 4 * (i <= nz ? i : nz)); }
+                        stsu8(crow + NCOL * L, i);
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < WB; ++j) cur[j] = nxt[j];
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(cfull + 8 * (row & 1));
+        }
+        return;
+    }
     if (warp >= nfw) {
         // ---------------- geometry warp gw: lane = fine column x of the CTA's 32, level 3 chunk + gw ----
         const int gw = warp - nfw;
@@ -608,7 +660,7 @@ plevel_pair_kernel(const __grid_constant__ Params p)
                 }
             }
         }
-        asm volatile("bar.sync 1, %0;" ::"n"(NGW * 32) : "memory");
+        asm volatile("bar.sync 6, %0;" ::"n"((NGW + 1) * 32) : "memory");   // with the column walker
         CellG g;
         g.pe2 = sbase + lay.cell0 + cell * lay.cell_bytes + lay.pe2;
         g.rdp2 = sbase + lay.cell0 + cell * lay.cell_bytes + lay.rdp2;
@@ -635,7 +687,8 @@ plevel_pair_kernel(const __grid_constant__ Params p)
             col.w = lds32(colw + 4 * (row * NCOL + x));
             col.ps = lds32(colps + 4 * (row * NCOL + x));
             float plast = toa, dcar = 0.f;                           // P(t-3) and the thickness of level t-3
-            int icnt = 0;
+            mbar_wait(cfull + 8 * (row & 1), (row >> 1) & 1);
+            const uint32_t cnt = sbase + lay.cnt + (row & 1) * lay.cnt_bytes + x;
             for (int chunk = 0; chunk < nch; ++chunk) {
                 const int it = row * nch + chunk, b = it % NSTAGE;
                 // interface pressures by the reference's sequential cumsum (vertically_dependent.py:61-63):
@@ -655,11 +708,12 @@ plevel_pair_kernel(const __grid_constant__ Params p)
                 if (lane < mine)
                     tma_load_3d(mydst + b * lay.stage_bytes, mymap, NCOL * bx, 8 * by + row, (int)(o * nz) + chunk * KC, bars + 8 * b);
                 if (chunk * KC + gw >= 2)                            // (the records of steps 0 and 1 are not read)
-                    geometry_step<NS>(icnt, pm3, pm2, pm1, p0, pp1, g, col, chunk * KC + gw, gw, x, rec0 + b * REC_BYTES,
+                    geometry_step<NS>(cnt, pm3, pm2, pm1, p0, pp1, g, col, chunk * KC + gw, gw, x, rec0 + b * REC_BYTES,
                                       ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, tail, edge, nz, mask_below, toa, lay.acc_stride);
                 __syncwarp();
                 if (lane == 0) mbar_arrive(gfull + 8 * b);
             }
+            if (lane == 0) mbar_arrive(cempty + 8 * (row & 1));      // (after the __syncwarp of the last step)
         }
         return;
     }
@@ -863,7 +917,7 @@ static int launch_group(const cg_field *fields, float *const *outs, int nfields,
         if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(carveout)");
     }
     dim3 grid(nx / 32, ny / 8, (unsigned)n_outer);
-    const int nthreads = (nfw + NGW) * 32;
+    const int nthreads = (nfw + NGW + 1) * 32;
     if (!nansafe_only) {
         p.flags = flags;
         plevel_pair_kernel<false><<<grid, nthreads, lay.total, st>>>(p);
