@@ -30,8 +30,8 @@ using namespace plv;
 constexpr int NCELL = 4;             // coarse cells per CTA
 constexpr int NCOL = 32;             // fine columns per CTA row = lanes of a geometry warp
 constexpr int NPAIR = NCOL / 2;      // column pairs per CTA row
-constexpr int KC = 3;                // levels per pipeline stage = geometry warps
-constexpr int NGW = KC;
+constexpr int KC = 3;                // levels per pipeline stage
+constexpr int NGW = 2 * KC;          // geometry warps: one per level of a stage, two stages in flight
 constexpr int NSTAGE = 3;
 constexpr int BOX_BYTES = KC * 128;  // one source, one stage: 3 rows of 32 columns (odd row count: 8 swizzle phases over 8 sources)
 constexpr int MAXFW = 13;            // field warps: 16 warps with the geometry warps, 128 registers each
@@ -529,28 +529,29 @@ plevel_pair_kernel(const __grid_constant__ Params p)
     const Layout lay = make_layout(nsrc, nz, nfw);
     const uint32_t sbase = smem_u32(smem);
     const uint32_t ring = sbase + lay.ring;
-    // mbarriers: full[NSTAGE] (field ring), gfull[NSTAGE] (geometry buffers); stage / buffer b is handed back to
-    // the geometry warps through named barrier 2 + b (bar.arrive by the field warps, bar.sync by the geometry
-    // warps: a blocked warp does not poll)
+    // mbarriers: full[NSTAGE] (field ring, TMA).  Named barriers (a blocked warp does not poll): 7 + b = the
+    // records of geometry buffer b are written (bar.arrive by the three geometry warps of the stage, bar.sync by the
+    // field warps); 2 + b = stage / buffer b is handed back (bar.arrive by the field warps, bar.sync by the
+    // geometry warps)
     const uint32_t bars = sbase + lay.bars;
-    const uint32_t gfull = bars + 8 * NSTAGE;
+    const uint32_t gfull = bars + 8 * NSTAGE;                   // (mbarrier slots kept for the layout; unused)
     // count tables of the column walker, one per row parity: cfull (walker -> geometry warps), cempty (back)
     const uint32_t cfull = gfull + 8 * NSTAGE, cempty = cfull + 16;
     const uint32_t sctx = sbase + lay.ctx;
     const int nch = (nz + 3 + KC - 1) / KC;                     // steps t = 0 .. nz + 2
+    const int total = 8 * nch;                                  // stages of the CTA
     const int bx = blockIdx.x, by = blockIdx.y;
     const long o = blockIdx.z;
     const float toa = p.toa;
     const int mask_below = p.mask_below;
     const uint32_t rec0 = sbase + lay.rec, ova0 = sbase + lay.ova, ovb0 = sbase + lay.ovb, edge = sbase + lay.edge;
     const uint32_t tail = sbase + lay.tail;
-    const int nthreads = (nfw + NGW) * 32;
+    const int nthreads = (nfw + KC) * 32;                       // field warps + the geometry warps of one stage
 
     if (tid == 0) {
         if (!NS) p.flags[cta] = 0;
         for (int s = 0; s < NSTAGE; ++s) {
-            mbar_init(bars + 8 * s, NGW);                   // full: one expect_tx arrival per geometry warp
-            mbar_init(gfull + 8 * s, NGW);                  // geometry buffer: one arrival per geometry warp
+            mbar_init(bars + 8 * s, KC);                    // full: one expect_tx arrival per geometry warp of the stage
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(cfull + 8 * s, 1);
@@ -664,57 +665,63 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         CellG g;
         g.pe2 = sbase + lay.cell0 + cell * lay.cell_bytes + lay.pe2;
         g.rdp2 = sbase + lay.cell0 + cell * lay.cell_bytes + lay.rdp2;
+        // warp gw takes level sub of the stages it = par, par + 2, ...: two stages are in the making at any time
+        const int sub = gw % KC, par = gw / KC;
         const float *dcol = p.delp + o * nz * h + (long)(8 * by) * nx + NCOL * bx + x;
-        // thicknesses of levels t-2 .. t of the chunk to come, t = 3 chunk + gw (level t-3 is carried over)
-        float dn[KC];
-        const float *dptr = dcol + (long)(gw - 2) * h;
-        int dlvl = gw - 2;
-        auto load_delp = [&]() {
+        // Interface pressures by the reference's sequential cumsum (vertically_dependent.py:61-63): every warp
+        // carries the running sum of its own column walk, same order of additions.  A step at level t needs
+        // P(t-3) .. P(t+1); the warp's next step of the row is at t + 6.  dn = thicknesses of levels t-3 .. t+2,
+        // loaded one step ahead; e0, e1 = levels t-5, t-4 at the first step of a row, where t <= 5.
+        float dn[2 * KC], e0 = 0.f, e1 = 0.f, pbase = toa;
+        auto load_delp = [&](int it2) {
+            const int row2 = it2 / nch, t2 = (it2 - row2 * nch) * KC + sub;
+            const float *d = dcol + (long)row2 * nx;
 #pragma unroll
-            for (int i = 0; i < KC; ++i) {
-                const int lvl = dlvl + i;
-                dn[i] = (lvl >= 0 && lvl < nz) ? ldg_stream(dptr + i * h) : 0.f;
+            for (int i = 0; i < 2 * KC; ++i) {
+                const int lvl = t2 - 3 + i;
+                dn[i] = (lvl >= 0 && lvl < nz) ? __ldg(d + (long)lvl * h) : 0.f;
             }
-            dptr += KC * h;
-            dlvl += KC;
+            if (t2 < 2 * KC) {                                       // first step of the warp in this row
+                e0 = t2 >= 5 ? __ldg(d + (long)(t2 - 5) * h) : 0.f;
+                e1 = t2 >= 4 ? __ldg(d + (long)(t2 - 4) * h) : 0.f;
+            }
         };
-        load_delp();
-        const int mine = (nsrc - gw + NGW - 1) / NGW;                // this warp's share of the TMA boxes: gw, gw + 3, ... (<= 18)
-        const CUtensorMap *mymap = &p.maps[gw + NGW * (lane < mine ? lane : 0)];
-        const uint32_t mydst = ring + (gw + NGW * lane) * BOX_BYTES;
-        for (int row = 0; row < 8; ++row) {
-            ColG col;
-            col.w = lds32(colw + 4 * (row * NCOL + x));
-            col.ps = lds32(colps + 4 * (row * NCOL + x));
-            float plast = toa, dcar = 0.f;                           // P(t-3) and the thickness of level t-3
-            mbar_wait(cfull + 8 * (row & 1), (row >> 1) & 1);
-            const uint32_t cnt = sbase + lay.cnt + (row & 1) * lay.cnt_bytes + x;
-            for (int chunk = 0; chunk < nch; ++chunk) {
-                const int it = row * nch + chunk, b = it % NSTAGE;
-                // interface pressures by the reference's sequential cumsum (vertically_dependent.py:61-63):
-                // every warp carries the running sum of its own column walk, same order of additions
-                const float pm3 = plast, pm2 = pm3 + dcar, pm1 = pm2 + dn[0], p0 = pm1 + dn[1], pp1 = p0 + dn[2];
-                plast = p0;
-                dcar = dn[2];
-                if (chunk + 1 == nch) {                              // on to the next row
-                    dptr = dcol + (long)(gw - 2) * h + (long)(row + 1) * nx;
-                    dlvl = gw - 2;
-                }
-                if (chunk + 1 < nch || row + 1 < 8) load_delp();
-                // stage b of the field ring and geometry buffer b are released together by the field warps
-                if (it >= NSTAGE) asm volatile("bar.sync %0, %1;" ::"r"(2 + b), "r"(nthreads) : "memory");
-                if (lane == 0) mbar_expect_tx(bars + 8 * b, mine * BOX_BYTES);
-                __syncwarp();
-                if (lane < mine)
-                    tma_load_3d(mydst + b * lay.stage_bytes, mymap, NCOL * bx, 8 * by + row, (int)(o * nz) + chunk * KC, bars + 8 * b);
-                if (chunk * KC + gw >= 2)                            // (the records of steps 0 and 1 are not read)
-                    geometry_step<NS>(cnt, pm3, pm2, pm1, p0, pp1, g, col, chunk * KC + gw, gw, x, rec0 + b * REC_BYTES,
-                                      ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, tail, edge, nz, mask_below, toa, lay.acc_stride);
-                __syncwarp();
-                if (lane == 0) mbar_arrive(gfull + 8 * b);
+        if (par < total) load_delp(par);
+        const int mine = (nsrc - sub + KC - 1) / KC;                 // this warp's share of the TMA boxes: sub, sub + 3, ... (<= 18)
+        const CUtensorMap *mymap = &p.maps[sub + KC * (lane < mine ? lane : 0)];
+        const uint32_t mydst = ring + (sub + KC * lane) * BOX_BYTES;
+        int row = -1;
+        ColG col = {0.f, 0.f};
+        uint32_t cnt = 0;
+        for (int it = par; it < total; it += 2) {
+            const int r2 = it / nch, chunk = it - r2 * nch, b = it % NSTAGE;
+            if (r2 != row) {
+                if (row >= 0) { __syncwarp(); if (lane == 0) mbar_arrive(cempty + 8 * (row & 1)); }
+                row = r2;
+                col.w = lds32(colw + 4 * (row * NCOL + x));
+                col.ps = lds32(colps + 4 * (row * NCOL + x));
+                mbar_wait(cfull + 8 * (row & 1), (row >> 1) & 1);
+                cnt = sbase + lay.cnt + (row & 1) * lay.cnt_bytes + x;
+                pbase = (toa + e0) + e1;
             }
-            if (lane == 0) mbar_arrive(cempty + 8 * (row & 1));      // (after the __syncwarp of the last step)
+            const float pm3 = pbase, pm2 = pm3 + dn[0], pm1 = pm2 + dn[1], p0 = pm1 + dn[2], pp1 = p0 + dn[3];
+            pbase = (pp1 + dn[4]) + dn[5];
+            if (it + 2 < total) load_delp(it + 2);
+            // stage b of the field ring and geometry buffer b are released together by the field warps
+            if (it >= NSTAGE) asm volatile("bar.sync %0, %1;" ::"r"(2 + b), "r"(nthreads) : "memory");
+            if (lane == 0) mbar_expect_tx(bars + 8 * b, mine * BOX_BYTES);
+            __syncwarp();
+            if (lane < mine)
+                tma_load_3d(mydst + b * lay.stage_bytes, mymap, NCOL * bx, 8 * by + row, (int)(o * nz) + chunk * KC, bars + 8 * b);
+            if (chunk * KC + sub >= 2)                               // (the records of steps 0 and 1 are not read)
+                geometry_step<NS>(cnt, pm3, pm2, pm1, p0, pp1, g, col, chunk * KC + sub, sub, x, rec0 + b * REC_BYTES,
+                                  ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, tail, edge, nz, mask_below, toa, lay.acc_stride);
+            __threadfence_block();
+            __syncwarp();
+            asm volatile("bar.arrive %0, %1;" ::"r"(7 + b), "r"(nthreads) : "memory");
         }
+        __syncwarp();
+        if (lane == 0 && row >= 0) mbar_arrive(cempty + 8 * (row & 1));
         return;
     }
 
@@ -739,7 +746,6 @@ plevel_pair_kernel(const __grid_constant__ Params p)
     const int any_derived = p.any_derived;
     const uint32_t recp = rec0 + 16 * pr;
     const int hot_end = nz / KC;                                     // chunks 1 .. hot_end - 1 hold levels 3 .. nz - 1 only
-    const int total = 8 * nch;
 
     u64 chk = 0;
     for (int row = 0; row < 8; ++row) {
@@ -747,7 +753,8 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         st.q[0] = st.q[1] = st.q[2] = 0; st.dq = 0; st.dc = 0; st.xp = 0; st.mk = 0; st.run = 0;
         for (int chunk = 0; chunk < nch; ++chunk) {
             const int it = row * nch + chunk, b = it % NSTAGE;
-            mbar_wait(gfull + 8 * b, (it / NSTAGE) & 1);
+            // (the records of stage 1 of a row were awaited together with stage 0's, see below)
+            if (chunk != 1) asm volatile("bar.sync %0, %1;" ::"r"(7 + b), "r"(nthreads) : "memory");
             mbar_wait(bars + 8 * b, (it / NSTAGE) & 1);
             const uint32_t stage = ring + b * lay.stage_bytes;
             const uint32_t rec = recp + b * REC_BYTES;
@@ -756,7 +763,7 @@ plevel_pair_kernel(const __grid_constant__ Params p)
                 // the walk starts at t = 2: levels 0 and 1 only seed the rolling state; the one-sided cubic at the
                 // top needs level 3 and the record of step 3, which are the head of the next stage
                 const int b1 = (it + 1) % NSTAGE;
-                mbar_wait(gfull + 8 * b1, ((it + 1) / NSTAGE) & 1);
+                asm volatile("bar.sync %0, %1;" ::"r"(7 + b1), "r"(nthreads) : "memory");
                 mbar_wait(bars + 8 * b1, ((it + 1) / NSTAGE) & 1);
                 const u64 l0 = load_q<0>(stage, fld, any_derived), l1 = load_q<1>(stage, fld, any_derived);
                 const u64 l2 = load_q<2>(stage, fld, any_derived);

@@ -25,7 +25,7 @@ if len(sys.argv) > 3:
     print("-- regions")
     for spec in sys.argv[3:]:
         name, a, b = spec.split(':'); a = int(a); b = int(b)
-        sel = [v for k, v in lines.items() if k[0] == 'plevel_stream.cu' and a <= k[1] <= b]
+        sel = [v for k, v in lines.items() if k[0].startswith('plevel_') and a <= k[1] <= b]
         agg = {}
         for v in sel:
             for i, n in enumerate(names):
