@@ -74,7 +74,7 @@ struct Params {
 // ---- shared-memory carve-up --------------------------------------------------------------------
 struct Layout {
     int ring, stage_bytes, bars, cell0, cell_bytes;
-    int pe2, rdp2, den;              // within a cell block
+    int pe2, rdp2, den, ratio;       // within a cell block
     int rec, ova, ovb, tail, ctx, edge, colw, colps, cnt, cnt_bytes, acc, acc_stride, total;
 };
 
@@ -89,7 +89,8 @@ __host__ __device__ inline Layout make_layout(int nsrc, int nz, int nfw)
     int w = 0;
     L.pe2 = w;   w += (nz + 2) * 4;              w = (w + 15) & ~15;
     L.rdp2 = w;  w += (nz + 1) * 4;              w = (w + 15) & ~15;
-    L.den = w;   w += (nz + 1) * 4;
+    L.den = w;   w += (nz + 1) * 4;              w = (w + 15) & ~15;
+    L.ratio = w; w += (nz + 1) * 4;              // thickness of level k - 1 over thickness of level k
     L.cell_bytes = (w + 127) & ~127;
     o += NCELL * L.cell_bytes;
     L.rec = o;   o += NSTAGE * REC_BYTES;
@@ -223,6 +224,92 @@ __device__ __forceinline__ void geometry_step(uint32_t cnt, float pm3, float pm2
     sts32(r + 3 * GROUP_BYTES, e0.x);       sts32(r + 3 * GROUP_BYTES + 8, e0.y);
     sts32(r + 4 * GROUP_BYTES, e0.z);       sts32(r + 4 * GROUP_BYTES + 8, -e0.w);
     stsi32(r + 5 * GROUP_BYTES, e0.slot * astride);
+    stsi32(r + 5 * GROUP_BYTES + 8, (x & 1) ? ((info > 1 || other > 1) ? 1 : 0) : (info | other << 8));
+}
+
+// The same for an interior step, 3 <= t <= nz + 1, t != nz: layer L = t - 2 lies inside the column (1 <= L < nz) and
+// every coarse interface it meets lies below the column top, so make_event reduces to one straight line.
+//   interface i in the layer, s = (pe2[i] - pt) / dpl:  a = scale * dpl * s,  I = a (q + (1-s)^2 x' - s (1-s) y')
+//   closes level i - 1 (i >= 2; level 0 is filled from the top layer's mean, mappm.f90:62-64) and restarts the
+//   running sum of level i at -(thickness(i-1) / thickness(i)) I
+template <bool NS>
+__device__ __forceinline__ void geometry_interior(uint32_t cnt, float pm3, float pm2, float pm1, float p0, float pp1,
+                                                  const CellG &g, uint32_t gratio, float cw, float cps, int t, int kk,
+                                                  int x, uint32_t rec, uint32_t ova, uint32_t ovb, int nz,
+                                                  int mask_below, int astride)
+{
+    float E1 = 0.f, E2 = 0.f, Fm = 0.f, G = 0.f, H = 0.f;
+    if (t <= nz - 1) {                                                  // layer j = t - 1 in 2 .. nz - 2
+        const float dm2 = pm2 - pm3, dm1 = pm1 - pm2, d0 = p0 - pm1, dp1 = pp1 - p0;    // mappm.f90:43 (from the rounded sums)
+        const float d4 = dm1 + d0, d4p = d0 + dp1, d4m = dm2 + dm1;
+        const float r4 = __fdividef(1.f, d4), inv = __fdividef(d0, d4 + dp1);
+        E1 = __fdividef(dm1 + 0.5f * d0, d4p) * inv;
+        E2 = (dp1 + 0.5f * d0) * r4 * inv;
+        const float cq = dm1 * r4, a1 = __fdividef(d4m, d4 + dm1), a2 = __fdividef(d4p, d4 + d0);
+        const float gg = __fdividef(2.f, d4m + d4p);
+        Fm = cq * (1.f + gg * d0 * (a1 - a2)) - 1.f;
+        G = gg * d0 * a2;
+        H = gg * dm1 * a1;
+    }
+    const int L = t - 2;
+    const float pt = pm2, dpl = pm1 - pm2;
+    // the column walker's table: coarse interfaces at or above the top / the bottom of the layer (>= 1)
+    const int i0 = ldsu8(cnt + NCOL * L), i1 = ldsu8(cnt + NCOL * (L + 1));
+    const int n = i1 - i0, ko = i1 - 1;                                 // ko = level open at the bottom of the layer
+    auto scale = [&](int k) {                                           // weight / thickness of level k, 0 <= k < nz
+        float v = cw * lds32(g.rdp2 + 4 * k);
+        if (mask_below) v = lds32(g.pe2 + 4 * (k + 1)) < cps ? v : 0.f; // regridz.py:150-161
+        return v;
+    };
+    auto restart = [&](int i) {                                         // scale(i) / scale(i - 1), 2 <= i <= nz
+        float v = lds32(gratio + 4 * i);                                // (0 at i == nz)
+        if (mask_below) v = lds32(g.pe2 + 4 * (i + 1)) < cps ? v : 0.f; // (the mask only switches off downwards)
+        return v;
+    };
+    const bool open = ko >= 1 && ko < nz;
+    const float dpw = open ? scale(ko < nz ? ko : nz - 1) * dpl : 0.f;
+    const int open_slot = open ? ko + 1 : DUMMY_SLOT;
+    const float rdpl = __fdividef(1.f, dpl);
+    const uint32_t oa = ova + (kk * NCOL + x) * (MAXE * 16), ob = ovb + (kk * NCOL + x) * (MAXE * 4);
+    float ex = 0.f, ey = 0.f, ez = 0.f, ew = 0.f;
+    int slot = NS ? DUMMY_SLOT : open_slot;                             // no interface in the layer: see geometry_step
+    int info = n;
+    {
+        const int i = i0 < nz ? i0 : nz;
+        const bool end_ok = i0 >= 2;
+        const int ks = end_ok ? i - 1 : (i < nz ? i : nz - 1);
+        const float s = (lds32(g.pe2 + 4 * i) - pt) * rdpl, oms = 1.f - s;
+        const float a = scale(ks) * dpl * s;
+        if (n > 0) {
+            ex = a; ey = a * oms * oms; ez = -a * s * oms;
+            ew = end_ok ? restart(i) : 1.f;
+            slot = end_ok ? i : DUMMY_SLOT;
+        }
+    }
+    if (n > 1) {
+        if (n - 1 <= MAXE) {
+            for (int e = 1; e < n; ++e) {
+                const int i = i0 + e;                                   // 2 <= i <= nz
+                const float s = (lds32(g.pe2 + 4 * i) - pt) * rdpl, oms = 1.f - s;
+                const float a = scale(i - 1) * dpl * s;
+                sts128(oa + 16 * (e - 1), make_float4(a, a * oms * oms, -a * s * oms, -restart(i)));
+                stsi32(ob + 4 * (e - 1), i * astride);
+            }
+        } else {                                                        // park what the field threads need to form them
+            sts128(oa, make_float4(pt, pm1, cw, cps));
+            stsi32(ob, i0);
+            stsi32(ob + 4, n);
+            info = INFO_SLOW;
+        }
+    }
+    const int other = __shfl_xor_sync(0xffffffffu, info, 1);
+    const uint32_t r = rec + kk * REC_LEVEL + (x >> 1) * 16 + 4 * (x & 1);
+    sts32(r, E1);                           sts32(r + 8, E2);
+    sts32(r + GROUP_BYTES, Fm);             sts32(r + GROUP_BYTES + 8, G);
+    sts32(r + 2 * GROUP_BYTES, -H);         sts32(r + 2 * GROUP_BYTES + 8, dpw);
+    sts32(r + 3 * GROUP_BYTES, ex);         sts32(r + 3 * GROUP_BYTES + 8, ey);
+    sts32(r + 4 * GROUP_BYTES, ez);         sts32(r + 4 * GROUP_BYTES + 8, -ew);
+    stsi32(r + 5 * GROUP_BYTES, slot * astride);
     stsi32(r + 5 * GROUP_BYTES + 8, (x & 1) ? ((info > 1 || other > 1) ? 1 : 0) : (info | other << 8));
 }
 
@@ -638,6 +725,9 @@ plevel_pair_kernel(const __grid_constant__ Params p)
             __syncwarp();
             for (int k = lane; k < nz; k += 32)
                 sts32(cbw + lay.rdp2 + 4 * k, 1.f / (lds32(cbw + lay.pe2 + 4 * (k + 1)) - lds32(cbw + lay.pe2 + 4 * k)));
+            __syncwarp();
+            for (int k = lane; k <= nz; k += 32)
+                sts32(cbw + lay.ratio + 4 * k, (k >= 1 && k < nz) ? lds32(cbw + lay.rdp2 + 4 * k) / lds32(cbw + lay.rdp2 + 4 * (k - 1)) : 0.f);
         }
         asm volatile("bar.sync 1, %0;" ::"n"(NGW * 32) : "memory");     // the geometry warps: weights and cell arrays are in place
         for (int c = gw; c < NCELL; c += NGW) {
@@ -665,6 +755,7 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         CellG g;
         g.pe2 = sbase + lay.cell0 + cell * lay.cell_bytes + lay.pe2;
         g.rdp2 = sbase + lay.cell0 + cell * lay.cell_bytes + lay.rdp2;
+        const uint32_t gratio = sbase + lay.cell0 + cell * lay.cell_bytes + lay.ratio;
         // warp gw takes level sub of the stages it = par, par + 2, ...: two stages are in the making at any time
         const int sub = gw % KC, par = gw / KC;
         const float *dcol = p.delp + o * nz * h + (long)(8 * by) * nx + NCOL * bx + x;
@@ -673,52 +764,69 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         // P(t-3) .. P(t+1); the warp's next step of the row is at t + 6.  dn = thicknesses of levels t-3 .. t+2,
         // loaded one step ahead; e0, e1 = levels t-5, t-4 at the first step of a row, where t <= 5.
         float dn[2 * KC], e0 = 0.f, e1 = 0.f, pbase = toa;
-        auto load_delp = [&](int it2) {
-            const int row2 = it2 / nch, t2 = (it2 - row2 * nch) * KC + sub;
-            const float *d = dcol + (long)row2 * nx;
+        auto load_delp = [&](int row2, int chunk2) {
+            const int t2 = chunk2 * KC + sub;
+            const float *d = dcol + (long)row2 * nx + (long)(t2 - 3) * h;
+            if (t2 >= 2 * KC && t2 + 2 < nz) {                       // inside the column
 #pragma unroll
-            for (int i = 0; i < 2 * KC; ++i) {
-                const int lvl = t2 - 3 + i;
-                dn[i] = (lvl >= 0 && lvl < nz) ? __ldg(d + (long)lvl * h) : 0.f;
-            }
-            if (t2 < 2 * KC) {                                       // first step of the warp in this row
-                e0 = t2 >= 5 ? __ldg(d + (long)(t2 - 5) * h) : 0.f;
-                e1 = t2 >= 4 ? __ldg(d + (long)(t2 - 4) * h) : 0.f;
+                for (int i = 0; i < 2 * KC; ++i) dn[i] = __ldg(d + i * h);
+            } else {
+#pragma unroll
+                for (int i = 0; i < 2 * KC; ++i) {
+                    const int lvl = t2 - 3 + i;
+                    dn[i] = (lvl >= 0 && lvl < nz) ? __ldg(d + i * h) : 0.f;
+                }
+                if (t2 < 2 * KC) {                                   // first step of the warp in this row
+                    e0 = t2 >= 5 ? __ldg(d - 2 * h) : 0.f;
+                    e1 = t2 >= 4 ? __ldg(d - h) : 0.f;
+                }
             }
         };
-        if (par < total) load_delp(par);
+        int row_n = 0, chunk_n = par, b = par;                       // (nch >= 3: the first stages are in row 0)
+        load_delp(row_n, chunk_n);
         const int mine = (nsrc - sub + KC - 1) / KC;                 // this warp's share of the TMA boxes: sub, sub + 3, ... (<= 18)
         const CUtensorMap *mymap = &p.maps[sub + KC * (lane < mine ? lane : 0)];
         const uint32_t mydst = ring + (sub + KC * lane) * BOX_BYTES;
         int row = -1;
-        ColG col = {0.f, 0.f};
+        float cw = 0.f, cps = 0.f;
         uint32_t cnt = 0;
         for (int it = par; it < total; it += 2) {
-            const int r2 = it / nch, chunk = it - r2 * nch, b = it % NSTAGE;
+            const int chunk = chunk_n, r2 = row_n;
+            chunk_n += 2;
+            if (chunk_n >= nch) { chunk_n -= nch; ++row_n; }
             if (r2 != row) {
                 if (row >= 0) { __syncwarp(); if (lane == 0) mbar_arrive(cempty + 8 * (row & 1)); }
                 row = r2;
-                col.w = lds32(colw + 4 * (row * NCOL + x));
-                col.ps = lds32(colps + 4 * (row * NCOL + x));
+                cw = lds32(colw + 4 * (row * NCOL + x));
+                cps = lds32(colps + 4 * (row * NCOL + x));
                 mbar_wait(cfull + 8 * (row & 1), (row >> 1) & 1);
                 cnt = sbase + lay.cnt + (row & 1) * lay.cnt_bytes + x;
                 pbase = (toa + e0) + e1;
             }
             const float pm3 = pbase, pm2 = pm3 + dn[0], pm1 = pm2 + dn[1], p0 = pm1 + dn[2], pp1 = p0 + dn[3];
             pbase = (pp1 + dn[4]) + dn[5];
-            if (it + 2 < total) load_delp(it + 2);
+            if (it + 2 < total) load_delp(row_n, chunk_n);
             // stage b of the field ring and geometry buffer b are released together by the field warps
             if (it >= NSTAGE) asm volatile("bar.sync %0, %1;" ::"r"(2 + b), "r"(nthreads) : "memory");
             if (lane == 0) mbar_expect_tx(bars + 8 * b, mine * BOX_BYTES);
             __syncwarp();
             if (lane < mine)
                 tma_load_3d(mydst + b * lay.stage_bytes, mymap, NCOL * bx, 8 * by + row, (int)(o * nz) + chunk * KC, bars + 8 * b);
-            if (chunk * KC + sub >= 2)                               // (the records of steps 0 and 1 are not read)
-                geometry_step<NS>(cnt, pm3, pm2, pm1, p0, pp1, g, col, chunk * KC + sub, sub, x, rec0 + b * REC_BYTES,
+            const int t = chunk * KC + sub;
+            if (t >= 3 && t <= nz + 1 && t != nz) {
+                geometry_interior<NS>(cnt, pm3, pm2, pm1, p0, pp1, g, gratio, cw, cps, t, sub, x, rec0 + b * REC_BYTES,
+                                      ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, nz, mask_below, lay.acc_stride);
+            } else if (t >= 2) {                                     // (the records of steps 0 and 1 are not read)
+                ColG col;
+                col.w = cw;
+                col.ps = cps;
+                geometry_step<NS>(cnt, pm3, pm2, pm1, p0, pp1, g, col, t, sub, x, rec0 + b * REC_BYTES,
                                   ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, tail, edge, nz, mask_below, toa, lay.acc_stride);
+            }
             __threadfence_block();
             __syncwarp();
             asm volatile("bar.arrive %0, %1;" ::"r"(7 + b), "r"(nthreads) : "memory");
+            b = b == 0 ? 2 : b - 1;                                  // (it + 2) % 3
         }
         __syncwarp();
         if (lane == 0 && row >= 0) mbar_arrive(cempty + 8 * (row & 1));
