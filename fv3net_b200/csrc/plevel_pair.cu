@@ -34,7 +34,7 @@ constexpr int KC = 3;                // levels per pipeline stage
 constexpr int NGW = 2 * KC;          // geometry warps: one per level of a stage, two stages in flight
 constexpr int NSTAGE = 3;
 constexpr int BOX_BYTES = KC * 128;  // one source, one stage: 3 rows of 32 columns (odd row count: 8 swizzle phases over 8 sources)
-constexpr int MAXFW = 13;            // field warps: 16 warps with the geometry warps, 128 registers each
+constexpr int MAXFW = 13;            // field warps: 20 warps with the geometry warps and the column walker = 5 per scheduler, 96 registers
 constexpr int MAXV = MAXFW * 32 / NPAIR;     // 26 output fields per launch
 constexpr int MAXSRC = 2 * MAXV;
 // geometry record of one step, structure of arrays over the 16 pairs: group g of pair p at g * GROUP_BYTES + 16 p
@@ -56,7 +56,7 @@ enum { CTX_NZ, CTX_MASK, CTX_TOA, CTX_REC, CTX_OVA, CTX_OVB, CTX_EDGE, CTX_TAIL,
        CTX_RDP2, CTX_ASTRIDE, CTX_WORDS };
 
 struct Params {
-    CUtensorMap maps[MAXSRC];
+    const float *src[MAXSRC];        // distinct parent arrays, (n_outer, nz, ny, nx)
     float *outs[MAXV];
     int fa[MAXV], fb[MAXV];          // TMA sources of the parents (fb = fa for a plain field)
     const float *area;               // (n_outer, ny, nx)
@@ -75,7 +75,7 @@ struct Params {
 struct Layout {
     int ring, stage_bytes, bars, cell0, cell_bytes;
     int pe2, rdp2, den, ratio;       // within a cell block
-    int rec, ova, ovb, tail, ctx, edge, colw, colps, cnt, cnt_bytes, acc, acc_stride, total;
+    int rec, ova, ovb, tail, ctx, edge, colw, colps, cnt, cnt_bytes, srow, acc, acc_stride, total;
 };
 
 __host__ __device__ inline Layout make_layout(int nsrc, int nz, int nfw)
@@ -103,12 +103,21 @@ __host__ __device__ inline Layout make_layout(int nsrc, int nz, int nfw)
     L.colps = o; o += 8 * NCOL * 4;
     L.cnt_bytes = ((nz + 2) * NCOL + 127) & ~127;    // per row: coarse interfaces at or above every fine interface
     L.cnt = o;   o += 2 * L.cnt_bytes;
+    L.srow = o;  o += ((nsrc * KC * 8) + 127) & ~127;    // per ring row (source, level of the stage): address of its level 0 plane | level
     L.acc_stride = nfw * 32 * 4;                 // bytes per accumulator slot: one float per work item
     L.acc = o;   o += (nz + 1) * L.acc_stride;
     L.total = o;
     return L;
 }
 
+// 1 / x for the pressure differences of the geometry (never denormal or huge): one MUFU.RCP, none of the range
+// tests that div.approx carries
+__device__ __forceinline__ float frcp(float x)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
 __device__ __forceinline__ int ldsu8(uint32_t addr)
 {
     int v;
@@ -119,6 +128,15 @@ __device__ __forceinline__ void stsu8(uint32_t addr, int v)
 {
     asm volatile("st.shared.u8 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
 }
+
+#ifdef CG_PAIR_TRACE
+// timeline of one CTA (debug builds only): clock64 at the hand-over points of every stage
+constexpr int TRACE_CTA = 700, TRACE_SLOTS = 10, TRACE_STAGES = 256, TRACE_VALS = 6;
+__device__ long long g_trace[TRACE_SLOTS * TRACE_STAGES * TRACE_VALS];
+#define TRACE(slot, it, k) do { if (!NS && cta == TRACE_CTA && lane == 0 && (it) < TRACE_STAGES) g_trace[((slot) * TRACE_STAGES + (it)) * TRACE_VALS + (k)] = clock64(); } while (0)
+#else
+#define TRACE(slot, it, k) do { } while (0)
+#endif
 
 // ---- geometry warps ---------------------------------------------------------------------------------
 // Step t of column x (geometry warp g handles t = 3 chunk + g): level t arrives.  P(t-3) .. P(t+1) are the
@@ -235,18 +253,18 @@ __device__ __forceinline__ void geometry_step(uint32_t cnt, float pm3, float pm2
 template <bool NS>
 __device__ __forceinline__ void geometry_interior(uint32_t cnt, float pm3, float pm2, float pm1, float p0, float pp1,
                                                   const CellG &g, uint32_t gratio, float cw, float cps, int t, int kk,
-                                                  int x, uint32_t rec, uint32_t ova, uint32_t ovb, int nz,
-                                                  int mask_below, int astride)
+                                                  int x, uint32_t rec, uint32_t ova, uint32_t ovb, uint32_t edge,
+                                                  int nz, int mask_below, int astride)
 {
     float E1 = 0.f, E2 = 0.f, Fm = 0.f, G = 0.f, H = 0.f;
     if (t <= nz - 1) {                                                  // layer j = t - 1 in 2 .. nz - 2
         const float dm2 = pm2 - pm3, dm1 = pm1 - pm2, d0 = p0 - pm1, dp1 = pp1 - p0;    // mappm.f90:43 (from the rounded sums)
         const float d4 = dm1 + d0, d4p = d0 + dp1, d4m = dm2 + dm1;
-        const float r4 = __fdividef(1.f, d4), inv = __fdividef(d0, d4 + dp1);
-        E1 = __fdividef(dm1 + 0.5f * d0, d4p) * inv;
+        const float r4 = frcp(d4), inv = d0 * frcp(d4 + dp1);
+        E1 = (dm1 + 0.5f * d0) * frcp(d4p) * inv;
         E2 = (dp1 + 0.5f * d0) * r4 * inv;
-        const float cq = dm1 * r4, a1 = __fdividef(d4m, d4 + dm1), a2 = __fdividef(d4p, d4 + d0);
-        const float gg = __fdividef(2.f, d4m + d4p);
+        const float cq = dm1 * r4, a1 = d4m * frcp(d4 + dm1), a2 = d4p * frcp(d4 + d0);
+        const float gg = 2.f * frcp(d4m + d4p);
         Fm = cq * (1.f + gg * d0 * (a1 - a2)) - 1.f;
         G = gg * d0 * a2;
         H = gg * dm1 * a1;
@@ -269,7 +287,7 @@ __device__ __forceinline__ void geometry_interior(uint32_t cnt, float pm3, float
     const bool open = ko >= 1 && ko < nz;
     const float dpw = open ? scale(ko < nz ? ko : nz - 1) * dpl : 0.f;
     const int open_slot = open ? ko + 1 : DUMMY_SLOT;
-    const float rdpl = __fdividef(1.f, dpl);
+    const float rdpl = frcp(dpl);
     const uint32_t oa = ova + (kk * NCOL + x) * (MAXE * 16), ob = ovb + (kk * NCOL + x) * (MAXE * 4);
     float ex = 0.f, ey = 0.f, ez = 0.f, ew = 0.f;
     int slot = NS ? DUMMY_SLOT : open_slot;                             // no interface in the layer: see geometry_step
@@ -387,6 +405,26 @@ __device__ __noinline__ u64 extras_pair(uint32_t sctx, int code, u64 q2, u64 x2,
     return pk(rv[0], rv[1]);
 }
 
+// Loads of the hot step the compiler may schedule freely (no volatile, no memory clobber): the records and the field
+// boxes are read-only while a stage is being consumed.  Their addresses derive from opaque() values formed after
+// the stage's barrier waits, and the state they feed is pinned before the stage is handed back (pin_state).
+__device__ __forceinline__ void lds2x64_s(uint32_t addr, u64 &a, u64 &b)
+{
+    asm("ld.shared.v2.b64 {%0,%1}, [%2];" : "=l"(a), "=l"(b) : "r"(addr));
+}
+__device__ __forceinline__ u64 lds64_s(uint32_t addr)
+{
+    u64 a;
+    asm("ld.shared.b64 %0, [%1];" : "=l"(a) : "r"(addr));
+    return a;
+}
+__device__ __forceinline__ int4 lds128i_s(uint32_t addr)
+{
+    int4 v;
+    asm("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+
 // one pair's record of one step
 struct PairRec {
     u64 E1, E2, Fm, G, NH, DPW, EX, EY, EZ, NW;
@@ -400,6 +438,15 @@ __device__ __forceinline__ void load_pair_rec(PairRec &r, uint32_t rb)      // r
     lds2x64(rb + 3 * GROUP_BYTES, r.EX, r.EY);
     lds2x64(rb + 4 * GROUP_BYTES, r.EZ, r.NW);
     r.oi = lds128i(rb + 5 * GROUP_BYTES);
+}
+__device__ __forceinline__ void load_pair_rec_s(PairRec &r, uint32_t rb)
+{
+    lds2x64_s(rb, r.E1, r.E2);
+    lds2x64_s(rb + GROUP_BYTES, r.Fm, r.G);
+    lds2x64_s(rb + 2 * GROUP_BYTES, r.NH, r.DPW);
+    lds2x64_s(rb + 3 * GROUP_BYTES, r.EX, r.EY);
+    lds2x64_s(rb + 4 * GROUP_BYTES, r.EZ, r.NW);
+    r.oi = lds128i_s(rb + 5 * GROUP_BYTES);
 }
 
 // Both columns of a pair at one of the end steps of the walk (t == 2: nothing above / one-sided cubic at the top,
@@ -515,9 +562,9 @@ struct Field {
 template <int KK>
 __device__ __forceinline__ u64 load_q(uint32_t stage, const Field &f, int any_derived)
 {
-    u64 q = lds64(stage + f.offa[KK]);
+    u64 q = lds64_s(stage + f.offa[KK]);
     if (any_derived) {                                   // uniform across the launch (budgets.py:80, :151)
-        const u64 b = lds64(stage + f.offb[KK]);
+        const u64 b = lds64_s(stage + f.offb[KK]);
         q = mul2(fma2(b, f.n1, q), fma2(b, f.m2, f.a3));
     }
     return q;
@@ -544,7 +591,7 @@ __device__ __forceinline__ void hot_step(Pair &s, uint32_t recp, u64 qn, uint32_
 {
     constexpr int a = (S + 2) % 3, b = (S + 1) % 3;                     // slots of q(t-1), q(t-2)
     PairRec r;
-    load_pair_rec(r, recp);
+    load_pair_rec_s(r, recp);
     const u64 A = s.q[a], B = s.q[b], dq1 = s.dq;
     const u64 dqn = sub2(qn, A);                                        // delq(t)
     const u64 df2 = fma2(r.E1, dqn, mul2(r.E2, dq1));                   // layer t-1, mappm.f90:661
@@ -616,12 +663,11 @@ plevel_pair_kernel(const __grid_constant__ Params p)
     const Layout lay = make_layout(nsrc, nz, nfw);
     const uint32_t sbase = smem_u32(smem);
     const uint32_t ring = sbase + lay.ring;
-    // mbarriers: full[NSTAGE] (field ring, TMA).  Named barriers (a blocked warp does not poll): 7 + b = the
-    // records of geometry buffer b are written (bar.arrive by the three geometry warps of the stage, bar.sync by the
-    // field warps); 2 + b = stage / buffer b is handed back (bar.arrive by the field warps, bar.sync by the
-    // geometry warps)
+    // mbarriers: full[NSTAGE] (field ring, TMA), gfull[NSTAGE] (records of geometry buffer b are written): the
+    // field warps wait on them one by one, so that they are not tied to each other.  Named barrier 2 + b = stage /
+    // buffer b is handed back (bar.arrive by the field warps, bar.sync by the geometry warps)
     const uint32_t bars = sbase + lay.bars;
-    const uint32_t gfull = bars + 8 * NSTAGE;                   // (mbarrier slots kept for the layout; unused)
+    const uint32_t gfull = bars + 8 * NSTAGE;
     // count tables of the column walker, one per row parity: cfull (walker -> geometry warps), cempty (back)
     const uint32_t cfull = gfull + 8 * NSTAGE, cempty = cfull + 16;
     const uint32_t sctx = sbase + lay.ctx;
@@ -635,10 +681,16 @@ plevel_pair_kernel(const __grid_constant__ Params p)
     const uint32_t tail = sbase + lay.tail;
     const int nthreads = (nfw + KC) * 32;                       // field warps + the geometry warps of one stage
 
+    for (int R = tid; R < nsrc * KC; R += blockDim.x) {
+        const int kk = R % KC;
+        const u64 a = (u64)(uintptr_t)(p.src[R / KC] + (long)kk * p.ny * p.nx) | (u64)kk;     // (16-byte aligned planes)
+        asm volatile("st.shared.b64 [%0], %1;" ::"r"(sbase + lay.srow + 8 * R), "l"(a) : "memory");
+    }
     if (tid == 0) {
         if (!NS) p.flags[cta] = 0;
         for (int s = 0; s < NSTAGE; ++s) {
-            mbar_init(bars + 8 * s, KC);                    // full: one expect_tx arrival per geometry warp of the stage
+            mbar_init(bars + 8 * s, KC * 32);               // full: every thread of the stage's geometry warps, when its copies have landed
+            mbar_init(gfull + 8 * s, KC);                   // records: one arrival per geometry warp of the stage
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(cfull + 8 * s, 1);
@@ -675,7 +727,9 @@ plevel_pair_kernel(const __grid_constant__ Params p)
             float cur[WB], nxt[WB];
 #pragma unroll
             for (int i = 0; i < WB; ++i) cur[i] = i < nz ? ldg_stream(d + (long)i * h) : 0.f;
+            TRACE(9, row, 0);
             if (row >= 2) mbar_wait(cempty + 8 * (row & 1), ((row >> 1) - 1) & 1);
+            TRACE(9, row, 1);
             const uint32_t crow = sbase + lay.cnt + (row & 1) * lay.cnt_bytes + x;
             float P = toa, pnext = lds32(pe2);
             int i = 0;
@@ -695,6 +749,7 @@ plevel_pair_kernel(const __grid_constant__ Params p)
                 for (int j = 0; j < WB; ++j) cur[j] = nxt[j];
             }
             __syncwarp();
+            TRACE(9, row, 2);
             if (lane == 0) mbar_arrive(cfull + 8 * (row & 1));
         }
         return;
@@ -784,14 +839,18 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         };
         int row_n = 0, chunk_n = par, b = par;                       // (nch >= 3: the first stages are in row 0)
         load_delp(row_n, chunk_n);
-        const int mine = (nsrc - sub + KC - 1) / KC;                 // this warp's share of the TMA boxes: sub, sub + 3, ... (<= 18)
-        const CUtensorMap *mymap = &p.maps[sub + KC * (lane < mine ? lane : 0)];
-        const uint32_t mydst = ring + (sub + KC * lane) * BOX_BYTES;
+        // The field boxes of a stage, [source][level][32 columns] with the 16-byte chunks of a row xor-swizzled by
+        // the row index (the field threads' 8-byte reads of a column pair are then conflict-free), are filled by
+        // asynchronous 16-byte copies: an instruction moves four rows; warp sub takes instructions sub, sub + 3, ...
+        const uint32_t srow = sbase + lay.srow;
+        const int nrows = nsrc * KC;
+        const long lane_off = 4 * (long)(NCOL * bx + 4 * (lane & 7));        // bytes
         int row = -1;
         float cw = 0.f, cps = 0.f;
         uint32_t cnt = 0;
         for (int it = par; it < total; it += 2) {
             const int chunk = chunk_n, r2 = row_n;
+            TRACE(gw, it, 0);
             chunk_n += 2;
             if (chunk_n >= nch) { chunk_n -= nch; ++row_n; }
             if (r2 != row) {
@@ -807,25 +866,37 @@ plevel_pair_kernel(const __grid_constant__ Params p)
             pbase = (pp1 + dn[4]) + dn[5];
             if (it + 2 < total) load_delp(row_n, chunk_n);
             // stage b of the field ring and geometry buffer b are released together by the field warps
+            TRACE(gw, it, 1);
             if (it >= NSTAGE) asm volatile("bar.sync %0, %1;" ::"r"(2 + b), "r"(nthreads) : "memory");
-            if (lane == 0) mbar_expect_tx(bars + 8 * b, mine * BOX_BYTES);
-            __syncwarp();
-            if (lane < mine)
-                tma_load_3d(mydst + b * lay.stage_bytes, mymap, NCOL * bx, 8 * by + row, (int)(o * nz) + chunk * KC, bars + 8 * b);
+            TRACE(gw, it, 2);
+            {
+                const long stage_off = 4 * (((o * nz + chunk * KC) * (long)ny + 8 * by + row) * nx) + lane_off;
+                const uint32_t dst0 = ring + b * lay.stage_bytes;
+                for (int R = 4 * sub + (lane >> 3); R < nrows; R += 4 * KC) {
+                    const u64 e = lds64(srow + 8 * R);
+                    const int kk = (int)e & 3;
+                    const char *src = (const char *)(uintptr_t)(e & ~15ull) + stage_off;
+                    const uint32_t dst = dst0 + R * 128 + ((((uint32_t)lane ^ (uint32_t)R) & 7u) << 4);
+                    const int sz = chunk * KC + kk < nz ? 16 : 0;            // levels past the column bottom: zeros
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
+                }
+                asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bars + 8 * b) : "memory");
+            }
+            TRACE(gw, it, 4);
             const int t = chunk * KC + sub;
             if (t >= 3 && t <= nz + 1 && t != nz) {
                 geometry_interior<NS>(cnt, pm3, pm2, pm1, p0, pp1, g, gratio, cw, cps, t, sub, x, rec0 + b * REC_BYTES,
-                                      ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, nz, mask_below, lay.acc_stride);
-            } else if (t >= 2) {                                     // (the records of steps 0 and 1 are not read)
+                                      ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, edge, nz, mask_below, lay.acc_stride);
+            } else if (t >= 2) {
                 ColG col;
                 col.w = cw;
                 col.ps = cps;
                 geometry_step<NS>(cnt, pm3, pm2, pm1, p0, pp1, g, col, t, sub, x, rec0 + b * REC_BYTES,
                                   ova0 + b * OVA_BYTES, ovb0 + b * OVB_BYTES, tail, edge, nz, mask_below, toa, lay.acc_stride);
             }
-            __threadfence_block();
-            __syncwarp();
-            asm volatile("bar.arrive %0, %1;" ::"r"(7 + b), "r"(nthreads) : "memory");
+            __syncwarp();                                            // (mbarrier.arrive releases the warp's writes)
+            TRACE(gw, it, 3);
+            if (lane == 0) mbar_arrive(gfull + 8 * b);
             b = b == 0 ? 2 : b - 1;                                  // (it + 2) % 3
         }
         __syncwarp();
@@ -861,21 +932,23 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         st.q[0] = st.q[1] = st.q[2] = 0; st.dq = 0; st.dc = 0; st.xp = 0; st.mk = 0; st.run = 0;
         for (int chunk = 0; chunk < nch; ++chunk) {
             const int it = row * nch + chunk, b = it % NSTAGE;
-            // (the records of stage 1 of a row were awaited together with stage 0's, see below)
-            if (chunk != 1) asm volatile("bar.sync %0, %1;" ::"r"(7 + b), "r"(nthreads) : "memory");
+            if (warp == 0 || warp == nfw - 1) TRACE(warp == 0 ? 7 : 8, it, 0);
+            mbar_wait(gfull + 8 * b, (it / NSTAGE) & 1);
+            if (warp == 0 || warp == nfw - 1) TRACE(warp == 0 ? 7 : 8, it, 1);
             mbar_wait(bars + 8 * b, (it / NSTAGE) & 1);
-            const uint32_t stage = ring + b * lay.stage_bytes;
-            const uint32_t rec = recp + b * REC_BYTES;
+            if (warp == 0 || warp == nfw - 1) TRACE(warp == 0 ? 7 : 8, it, 2);
+            const uint32_t stage = opaque(ring + b * lay.stage_bytes);
+            const uint32_t rec = opaque(recp + b * REC_BYTES);
             const int code = b << 2 | pr << 4;
             if (chunk == 0) {
                 // the walk starts at t = 2: levels 0 and 1 only seed the rolling state; the one-sided cubic at the
                 // top needs level 3 and the record of step 3, which are the head of the next stage
                 const int b1 = (it + 1) % NSTAGE;
-                asm volatile("bar.sync %0, %1;" ::"r"(7 + b1), "r"(nthreads) : "memory");
+                mbar_wait(gfull + 8 * b1, ((it + 1) / NSTAGE) & 1);
                 mbar_wait(bars + 8 * b1, ((it + 1) / NSTAGE) & 1);
                 const u64 l0 = load_q<0>(stage, fld, any_derived), l1 = load_q<1>(stage, fld, any_derived);
                 const u64 l2 = load_q<2>(stage, fld, any_derived);
-                const u64 l3 = load_q<0>(ring + b1 * lay.stage_bytes, fld, any_derived);
+                const u64 l3 = load_q<0>(opaque(ring + b1 * lay.stage_bytes), fld, any_derived);
                 if (!NS) chk = fma2(l2, 0ull, fma2(l1, 0ull, fma2(l0, 0ull, chk)));
                 const EndOut e = end_pair<NS>(sctx, 2, 2 | code, l2, l3, l1, l0, sub2(l1, l0), 0ull, 0ull, 0ull);
                 st.q[0] = l0; st.q[1] = l1; st.q[2] = l2;
@@ -905,7 +978,11 @@ plevel_pair_kernel(const __grid_constant__ Params p)
                     }
                 }
             }
+            // every load of the stage has been consumed before it is handed back
+            asm volatile("" ::"l"(st.q[0]), "l"(st.q[1]), "l"(st.q[2]), "l"(st.dq), "l"(st.dc), "l"(st.xp), "l"(st.mk),
+                         "l"(st.run), "l"(chk) : "memory");
             __syncwarp();
+            if (warp == 0 || warp == nfw - 1) TRACE(warp == 0 ? 7 : 8, it, 3);
             if (it + NSTAGE < total) asm volatile("bar.arrive %0, %1;" ::"r"(2 + b), "r"(nthreads) : "memory");
         }
     }
@@ -932,58 +1009,6 @@ plevel_pair_kernel(const __grid_constant__ Params p)
 }
 
 // ---- host side ----------------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
-                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
-                                  CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_fn()
-{
-    static EncodeTiledFn fn = [] {
-        void *f = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess) f = nullptr;
-        return (EncodeTiledFn)f;
-    }();
-    return fn;
-}
-
-struct MapKey {
-    const void *ptr;
-    long n_outer;
-    int nz, ny, nx;
-    bool operator==(const MapKey &o) const
-    { return ptr == o.ptr && n_outer == o.n_outer && nz == o.nz && ny == o.ny && nx == o.nx; }
-};
-
-// (n_outer, nz, ny, nx) fp32 as a 3-D tensor (x, y, outer*z); box = [KC levels][1 row][32 columns], 128B swizzle
-static int tensor_map_for(CUtensorMap *out, const float *ptr, long n_outer, int nz, int ny, int nx)
-{
-    struct Entry { MapKey key; CUtensorMap map; };
-    static thread_local Entry cache[128];
-    static thread_local int ncache = 0, next = 0;
-    const MapKey key{ptr, n_outer, nz, ny, nx};
-    for (int i = 0; i < ncache; ++i)
-        if (cache[i].key == key) { *out = cache[i].map; return CG_OK; }
-    EncodeTiledFn enc = encode_fn();
-    if (!enc) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return CG_ECUDA; }
-    const cuuint64_t dims[3] = {(cuuint64_t)nx, (cuuint64_t)ny, (cuuint64_t)(n_outer * nz)};
-    const cuuint64_t strides[2] = {(cuuint64_t)nx * 4, (cuuint64_t)nx * ny * 4};
-    const cuuint32_t box[3] = {32, 1, KC};
-    const cuuint32_t es[3] = {1, 1, 1};
-    CUtensorMap m;
-    const CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void *)ptr, dims, strides, box, es,
-                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                           CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return CG_ECUDA; }
-    cache[next].key = key;
-    cache[next].map = m;
-    next = (next + 1) % 128;
-    if (ncache < 128) ++ncache;
-    *out = m;
-    return CG_OK;
-}
-
 constexpr int SMEM_LIMIT = 227 * 1024 - 1024;
 
 // one launch: nfields <= MAXV output fields
@@ -1017,8 +1042,7 @@ static int launch_group(const cg_field *fields, float *const *outs, int nfields,
     if (lay.total > SMEM_LIMIT) return CG_ENOTSUP;
     for (int i = 0; i < nsrc; ++i) {
         if (((uintptr_t)srcs[i]) & 15) return CG_ENOTSUP;
-        const int rc = tensor_map_for(&p.maps[i], srcs[i], n_outer, nz, ny, nx);
-        if (rc) return rc;
+        p.src[i] = srcs[i];
     }
     p.area = area; p.psurf = psurf; p.delp_coarse = delp_coarse; p.delp = delp;
     p.nsrc = nsrc; p.nfields = nfields; p.nz = nz; p.ny = ny; p.nx = nx; p.mask_below = mask_below; p.toa = toa;
@@ -1045,6 +1069,14 @@ static int launch_group(const cg_field *fields, float *const *outs, int nfields,
 }
 
 }  // namespace pairk
+
+#ifdef CG_PAIR_TRACE
+extern "C" int cg_debug_pair_trace(long long *dst, long n)
+{
+    const long have = pairk::TRACE_SLOTS * pairk::TRACE_STAGES * pairk::TRACE_VALS;
+    return (int)cudaMemcpyFromSymbol(dst, pairk::g_trace, 8 * (n < have ? n : have));
+}
+#endif
 
 // groups of at most 26 output fields, each as one launch of 16 V work items per CTA row
 static void pair_groups(int nfields, int &ngroups, int &per)
