@@ -125,6 +125,12 @@ def traffic_from_profiles(spec):
         t = json.load(f)
     if t.get("plevel_cells") != spec["plevel_cells"]:
         return None, None
+    # a capture of another version of the kernel is stale: refuse it (tools/make_profiles.py rewrites the file)
+    import hashlib
+    src = b"".join(open(os.path.join(ROOT, "fv3net_b200", "csrc", f), "rb").read()
+                   for f in ("plevel_pair.cu", "plevel_common.cuh"))
+    if t.get("kernel_source_sha256_16") != hashlib.sha256(src).hexdigest()[:16]:
+        return None, "profiles/traffic.json was captured from another version of the kernel source"
     return float(t["dram_bytes_read"]) + float(t["dram_bytes_write"]), t.get("source")
 
 
@@ -307,9 +313,9 @@ def run_ours(args):
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
-                         "kernel": "cg::stream::plevel_stream_kernel, timed with its two small "
-                                   "prologue launches (delp block average, surface pressure) as "
-                                   "one cg_pressure_level_average call",
+                         "kernel": "cg::pairk::plevel_pair_kernel (fast pass + the NaN-safe pass that returns at "
+                                   "once), timed with its small prologue launch (delp block average) "
+                                   "as one cg_pressure_level_average call",
                          "ms": plevel_ms, "algorithmic_bytes": spec["plevel_bytes"],
                          "peak_source": peak_src,
                          "impl": os.environ.get("CG_PLEVEL_IMPL", "default")},

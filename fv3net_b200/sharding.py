@@ -32,8 +32,9 @@ def plan(n_time, world, n_tile=6, ny=None, factor=1):
     """Shards for every rank: a list (one entry per rank) of lists of `Shard`.
 
     n_time >= world: whole timesteps, dealt in contiguous runs.  Fewer timesteps than ranks:
-    the ranks are divided among the timesteps and each group splits its timestep by tile, and
-    (more ranks than tiles) each tile by row bands that are multiples of `factor`."""
+    the ranks are divided among the timesteps and each group splits its timestep by whole tiles
+    when they divide evenly, else by row bands that are multiples of `factor` (coarsen_surface_c3072.py:29-76
+    cuts a tile into sub-tiles the same way)."""
     if world < 1 or n_time < 1:
         raise ValueError("need at least one rank and one timestep")
     shards = [[] for _ in range(world)]
@@ -45,23 +46,28 @@ def plan(n_time, world, n_tile=6, ny=None, factor=1):
     for t in range(n_time):
         r0, r1 = split_range(world, n_time, t)                 # ranks working on timestep t
         group = r1 - r0
-        if group <= n_tile:
+        if group <= n_tile and n_tile % group == 0:
             for g in range(group):
                 a, b = split_range(n_tile, group, g)
                 shards[r0 + g].append(Shard(t, a, b, 0, ny))
             continue
+        # Otherwise the timestep's n_tile * (ny / factor) row bands of `factor` rows, taken tile after tile, are
+        # dealt evenly: a rank owns a contiguous run of bands, which may continue into the next tile (one Shard
+        # per tile it touches).  Every rank then has the same work to within one band.
         if ny is None:
             raise ValueError("ny is needed to split tiles into row bands")
-        for tile in range(n_tile):                             # ranks of the group over one tile
-            g0, g1 = split_range(group, n_tile, tile)
-            bands = g1 - g0
-            if bands == 0:
-                raise ValueError(f"{group} ranks cannot be divided over {n_tile} tiles")
-            if ny // factor < bands:
-                raise ValueError(f"{ny} rows give fewer than {bands} bands of {factor} rows")
-            for b in range(bands):
-                y0, y1 = split_range(ny, bands, b, multiple=factor)
-                shards[r0 + g0 + b].append(Shard(t, tile, tile + 1, y0, y1))
+        if ny % factor:
+            raise ValueError(f"{ny} is not a multiple of {factor}")
+        per_tile = ny // factor
+        if n_tile * per_tile < group:
+            raise ValueError(f"{n_tile} tiles of {ny} rows give fewer than {group} bands of {factor} rows")
+        for g in range(group):
+            u0, u1 = split_range(n_tile * per_tile, group, g)
+            while u0 < u1:
+                tile, first = divmod(u0, per_tile)
+                last = min(per_tile, first + (u1 - u0))
+                shards[r0 + g].append(Shard(t, tile, tile + 1, first * factor, last * factor))
+                u0 += last - first
     return shards
 
 
@@ -87,7 +93,8 @@ def coarse_shape(shard, lead, ny, nx, factor):
 
 
 def gather_coarse(local, shards, shapes, dst=0, group=None):
-    """One collective per step: every rank's coarse outputs onto rank `dst`.
+    """One collective per step: every rank's coarse outputs onto rank `dst` (`dst=None`: onto every rank,
+    one all-gather).
 
     local:  {name: [tensor per shard of this rank]} in the order of `shards[rank]`
     shapes: {name: (lead, ny, nx, factor)} describing every output (same on all ranks)
@@ -121,12 +128,17 @@ def gather_coarse(local, shards, shapes, dst=0, group=None):
             pos += flat.numel()
     if pos != rank_numel(rank):
         raise ValueError(f"rank {rank} packed {pos} values, the plan says {rank_numel(rank)}")
-    parts = [torch.empty_like(buf) for _ in range(world)] if rank == dst else None
-    if world > 1:
+    if world > 1 and dst is None:
+        # every rank gets every shard: ONE ncclAllGather (ring / NVLS over NVSwitch), no per-peer send / recv
+        whole = torch.empty(world * buf.numel(), dtype=dtype, device=device)
+        dist.all_gather_into_tensor(whole, buf, group=group)
+        parts = list(whole.split(buf.numel()))
+    elif world > 1:
+        parts = [torch.empty_like(buf) for _ in range(world)] if rank == dst else None
         dist.gather(buf, parts, dst=dst, group=group)
     else:
         parts = [buf]
-    if rank != dst:
+    if dst is not None and rank != dst:
         return None
     out = OrderedDict((name, OrderedDict()) for name in names)
     for r in range(world):

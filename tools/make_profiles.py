@@ -15,7 +15,7 @@ for r in rows[1:]:
     if len(r) <= iv: continue
     us = float(r[iv].replace(",", "")) * {"ns": 1e-3, "us": 1.0, "ms": 1e3, "usecond": 1.0, "nsecond": 1e-3, "msecond": 1e3}.get(r[iu], 1.0)
     name = r[ik]
-    d = lib if ("cg::" in name or "stream::" in name) else other
+    d = lib if ("cg::" in name or "stream::" in name or "pairk::" in name or "plevel_pair" in name) else other
     n, t = d.get(name, (0, 0.0)); d[name] = (n + 1, t + us)
 tot = sum(t for _, t in lib.values())
 with open(os.path.join(P, f"{tag}_launches_summary.txt"), "w") as f:
@@ -43,20 +43,37 @@ keep = ["dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.a
         "sm__inst_executed_pipe_tma.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.pct_of_peak_sustained_active",
         "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active"]
 keep += [k for k in h if k.startswith("smsp__average_warps_issue_stalled_") and k.endswith("_per_issue_active.ratio")]
-with open(os.path.join(P, f"{tag}_ncu_plevel_stream.txt"), "w") as f:
-    f.write("# ncu --set full --clock-control none --import-source on -k regex:plevel_stream -s 2 -c 1: python bench.py --steps 1 --warmup 3 --no-cpu --e2e-steps 0\n")
+with open(os.path.join(P, f"{tag}_ncu_plevel.txt"), "w") as f:
+    f.write("# ncu --set full --clock-control none --import-source on -k regex:plevel_pair_kernel -s 2 -c 1: python bench.py --steps 1 --warmup 3 --no-cpu --e2e-steps 0\n")
     f.write(f"# kernel: {v[h.index('Kernel Name')]}, C384 budget timestep (26 fields, 6 tiles x 79 levels)\n")
     for k in sorted(set(keep)):
         if k in h: f.write(f"{k:100s} {v[h.index(k)]:>20s} {u[h.index(k)]}\n")
-    reg = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_regions.py"), rep], capture_output=True, text=True).stdout
-    f.write("# warp-state samples and executed instructions by role (tools/ncu_regions.py):\n")
-    for line in reg.strip().splitlines(): f.write("#   " + line + "\n")
+    # warp-state samples and executed instructions by role: source-line ranges of plevel_pair.cu (tools/ncu_lines.py)
+    src = open(os.path.join(ROOT, "fv3net_b200", "csrc", "plevel_pair.cu")).read().splitlines()
+    def line_of(marker, start=0):
+        return next(i + 1 for i, l in enumerate(src) if i >= start and marker in l)
+    marks = [("geometry_general", "void geometry_step("), ("geometry_interior", "void geometry_interior("),
+             ("extras_pair", "u64 extras_pair("), ("record_loads", "struct PairRec {"), ("end_pair", "EndOut end_pair("),
+             ("load_q", "u64 load_q("), ("hot_step", "void hot_step("), ("kernel_setup", "plevel_pair_kernel(const __grid_constant__"),
+             ("column_walker", "column walker: lane = fine column"), ("geometry_prologue", "geometry warp gw: lane = fine column"),
+             ("geometry_loop", "warp gw takes level sub of the stages"), ("field_loop", "field threads: work item ="),
+             ("output", "coarse outputs: the four pairs"), ("host", "---- host side")]
+    pos = [(n, line_of(m)) for n, m in marks]
+    specs = [f"{n}:{a}:{pos[i + 1][1] - 1}" for i, (n, a) in enumerate(pos[:-1])]
+    reg = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "ncu_lines.py"), rep, "12"] + specs + ["shared_helpers:1:272"],
+                         capture_output=True, text=True).stdout
+    f.write("# top source lines by samples / instructions, then warp-state samples and executed instructions by region (tools/ncu_lines.py;\n")
+    f.write("# shared_helpers = plevel_common.cuh lines, counted for whichever role inlines them):\n")
+    for line in reg.strip().splitlines(): f.write("#   " + line[:230] + "\n")
 def val(k):
     x = float(v[h.index(k)].replace(",", "")); un = u[h.index(k)]
     return x * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}.get(un, 1.0)
-json.dump({"kernel": v[h.index("Kernel Name")], "dram_bytes_read": val("dram__bytes_read.sum"),
+import hashlib
+khash = hashlib.sha256(open(os.path.join(ROOT, "fv3net_b200", "csrc", "plevel_pair.cu"), "rb").read()
+                       + open(os.path.join(ROOT, "fv3net_b200", "csrc", "plevel_common.cuh"), "rb").read()).hexdigest()[:16]
+json.dump({"kernel": v[h.index("Kernel Name")], "kernel_source_sha256_16": khash, "dram_bytes_read": val("dram__bytes_read.sum"),
            "dram_bytes_write": val("dram__bytes_write.sum"), "plevel_cells": 1817247744,
-           "source": f"profiles/{tag}_ncu_plevel_stream.txt (ncu --set full, one launch, C384 budget timestep)"},
+           "source": f"profiles/{tag}_ncu_plevel.txt (ncu --set full, one launch, C384 budget timestep)"},
           open(os.path.join(P, "traffic.json"), "w"), indent=1)
 for src, dst in (("bench.json", f"{tag}_bench.json"), ("bench_reference.json", f"{tag}_bench_reference.json")):
     if os.path.exists(os.path.join(G, src)): shutil.copy(os.path.join(G, src), os.path.join(P, dst))
@@ -69,7 +86,7 @@ if os.path.exists(kn):
     hdr = rows[0]; ik = hdr.index("Kernel Name"); iv = hdr.index("Metric Value"); iu = hdr.index("Metric Unit")
     agg = collections.OrderedDict()
     for r in rows[1:]:
-        if len(r) <= iv or not ("cg::" in r[ik] or "stream::" in r[ik]): continue
+        if len(r) <= iv or not ("cg::" in r[ik] or "stream::" in r[ik] or "pairk" in r[ik]): continue
         us = float(r[iv].replace(",", "")) * {"ns": 1e-3, "us": 1.0, "ms": 1e3, "usecond": 1.0, "nsecond": 1e-3, "msecond": 1e3}.get(r[iu], 1.0)
         n, t, lo = agg.get(r[ik], (0, 0.0, 1e30)); agg[r[ik]] = (n + 1, t + us, min(lo, us))
     with open(os.path.join(P, f"{tag}_kernels_ncu.txt"), "w") as f:
