@@ -280,7 +280,26 @@ def run_ours(args):
     ms_per_step = total_ms / args.steps
 
     # ---- end to end through the public API with host buffers (pinned) --------------------
-    e2e = e2e_run(args, spec, inp, device, world, barrier) if args.e2e_steps > 0 else None
+    import bench_cases
+
+    peak, peak_src = peaks()
+    ctx = bench_cases.Ctx(world, rank, device, peak, min(args.steps, 5), 3)
+    e2e = e2e_run(args, spec, inp, device, world, barrier, ctx) if args.e2e_steps > 0 else None
+
+    # ---- the other named workloads and the strong-scaling regime (sub-records) -------------
+    sub, strong = {}, None
+    if args.config == "all":
+        ops.release_workspaces()
+        if args.scaling in ("both", "strong"):
+            inp0 = inp if rank == 0 else make_inputs(spec, device, seed=0)    # rank 0's timestep on every rank
+            strong = bench_cases.strong_config2(ctx, inp0, n=args.n, n_tile=args.tiles)
+            del inp0
+        del inp
+        bench_cases._free()
+        sub["configs[1]"] = bench_cases.config1(ctx, n=args.n, n_tile=args.tiles)
+        sub["configs[3]"] = bench_cases.config3(ctx, n=args.n, n_tile=args.tiles)
+        sub["configs[4]"] = bench_cases.config4(ctx)
+
 
     # ---- CPU baseline beside it (rank 0, N = 1 only; bounded sample) ---------------------
     cpu = None
@@ -302,7 +321,6 @@ def run_ours(args):
                          f"reference-shaped numpy passes + C restatement of mappm.f90, {dt:.1f} s"}
 
     if rank == 0:
-        peak, peak_src = peaks()
         achieved = spec["plevel_bytes"] / (plevel_ms * 1e-3) / 1e9
         traffic, traffic_src = (args.traffic, "--traffic") if args.traffic else traffic_from_profiles(spec)
         line = {
@@ -318,16 +336,57 @@ def run_ours(args):
                                    "as one cg_pressure_level_average call",
                          "ms": plevel_ms, "algorithmic_bytes": spec["plevel_bytes"],
                          "peak_source": peak_src,
-                         "impl": os.environ.get("CG_PLEVEL_IMPL", "default")},
+                         "impl": lib.cg_pressure_level_last_impl().decode()},
             "cpu_baseline": cpu,
         }
+        if sub:
+            line["configs"] = sub
+        if strong is not None:
+            line["strong"] = strong
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
-def e2e_run(args, spec, inp, device, world, barrier):
+def run_one_case(args):
+    """--config 1 | 3 | 4 or --scaling strong alone: that record as the JSON line."""
+    import torch
+    import torch.distributed as dist
+
+    import bench_cases
+    from fv3net_b200 import _lib
+
+    world, rank = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=device)
+    lib = _lib.lib()
+    peak, _ = peaks()
+    ctx = bench_cases.Ctx(world, rank, device, peak, args.steps, args.warmup)
+    launches0 = lib.cg_launch_count()
+    if args.scaling == "strong":
+        rec = bench_cases.strong_config2(ctx, make_inputs(workload(args), device, seed=0), n=args.n, n_tile=args.tiles)
+    else:
+        rec = {"1": bench_cases.config1, "3": bench_cases.config3, "4": bench_cases.config4}[args.config](ctx)
+    if rank == 0:
+        line = {"metric": "fine-grid cells/s, " + rec["workload"].split(":")[0], "value": rec["value"], "unit": UNIT,
+                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": rec["ms_per_step"],
+                "higher_is_better": True, "scaling": rec["scaling"], "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": {"workload": rec["workload"]},
+                "gpu_launches": int(lib.cg_launch_count() - launches0)}
+        line.update({k: v for k, v in rec.items() if k not in ("workload", "value", "unit", "scaling", "ms_per_step")})
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def e2e_run(args, spec, inp, device, world, barrier, ctx):
     """Same metric through the public API with HOST buffers (fv3net_b200.staging.BudgetPipeline):
     per step every input goes pinned host -> device, tile by tile through two device buffer sets
     so that the kernels of tile i run under the copies of tile i + 1, and every coarse output comes
@@ -363,9 +422,19 @@ def e2e_run(args, spec, inp, device, world, barrier):
             import torch.distributed as dist
 
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return {"value": world * spec["cells"] / (ms.item() * 1e-3), "unit": UNIT,
-                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                "ms_per_step": ms.item(), "steps": steps}
+        rec = {"value": world * spec["cells"] / (ms.item() * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+               "ms_per_step": ms.item(), "steps": steps,
+               "h2d_gbs_all_ranks": world * h2d / (ms.item() * 1e-3) / 1e9}
+        # the ceiling under it: the same pinned buffers and chunks copied host -> device with nothing else going on,
+        # every rank at once (one cudaMemcpyAsync per buffer and chunk)
+        import bench_cases
+
+        ceil = bench_cases.h2d_ceiling(ctx, host)
+        rec["h2d_ceiling_gbs"] = ceil["gbs_all_ranks"]
+        rec["h2d_ceiling_ms"] = ceil["ms"]
+        rec["frac_of_h2d_ceiling"] = rec["h2d_gbs_all_ranks"] / ceil["gbs_all_ranks"]
+        return rec
     except RuntimeError as e:  # e.g. pinned allocation refused
         return {"value": None, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0,
                 "error": str(e)[:200]}
@@ -386,6 +455,11 @@ def main():
                     help="3-D fields of tile 0 in the bounded CPU sample (26 = every remapped field)")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--config", default="all", choices=["all", "1", "2", "3", "4"],
+                    help="BASELINE.json configs[i]; all = the headline configs[2] line with the others as sub-records")
+    ap.add_argument("--scaling", default="both", choices=["both", "weak", "strong"],
+                    help="strong = one configs[2] timestep cut over the ranks, coarse outputs gathered inside the timed "
+                         "region (a sub-record of the default line; with --config 2 the line itself)")
     ap.add_argument("--traffic", type=float, default=None,
                     help="dram bytes per launch of the dominant kernel; default: the committed "
                          "ncu capture named in profiles/traffic.json")
@@ -393,6 +467,8 @@ def main():
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
         return run_reference(args)
+    if args.config in ("1", "3", "4") or (args.scaling == "strong" and args.config == "2"):
+        return run_one_case(args)
     return run_ours(args)
 
 

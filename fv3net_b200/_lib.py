@@ -26,6 +26,7 @@ _pp = _c.POINTER(_c.c_void_p)
 SIGNATURES = {
     "cg_last_error": (_c.c_char_p, []),
     "cg_version": (_i, []),
+    "cg_set_option": (_i, [_c.c_char_p, _c.c_char_p]),
     "cg_launch_count": (_l, []),
     "cg_device_info": (_i, [_c.POINTER(_i), _c.POINTER(_i), _c.POINTER(_l)]),
     "cg_weighted_block_average": (_i, [_pp, _pp, _i, _vp, _vp, _i, _l, _i, _i, _i,
@@ -40,6 +41,7 @@ SIGNATURES = {
     "cg_mappm": (_i, [_vp, _vp, _vp, _vp, _l, _l, _i, _i, _c.POINTER(_l), _i, _i, _vp]),
     "cg_pressure_level_last_impl": (_c.c_char_p, []),
     "cg_pressure_level_workspace_bytes": (_l, [_i, _l, _i, _i, _i, _i]),
+    "cg_pressure_level_fallback_workspace_bytes": (_l, [_i, _l, _i, _i, _i, _i]),
     "cg_pressure_level_average": (_i, [_vp, _pp, _i, _vp, _vp, _vp, _l, _i, _i, _i, _i, _i, _d,
                                        _vp, _l, _vp]),
     "cg_area_above_fine_surface": (_i, [_vp, _vp, _vp, _vp, _l, _i, _i, _i, _i, _d, _vp]),
@@ -109,6 +111,11 @@ def check(rc):
     if rc == CG_ENOTSUP:
         raise NotImplementedError(msg)
     raise CoarsenLibraryError(msg)
+
+
+def set_option(name, value):
+    """Per-thread behaviour switch of the library (include/coarsen_b200.h, cg_set_option)."""
+    check(lib().cg_set_option(name.encode(), str(value).encode()))
 
 
 def ptr_array(ptrs):

@@ -8,8 +8,17 @@
 
 namespace cg {
 
-// thread-local last-error text (the only state in the library)
+// thread-local last-error text and option block: the only state in the library, none of it process-wide
 void set_error(const char *fmt, ...);
+
+enum { PLEVEL_AUTO, PLEVEL_PAIR, PLEVEL_STREAM, PLEVEL_FUSED, PLEVEL_COMPOSED };
+struct Options {
+    int plevel_impl = PLEVEL_AUTO;   // which cg_pressure_level_average implementation runs where its shape constraints hold
+    bool plevel_nansafe = false;     // the NaN-skipping variant alone, without the fast first pass
+    int mappm_arrays = 0;            // 1: the generic remapper keeps its column arrays in shared memory
+    int mappm_impl = 0;              // 1: the generic remapper even where the streaming one applies
+};
+const Options &options();            // of the calling thread (cg_set_option)
 
 inline int cuda_fail(cudaError_t e, const char *what)
 {

@@ -15,6 +15,10 @@ void set_error(const char *fmt, ...)
     va_end(ap);
 }
 
+// Behaviour switches of the calling thread (cg_set_option): tests and A/B timing pin an implementation with them.
+static thread_local Options g_opt;
+const Options &options() { return g_opt; }
+
 static std::atomic<long> g_launches{0};
 void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
@@ -36,7 +40,33 @@ int sm_count()
 
 extern "C" const char *cg_last_error(void) { return cg::g_err; }
 
-extern "C" int cg_version(void) { return 100; }
+extern "C" int cg_version(void) { return 101; }
+
+extern "C" int cg_set_option(const char *name, const char *value)
+{
+    CG_REQUIRE(name && value, "null option");
+    cg::Options &o = cg::g_opt;
+    if (!strcmp(name, "plevel_impl")) {
+        static const char *const names[] = {"auto", "pair", "stream", "fused", "composed"};
+        for (int i = 0; i < 5; ++i)
+            if (!strcmp(value, names[i])) { o.plevel_impl = i; return CG_OK; }
+    } else if (!strcmp(name, "plevel_nansafe")) {
+        if (!strcmp(value, "0") || !strcmp(value, "1")) { o.plevel_nansafe = value[0] == '1'; return CG_OK; }
+    } else if (!strcmp(name, "mappm_arrays")) {
+        static const char *const names[] = {"auto", "shared"};
+        for (int i = 0; i < 2; ++i)
+            if (!strcmp(value, names[i])) { o.mappm_arrays = i; return CG_OK; }
+    } else if (!strcmp(name, "mappm_impl")) {
+        static const char *const names[] = {"auto", "generic"};
+        for (int i = 0; i < 2; ++i)
+            if (!strcmp(value, names[i])) { o.mappm_impl = i; return CG_OK; }
+    } else {
+        cg::set_error("cg_set_option: unknown option '%s'", name);
+        return CG_EINVAL;
+    }
+    cg::set_error("cg_set_option: '%s' is not a value of option '%s'", value, name);
+    return CG_EINVAL;
+}
 
 extern "C" long cg_launch_count(void) { return cg::g_launches.load(std::memory_order_relaxed); }
 

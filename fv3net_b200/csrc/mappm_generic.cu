@@ -557,8 +557,7 @@ int launch_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,
     Strides s;
     for (int i = 0; i < 12; ++i) s.v[i] = strides[i];
     Pe2Block pb{pe2_f, pe2_nx, pe2_nxc};
-    const char *home = getenv("CG_MAPPM_ARRAYS");                        // "shared" forces the shared-memory variant (tests)
-    if (km <= KMAX_LOCAL && !(home && home[0] == 's')) {
+    if (km <= KMAX_LOCAL && !options().mappm_arrays) {                  // (option mappm_arrays = shared: tests)
         mappm_generic_kernel<true><<<cdiv(ncol, TPB_LOCAL), TPB_LOCAL, 0, st>>>(pe1, q1, pe2, q2, ncol, n_inner, km, kn, s, pb, iv, kord);
         CG_LAUNCH_CHECK("cg_mappm");
         return CG_OK;

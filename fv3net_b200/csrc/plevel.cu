@@ -351,14 +351,10 @@ static int composed(const cg_field *fields, float *const *outs, int nfields, con
     return CG_OK;
 }
 
-// CG_PLEVEL_IMPL = composed | fused | stream pins one implementation (tests, A/B timing);
-// default: stream where its shape constraints hold, else fused, else composed.
-static bool impl_is(const char *name)
-{
-    const char *e = getenv("CG_PLEVEL_IMPL");
-    return e && strcmp(e, name) == 0;
-}
-static bool want_composed() { return impl_is("composed"); }
+// cg_set_option("plevel_impl", composed | fused | stream | pair) pins one implementation (tests, A/B timing);
+// default: pair where its shape constraints hold, else stream, else fused, else composed.
+static bool impl_is(int which) { return options().plevel_impl == which; }
+static bool want_composed() { return impl_is(PLEVEL_COMPOSED); }
 static thread_local const char *g_last_impl = "none";
 
 static int stream_path(const cg_field *fields, float *const *outs, int nfields, const float *delp,
@@ -378,11 +374,10 @@ static int stream_path(const cg_field *fields, float *const *outs, int nfields, 
                                        nyc, nxc, CG_F32, CG_F32, st);
     if (rc) return rc;
     if (mask_below && (rc = launch_surface_pressure_seq(delp, ps, toa, n_outer, nz, h, st))) return rc;
-    // the pair-thread kernel where its shared-memory layout fits (CG_PLEVEL_IMPL=stream pins the round-1 kernel)
-    if (!impl_is("stream") && pair_supported(nfields, nz, ny, nx, 8)) {
-        const char *env = getenv("CG_PLEVEL_NANSAFE");
+    // the pair-thread kernel where its shared-memory layout fits (option plevel_impl = stream pins the round-1 kernel)
+    if (!impl_is(PLEVEL_STREAM) && pair_supported(nfields, nz, ny, nx, 8)) {
         rc = launch_plevel_pair(fields, outs, nfields, delp, area, dc, mask_below ? ps : nullptr, flags, n_outer, nz,
-                                ny, nx, mask_below, toa, env && env[0] == '1', st);
+                                ny, nx, mask_below, toa, options().plevel_nansafe, st);
         if (rc != CG_ENOTSUP) { g_last_impl = "pair"; return rc; }
     }
     if (!stream_supported(nfields, nz, ny, nx, 8)) return CG_ENOTSUP;
@@ -400,9 +395,22 @@ extern "C" const char *cg_pressure_level_last_impl(void) { return g_last_impl; }
 extern "C" long cg_pressure_level_workspace_bytes(int nfields, long n_outer, int nz, int ny, int nx, int f)
 {
     if (f < 1 || ny < 1 || nx < 1 || nz < 1 || n_outer < 0) return 0;
-    long a = composed_workspace_bytes(n_outer, nz, ny, nx, f);
-    long b = fused_supported(nz, ny, nx, f) ? fused_workspace_bytes(nfields, n_outer, nz, ny, nx, f) : 0;
-    return a > b ? a : b;   // composed-path size: also the fallback for misaligned inputs
+    // what the implementation that will run needs: the streaming kernels keep delp_coarse, one surface pressure per
+    // column and one flag per CTA (a few MB at C384); only the composed recipe needs fine-grid temporaries
+    const int impl = options().plevel_impl;
+    if (impl != PLEVEL_COMPOSED && impl != PLEVEL_FUSED && nfields > 0 &&
+        (stream_supported(nfields, nz, ny, nx, f) || pair_supported(nfields, nz, ny, nx, f)))
+        return stream_workspace_bytes(n_outer, nz, ny, nx);
+    if (impl != PLEVEL_COMPOSED && impl != PLEVEL_STREAM && fused_supported(nz, ny, nx, f))
+        return fused_workspace_bytes(nfields, n_outer, nz, ny, nx, f);
+    return composed_workspace_bytes(n_outer, nz, ny, nx, f);
+}
+
+extern "C" long cg_pressure_level_fallback_workspace_bytes(int nfields, long n_outer, int nz, int ny, int nx, int f)
+{
+    (void)nfields;
+    if (f < 1 || ny < 1 || nx < 1 || nz < 1 || n_outer < 0) return 0;
+    return composed_workspace_bytes(n_outer, nz, ny, nx, f);
 }
 
 extern "C" int cg_pressure_level_average(const cg_field *fields, float *const *outs, int nfields,
@@ -422,18 +430,26 @@ extern "C" int cg_pressure_level_average(const cg_field *fields, float *const *o
     }
     if (n_outer == 0) return CG_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    if (!want_composed() && !impl_is("fused") && nfields > 0 &&
+    if (!want_composed() && !impl_is(PLEVEL_FUSED) && nfields > 0 &&
         (stream_supported(nfields, nz, ny, nx, f) || pair_supported(nfields, nz, ny, nx, f))) {
         const int rc = stream_path(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz, ny, nx,
                                    mask_below, (float)toa, workspace, workspace_bytes, st);
         if (rc != CG_ENOTSUP) return rc;        // misaligned pointers / no workspace: next implementation
     }
-    if (!want_composed() && !impl_is("stream") && fused_supported(nz, ny, nx, f)) {
+    if (!want_composed() && !impl_is(PLEVEL_STREAM) && fused_supported(nz, ny, nx, f)) {
         const int rc = launch_plevel_fused(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz,
                                            ny, nx, f, mask_below, (float)toa, workspace, workspace_bytes, st);
         if (rc != CG_ENOTSUP) { g_last_impl = "fused"; return rc; }     // misaligned pointers: use the composed path
     }
     g_last_impl = "composed";
+    if (!workspace || workspace_bytes < composed_workspace_bytes(n_outer, nz, ny, nx, f)) {
+        // e.g. pointers the streaming kernels cannot take (16-byte alignment): the caller comes back with the
+        // composed recipe's workspace (cg_pressure_level_fallback_workspace_bytes)
+        set_error("cg_pressure_level_average: the streaming kernels do not take these arguments and the workspace "
+                  "(%ld bytes) is too small for the composed recipe (%ld bytes)", workspace_bytes,
+                  composed_workspace_bytes(n_outer, nz, ny, nx, f));
+        return CG_ENOTSUP;
+    }
     return composed(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz, ny, nx, f, mask_below,
                     (float)toa, workspace, workspace_bytes, st);
 }

@@ -1259,8 +1259,8 @@ int launch_plevel_stream(const cg_field *fields, float *const *outs, int nfields
     if (lay.total > 227 * 1024 - 1024) return CG_ENOTSUP;
     p.area = area; p.psurf = psurf; p.delp_coarse = delp_coarse; p.delp = delp;
     p.nsrc = nsrc; p.nfields = nfields; p.nz = nz; p.ny = ny; p.nx = nx; p.mask_below = mask_below; p.toa = toa;
-    static int max_set = 0;
-    if (lay.total > max_set) {
+    // function attributes are per device and cheap to set: on every call (a process may drive several devices)
+    {
         for (int v = 0; v < 2; ++v) {
             const void *fn = v ? (const void *)plevel_stream_kernel<true> : (const void *)plevel_stream_kernel<false>;
             cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
@@ -1268,13 +1268,11 @@ int launch_plevel_stream(const cg_field *fields, float *const *outs, int nfields
             e = cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
             if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(carveout)");
         }
-        max_set = 227 * 1024 - 1024;
     }
     dim3 grid(nx / 32, ny / 8, (unsigned)n_outer);
-    // CG_PLEVEL_NANSAFE=1: the NaN-safe variant alone (tests); default: the fast variant, then the NaN-safe one
+    // option plevel_nansafe: the NaN-safe variant alone (tests); default: the fast variant, then the NaN-safe one
     // over the CTAs that met a non-finite field value
-    const char *env = getenv("CG_PLEVEL_NANSAFE");
-    const bool nansafe_only = env && env[0] == '1';
+    const bool nansafe_only = options().plevel_nansafe;
     if (!nansafe_only) {
         p.flags = flags;
         plevel_stream_kernel<false><<<grid, NTHREADS, lay.total, st>>>(p);

@@ -212,6 +212,11 @@ def _workspace(nbytes, dev):
     return ws
 
 
+def release_workspaces():
+    """Drop the cached workspaces (one per device and stream; they only grow otherwise)."""
+    _WORKSPACE.clear()
+
+
 def product(a, b):
     """Field descriptor: q = a * b, formed inside the kernel (budgets.py:151)."""
     return ("product", a, b, 1.0)
@@ -266,10 +271,15 @@ def pressure_level_average(fields, delp, area, f, mask_below=False, toa=300.0, w
         ws = _workspace(nbytes, dev)
         descs, _keep = _describe(chunk)
         pout, _k2 = L.ptr_array([t.data_ptr() for t in res])
-        L.check(L.lib().cg_pressure_level_average(
-            ctypes.cast(descs, ctypes.c_void_p), pout, len(chunk), _p(delp), _p(area),
-            _p(dcoarse) if first else None,
-            n_outer, nz, ny, nx, f, int(mask_below), float(toa), _p(ws), ws.numel(), _stream()))
+        args = (ctypes.cast(descs, ctypes.c_void_p), pout, len(chunk), _p(delp), _p(area),
+                _p(dcoarse) if first else None, n_outer, nz, ny, nx, f, int(mask_below), float(toa))
+        rc = L.lib().cg_pressure_level_average(*args, _p(ws), ws.numel(), _stream())
+        if rc == L.CG_ENOTSUP:
+            # arguments the streaming kernels do not take (e.g. views that are not 16-byte aligned): the
+            # composed recipe needs its fine-grid temporaries
+            ws = _workspace(L.lib().cg_pressure_level_fallback_workspace_bytes(len(chunk), n_outer, nz, ny, nx, f), dev)
+            rc = L.lib().cg_pressure_level_average(*args, _p(ws), ws.numel(), _stream())
+        L.check(rc)
         first = False
     return outs, dcoarse
 

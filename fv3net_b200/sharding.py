@@ -101,7 +101,10 @@ def gather_coarse(local, shards, shapes, dst=0, group=None):
     Returns on `dst` {name: {shard: tensor}} for every shard of every rank, elsewhere None.
     The buffers are padded to the largest rank's size so a plain gather (NCCL or gloo) works
     for ragged plans; the plan is known everywhere, so no sizes are exchanged."""
-    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    if dist.is_available() and dist.is_initialized():
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+    else:
+        rank, world = 0, 1                                   # one process: the plan has one rank
     names = list(shapes)
 
     def rank_numel(r):

@@ -17,8 +17,9 @@
  *   - dtype codes: CG_F32 / CG_F64; "wdtype" is the dtype of the weights
  *     (the reference mixes f64 restart fields with f32 grid weights);
  *   - return value: CG_OK or a negative CG_E* code; cg_last_error() gives the
- *     text for the calling thread.  No exceptions, no global state besides the
- *     thread-local error string.  There is NO CPU fallback anywhere.
+ *     text for the calling thread.  No exceptions.  The only state is per calling
+ *     thread: the error string and the option block of cg_set_option; nothing is
+ *     read from the environment.  There is NO CPU fallback anywhere.
  */
 #ifndef COARSEN_B200_H
 #define COARSEN_B200_H
@@ -51,6 +52,14 @@ extern "C" {
 
 const char *cg_last_error(void);
 int cg_version(void);
+/* Behaviour switches of the CALLING THREAD, for tests and A/B timing (defaults in brackets):
+ *   "plevel_impl"    [auto] | pair | stream | fused | composed   implementation of cg_pressure_level_average
+ *                    that runs wherever its shape constraints hold (otherwise the next one in that order)
+ *   "plevel_nansafe" [0] | 1   the NaN-skipping variant of the streaming kernels alone, no fast first pass
+ *   "mappm_arrays"   [auto] | shared   column work arrays of the generic remapper in shared memory
+ *   "mappm_impl"     [auto] | generic  the generic remapper even where the streaming one applies
+ * CG_EINVAL for an unknown name or value. */
+int cg_set_option(const char *name, const char *value);
 /* number of CUDA kernels this library has launched in this process (monotonic) */
 long cg_launch_count(void);
 /* sm count, major*10+minor compute capability; any may be NULL */
@@ -160,6 +169,9 @@ typedef struct cg_field {
 } cg_field;
 
 long cg_pressure_level_workspace_bytes(int nfields, long n_outer, int nz, int ny, int nx, int f);
+/* workspace of the composed recipe (fine-grid temporaries), which cg_pressure_level_average falls back to when
+ * the streaming kernels cannot take the arguments (it then returns CG_ENOTSUP if the workspace is smaller) */
+long cg_pressure_level_fallback_workspace_bytes(int nfields, long n_outer, int nz, int ny, int nx, int f);
 /* which implementation the calling thread's last cg_pressure_level_average ran: "pair", "stream",
  * "fused", "composed" ("none" before the first call) - for tests and bench records */
 const char *cg_pressure_level_last_impl(void);

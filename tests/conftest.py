@@ -16,3 +16,14 @@ def pytest_configure(config):
 @pytest.fixture(scope="session")
 def golden_dir():
     return os.path.join(ROOT, "tests", "golden")
+
+
+@pytest.fixture(autouse=True)
+def _library_options_back_to_default():
+    """Tests pin implementations with cg_set_option (per thread); nothing pinned leaks into the next test."""
+    yield
+    from fv3net_b200 import _lib
+
+    if _lib._LIB is not None:
+        for name, value in (("plevel_impl", "auto"), ("plevel_nansafe", "0"), ("mappm_arrays", "auto"), ("mappm_impl", "auto")):
+            _lib.set_option(name, value)

@@ -97,12 +97,13 @@ def test_mappm_cs_profile_bit_exact_vs_oracle(ops, km, kn, iv, kord):
 
 @pytest.mark.parametrize("kord", [1, 7, 9, 13])
 def test_mappm_shared_memory_variant(ops, monkeypatch, kord):
-    """km <= 96 keeps the column's work arrays in local memory; deeper columns (and CG_MAPPM_ARRAYS=shared)
+    """km <= 96 keeps the column's work arrays in local memory; deeper columns (and the option mappm_arrays = shared)
     use the shared-memory variant.  Both are the same code over two array homes: same bits."""
     rng = np.random.RandomState(40 + kord)
     pe1, q, pe2 = _random_columns(rng, 200, 79, 79)
     local = gpu_mappm_zlast(ops, pe1, q, pe2, 1, kord)
-    monkeypatch.setenv("CG_MAPPM_ARRAYS", "shared")
+    from fv3net_b200 import _lib
+    _lib.set_option("mappm_arrays", "shared")
     shared = gpu_mappm_zlast(ops, pe1, q, pe2, 1, kord)
     np.testing.assert_array_equal(local, shared)
     np.testing.assert_array_equal(shared, oracle.mappm(pe1, q, pe2, iv=1, kord=kord))
@@ -164,14 +165,10 @@ def _pin_impl(monkeypatch, impl):
     _PINNED["impl"] = impl
     """composed | fused | stream pin one implementation where its shape constraints hold
     (otherwise the next one runs); default = the library's own choice."""
-    monkeypatch.delenv("CG_PLEVEL_NANSAFE", raising=False)
-    if impl == "default":
-        monkeypatch.delenv("CG_PLEVEL_IMPL", raising=False)
-    elif impl in ("stream_nansafe", "pair_nansafe"):    # the NaN-skipping variant alone (no fast first pass)
-        monkeypatch.setenv("CG_PLEVEL_IMPL", impl.split("_")[0])
-        monkeypatch.setenv("CG_PLEVEL_NANSAFE", "1")
-    else:
-        monkeypatch.setenv("CG_PLEVEL_IMPL", impl)
+    from fv3net_b200 import _lib
+    name = "auto" if impl == "default" else impl.split("_")[0]
+    _lib.set_option("plevel_impl", name)
+    _lib.set_option("plevel_nansafe", "1" if impl.endswith("_nansafe") else "0")   # the NaN-skipping variant alone
 
 
 @pytest.mark.parametrize("impl", ["composed", "fused", "stream", "stream_nansafe", "pair", "pair_nansafe", "default"])

@@ -64,21 +64,25 @@ def _worker(rank, world, port, n_time, n_tile, case, result_file):
             local["q"].append(torch.from_numpy(oracle.weighted_block_average(q, a[:, None], f)))
             local["area"].append(torch.from_numpy(oracle.block_sum(a, f)))
         shapes = {"q": ((nz,), ny, nx, f), "area": ((), ny, nx, f)}
-        gathered = S.gather_coarse(local, shards, shapes, dst=0)
+        everywhere = case.endswith("(all ranks)")
+        gathered = S.gather_coarse(local, shards, shapes, dst=None if everywhere else 0)
+        if everywhere:
+            assert gathered is not None                     # one all-gather: every rank holds every shard
         if rank == 0:
             got_q = S.assemble(gathered["q"], n_time, n_tile, (nz,), ny, nx, f).numpy()
             got_a = S.assemble(gathered["area"], n_time, n_tile, (), ny, nx, f).numpy()
             exp_q = np.stack([oracle.weighted_block_average(field[t], area[:, None], f) for t in range(n_time)])
             exp_a = np.stack([oracle.block_sum(area, f)] * n_time)
             np.save(result_file, np.array([np.array_equal(got_q, exp_q), np.array_equal(got_a, exp_a)]))
-        else:
+        elif not everywhere:
             assert gathered is None
     finally:
         dist.destroy_process_group()
 
 
 @pytest.mark.parametrize("n_time,n_tile,case", [(4, 6, "by time"), (3, 6, "ragged by time"),
-                                                (1, 6, "by tile"), (1, 1, "by row band")])
+                                                (1, 6, "by tile"), (1, 1, "by row band"),
+                                                (1, 6, "by tile (all ranks)"), (1, 5, "by row band across tiles (all ranks)")])
 def test_world_size_2_gloo_matches_unsharded(tmp_path, n_time, n_tile, case):
     result_file = str(tmp_path / "ok.npy")
     mp.spawn(_worker, args=(2, _free_port(), n_time, n_tile, case, result_file), nprocs=2, join=True)

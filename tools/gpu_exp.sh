@@ -6,5 +6,5 @@ for e in "$@"; do
   i=$((i+1))
   touch fv3net_b200/csrc/plevel_stream.cu fv3net_b200/csrc/plevel_pair.cu
   make -C fv3net_b200/csrc EXTRA="$e" > gpurun_out/build_exp$i.log 2>&1 || { echo "EXP [$e] build failed"; tail -5 gpurun_out/build_exp$i.log; continue; }
-  timeout 120 python bench.py --steps 10 --warmup 3 --no-cpu --e2e-steps 0 2> gpurun_out/exp$i.err | python -c "import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('EXP [$e] plevel ms', round(d['roofline']['ms'],3), 'step ms', round(d['ms_per_step'],3))"
+  timeout 120 python bench.py --steps 10 --warmup 3 --no-cpu --e2e-steps 0 --config 2 2> gpurun_out/exp$i.err | python -c "import json,sys; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('EXP [$e] plevel ms', round(d['roofline']['ms'],3), 'step ms', round(d['ms_per_step'],3))"
 done

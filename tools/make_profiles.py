@@ -19,7 +19,7 @@ for r in rows[1:]:
     n, t = d.get(name, (0, 0.0)); d[name] = (n + 1, t + us)
 tot = sum(t for _, t in lib.values())
 with open(os.path.join(P, f"{tag}_launches_summary.txt"), "w") as f:
-    f.write("# ncu --metrics gpu__time_duration.sum --clock-control none -c 400: python bench.py --steps 2 --warmup 3 --no-cpu --e2e-steps 0\n")
+    f.write("# ncu --metrics gpu__time_duration.sum --clock-control none -c 400: python bench.py --steps 2 --warmup 3 --no-cpu --e2e-steps 0 --config 2\n")
     f.write("# Cold-cache, serialised launches: compare SHARES, not absolutes.  The capture holds torch's synthetic input\n")
     f.write("# generation first, then 5 steps (3 warm-up + 2 timed).\n")
     f.write(f"# library kernels: {sum(n for n, _ in lib.values())} launches, {tot/1e3:.3f} ms total\n")
@@ -44,7 +44,7 @@ keep = ["dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.a
         "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active"]
 keep += [k for k in h if k.startswith("smsp__average_warps_issue_stalled_") and k.endswith("_per_issue_active.ratio")]
 with open(os.path.join(P, f"{tag}_ncu_plevel.txt"), "w") as f:
-    f.write("# ncu --set full --clock-control none --import-source on -k regex:plevel_pair_kernel -s 2 -c 1: python bench.py --steps 1 --warmup 3 --no-cpu --e2e-steps 0\n")
+    f.write("# ncu --set full --clock-control none --import-source on -k regex:plevel_pair_kernel -s 2 -c 1: python bench.py --steps 1 --warmup 3 --no-cpu --e2e-steps 0 --config 2\n")
     f.write(f"# kernel: {v[h.index('Kernel Name')]}, C384 budget timestep (26 fields, 6 tiles x 79 levels)\n")
     for k in sorted(set(keep)):
         if k in h: f.write(f"{k:100s} {v[h.index(k)]:>20s} {u[h.index(k)]}\n")
