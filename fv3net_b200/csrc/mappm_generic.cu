@@ -10,9 +10,11 @@
 // Compiled with --fmad=false: every statement keeps the Fortran's operation order
 // and rounding, so results are bit-identical to the CPU oracle (gcc
 // -ffp-contract=off), which is what gfortran produces without FMA contraction.
-#include "common.cuh"
+#include "mappm_common.cuh"
 #include <cstdlib>
 #include <cmath>
+#include <mutex>
+#include <vector>
 
 namespace cg {
 
@@ -34,54 +36,6 @@ struct ColumnViews {
     __device__ __forceinline__ float D4(int k) const { return DP(k - 1) + DP(k); }
     __device__ __forceinline__ float DELQ(int k) const { return Q(k + 1) - Q(k); }
 };
-
-__device__ __forceinline__ float max3f(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
-__device__ __forceinline__ float min3f(float a, float b, float c) { return fminf(fminf(a, b), c); }
-__device__ __forceinline__ float curv(float q, float al, float ar) { return 3.f * (2.f * q - (al + ar)); }
-
-// ppm_limiters, one layer (mappm.f90:854-931)
-__device__ __forceinline__ void limit_layer(float dm, float q, float &al, float &ar, float &a6, int lmt)
-{
-    if (lmt == 3) return;
-    if (lmt == 0) {
-        if (dm == 0.f) {
-            al = q; ar = q; a6 = 0.f;
-        } else {
-            const float da1 = ar - al;
-            const float da2 = da1 * da1;
-            const float a6da = a6 * da1;
-            if (a6da < -da2) {
-                a6 = 3.f * (al - q);
-                ar = al - a6;
-            } else if (a6da > da2) {
-                a6 = 3.f * (ar - q);
-                al = ar - a6;
-            }
-        }
-    } else if (lmt == 1) {
-        const float qmp = 2.f * dm;
-        al = q - copysignf(fminf(fabsf(qmp), fabsf(al - q)), qmp);
-        ar = q + copysignf(fminf(fabsf(qmp), fabsf(ar - q)), qmp);
-        a6 = 3.f * (2.f * q - (al + ar));
-    } else {
-        const float r12 = 1.f / 12.f;
-        if (fabsf(ar - al) < -a6) {
-            const float d = ar - al;
-            const float fmin = q + 0.25f * (d * d) / a6 + a6 * r12;
-            if (fmin < 0.f) {
-                if (q < ar && q < al) {
-                    ar = q; al = q; a6 = 0.f;
-                } else if (ar > al) {
-                    a6 = 3.f * (al - q);
-                    ar = al - a6;
-                } else {
-                    a6 = 3.f * (ar - q);
-                    al = ar - a6;
-                }
-            }
-        }
-    }
-}
 
 __device__ __forceinline__ void limit_at(const ColumnViews &c, int j, int lmt)
 {
@@ -419,11 +373,6 @@ __device__ void cs_column(const ColumnViews &cv, float *fl, int km, int iv, int 
     c.limit(km, 1);
 }
 
-struct Strides { long v[12]; };
-// f > 0: target pressures live on the coarse grid; fine column i = (y, x) of a
-// (ny, nx) tile reads coarse column (y/f, x/f) of a (ny/f, nx/f) tile.
-struct Pe2Block { int f, nx, nxc; };
-
 // Two homes for the column's work arrays (pe, q, AL, AR, A6, dc, h2 [, flags]: 7-8 values per level).  SHARED:
 // interleaved in shared memory, 32 columns per block - 71 KB per warp at km = 79, i.e. 3 warps per SM, for any
 // km that fits 227 KB.  LOCAL (km <= KMAX_LOCAL): thread-private arrays in local memory, which the hardware
@@ -434,12 +383,14 @@ __global__ void __launch_bounds__(LOCAL ? TPB_LOCAL : TPB)
 mappm_generic_kernel(const float *__restrict__ pe1, const float *__restrict__ q1,
                      const float *__restrict__ pe2, float *__restrict__ q2,
                      long ncol, long n_inner, int km, int kn, Strides s, Pe2Block pb,
-                     int iv, int kord)
+                     int iv, int kord, const int *flags)
 {
     extern __shared__ float smem[];
     float local_buf[LOCAL ? 8 * KMAX_LOCAL + 2 : 1];
     const long col = blockIdx.x * (long)(LOCAL ? TPB_LOCAL : TPB) + threadIdx.x;
     if (col >= ncol) return;  // no block-level synchronisation below
+    // second pass behind the streaming remapper: only the column groups it could not take
+    if (flags && flags[col / STREAM_TPB] == 0) return;
     ColumnViews c;
     c.tid = LOCAL ? 0 : threadIdx.x;
     c.stride = LOCAL ? 1 : TPB;
@@ -540,6 +491,43 @@ mappm_generic_kernel(const float *__restrict__ pe1, const float *__restrict__ q1
     }
 }
 
+int launch_mappm_stream(const float *pe1, const float *q1, const float *pe2, float *q2, long ncol, long n_inner,
+                        int km, int kn, const Strides &s, const Pe2Block &pb, int iv, int kord, int *flags,
+                        cudaStream_t st);
+
+static int launch_generic(const float *pe1, const float *q1, const float *pe2, float *q2, long ncol, long n_inner,
+                          int km, int kn, const Strides &s, const Pe2Block &pb, int iv, int kord, const int *flags,
+                          cudaStream_t st);
+
+// One int per 128 columns between the streaming pass and the generic pass behind it.  Kept per (device, stream) and
+// grown on demand: a stream-ordered allocation per call would go back to the driver at every synchronisation
+// (5 ms per call, measured), and calls on different streams must not share flags.  A few KB each (1.7 MB at C3072).
+static int *flag_buffer(size_t bytes, cudaStream_t st)
+{
+    struct Entry { int dev; cudaStream_t st; int *ptr; size_t bytes; };
+    static std::mutex mu;
+    static std::vector<Entry> cache;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { set_error("cudaGetDevice failed"); return nullptr; }
+    std::lock_guard<std::mutex> lock(mu);
+    for (Entry &e : cache)
+        if (e.dev == dev && e.st == st) {
+            if (e.bytes >= bytes) return e.ptr;
+            cudaStreamSynchronize(st);                                     // (earlier calls on the stream still read it)
+            cudaFree(e.ptr);
+            e.ptr = nullptr; e.bytes = 0;
+            const cudaError_t err = cudaMalloc((void **)&e.ptr, bytes);
+            if (err != cudaSuccess) { cuda_fail(err, "cudaMalloc(mappm flags)"); return nullptr; }
+            e.bytes = bytes;
+            return e.ptr;
+        }
+    Entry e{dev, st, nullptr, bytes};
+    const cudaError_t err = cudaMalloc((void **)&e.ptr, bytes);
+    if (err != cudaSuccess) { cuda_fail(err, "cudaMalloc(mappm flags)"); return nullptr; }
+    cache.push_back(e);
+    return e.ptr;
+}
+
 int launch_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,
                  long n_outer, long n_inner, int km, int kn, const long *strides,
                  int pe2_f, int pe2_nx, int pe2_nxc, int iv, int kord, cudaStream_t st)
@@ -557,8 +545,27 @@ int launch_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,
     Strides s;
     for (int i = 0; i < 12; ++i) s.v[i] = strides[i];
     Pe2Block pb{pe2_f, pe2_nx, pe2_nxc};
+    if (kord <= 6 && km >= 5 && !options().mappm_impl && !options().mappm_arrays) {
+        // the streaming remapper; column groups it flags (pressures that do not increase downward, NaN) are redone
+        // by the generic kernel, whose other blocks return at once
+        const size_t fbytes = sizeof(int) * (size_t)((ncol + STREAM_TPB - 1) / STREAM_TPB);
+        int *flags = flag_buffer(fbytes, st);
+        if (!flags) return CG_ECUDA;
+        cudaError_t e = cudaMemsetAsync(flags, 0, fbytes, st);
+        int rc = e == cudaSuccess ? CG_OK : cuda_fail(e, "cudaMemsetAsync(mappm flags)");
+        if (rc == CG_OK) rc = launch_mappm_stream(pe1, q1, pe2, q2, ncol, n_inner, km, kn, s, pb, iv, kord, flags, st);
+        if (rc == CG_OK) rc = launch_generic(pe1, q1, pe2, q2, ncol, n_inner, km, kn, s, pb, iv, kord, flags, st);
+        return rc;
+    }
+    return launch_generic(pe1, q1, pe2, q2, ncol, n_inner, km, kn, s, pb, iv, kord, nullptr, st);
+}
+
+static int launch_generic(const float *pe1, const float *q1, const float *pe2, float *q2, long ncol, long n_inner,
+                          int km, int kn, const Strides &s, const Pe2Block &pb, int iv, int kord, const int *flags,
+                          cudaStream_t st)
+{
     if (km <= KMAX_LOCAL && !options().mappm_arrays) {                  // (option mappm_arrays = shared: tests)
-        mappm_generic_kernel<true><<<cdiv(ncol, TPB_LOCAL), TPB_LOCAL, 0, st>>>(pe1, q1, pe2, q2, ncol, n_inner, km, kn, s, pb, iv, kord);
+        mappm_generic_kernel<true><<<cdiv(ncol, TPB_LOCAL), TPB_LOCAL, 0, st>>>(pe1, q1, pe2, q2, ncol, n_inner, km, kn, s, pb, iv, kord, flags);
         CG_LAUNCH_CHECK("cg_mappm");
         return CG_OK;
     }
@@ -568,7 +575,7 @@ int launch_mappm(const float *pe1, const float *q1, const float *pe2, float *q2,
         cudaError_t e = cudaFuncSetAttribute(mappm_generic_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(mappm)");
     }
-    mappm_generic_kernel<false><<<cdiv(ncol, TPB), TPB, smem, st>>>(pe1, q1, pe2, q2, ncol, n_inner, km, kn, s, pb, iv, kord);
+    mappm_generic_kernel<false><<<cdiv(ncol, TPB), TPB, smem, st>>>(pe1, q1, pe2, q2, ncol, n_inner, km, kn, s, pb, iv, kord, flags);
     CG_LAUNCH_CHECK("cg_mappm");
     return CG_OK;
 }

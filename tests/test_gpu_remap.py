@@ -82,6 +82,49 @@ def test_mappm_bit_exact_vs_oracle(ops, km, kn, iv, kord):
     np.testing.assert_array_equal(got, exp)
 
 
+# ---- the streaming remapper (kord <= 6, km >= 5) against the generic kernel and the oracle ----------------------
+@pytest.mark.parametrize("iv,kord", [(1, 1), (0, 2), (-1, 3), (2, 4), (-2, 5), (1, 6), (0, 5)])
+@pytest.mark.parametrize("km,kn", [(79, 79), (5, 7), (6, 3), (33, 80)])
+def test_mappm_stream_ties_and_ends(ops, km, kn, iv, kord):
+    """Target interfaces that coincide with source interfaces, targets above the column top and below its bottom,
+    one target layer that spans the whole column: the forward merge takes the Fortran's branch at every tie."""
+    from fv3net_b200 import _lib
+    rng = np.random.RandomState(17 * km + kn + kord)
+    pe1, q, pe2 = _random_columns(rng, 300, km, kn, spread=0.3)
+    for c in range(0, 300, 3):                         # ties: copy some source interfaces into the target column
+        idx = rng.randint(0, km + 1, size=kn + 1)
+        pe2[c] = np.sort(np.where(rng.uniform(size=kn + 1) < 0.5, pe1[c, idx], pe2[c]))
+    pe2[5::7, 0] = 100.0                               # target top above the column top
+    pe2[6::7, :2] = [50.0, 200.0]                      # a whole target layer above the column
+    pe2[4::11, -1] = pe1[4::11, -1] + 5000.0           # target reaching far below the column
+    pe2[9::13, 1:] = np.maximum(pe2[9::13, 1:], pe1[9::13, -1:] + 10.0)   # one layer spans everything
+    pe2 = np.sort(pe2, axis=1)
+    got = gpu_mappm_zlast(ops, pe1, q, pe2, iv, kord)
+    _lib.set_option("mappm_impl", "generic")
+    gen = gpu_mappm_zlast(ops, pe1, q, pe2, iv, kord)
+    np.testing.assert_array_equal(got, gen)
+    np.testing.assert_array_equal(got, oracle.mappm(pe1, q, pe2, iv=iv, kord=kord))
+
+
+def test_mappm_stream_hands_bad_columns_to_the_generic_kernel(ops):
+    """Non-increasing or NaN pressures: undefined in the Fortran, defined by the generic kernel (NaN where no layer
+    brackets).  The streaming kernel flags such column groups and the generic kernel redoes them: same bits."""
+    from fv3net_b200 import _lib
+    rng = np.random.RandomState(99)
+    pe1, q, pe2 = _random_columns(rng, 1000, 40, 37)
+    pe1[3, 10] = pe1[3, 9]                              # zero thickness
+    pe1[130, 20] = pe1[130, 18]                         # decreasing source pressure
+    pe1[260, 5] = np.nan
+    pe2[400, 8] = pe2[400, 6]                           # decreasing target pressure
+    pe2[530, 3] = np.nan
+    q[777, 11] = np.nan                                 # a NaN VALUE is ordinary data: no flag needed, same propagation
+    got = gpu_mappm_zlast(ops, pe1, q, pe2, 1, 1)
+    _lib.set_option("mappm_impl", "generic")
+    gen = gpu_mappm_zlast(ops, pe1, q, pe2, 1, 1)
+    np.testing.assert_array_equal(got, gen)
+    assert np.isnan(got[777]).any() and np.isfinite(got[778]).all()
+
+
 @pytest.mark.parametrize("km,kn", [(79, 79), (4, 3), (6, 9), (32, 79)])
 @pytest.mark.parametrize("kord", [8, 9, 10, 11, 12, 13, 14, 15, 16, 17])
 @pytest.mark.parametrize("iv", [1, 0, -1, 2])

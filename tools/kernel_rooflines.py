@@ -81,9 +81,15 @@ dcu = torch.repeat_interleave(torch.repeat_interleave(dc, F, dim=2), F, dim=3)
 pe2 = ops.pressure_at_interface(dcu)
 out = torch.empty_like(delp)
 h = n * n
-report("cg_mappm kord=1 (one C384 field, fine-grid result)", 4 * f3 + 2 * f3 // nz,
+from fv3net_b200 import _lib  # noqa: E402
+report("cg_mappm kord=1, streaming remapper (one C384 field, fine-grid result)", 4 * f3 + 2 * f3 // nz,
        lambda: ops.mappm(pe1, fields[0], pe2, nt, h, nz, nz, ((nz + 1) * h, 1, h), (nz * h, 1, h), ((nz + 1) * h, 1, h),
                          (nz * h, 1, h), out, iv=1, kord=1))
+_lib.set_option("mappm_impl", "generic")
+report("cg_mappm kord=1, generic kernel (column work arrays in local memory)", 4 * f3 + 2 * f3 // nz,
+       lambda: ops.mappm(pe1, fields[0], pe2, nt, h, nz, nz, ((nz + 1) * h, 1, h), (nz * h, 1, h), ((nz + 1) * h, 1, h),
+                         (nz * h, 1, h), out, iv=1, kord=1))
+_lib.set_option("mappm_impl", "auto")
 report("cg_mappm kord=9 (cubic-spline profile)", 4 * f3 + 2 * f3 // nz,
        lambda: ops.mappm(pe1, fields[0], pe2, nt, h, nz, nz, ((nz + 1) * h, 1, h), (nz * h, 1, h), ((nz + 1) * h, 1, h),
                          (nz * h, 1, h), out, iv=1, kord=9))
