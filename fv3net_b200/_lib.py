@@ -50,6 +50,9 @@ SIGNATURES = {
     "cg_interpolate_2d": (_i, [_vp, _vp, _vp, _vp, _d, _l, _i, _i, _c.POINTER(_l), _vp]),
     "cg_elementwise": (_i, [_i, _vp, _vp, _vp, _d, _vp, _l, _i, _vp]),
     "cg_surface_pressure": (_i, [_vp, _vp, _d, _l, _i, _l, _i, _vp]),
+    "cg_surface_pressure_nansum": (_i, [_vp, _vp, _d, _l, _i, _l, _i, _vp]),
+    "cg_pressure_at_midpoint_log": (_i, [_vp, _vp, _d, _l, _i, _l, _i, _vp]),
+    "cg_shift_to_center": (_i, [_vp, _vp, _l, _i, _l, _i, _vp]),
     "cg_blending_weights": (_i, [_vp, _vp, _vp, _d, _d, _l, _i, _l, _i, _vp]),
     "cg_hydrostatic_balance": (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _d, _l, _i, _l, _i, _vp]),
 }

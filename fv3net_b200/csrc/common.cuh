@@ -17,6 +17,7 @@ struct Options {
     bool plevel_nansafe = false;     // the NaN-skipping variant alone, without the fast first pass
     int mappm_arrays = 0;            // 1: the generic remapper keeps its column arrays in shared memory
     int mappm_impl = 0;              // 1: the generic remapper even where the streaming one applies
+    int exposed_impl = 0;            // cg_area_above_fine_surface: 0 auto, 1 strip, 2 warp per cell, 3 three kernels
 };
 const Options &options();            // of the calling thread (cg_set_option)
 

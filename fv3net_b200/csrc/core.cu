@@ -60,6 +60,10 @@ extern "C" int cg_set_option(const char *name, const char *value)
         static const char *const names[] = {"auto", "generic"};
         for (int i = 0; i < 2; ++i)
             if (!strcmp(value, names[i])) { o.mappm_impl = i; return CG_OK; }
+    } else if (!strcmp(name, "exposed_area_impl")) {
+        static const char *const names[] = {"auto", "strip", "cell", "three"};
+        for (int i = 0; i < 4; ++i)
+            if (!strcmp(value, names[i])) { o.exposed_impl = i; return CG_OK; }
     } else {
         cg::set_error("cg_set_option: unknown option '%s'", name);
         return CG_EINVAL;

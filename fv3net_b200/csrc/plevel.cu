@@ -464,7 +464,8 @@ extern "C" int cg_area_above_fine_surface(const float *delp, const float *delp_c
     if (n_outer == 0) return CG_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const long h = (long)ny * nx, hc = (long)(ny / f) * (nx / f);
-    if (f == 8 && nz <= 128 && (nx / 8) % 4 == 0 && (size_t)EXPOSED_WARPS * (512 + nz + 1) * sizeof(float) <= 48 * 1024) {
+    const int pin = options().exposed_impl;                               // (tests: the formulations agree bit for bit)
+    if (pin <= 1 && f == 8 && nz <= 128 && (nx / 8) % 4 == 0 && (size_t)EXPOSED_WARPS * (512 + nz + 1) * sizeof(float) <= 48 * 1024) {
         const long blocks = (n_outer * (ny / 8) * (nx / 32) + EXPOSED_WARPS - 1) / EXPOSED_WARPS;
         exposed_area_strip_kernel<<<(unsigned)(blocks < 0x7fffffffL ? blocks : 0x7fffffffL), 32 * EXPOSED_WARPS,
                                     (size_t)EXPOSED_WARPS * (512 + nz + 1) * sizeof(float), st>>>(
@@ -473,7 +474,7 @@ extern "C" int cg_area_above_fine_surface(const float *delp, const float *delp_c
         return CG_OK;
     }
     const size_t smem = (size_t)EXPOSED_WARPS * (2 * f * f + nz + 1) * sizeof(float);
-    if (smem <= 48 * 1024) {
+    if (pin <= 2 && smem <= 48 * 1024) {
         const long blocks = (n_outer * hc + EXPOSED_WARPS - 1) / EXPOSED_WARPS;
         const unsigned g = (unsigned)(blocks < 0x7fffffffL ? blocks : 0x7fffffffL);
         if (f == 8) exposed_area_fused_kernel<true><<<g, 32 * EXPOSED_WARPS, smem, st>>>(delp, delp_coarse, area, out, n_outer, nz, ny, nx, f, (float)toa);

@@ -59,6 +59,57 @@ __global__ void surface_pressure_sum_kernel(const T *__restrict__ delp, T *__res
     }
 }
 
+// the same with xarray's default skipna: NaN thicknesses count as zero (DataArray.sum -> nansum)
+template <typename T>
+__global__ void surface_pressure_nansum_kernel(const T *__restrict__ delp, T *__restrict__ out, T toa, long n_outer, int nz, long h)
+{
+    const long n = n_outer * h;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+        const long o = i / h, c = i - o * h;
+        const T *p = delp + o * nz * h + c;
+        T s = 0;
+        for (int k = 0; k < nz; ++k) {
+            const T d = p[(long)k * h];
+            s += d == d ? d : T(0);
+        }
+        out[i] = s + toa;
+    }
+}
+
+// vertically_dependent.py:153-179 pressure_at_midpoint_log: delp / diff(log(p_interface)), interfaces by the
+// sequential cumsum from toa (:61-63)
+template <typename T>
+__global__ void midpoint_log_kernel(const T *__restrict__ delp, T *__restrict__ out, T toa, long n_outer, int nz, long h)
+{
+    const long n = n_outer * h;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+        const long o = i / h, c = i - o * h;
+        const T *p = delp + o * nz * h + c;
+        T *w = out + o * nz * h + c;
+        T pi = toa, lp = log(pi);
+        for (int k = 0; k < nz; ++k) {
+            const T d = p[(long)k * h];
+            pi = pi + d;
+            const T ln = log(pi);
+            w[(long)k * h] = d / (ln - lp);
+            lp = ln;
+        }
+    }
+}
+
+// coarsen.py:54-80 shift_edge_var_to_center: 0.5 * (a[i] + a[i-1]) along the staggered dim, (outer, n, inner) ->
+// (outer, n - 1, inner)
+template <typename T>
+__global__ void shift_to_center_kernel(const T *__restrict__ a, T *__restrict__ out, long n_outer, int n, long inner)
+{
+    const long total = n_outer * (n - 1) * inner;
+    for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        const long o = i / ((n - 1) * inner), r = i - o * (n - 1) * inner;
+        const long src = o * n * inner + r;                             // element (o, j, x) with j = r / inner
+        out[i] = T(0.5) * (a[src + inner] + a[src]);
+    }
+}
+
 // coarsen_restarts.py:519-581 (compute_blending_weights on one coarse column):
 //   ps = sum(delp) + toa;  pfull_k = delp_k / (log pi_{k+1} - log pi_k)  (pressure_at_midpoint_log)
 //   pb = sigma * min over the block of the fine surface pressure (given)
@@ -166,6 +217,61 @@ extern "C" int cg_surface_pressure(const void *delp, void *out, double toa, long
         surface_pressure_sum_kernel<double><<<grid_for(n, 128), 128, 0, st>>>((const double *)delp, (double *)out, toa,
                                                                               n_outer, nz, h);
     CG_LAUNCH_CHECK("cg_surface_pressure");
+    return CG_OK;
+}
+
+extern "C" int cg_surface_pressure_nansum(const void *delp, void *out, double toa, long n_outer, int nz, long h, int dtype,
+                                          void *stream)
+{
+    using namespace cg;
+    CG_REQUIRE(delp && out, "cg_surface_pressure_nansum: null array");
+    CG_REQUIRE(n_outer >= 0 && nz >= 1 && h >= 0, "cg_surface_pressure_nansum: bad shape");
+    CG_REQUIRE(dtype == CG_F32 || dtype == CG_F64, "cg_surface_pressure_nansum: bad dtype %d", dtype);
+    const long n = n_outer * h;
+    if (n == 0) return CG_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == CG_F32)
+        surface_pressure_nansum_kernel<float><<<grid_for(n, 128), 128, 0, st>>>((const float *)delp, (float *)out, (float)toa,
+                                                                                n_outer, nz, h);
+    else
+        surface_pressure_nansum_kernel<double><<<grid_for(n, 128), 128, 0, st>>>((const double *)delp, (double *)out, toa,
+                                                                                 n_outer, nz, h);
+    CG_LAUNCH_CHECK("cg_surface_pressure_nansum");
+    return CG_OK;
+}
+
+extern "C" int cg_pressure_at_midpoint_log(const void *delp, void *out, double toa, long n_outer, int nz, long h, int dtype,
+                                           void *stream)
+{
+    using namespace cg;
+    CG_REQUIRE(delp && out, "cg_pressure_at_midpoint_log: null array");
+    CG_REQUIRE(n_outer >= 0 && nz >= 1 && h >= 0, "cg_pressure_at_midpoint_log: bad shape");
+    CG_REQUIRE(dtype == CG_F32 || dtype == CG_F64, "cg_pressure_at_midpoint_log: bad dtype %d", dtype);
+    const long n = n_outer * h;
+    if (n == 0) return CG_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == CG_F32)
+        midpoint_log_kernel<float><<<grid_for(n, 128), 128, 0, st>>>((const float *)delp, (float *)out, (float)toa, n_outer, nz, h);
+    else
+        midpoint_log_kernel<double><<<grid_for(n, 128), 128, 0, st>>>((const double *)delp, (double *)out, toa, n_outer, nz, h);
+    CG_LAUNCH_CHECK("cg_pressure_at_midpoint_log");
+    return CG_OK;
+}
+
+extern "C" int cg_shift_to_center(const void *in, void *out, long n_outer, int n, long inner, int dtype, void *stream)
+{
+    using namespace cg;
+    CG_REQUIRE(in && out, "cg_shift_to_center: null array");
+    CG_REQUIRE(n_outer >= 0 && n >= 1 && inner >= 0, "cg_shift_to_center: bad shape");
+    CG_REQUIRE(dtype == CG_F32 || dtype == CG_F64, "cg_shift_to_center: bad dtype %d", dtype);
+    const long total = n_outer * (n - 1) * inner;
+    if (total == 0) return CG_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == CG_F32)
+        shift_to_center_kernel<float><<<grid_for(total, 256), 256, 0, st>>>((const float *)in, (float *)out, n_outer, n, inner);
+    else
+        shift_to_center_kernel<double><<<grid_for(total, 256), 256, 0, st>>>((const double *)in, (double *)out, n_outer, n, inner);
+    CG_LAUNCH_CHECK("cg_shift_to_center");
     return CG_OK;
 }
 

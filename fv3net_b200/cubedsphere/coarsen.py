@@ -605,11 +605,7 @@ def shift_edge_var_to_center(edge, edge_to_center_dims=None):
     for staggered_dim in [d for d in edge_to_center_dims if d in da.dims]:
         axis = da.get_axis_num(staggered_dim)
         n = da.sizes[staggered_dim]
-        data = da.data
-        hi = [slice(None)] * da.ndim
-        lo = [slice(None)] * da.ndim
-        hi[axis], lo[axis] = slice(1, n), slice(0, n - 1)
-        centred = 0.5 * (data[tuple(hi)] + data[tuple(lo)])
+        centred = lay.finish(ops.shift_to_center(lay.device_tensor(da), axis), da.dims, da.dims, da)   # cg_shift_to_center
         coords = OrderedDict()
         for k, c in da.coords.items():
             if staggered_dim in c.dims:

@@ -12,7 +12,7 @@ from collections import OrderedDict
 
 import numpy as np
 
-try:  # pragma: no cover - exercised only where xarray exists
+try:  # (tests/test_xarray_boundary.py drives the boundary with stand-ins where xarray is absent)
     import xarray as _xr
 except Exception:  # noqa: BLE001
     _xr = None
@@ -341,8 +341,10 @@ def restore(result, like):
     coords = {k: _xr.Variable(c.dims, c.values, c.attrs) for k, c in result.coords.items()}
     data = result.values
     src = like if isinstance(like, _xr.DataArray) else None
-    if src is not None and type(src.data).__module__.startswith("dask"):
-        import dask.array as da
+    if src is not None and hasattr(src.data, "compute") and hasattr(src.data, "chunks"):
+        # lazy (dask) in -> lazy out (regridz.py:254-265, test_regridz.py:63): the values were computed on the GPU
+        # when the call was made; they are handed back as one chunk of the input's own array type
+        import sys
 
-        data = da.from_array(data, chunks=data.shape)
+        data = sys.modules[type(src.data).__module__].from_array(data, chunks=data.shape)
     return _xr.DataArray(data, dims=result.dims, coords=coords, name=result.name, attrs=result.attrs)

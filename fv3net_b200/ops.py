@@ -331,6 +331,36 @@ def surface_pressure(delp, toa=300.0):
     return out
 
 
+def surface_pressure_nansum(delp, toa=300.0):
+    """(n_outer, nz, *h) -> (n_outer, *h): NaN-skipping sum over z + toa (xarray's DataArray.sum)."""
+    n_outer, nz, h = _column_shape(delp)
+    out = torch.empty((n_outer,) + tuple(delp.shape[2:]), dtype=delp.dtype, device=delp.device)
+    L.check(L.lib().cg_surface_pressure_nansum(_p(delp), _p(out), float(toa), n_outer, nz, h,
+                                               _DT[delp.dtype], _stream()))
+    return out
+
+
+def pressure_at_midpoint_log(delp, toa=300.0):
+    """(n_outer, nz, *h) -> same shape: delp / diff(log(p_interface)) (vertically_dependent.py:153-179)."""
+    n_outer, nz, h = _column_shape(delp)
+    out = torch.empty_like(delp)
+    L.check(L.lib().cg_pressure_at_midpoint_log(_p(delp), _p(out), float(toa), n_outer, nz, h,
+                                                _DT[delp.dtype], _stream()))
+    return out
+
+
+def shift_to_center(a, axis):
+    """0.5 * (a[i + 1] + a[i]) along `axis` (coarsen.py:54-80): that dim shrinks by one."""
+    a = a.contiguous()
+    shape = list(a.shape)
+    n_outer = int(np.prod(shape[:axis], dtype=np.int64)) if axis else 1
+    inner = int(np.prod(shape[axis + 1:], dtype=np.int64)) if axis + 1 < len(shape) else 1
+    shape[axis] -= 1
+    out = torch.empty(shape, dtype=a.dtype, device=a.device)
+    L.check(L.lib().cg_shift_to_center(_p(a), _p(out), n_outer, a.shape[axis], inner, _DT[a.dtype], _stream()))
+    return out
+
+
 def blending_weights(delp_coarse, ps_min, toa=300.0, sigma=0.9):
     """coarsen_restarts.py:519-581: delp_coarse (n_outer, nz, *h), ps_min (n_outer, *h) the block
     minimum of the fine surface pressure -> weights (n_outer, nz, *h)."""

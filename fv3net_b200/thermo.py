@@ -2,12 +2,11 @@
 (external/vcm/vcm/calc/thermo/vertically_dependent.py:41-66, 153-179, 189-208).
 
 `pressure_at_interface` is the sequential top-down cumulative sum from 300 Pa that feeds the
-remapper (the order of the additions is part of parity); it runs as a CUDA kernel.  The other
-two are thin compositions used by the budget workflow's exposed-area diagnostic.
+remapper (the order of the additions is part of parity).  All three run as CUDA kernels
+(cg_pressure_at_interface, cg_pressure_at_midpoint_log, cg_surface_pressure_nansum); this module only
+carries dims, coords and attrs.
 """
 from collections import OrderedDict
-
-import torch
 
 from . import labeled as lab
 from . import ops
@@ -46,11 +45,10 @@ def pressure_at_midpoint_log(delp, toa_pressure=TOA_PRESSURE, dim=COORD_Z_CENTER
     src = delp
     delp = lab.adapt(delp)
     axis = delp.get_axis_num(dim)
-    pi = _interface_tensor(delp, float(toa_pressure), dim)
-    logp = torch.log(pi)
-    n = logp.shape[axis]
-    dlogp = logp.narrow(axis, 1, n - 1) - logp.narrow(axis, 0, n - 1)
-    out = lay.device_tensor(delp) / dlogp
+    t = lay.device_tensor(delp)
+    shape = list(t.shape)
+    out = ops.pressure_at_midpoint_log(
+        t.reshape(lay.numel(shape[:axis]), shape[axis], lay.numel(shape[axis + 1:])), toa=float(toa_pressure)).reshape(shape)
     coords = OrderedDict(delp.coords)
     return lab.restore(DataArray(lay.finish(out, delp.dims, delp.dims, delp), delp.dims, coords,
                                  delp.name, None), src)
@@ -61,7 +59,13 @@ def surface_pressure_from_delp(delp, p_toa=300.0, vertical_dim="z"):
     src = delp
     delp = lab.adapt(delp)
     axis = delp.get_axis_num(vertical_dim)
-    out = lay.device_tensor(delp).sum(dim=axis) + p_toa
+    t = lay.device_tensor(delp)
+    shape = list(t.shape)
+    # xarray's sum skips NaN (skipna defaults to True for floats); additions top-down like numpy's reduction over
+    # an outer axis
+    out = ops.surface_pressure_nansum(
+        t.reshape(lay.numel(shape[:axis]), shape[axis], lay.numel(shape[axis + 1:])), toa=float(p_toa))
+    out = out.reshape(shape[:axis] + shape[axis + 1:])
     dims = tuple(d for d in delp.dims if d != vertical_dim)
     coords = OrderedDict((k, c) for k, c in delp.coords.items() if vertical_dim not in c.dims)
     return lab.restore(DataArray(lay.finish(out, dims, dims, delp), dims, coords, delp.name,

@@ -58,6 +58,7 @@ int cg_version(void);
  *   "plevel_nansafe" [0] | 1   the NaN-skipping variant of the streaming kernels alone, no fast first pass
  *   "mappm_arrays"   [auto] | shared   column work arrays of the generic remapper in shared memory
  *   "mappm_impl"     [auto] | generic  the generic remapper even where the streaming one applies
+ *   "exposed_area_impl" [auto] | strip | cell | three   formulation of cg_area_above_fine_surface (same bits)
  * CG_EINVAL for an unknown name or value. */
 int cg_set_option(const char *name, const char *value);
 /* number of CUDA kernels this library has launched in this process (monotonic) */
@@ -229,6 +230,17 @@ int cg_elementwise(int op, const void *a, const void *b, const void *c, double s
  * (n_outer, nz, h) -> (n_outer, h), sum over z (top-down) + toa. */
 int cg_surface_pressure(const void *delp, void *out, double toa, long n_outer, int nz, long h,
                         int dtype, void *stream);
+/* the same with xarray's default skipna=True of DataArray.sum (NaN thicknesses count as zero): what
+ * surface_pressure_from_delp returns for xarray inputs (vertically_dependent.py:203) */
+int cg_surface_pressure_nansum(const void *delp, void *out, double toa, long n_outer, int nz, long h,
+                               int dtype, void *stream);
+/* calc/thermo/vertically_dependent.py:153-179 pressure_at_midpoint_log: (n_outer, nz, h) -> same shape,
+ * delp / diff(log(p_interface)) with the interfaces of cg_pressure_at_interface (sequential cumsum from toa). */
+int cg_pressure_at_midpoint_log(const void *delp, void *out, double toa, long n_outer, int nz, long h,
+                                int dtype, void *stream);
+/* cubedsphere/coarsen.py:54-80 shift_edge_var_to_center: (n_outer, n, inner) -> (n_outer, n-1, inner),
+ * out[o,j,x] = 0.5 * (in[o,j+1,x] + in[o,j,x]) along the staggered dim. */
+int cg_shift_to_center(const void *in, void *out, long n_outer, int n, long inner, int dtype, void *stream);
 
 /* coarsen_restarts.py:519-581 (compute_blending_weights with pressure_at_midpoint_log and
  * surface_pressure_from_delp of the coarse delp): delp_coarse (n_outer, nz, h), ps_min

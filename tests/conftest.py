@@ -25,5 +25,6 @@ def _library_options_back_to_default():
     from fv3net_b200 import _lib
 
     if _lib._LIB is not None:
-        for name, value in (("plevel_impl", "auto"), ("plevel_nansafe", "0"), ("mappm_arrays", "auto"), ("mappm_impl", "auto")):
+        for name, value in (("plevel_impl", "auto"), ("plevel_nansafe", "0"), ("mappm_arrays", "auto"), ("mappm_impl", "auto"),
+                            ("exposed_area_impl", "auto")):
             _lib.set_option(name, value)

@@ -406,6 +406,40 @@ def test_pressure_at_interface_and_friends():
     np.testing.assert_allclose(pm.values, oracle.pressure_at_midpoint_log(delp, axis=1), rtol=2e-5)
 
 
+def test_thermo_helpers_run_on_the_library_bit_level():
+    """surface_pressure_from_delp, pressure_at_midpoint_log and shift_edge_var_to_center call CUDA kernels (not
+    torch expressions): launch counter moves, results equal the numpy restatements of the reference
+    (vertically_dependent.py:153-208, coarsen.py:54-80) bit for bit, except the logarithm, whose last bit is the
+    math library's: |d log p| <= 2 ulp of log(1e5) on each side of the difference."""
+    from fv3net_b200 import _lib, synthetic as syn
+    rng = np.random.RandomState(5)
+    delp = syn.delp_from_ps(syn.surface_pressure((2, 8, 8), seed=3))          # (2, 79, 8, 8) float32
+    delp[0, 5, 2, 3] = np.nan                                                  # xarray's sum skips it
+    da = DataArray(delp, ["tile", "pfull", "y", "x"])
+    n0 = _lib.lib().cg_launch_count()
+    ps = thermo.surface_pressure_from_delp(da, vertical_dim="pfull")
+    np.testing.assert_array_equal(ps.values, oracle.surface_pressure_from_delp(delp, axis=1))
+    zlast = thermo.surface_pressure_from_delp(DataArray(delp.transpose(0, 2, 3, 1), ["tile", "y", "x", "z"]))
+    np.testing.assert_array_equal(zlast.values, ps.values)                     # layout does not change the order of additions
+    delp = np.nan_to_num(delp, nan=400.0).astype(np.float32)
+    pm = thermo.pressure_at_midpoint_log(DataArray(delp, ["tile", "pfull", "y", "x"]), dim="pfull")
+    exp = oracle.pressure_at_midpoint_log(delp, axis=1)
+    pi = oracle.pressure_at_interface(delp, axis=1)
+    dlogp = np.diff(np.log(pi.astype(np.float64)), axis=1)
+    bound = 4 * np.spacing(np.float32(np.log(1.1e5))) / dlogp                  # relative: 2 ulp per logarithm
+    assert (np.abs(pm.values - exp) <= bound * np.abs(exp) + 2 * np.spacing(np.abs(exp))).all()
+    pm64 = thermo.pressure_at_midpoint_log(DataArray(delp.astype(np.float64), ["tile", "pfull", "y", "x"]), dim="pfull")
+    np.testing.assert_allclose(pm64.values, oracle.pressure_at_midpoint_log(delp.astype(np.float64), axis=1), rtol=1e-12)
+    u = rng.uniform(-30, 30, (2, 5, 9, 8)).astype(np.float32)
+    got = shift_edge_var_to_center(DataArray(u, ["tile", "z", "grid_y", "grid_xt"]))
+    np.testing.assert_array_equal(got.values, (np.float32(0.5) * (u[:, :, 1:] + u[:, :, :-1])))
+    v = rng.uniform(-30, 30, (2, 5, 8, 9))
+    got = shift_edge_var_to_center(DataArray(v, ["tile", "z", "grid_yt", "grid_x"]))
+    assert got.dims == ("tile", "z", "grid_yt", "grid_xt")
+    np.testing.assert_array_equal(got.values, 0.5 * (v[..., 1:] + v[..., :-1]))
+    assert _lib.lib().cg_launch_count() - n0 >= 6
+
+
 # ================================================================= compositions vs the oracle
 def _column_inputs(nt, n, seed, nvar=2):
     from fv3net_b200 import synthetic as syn

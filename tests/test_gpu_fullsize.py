@@ -187,6 +187,9 @@ def test_config3_deterministic_under_load(ops, mask_below):
         ok = np.isfinite(e)
         assert np.array_equal(np.isfinite(gg), ok)
         assert np.abs(gg[ok] - e[ok]).max() <= 1e-4 * np.abs(x).max()
+        # the bar above 3e-5 is adjudicated by the f64 evaluation (tests/parity.py); delp_coarse as the oracle forms it
+        from tests import parity
+        parity.assert_within_fp32_conditioning(gg, x, d_h, a_h, F, mask_below, threads=8, dc_gpu=dc_h)
 
 
 def test_config3_exposed_area_c384(ops):
@@ -200,11 +203,12 @@ def test_config3_exposed_area_c384(ops):
     exp = recipes.area_above_fine_surface(host(delp[tile:tile + 1, :, r0:r0 + 2 * F]), host(dc[tile:tile + 1, :, r0 // F:r0 // F + 2]),
                                           host(area[tile:tile + 1, r0:r0 + 2 * F]), F)
     g = host(got[tile:tile + 1, :, r0 // F:r0 // F + 2])
-    # a 1-ulp difference between libm's and CUDA's logf can flip a single column whose surface pressure sits on a
-    # coarse mid-level (see test_gpu_remap.test_area_above_fine_surface): allow a few, each at most 3 columns' area
-    bad = ~np.isclose(g, exp, rtol=2e-6, atol=0)
-    assert bad.mean() < 1e-2
-    assert np.abs(g - exp)[bad].max(initial=0.0) <= 3 * float(area.max())
+    # a cell may differ only by the area of columns whose surface pressure sits within the logarithm's rounding of
+    # the level's mid pressure (tests/parity.py)
+    from tests import parity
+    nflip = parity.assert_exposed_area_matches(g, host(delp[tile:tile + 1, :, r0:r0 + 2 * F]), host(dc[tile:tile + 1, :, r0 // F:r0 // F + 2]),
+                                               host(area[tile:tile + 1, r0:r0 + 2 * F]), F)
+    assert nflip <= 0.01 * g.size
     # the exposed area never exceeds the block's area and grows monotonically upward (lower pressure)
     tot = ops.block_reduce(area, "sum", F, F)
     assert (got <= tot[:, None] * (1 + 1e-6)).all()
