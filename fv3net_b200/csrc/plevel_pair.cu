@@ -848,6 +848,7 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         int row = -1;
         float cw = 0.f, cps = 0.f;
         uint32_t cnt = 0;
+        bool bad_geometry = false;                                   // a thickness that is not positive and finite
         for (int it = par; it < total; it += 2) {
             const int chunk = chunk_n, r2 = row_n;
             TRACE(gw, it, 0);
@@ -864,6 +865,12 @@ plevel_pair_kernel(const __grid_constant__ Params p)
             }
             const float pm3 = pbase, pm2 = pm3 + dn[0], pm1 = pm2 + dn[1], p0 = pm1 + dn[2], pp1 = p0 + dn[3];
             pbase = (pp1 + dn[4]) + dn[5];
+            if (!NS) {
+                // the fast variant's block sums have no NaN tests: a source layer without thickness (0 / 0 in
+                // mappm.f90:75) sends the CTA to the NaN-safe variant, like a non-finite field value does
+                const int t1 = chunk * KC + sub;
+                if (t1 >= 1 && t1 <= nz) bad_geometry = bad_geometry || !(p0 - pm1 > 0.f) || !(p0 - pm1 < 3.0e38f);
+            }
             if (it + 2 < total) load_delp(row_n, chunk_n);
             // stage b of the field ring and geometry buffer b are released together by the field warps
             TRACE(gw, it, 1);
@@ -901,6 +908,7 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         }
         __syncwarp();
         if (lane == 0 && row >= 0) mbar_arrive(cempty + 8 * (row & 1));
+        if (!NS && bad_geometry) p.flags[cta] = 1;
         return;
     }
 

@@ -1033,6 +1033,7 @@ plevel_stream_kernel(const __grid_constant__ Params p)
         const int mine = (nsrc - gw + NCELL - 1) / NCELL;            // this warp's share of the TMA boxes: gw, gw + 4, ... (<= 16)
         const CUtensorMap *mymap = &p.maps[gw + NCELL * (lane < mine ? lane : 0)];
         const uint32_t mydst = ring + (gw + NCELL * lane) * BOX_BYTES;
+        bool bad_geometry = false;                                   // a thickness that is not positive and finite
         for (int row = 0; row < 8; ++row) {
             ColG col;
             col.w = lds32(colw + 4 * (row * NCOL + x));
@@ -1045,6 +1046,10 @@ plevel_stream_kernel(const __grid_constant__ Params p)
                 // every warp carries the running sum of its own column walk, same order of additions
                 const float pm3 = plast, pm2 = pm3 + dn[0], pm1 = pm2 + dn[1], p0 = pm1 + dn[2], pp1 = p0 + dn[3];
                 plast = pp1;
+                if (!NS) {                                           // the fast variant's sums have no NaN tests: see below
+                    const int t1 = chunk * KC + gw;
+                    if (t1 >= 1 && t1 <= nz) bad_geometry = bad_geometry || !(p0 - pm1 > 0.f) || !(p0 - pm1 < 3.0e38f);
+                }
                 if (chunk + 1 == nch) {                              // on to the next row
                     dptr = dcol + (long)(gw - 3) * h + (long)(row + 1) * nx;
                     dlvl = gw - 3;
@@ -1063,6 +1068,8 @@ plevel_stream_kernel(const __grid_constant__ Params p)
                 if (lane == 0) mbar_arrive(gfull + 8 * b);
             }
         }
+        // a source layer without thickness (0 / 0 in mappm.f90:75) or a NaN thickness: the NaN-safe variant reruns the CTA
+        if (!NS && bad_geometry) p.flags[cta] = 1;
         return;
     }
 

@@ -83,6 +83,36 @@ def test_weighted_block_average_mass_multi_field(ops, f, n):
         assert_sum_close(host(g), oracle.weighted_block_average(x, mass, f), scale=10.0)
 
 
+@pytest.mark.parametrize("mode", ["area", "mass", "w3d"])
+def test_weighted_block_average_f16_warp_path(ops, mode):
+    """f = 16 at widths that are multiples of 64: a warp per four cells with shuffle reduction; weights read once per
+    block for all fields; NaN products and NaN weights skipped like nansum."""
+    rng = np.random.RandomState(16)
+    n, f = 128, 16
+    fields = [rng.uniform(-10, 10, (2, 3, n, n)).astype(np.float32) for _ in range(4)]
+    delp = rng.uniform(3, 5, (2, 3, n, n)).astype(np.float32)
+    area = rng.uniform(0.5, 1, (2, n, n)).astype(np.float32)
+    fields[0][0, 1, 17, 33] = np.nan
+    fields[1][1, 2, 64:80, 16:32] = np.nan              # an all-NaN block: 0 / den
+    area[1, 100, 100] = np.nan
+    if mode == "area":
+        got = ops.weighted_block_average([dev(x) for x in fields], w2d=dev(area), fy=f, fx=f)
+        w = np.broadcast_to(area[:, None], delp.shape)
+    elif mode == "mass":
+        got = ops.weighted_block_average([dev(x) for x in fields], w2d=dev(area), w3d=dev(delp), fy=f, fx=f)
+        w = delp * area[:, None]
+    else:
+        w = delp * area[:, None]
+        got = ops.weighted_block_average([dev(x) for x in fields], w3d=dev(w), fy=f, fx=f)
+    for g, x in zip(got, fields):
+        assert_sum_close(host(g), oracle.weighted_block_average(x, w, f), scale=10.0)
+    assert host(got[1])[1, 2, 4, 1] == 0.0
+    again = ops.weighted_block_average([dev(x) for x in fields], w2d=dev(area), fy=f, fx=f)
+    if mode == "area":
+        for a, b in zip(got, again):
+            assert torch.equal(torch.nan_to_num(a), torch.nan_to_num(b))      # fixed reduction tree
+
+
 @pytest.mark.parametrize("f", [8, 4])
 def test_weighted_block_average_nan_skipping(ops, f):
     """xarray coarsen().sum() is nansum: NaN products are skipped, the weight stays in the

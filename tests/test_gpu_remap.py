@@ -412,6 +412,31 @@ def test_pressure_level_nonfinite_values_rerun_only_their_blocks(ops, monkeypatc
         np.testing.assert_allclose(a[~touched & fin], b[~touched & fin], rtol=0, atol=3e-5 * 5)
 
 
+@pytest.mark.parametrize("kernel", ["stream", "pair"])
+def test_pressure_level_degenerate_thickness(ops, monkeypatch, kernel):
+    """A source layer without thickness (0 / 0 in mappm.f90:75) or a NaN thickness makes the column's remap NaN where
+    the layer is touched; the block sums skip it like nansum.  The fast pass has no NaN tests in its sums, so it must
+    notice the geometry and hand the CTA to the NaN-safe variant: both give the same answer."""
+    nt, nc, f = 1, 8, 8
+    ny = nx = nc * f
+    delp = syn.delp_from_ps(syn.surface_pressure((nt, ny, nx), seed=31))
+    area = syn.area((nt, ny, nx), seed=32)
+    flds = [syn.field((nt, syn.NZ, ny, nx), 33 + i, scale=10.0 ** i) for i in range(2)]
+    delp[0, 30, 5, 6] = 0.0
+    delp[0, 50, 40, 41] = np.nan
+    res = {}
+    for impl in (kernel, kernel + "_nansafe"):
+        _pin_impl(monkeypatch, impl)
+        outs, _ = ops.pressure_level_average([dev(x) for x in flds], dev(delp), dev(area), f)
+        res[impl] = [host(o) for o in outs]
+    for a, b in zip(res[kernel], res[kernel + "_nansafe"]):
+        touched = np.zeros(a.shape, bool)
+        touched[:, :, 0, 0:4] = True
+        touched[:, :, 5, 4:8] = True
+        np.testing.assert_array_equal(a[touched], b[touched])          # the rerun CTAs: the NaN-safe variant's bits
+        np.testing.assert_allclose(a[~touched], b[~touched], rtol=0, atol=3e-5 * 10, equal_nan=True)
+
+
 def test_pressure_level_golden_restart_T(ops):
     """The reference's golden pressure-level T (test_coarsen_restarts.py) through CUDA."""
     tag = "pressure-level-without-agrid-winds"

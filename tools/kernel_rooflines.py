@@ -60,6 +60,11 @@ report("weighted_block_average, 1 field, area weights (C384, 79 levels)", f3 + f
        lambda: ops.weighted_block_average(fields[0], w2d=area, fy=F, fx=F))
 report("weighted_block_average, 13 fields, mass weights delp*area", 14 * f3 + f2 + 13 * c3,
        lambda: ops.weighted_block_average(fields, w2d=area, w3d=delp, fy=F, fx=F))
+c3_16 = 4 * nt * nz * (n // 16) ** 2
+report("weighted_block_average f=16 (C384 -> C24), 13 fields, mass weights", 14 * f3 + f2 + 13 * c3_16,
+       lambda: ops.weighted_block_average(fields, w2d=area, w3d=delp, fy=16, fx=16))
+report("weighted_block_average f=16, 1 field, area weights", f3 + f2 + c3_16,
+       lambda: ops.weighted_block_average(fields[0], w2d=area, fy=16, fx=16))
 u = syn.torch_field((nt, nz, n + 1, n), 40, dev)
 dx = syn.torch_area((nt, n + 1, n), 41, dev)
 report("edge_weighted_block_average u/dx (reads the 49 kept rows only)", (f3 + f2) // 8 + c3,
