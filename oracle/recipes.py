@@ -19,15 +19,25 @@ FACE_CONNECTIONS = {
 }
 
 
-def regrid_vertical(p_in, f_in, p_out, iv=1, kord=1, dtype=np.float32, threads=1):
+def regrid_vertical(p_in, f_in, p_out, iv=1, kord=1, dtype=np.float32, threads=1, zlast=True):
     """external/vcm/vcm/cubedsphere/regridz.py:164-279 on (tile, z, y, x) arrays:
-    columnwise mappm, fp32 inside (f2py casts to ``real``), float32 out."""
+    columnwise mappm, fp32 inside (f2py casts to ``real``), float32 out.
+
+    zlast (default): the reference's access pattern - the three arrays are transposed to z-last and copied
+    (regridz.py:206-242, :317-325 reshape to (ncol, nz) for f2py), the remapper walks contiguous columns, and the
+    result is transposed back.  zlast=False walks the columns in place at stride ny * nx (same values)."""
     p_in, f_in, p_out = (np.ascontiguousarray(a) for a in (p_in, f_in, p_out))
     nt, km, ny, nx = f_in.shape
     kn = p_out.shape[1] - 1
     if p_in.shape != (nt, km + 1, ny, nx) or p_out.shape != (nt, kn + 1, ny, nx):
         raise ValueError("All dimensions except vertical must be same size for p_in, f_in and p_out")
     h = ny * nx
+    if zlast:
+        pz, fz, oz = (np.ascontiguousarray(np.moveaxis(a, 1, -1)) for a in (p_in, f_in, p_out))
+        out = mappm_strided(pz, fz, oz, 1, nt * h, km, kn,
+                            (0, km + 1, 1), (0, km, 1), (0, kn + 1, 1), (0, kn, 1),
+                            iv=iv, kord=kord, dtype=dtype, threads=threads)
+        return np.ascontiguousarray(np.moveaxis(out.reshape(nt, ny, nx, kn), -1, 1))
     out = mappm_strided(p_in, f_in, p_out, nt, h, km, kn,
                         ((km + 1) * h, 1, h), (km * h, 1, h), ((kn + 1) * h, 1, h), (kn * h, 1, h),
                         iv=iv, kord=kord, dtype=dtype, threads=threads)
