@@ -712,7 +712,10 @@ plevel_pair_kernel(const __grid_constant__ Params p)
     const int ny = p.ny, nx = p.nx, nyc = ny >> 3, nxc = nx >> 3;
     const long h = (long)ny * nx, hc = (long)nyc * nxc;
 
-    if (warp == nfw + NGW) {
+    // roles of the last seven warps: the column walker sits in the middle (with 13 field warps it then shares its
+    // scheduler with four field warps and no geometry warp; the other three schedulers get three field warps and two
+    // geometry warps each)
+    if (warp == nfw + KC) {
         // ---------------- column walker: lane = fine column, one row ahead of the geometry warps ----------
         // The two-pointer merge of mappm.f90:70-75: walking the column down with the reference's sequential
         // cumsum of interface pressures (same additions as the geometry warps: bit-identical), count the coarse
@@ -756,7 +759,7 @@ plevel_pair_kernel(const __grid_constant__ Params p)
     }
     if (warp >= nfw) {
         // ---------------- geometry warp gw: lane = fine column x of the CTA's 32, level 3 chunk + gw ----
-        const int gw = warp - nfw;
+        const int gw = warp - nfw < KC ? warp - nfw : warp - nfw - 1;
         const int x = lane, cell = x >> 3;
         const uint32_t colw = sbase + lay.colw, colps = sbase + lay.colps;
         // CTA prologue: coarse interfaces (sequential cumsum, vertically_dependent.py:61-63), 1 / thickness,
@@ -845,6 +848,21 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         const uint32_t srow = sbase + lay.srow;
         const int nrows = nsrc * KC;
         const long lane_off = 4 * (long)(NCOL * bx + 4 * (lane & 7));        // bytes
+        // the first NCP of this lane's rows (all of them for up to 28 sources) with their addresses in registers
+        constexpr int NCP = 7;
+        const char *csrc[NCP];
+        uint32_t cdst[NCP];                                              // byte offset in the stage | level of the stage; ~0: none
+#pragma unroll
+        for (int i = 0; i < NCP; ++i) {
+            const int R = 4 * sub + (lane >> 3) + 4 * KC * i;
+            csrc[i] = nullptr;
+            cdst[i] = ~0u;
+            if (R < nrows) {
+                const u64 e = lds64(srow + 8 * R);
+                csrc[i] = (const char *)(uintptr_t)(e & ~15ull) + lane_off;
+                cdst[i] = (uint32_t)(R * 128 + ((((uint32_t)lane ^ (uint32_t)R) & 7u) << 4)) | ((uint32_t)e & 3u);
+            }
+        }
         int row = -1;
         float cw = 0.f, cps = 0.f;
         uint32_t cnt = 0;
@@ -877,14 +895,22 @@ plevel_pair_kernel(const __grid_constant__ Params p)
             if (it >= NSTAGE) asm volatile("bar.sync %0, %1;" ::"r"(2 + b), "r"(nthreads) : "memory");
             TRACE(gw, it, 2);
             {
-                const long stage_off = 4 * (((o * nz + chunk * KC) * (long)ny + 8 * by + row) * nx) + lane_off;
+                const long stage_off = 4 * (((o * nz + chunk * KC) * (long)ny + 8 * by + row) * nx);
                 const uint32_t dst0 = ring + b * lay.stage_bytes;
-                for (int R = 4 * sub + (lane >> 3); R < nrows; R += 4 * KC) {
+                const int lv0 = chunk * KC;
+#pragma unroll
+                for (int i = 0; i < NCP; ++i)
+                    if (cdst[i] != ~0u) {
+                        const int sz = lv0 + (int)(cdst[i] & 3u) < nz ? 16 : 0;   // levels past the column bottom: zeros
+                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst0 + (cdst[i] & ~15u)),
+                                     "l"(csrc[i] + stage_off), "r"(sz) : "memory");
+                    }
+                for (int R = 4 * sub + (lane >> 3) + 4 * KC * NCP; R < nrows; R += 4 * KC) {     // more than 28 sources
                     const u64 e = lds64(srow + 8 * R);
                     const int kk = (int)e & 3;
-                    const char *src = (const char *)(uintptr_t)(e & ~15ull) + stage_off;
+                    const char *src = (const char *)(uintptr_t)(e & ~15ull) + stage_off + lane_off;
                     const uint32_t dst = dst0 + R * 128 + ((((uint32_t)lane ^ (uint32_t)R) & 7u) << 4);
-                    const int sz = chunk * KC + kk < nz ? 16 : 0;            // levels past the column bottom: zeros
+                    const int sz = lv0 + kk < nz ? 16 : 0;
                     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
                 }
                 asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bars + 8 * b) : "memory");
