@@ -32,7 +32,12 @@ constexpr int NCOL = 32;             // fine columns per CTA row = lanes of a ge
 constexpr int NPAIR = NCOL / 2;      // column pairs per CTA row
 constexpr int KC = 3;                // levels per pipeline stage
 constexpr int NGW = 2 * KC;          // geometry warps: one per level of a stage, two stages in flight
-constexpr int NSTAGE = 3;
+#ifndef CG_NSTAGE
+#define CG_NSTAGE 3
+#endif
+constexpr int NSTAGE = CG_NSTAGE;    // stages of the field ring = geometry record buffers (3 or 4)
+constexpr int BAR_STAGE0 = 2;        // named barriers BAR_STAGE0 + b: stage / buffer b is handed back
+constexpr int BAR_OUT = BAR_STAGE0 + NSTAGE, BAR_WALK = BAR_OUT + 1;
 constexpr int BOX_BYTES = KC * 128;  // one source, one stage: 3 rows of 32 columns (odd row count: 8 swizzle phases over 8 sources)
 constexpr int MAXFW = 13;            // field warps: 20 warps with the geometry warps and the column walker = 5 per scheduler, 96 registers
 constexpr int MAXV = MAXFW * 32 / NPAIR;     // 26 output fields per launch
@@ -49,7 +54,7 @@ constexpr int MAXE = 2;              // listed further events per (column, layer
 constexpr int INFO_SLOW = 255;
 constexpr int OVA_BYTES = KC * NCOL * MAXE * 16;     // (x, y, z, -w) per event
 constexpr int OVB_BYTES = KC * NCOL * MAXE * 4;      // accumulator byte offset per event
-constexpr int TAILMAX = 16;          // listed further events of the layer below the surface: (x, offset) per event
+constexpr int TAILMAX = NSTAGE > 3 ? 8 : 16;         // listed further events of the layer below the surface: (x, offset) per event
 constexpr int TAIL_BYTES = NCOL * TAILMAX * 8;
 constexpr int EDGE_WORDS = 24;       // per column: one-sided cubic coefficients, top (0..8) and bottom (12..20)
 enum { CTX_NZ, CTX_MASK, CTX_TOA, CTX_REC, CTX_OVA, CTX_OVB, CTX_EDGE, CTX_TAIL, CTX_CELL0, CTX_CELLB, CTX_ACC, CTX_PE2,
@@ -722,7 +727,7 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         // interfaces at or above every fine interface.  cnt[L][x] for L = 1 .. nz; one byte each.
         const int x = lane;
         const uint32_t pe2 = sbase + lay.cell0 + (x >> 3) * lay.cell_bytes + lay.pe2;
-        asm volatile("bar.sync 6, %0;" ::"n"((NGW + 1) * 32) : "memory");   // the cells' coarse interfaces are in place
+        asm volatile("bar.sync %0, %1;" ::"n"(BAR_WALK), "n"((NGW + 1) * 32) : "memory");   // the cells' coarse interfaces are in place
         const float *dcol = p.delp + o * nz * h + (long)(8 * by) * nx + NCOL * bx + x;
         constexpr int WB = 8;                                            // levels per batch of loads
         for (int row = 0; row < 8; ++row) {
@@ -809,7 +814,7 @@ plevel_pair_kernel(const __grid_constant__ Params p)
                 }
             }
         }
-        asm volatile("bar.sync 6, %0;" ::"n"((NGW + 1) * 32) : "memory");   // with the column walker
+        asm volatile("bar.sync %0, %1;" ::"n"(BAR_WALK), "n"((NGW + 1) * 32) : "memory");   // with the column walker
         CellG g;
         g.pe2 = sbase + lay.cell0 + cell * lay.cell_bytes + lay.pe2;
         g.rdp2 = sbase + lay.cell0 + cell * lay.cell_bytes + lay.rdp2;
@@ -892,7 +897,7 @@ plevel_pair_kernel(const __grid_constant__ Params p)
             if (it + 2 < total) load_delp(row_n, chunk_n);
             // stage b of the field ring and geometry buffer b are released together by the field warps
             TRACE(gw, it, 1);
-            if (it >= NSTAGE) asm volatile("bar.sync %0, %1;" ::"r"(2 + b), "r"(nthreads) : "memory");
+            if (it >= NSTAGE) asm volatile("bar.sync %0, %1;" ::"r"(BAR_STAGE0 + b), "r"(nthreads) : "memory");
             TRACE(gw, it, 2);
             {
                 const long stage_off = 4 * (((o * nz + chunk * KC) * (long)ny + 8 * by + row) * nx);
@@ -930,7 +935,7 @@ plevel_pair_kernel(const __grid_constant__ Params p)
             __syncwarp();                                            // (mbarrier.arrive releases the warp's writes)
             TRACE(gw, it, 3);
             if (lane == 0) mbar_arrive(gfull + 8 * b);
-            b = b == 0 ? 2 : b - 1;                                  // (it + 2) % 3
+            b = (b + 2) % NSTAGE;
         }
         __syncwarp();
         if (lane == 0 && row >= 0) mbar_arrive(cempty + 8 * (row & 1));
@@ -1017,7 +1022,7 @@ plevel_pair_kernel(const __grid_constant__ Params p)
                          "l"(st.run), "l"(chk) : "memory");
             __syncwarp();
             if (warp == 0 || warp == nfw - 1) TRACE(warp == 0 ? 7 : 8, it, 3);
-            if (it + NSTAGE < total) asm volatile("bar.arrive %0, %1;" ::"r"(2 + b), "r"(nthreads) : "memory");
+            if (it + NSTAGE < total) asm volatile("bar.arrive %0, %1;" ::"r"(BAR_STAGE0 + b), "r"(nthreads) : "memory");
         }
     }
     if (!NS) {
@@ -1028,7 +1033,7 @@ plevel_pair_kernel(const __grid_constant__ Params p)
 
     // coarse outputs: the four pairs of a cell in a fixed order, block sum / weight sum (coarsen.py:213);
     // 0/0 -> NaN like the reference
-    asm volatile("bar.sync 5, %0;" ::"r"(nfw * 32) : "memory");
+    asm volatile("bar.sync %0, %1;" ::"n"(BAR_OUT), "r"(nfw * 32) : "memory");
     const uint32_t acc0 = sbase + lay.acc;
     for (int idx = tid; idx < nz * NCELL * V; idx += nfw * 32) {
         const int c = idx % NCELL, vv = (idx / NCELL) % V, k = idx / (NCELL * V);
