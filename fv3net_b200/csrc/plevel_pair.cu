@@ -827,9 +827,13 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         // P(t-3) .. P(t+1); the warp's next step of the row is at t + 6.  dn = thicknesses of levels t-3 .. t+2,
         // loaded one step ahead; e0, e1 = levels t-5, t-4 at the first step of a row, where t <= 5.
         float dn[2 * KC], e0 = 0.f, e1 = 0.f, pbase = toa;
-        auto load_delp = [&](int row2, int chunk2) {
+        // (addresses are carried from step to step: the next thicknesses at dnext, the stage's planes at snext bytes)
+        const long dstep = 2L * KC * h, dwrap = (long)nx - (long)nch * KC * h;
+        const float *dnext = dcol + (long)(par * KC + sub - 3) * h;
+        long snext = 4 * (((o * nz + par * KC) * (long)ny + 8 * by) * nx);
+        auto load_delp = [&](int chunk2) {
             const int t2 = chunk2 * KC + sub;
-            const float *d = dcol + (long)row2 * nx + (long)(t2 - 3) * h;
+            const float *d = dnext;
             if (t2 >= 2 * KC && t2 + 2 < nz) {                       // inside the column
 #pragma unroll
                 for (int i = 0; i < 2 * KC; ++i) dn[i] = __ldg(d + i * h);
@@ -846,7 +850,7 @@ plevel_pair_kernel(const __grid_constant__ Params p)
             }
         };
         int row_n = 0, chunk_n = par, b = par;                       // (nch >= 3: the first stages are in row 0)
-        load_delp(row_n, chunk_n);
+        load_delp(chunk_n);
         // The field boxes of a stage, [source][level][32 columns] with the 16-byte chunks of a row xor-swizzled by
         // the row index (the field threads' 8-byte reads of a column pair are then conflict-free), are filled by
         // asynchronous 16-byte copies: an instruction moves four rows; warp sub takes instructions sub, sub + 3, ...
@@ -875,8 +879,11 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         for (int it = par; it < total; it += 2) {
             const int chunk = chunk_n, r2 = row_n;
             TRACE(gw, it, 0);
+            const long stage_off = snext;
             chunk_n += 2;
-            if (chunk_n >= nch) { chunk_n -= nch; ++row_n; }
+            dnext += dstep;
+            snext += 4 * dstep;
+            if (chunk_n >= nch) { chunk_n -= nch; ++row_n; dnext += dwrap; snext += 4 * dwrap; }
             if (r2 != row) {
                 if (row >= 0) { __syncwarp(); if (lane == 0) mbar_arrive(cempty + 8 * (row & 1)); }
                 row = r2;
@@ -894,22 +901,29 @@ plevel_pair_kernel(const __grid_constant__ Params p)
                 const int t1 = chunk * KC + sub;
                 if (t1 >= 1 && t1 <= nz) bad_geometry = bad_geometry || !(p0 - pm1 > 0.f) || !(p0 - pm1 < 3.0e38f);
             }
-            if (it + 2 < total) load_delp(row_n, chunk_n);
+            if (it + 2 < total) load_delp(chunk_n);
             // stage b of the field ring and geometry buffer b are released together by the field warps
             TRACE(gw, it, 1);
             if (it >= NSTAGE) asm volatile("bar.sync %0, %1;" ::"r"(BAR_STAGE0 + b), "r"(nthreads) : "memory");
             TRACE(gw, it, 2);
             {
-                const long stage_off = 4 * (((o * nz + chunk * KC) * (long)ny + 8 * by + row) * nx);
                 const uint32_t dst0 = ring + b * lay.stage_bytes;
                 const int lv0 = chunk * KC;
+                if (lv0 + KC <= nz) {                                        // every level of the stage is in the column
 #pragma unroll
-                for (int i = 0; i < NCP; ++i)
-                    if (cdst[i] != ~0u) {
-                        const int sz = lv0 + (int)(cdst[i] & 3u) < nz ? 16 : 0;   // levels past the column bottom: zeros
-                        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst0 + (cdst[i] & ~15u)),
-                                     "l"(csrc[i] + stage_off), "r"(sz) : "memory");
-                    }
+                    for (int i = 0; i < NCP; ++i)
+                        if (cdst[i] != ~0u)
+                            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst0 + (cdst[i] & ~15u)),
+                                         "l"(csrc[i] + stage_off) : "memory");
+                } else {
+#pragma unroll
+                    for (int i = 0; i < NCP; ++i)
+                        if (cdst[i] != ~0u) {
+                            const int sz = lv0 + (int)(cdst[i] & 3u) < nz ? 16 : 0;   // levels past the column bottom: zeros
+                            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst0 + (cdst[i] & ~15u)),
+                                         "l"(csrc[i] + stage_off), "r"(sz) : "memory");
+                        }
+                }
                 for (int R = 4 * sub + (lane >> 3) + 4 * KC * NCP; R < nrows; R += 4 * KC) {     // more than 28 sources
                     const u64 e = lds64(srow + 8 * R);
                     const int kk = (int)e & 3;
