@@ -42,7 +42,7 @@ __device__ __forceinline__ float edge_al(float qm, float q, float dmm, float dm,
 }
 
 struct Target {                      // the walk over the target layers of the column
-    const float *p2;
+    const float *p2n;                // running pointers: interface k + 2, layer k
     float *f2;
     long l_pe2, l_q2;
     int k, kn, mode;                 // mode 1: target layer k is open (its top lies in a source layer above)
@@ -52,12 +52,14 @@ struct Target {                      // the walk over the target layers of the c
 
     __device__ __forceinline__ void emit(float v)
     {
-        f2[(long)k * l_q2] = v;
+        *f2 = v;
+        f2 += l_q2;
         ++k;
         bad = bad || !(bot >= top);
         top = bot;
         bot = botn;
-        if (k + 2 <= kn) botn = p2[(long)(k + 2) * l_pe2];
+        p2n += l_pe2;
+        if (k + 2 <= kn) botn = *p2n;
     }
 };
 
@@ -115,14 +117,15 @@ mappm_stream_kernel(const float *__restrict__ pe1, const float *__restrict__ q1,
     const long l_pe1 = s.v[2], l_q1 = s.v[5];
 
     Target t;
-    t.p2 = pe2 + o * s.v[6] + i2 * s.v[7];
+    const float *p2 = pe2 + o * s.v[6] + i2 * s.v[7];
     t.f2 = q2 + o * s.v[9] + i * s.v[10];
     t.l_pe2 = s.v[8];
     t.l_q2 = s.v[11];
     t.k = 0; t.kn = kn; t.mode = 0; t.qsum = 0.f; t.dpsum = 0.f; t.bad = false;
-    t.top = t.p2[0];
-    t.bot = t.p2[t.l_pe2];
-    t.botn = kn >= 2 ? t.p2[2 * t.l_pe2] : t.bot;
+    t.top = p2[0];
+    t.bot = p2[t.l_pe2];
+    t.botn = kn >= 2 ? p2[2 * t.l_pe2] : t.bot;
+    t.p2n = p2 + 2 * t.l_pe2;
 
     const float pe_top = p1[0], pe_bot = p1[(long)km * l_pe1];
     const float q_top = f1[0], q_bot = f1[(long)(km - 1) * l_q1];
@@ -176,7 +179,8 @@ mappm_stream_kernel(const float *__restrict__ pe1, const float *__restrict__ q1,
     float dL = d2, dN = d3, dNN = pd - pc;                               // levels L, L + 1, L + 2
     bad = bad || !(dNN > 0.f);
     float dcL = dc2, alL = al2;
-    if (km > 5) { qnext = f1[5 * l_q1]; pnext = p1[6 * l_pe1]; }
+    const float *f1n = f1 + 5 * l_q1, *p1n = p1 + 6 * l_pe1;            // level L + 3, interface L + 4 at L = 2
+    if (km > 5) { qnext = *f1n; pnext = *p1n; }
 
     for (int L = 2; L <= km - 3; ++L) {
         // level L + 2 has arrived: slope of L + 1, upper edge of L + 1 = lower edge of L
@@ -193,7 +197,8 @@ mappm_stream_kernel(const float *__restrict__ pe1, const float *__restrict__ q1,
             qc = qnext; pd = pnext;
             dNN = pd - pc;
             bad = bad || !(dNN > 0.f);
-            if (L + 4 <= km - 1) { qnext = f1[(long)(L + 4) * l_q1]; pnext = p1[(long)(L + 5) * l_pe1]; }
+            f1n += l_q1; p1n += l_pe1;
+            if (L + 4 <= km - 1) { qnext = *f1n; pnext = *p1n; }
         }
     }
     {                                                                     // bottom :729-761; now qa = q(km-2), qb = q(km-1)
