@@ -51,32 +51,41 @@ def bind_host_thread(device=None):
     process per GPU on an 8-GPU box the host -> device streams otherwise meet in one socket's memory.  Returns the
     CPU set, or None when NVML or the affinity call is not available (nothing is changed then)."""
     import os
+    import warnings
 
     try:
         import pynvml
 
         index = torch.cuda.current_device() if device is None else torch.device(device).index
         pynvml.nvmlInit()
-        # NVML enumerates physical devices; honour CUDA_VISIBLE_DEVICES through the PCI bus id
-        bus = torch.cuda.get_device_properties(index).pci_bus_id if hasattr(torch.cuda.get_device_properties(index), "pci_bus_id") else None
+        # NVML enumerates physical devices, CUDA the visible ones: match on the UUID, else on the full PCI id
+        # (domain:bus:device), never on the bus number alone
+        props = torch.cuda.get_device_properties(index)
+        uuid = str(getattr(props, "uuid", "") or "").lower().replace("gpu-", "")
+        pci = tuple(getattr(props, k, None) for k in ("pci_domain_id", "pci_bus_id", "pci_device_id"))
         handle = None
-        if bus is not None:
-            for i in range(pynvml.nvmlDeviceGetCount()):
-                h = pynvml.nvmlDeviceGetHandleByIndex(i)
-                if pynvml.nvmlDeviceGetPciInfo(h).bus == bus:
-                    handle = h
-                    break
+        for i in range(pynvml.nvmlDeviceGetCount()):
+            h = pynvml.nvmlDeviceGetHandleByIndex(i)
+            u = pynvml.nvmlDeviceGetUUID(h)
+            u = (u.decode() if isinstance(u, bytes) else str(u)).lower().replace("gpu-", "")
+            info = pynvml.nvmlDeviceGetPciInfo(h)
+            if (uuid and u == uuid) or (None not in pci and (info.domain, info.bus, info.device) == pci):
+                handle = h
+                break
         if handle is None:
-            handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            warnings.warn(f"bind_host_thread: cuda:{index} not found among NVML's devices; affinity left unchanged")
+            return None
         ncpu = os.cpu_count() or 1
         words = pynvml.nvmlDeviceGetCpuAffinity(handle, (ncpu + 63) // 64)
         cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
         cpus &= set(os.sched_getaffinity(0))
         if not cpus:
+            warnings.warn("bind_host_thread: NVML's CPU set for the device does not meet this process's; affinity left unchanged")
             return None
         os.sched_setaffinity(0, cpus)
         return cpus
-    except Exception:                       # no NVML, no permission, not Linux: leave the process where it is
+    except Exception as e:                  # no NVML, no permission, not Linux: leave the process where it is, and say so
+        warnings.warn(f"bind_host_thread: skipped ({type(e).__name__}: {e})")
         return None
 
 
