@@ -437,6 +437,31 @@ def test_pressure_level_degenerate_thickness(ops, monkeypatch, kernel):
         np.testing.assert_allclose(a[~touched], b[~touched], rtol=0, atol=3e-5 * 10, equal_nan=True)
 
 
+@pytest.mark.parametrize("kernel", ["pair", "stream", "fused"])
+def test_pressure_level_on_a_second_device_of_the_process(ops, monkeypatch, kernel):
+    """One process may drive several devices (BudgetPipeline(device=...)): the shared-memory opt-in of the fused
+    kernels is a per-device function attribute, so a launch on cuda:1 after cuda:0 must still get it."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs in one process")
+    nt, nc, f = 1, 8, 8
+    ny = nx = nc * f
+    delp = syn.delp_from_ps(syn.surface_pressure((nt, ny, nx), seed=41))
+    area = syn.area((nt, ny, nx), seed=42)
+    flds = [syn.field((nt, syn.NZ, ny, nx), 43 + i) for i in range(3)]
+    _pin_impl(monkeypatch, kernel)
+    res = []
+    for d in (0, 1, 0):
+        with torch.cuda.device(d):
+            outs, dc = ops.pressure_level_average([torch.from_numpy(x).cuda(d) for x in flds],
+                                                  torch.from_numpy(delp).cuda(d), torch.from_numpy(area).cuda(d), f)
+            torch.cuda.synchronize(d)
+            assert outs[0].device.index == d
+            res.append([host(o) for o in outs] + [host(dc)])
+    for other in res[1:]:
+        for a, b in zip(res[0], other):
+            np.testing.assert_array_equal(a, b)
+
+
 def test_pressure_level_golden_restart_T(ops):
     """The reference's golden pressure-level T (test_coarsen_restarts.py) through CUDA."""
     tag = "pressure-level-without-agrid-winds"
