@@ -54,13 +54,37 @@ def regrid_vertical(p_in, f_in, p_out, iv=1, kord=1, z_dim_center=RESTART_Z_CENT
     if z_dim_center == z_dim_outer:
         raise ValueError("'z_dim_center' and 'z_dim_outer' must not be equal.")
     src = f_in
+    lazy = next((a for a in (f_in, p_in, p_out) if lab.is_lazy(a)), None)
+    if lazy is not None:
+        # dask in -> dask out, nothing computed now (regridz.py:254-265 maps blocks lazily; test_regridz.py:63):
+        # the checks run on shapes alone, the inputs are materialised and the kernel runs when the graph is computed
+        mp, mf, mo = (lab.adapt(a, values=False) for a in (p_in, f_in, p_out))
+        _check_regrid_vertical(mp, mf, mo, z_dim_center, z_dim_outer)
+        shape = [mo.sizes[z_dim_outer] - 1 if d == z_dim_center else n for d, n in mf.sizes.items()]
+
+        def run():
+            return _regrid_vertical(lab.adapt(p_in), lab.adapt(f_in), lab.adapt(p_out), iv, kord, z_dim_center,
+                                    z_dim_outer).values
+
+        coords = OrderedDict((k, c) for k, c in mf.coords.items() if z_dim_center not in c.dims)
+        meta = DataArray(np.broadcast_to(np.zeros((), np.float32), shape), mf.dims, coords, mf.name, mf.attrs)
+        return lab.restore(meta, src, data=lab.defer(run, lazy, shape, np.float32))
     p_in, f_in, p_out = lab.adapt(p_in), lab.adapt(f_in), lab.adapt(p_out)
+    return lab.restore(_regrid_vertical(p_in, f_in, p_out, iv, kord, z_dim_center, z_dim_outer), src)
+
+
+def _check_regrid_vertical(p_in, f_in, p_out, z_dim_center, z_dim_outer):
     for name, da, zd in (("p_in", p_in, z_dim_outer), ("f_in", f_in, z_dim_center),
                          ("p_out", p_out, z_dim_outer)):
         if zd not in da.dims:
             raise ValueError(f"{name} has no dimension {zd!r}")
     _assert_equal_number_of_columns(p_in, f_in, p_out, z_dim_center, z_dim_outer)
     _assert_valid_vertical_dimension_sizes(p_in, f_in, z_dim_outer, z_dim_center)
+
+
+def _regrid_vertical(p_in, f_in, p_out, iv, kord, z_dim_center, z_dim_outer):
+    """The eager body of `regrid_vertical` on labelled arrays."""
+    _check_regrid_vertical(p_in, f_in, p_out, z_dim_center, z_dim_outer)
 
     dims = f_in.dims
     axis = f_in.get_axis_num(z_dim_center)
@@ -80,8 +104,7 @@ def regrid_vertical(p_in, f_in, p_out, iv=1, kord=1, z_dim_center=RESTART_Z_CENT
     ops.mappm(pe1, q, pe2, n_outer, n_inner, km, kn, strides(km + 1), strides(km), strides(kn + 1),
               strides(kn), out, iv=int(iv), kord=int(kord))
     coords = OrderedDict((k, c) for k, c in f_in.coords.items() if z_dim_center not in c.dims)
-    result = DataArray(lay.finish(out, dims, dims, f_in), dims, coords, f_in.name, f_in.attrs)
-    return lab.restore(result, src)
+    return DataArray(lay.finish(out, dims, dims, f_in), dims, coords, f_in.name, f_in.attrs)
 
 
 # ------------------------------------------------------------------ composition (a14, a15)

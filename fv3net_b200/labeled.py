@@ -317,20 +317,44 @@ def is_xarray(obj):
     return _xr is not None and isinstance(obj, (_xr.DataArray, _xr.Dataset))
 
 
-def adapt(obj):
-    """xarray -> labelled (dask-backed data are computed: the CUDA path is eager)."""
+def is_lazy(obj):
+    """An xarray DataArray whose data are a dask array (duck-typed: chunks + compute)."""
+    return (_xr is not None and isinstance(obj, _xr.DataArray) and hasattr(obj.data, "chunks")
+            and hasattr(obj.data, "compute"))
+
+
+def adapt(obj, values=True):
+    """xarray -> labelled (dask-backed data are computed here: the kernels are eager).  `values=False`: dims,
+    shape, coords, name and attrs only - the data become a zero-stride placeholder and nothing is computed."""
     if not is_xarray(obj):
         return obj
     if isinstance(obj, _xr.Dataset):
-        return Dataset({k: adapt(obj[k]) for k in obj.data_vars},
+        return Dataset({k: adapt(obj[k], values) for k in obj.data_vars},
                        {k: (c.dims, np.asarray(c.values), dict(c.attrs)) for k, c in obj.coords.items()
                         if not set(c.dims) - set(obj.dims)}, dict(obj.attrs))
     coords = {k: (c.dims, np.asarray(c.values), dict(c.attrs)) for k, c in obj.coords.items()}
-    return DataArray(np.asarray(obj.values), obj.dims, coords, obj.name, dict(obj.attrs))
+    if values:
+        data = np.asarray(obj.values)
+    else:
+        data = np.broadcast_to(np.zeros((), dtype=obj.data.dtype), tuple(obj.data.shape))
+    return DataArray(data, obj.dims, coords, obj.name, dict(obj.attrs))
 
 
-def restore(result, like):
-    """labelled -> xarray when the caller handed us xarray; lazy (dask) in -> lazy out."""
+def defer(fn, like, shape, dtype):
+    """An array of `like.data`'s own library (dask.array) whose values are `fn()` when the graph is computed:
+    `from_delayed(delayed(fn)(), shape, dtype)` - one chunk, the device work runs at compute time."""
+    import importlib
+    import sys
+
+    mod = sys.modules[type(like.data).__module__]
+    root = importlib.import_module(mod.__name__.split(".")[0])
+    delayed = getattr(root, "delayed", None) or getattr(mod, "delayed")
+    return mod.from_delayed(delayed(fn)(), shape=tuple(shape), dtype=np.dtype(dtype))
+
+
+def restore(result, like, data=None):
+    """labelled -> xarray when the caller handed us xarray; lazy (dask) in -> lazy out.  `data`: an array to put
+    in place of `result.values` (the deferred array of `defer`; `result` then only carries the metadata)."""
     if not is_xarray(like) or isinstance(result, (tuple, list)):
         if isinstance(result, tuple):
             return tuple(restore(r, like) for r in result)
@@ -339,11 +363,14 @@ def restore(result, like):
         return _xr.Dataset({k: restore(result[k], like[k] if k in like else like) for k in result.data_vars},
                            attrs=result.attrs)
     coords = {k: _xr.Variable(c.dims, c.values, c.attrs) for k, c in result.coords.items()}
+    if data is not None:
+        return _xr.DataArray(data, dims=result.dims, coords=coords, name=result.name, attrs=result.attrs)
     data = result.values
     src = like if isinstance(like, _xr.DataArray) else None
     if src is not None and hasattr(src.data, "compute") and hasattr(src.data, "chunks"):
-        # lazy (dask) in -> lazy out (regridz.py:254-265, test_regridz.py:63): the values were computed on the GPU
-        # when the call was made; they are handed back as one chunk of the input's own array type
+        # lazy (dask) in -> lazy out for the functions that do not defer their device work (regrid_vertical does,
+        # see there): the values were computed when the call was made and are handed back as one chunk of the
+        # input's own array type
         import sys
 
         data = sys.modules[type(src.data).__module__].from_array(data, chunks=data.shape)

@@ -101,10 +101,20 @@ def test_regrid_vertical_lazy_in_lazy_out(xr, lazy):
         d = fda.from_array(a, chunks=a.shape) if lazy else a
         return xr.DataArray(d, dims=("x", "y", zname), coords={"x": np.arange(4.0)}, name="f", attrs={"long_name": "field"})
 
+    from fv3net_b200 import _lib
+    computed, launched = fda.Array.computed, _lib.lib().cg_launch_count()
     out = regrid_vertical(wrap(p_in, "z_outer"), wrap(f_in, "z_center"), wrap(p_out, "z_outer"),
                           z_dim_center="z_center", z_dim_outer="z_outer")
     assert isinstance(out, xr.DataArray) and out.dims == ("x", "y", "z_center")
     assert isinstance(out.data, fda.Array) == lazy
+    assert out.shape == (4, 5, nz) and out.name == "f" and out.attrs == {"long_name": "field"}
+    if lazy:                # nothing was materialised and no kernel ran when the call was made ...
+        assert fda.Array.computed == computed and _lib.lib().cg_launch_count() == launched
+        with pytest.raises(ValueError):          # ... but the shape checks did (regridz.py:334-350)
+            regrid_vertical(wrap(p_in[:, :, :-1], "z_outer"), wrap(f_in, "z_center"), wrap(p_out, "z_outer"),
+                            z_dim_center="z_center", z_dim_outer="z_outer")
     eager = regrid_vertical(lab.DataArray(p_in, ["x", "y", "z_outer"]), lab.DataArray(f_in, ["x", "y", "z_center"], name="f"),
                             lab.DataArray(p_out, ["x", "y", "z_outer"]), z_dim_center="z_center", z_dim_outer="z_outer")
     np.testing.assert_array_equal(out.compute().values if lazy else out.values, eager.values)
+    if lazy:                # ... the three inputs and the result were materialised by compute(), on the GPU
+        assert fda.Array.computed == computed + 4 and _lib.lib().cg_launch_count() > launched

@@ -16,3 +16,7 @@ tail -2 gpurun_out/ncu_full.log
 python tools/kernel_rooflines.py > gpurun_out/kernel_rooflines.txt 2> gpurun_out/kernel_rooflines.err && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 2000 --csv --log-file gpurun_out/kernels_ncu.csv python tools/kernel_rooflines.py > gpurun_out/kernels_ncu.log 2>&1
 cat gpurun_out/kernel_rooflines.txt
+# the stand-alone remapper: timing, then one full capture of the streaming kernel
+python tools/mappm_bench.py 10 > gpurun_out/mappm_bench.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:mappm_stream_kernel -s 3 -c 1 -o gpurun_out/prof_mappm python tools/mappm_bench.py 2 > gpurun_out/ncu_mappm.log 2>&1
+cat gpurun_out/mappm_bench.log

@@ -97,3 +97,35 @@ if os.path.exists(kn):
             f.write(f"{k[:100]:100s} {n:8d} {t/n:10.1f} {lo:10.1f}\n")
     if os.path.exists(os.path.join(G, "kernel_rooflines.txt")):
         shutil.copy(os.path.join(G, "kernel_rooflines.txt"), os.path.join(P, f"{tag}_kernel_rooflines.txt"))
+
+# ---- the streaming remapper's capture -----------------------------------------------------------------------
+rep2 = os.path.join(G, "prof_mappm.ncu-rep")
+if os.path.exists(rep2):
+    raw = subprocess.run(["ncu", "-i", rep2, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    r = list(csv.reader(io.StringIO(raw))); h, u, v = r[0], r[1], r[2]
+    keep2 = ["gpu__time_duration.sum", "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+             "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread", "dram__bytes_read.sum",
+             "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+             "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
+             "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+             "smsp__thread_inst_executed_per_inst_executed.ratio"]
+    keep2 += [k for k in h if k.startswith("smsp__average_warps_issue_stalled_") and k.endswith("_per_issue_active.ratio")]
+    src_csv = subprocess.run(["ncu", "-i", rep2, "--page", "source", "--csv", "--print-source", "cuda,sass"],
+                             capture_output=True, text=True).stdout
+    cur = None; L = {}
+    for row in csv.reader(io.StringIO(src_csv)):
+        if not row: continue
+        if row[0] == "File Path": cur = row[1].split("/")[-1]; continue
+        if len(row) > 8 and row[0].isdigit() and row[2] == "-":
+            try: L[(cur, int(row[0]))] = (int(row[7]), int(row[6]), row[1])
+            except ValueError: pass
+    with open(os.path.join(P, f"{tag}_ncu_mappm_stream.txt"), "w") as f:
+        f.write("# ncu --set full --clock-control none --import-source on -k regex:mappm_stream_kernel -s 3 -c 1: python tools/mappm_bench.py 2\n")
+        f.write(f"# kernel: {v[h.index('Kernel Name')]}, one C384 field (6 x 79 x 384 x 384) to a fine-grid result, kord 1, iv 1\n")
+        if os.path.exists(os.path.join(G, "mappm_bench.log")):
+            for line in open(os.path.join(G, "mappm_bench.log")): f.write("# events, 10 launches: " + line)
+        for k in sorted(set(keep2)):
+            if k in h: f.write(f"{k:100s} {v[h.index(k)]:>20s} {u[h.index(k)]}\n")
+        f.write("# source lines by executed warp instructions (file line  Minst  samples  source):\n")
+        for k, x in sorted(L.items(), key=lambda kv: -kv[1][0])[:24]:
+            f.write(f"#   {k[0][:18]:18s}{k[1]:5d} {x[0]/1e6:8.1f}M {x[1]:7d}  {x[2][:110]}\n")
