@@ -15,6 +15,8 @@ Every record: `ms_per_step` = CUDA events on the launching stream, barrier + syn
 over ranks; `value` = fine-grid cells of every coarse-grained field per second, all ranks; `roofline` =
 algorithmic bytes of the rank's kernels / their time against the measured copy bandwidth.
 """
+from collections import OrderedDict
+
 import torch
 import torch.distributed as dist
 
@@ -164,26 +166,111 @@ def config4(ctx, n=3072, n_tile=6, band=768, f=8):
     fields, keep = _budget_fields(shape3, seed + 2, dev)
     nout = len(fields)
     hc = (band // f) * (n // f)
-    gathered = torch.empty(ctx.world * len(units[0::ctx.world]) * (nout + 1) * NZ * hc, device=dev) if ctx.world > 1 else None
+    # the kernels write straight into this rank's slot of the exchange buffer (slots padded to the longest rank of a
+    # ragged deal): nothing is packed or copied.  Two exchanges are timed: ONE in-place ncclAllGather after the kernels,
+    # and the fused form - the buffer in peer-mapped (symmetric) memory, the kernel storing every coarse value into
+    # all peers' copies over NVLink while it computes (cg_pressure_level_average_replicated), then one barrier
+    per_unit = (nout + 1) * NZ * hc
+    longest = len(units[0::ctx.world]) * per_unit
+    cshape = (1, NZ, band // f, n // f)
     k_ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
 
-    def step():
-        k_ev[0].record()
-        local = []
-        for _ in mine:
-            outs, dc = ops.pressure_level_average(fields, delp, area, f)
-            local.append(torch.cat([o.reshape(-1) for o in outs] + [dc.reshape(-1)]))
-        k_ev[1].record()
-        if ctx.world > 1:
-            buf = torch.cat(local) if local else torch.empty(0, device=dev)
-            if buf.numel() < gathered.numel() // ctx.world:                     # ragged deal: pad to the longest rank
-                buf = torch.cat([buf, buf.new_zeros(gathered.numel() // ctx.world - buf.numel())])
-            dist.all_gather_into_tensor(gathered, buf)
-        k_ev[2].record()
+    def run(fused):
+        handle, offs, mc = None, None, None
+        try:
+            if fused:
+                import torch.distributed._symmetric_memory as symm
+                gathered = symm.empty(ctx.world * longest, dtype=torch.float32, device=dev)
+                gathered.zero_()
+                handle = symm.rendezvous(gathered, dist.group.WORLD.group_name)
+                ptrs = list(handle.buffer_ptrs)
+                if fused == "peers":
+                    offs = [int(ptrs[r]) - int(ptrs[ctx.rank]) for r in range(ctx.world) if r != ctx.rank]
+                else:
+                    mc = int(getattr(handle, "multicast_ptr", 0) or 0)
+                    if not mc:
+                        raise RuntimeError("no multicast mapping (NVLS) for the symmetric buffer")
+                    mc -= int(gathered.data_ptr())
+            else:
+                gathered = torch.zeros(ctx.world * longest, device=dev)
+        except Exception as e:
+            if not fused:
+                raise
+            return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+        slot = gathered[ctx.rank * longest:(ctx.rank + 1) * longest]
+        unit_outs = [[slot[u * per_unit + v * NZ * hc:u * per_unit + (v + 1) * NZ * hc].view(cshape) for v in range(nout + 1)]
+                     for u in range(len(mine))]
 
-    ms = ctx.timed(step, steps=min(ctx.steps, 3))
-    torch.cuda.synchronize()
-    kernel_ms, gather_ms = ctx.max_over_ranks([k_ev[0].elapsed_time(k_ev[1]), k_ev[1].elapsed_time(k_ev[2])])
+        def step():
+            k_ev[0].record()
+            for o in unit_outs:
+                ops.pressure_level_average(fields, delp, area, f, outs=o[:nout], delp_coarse_out=o[nout], replica_offsets=offs,
+                                           multicast_offset=mc)
+            k_ev[1].record()
+            if handle is not None:
+                handle.barrier()
+            elif ctx.world > 1:
+                dist.all_gather_into_tensor(gathered, slot)
+            k_ev[2].record()
+
+        ms = ctx.timed(step, steps=min(ctx.steps, 3))
+        torch.cuda.synchronize()
+        kernel_ms, x_ms = ctx.max_over_ranks([k_ev[0].elapsed_time(k_ev[1]), k_ev[1].elapsed_time(k_ev[2])])
+        # the slots of the other ranks must hold what they computed: a checksum of every slot agrees on every rank
+        sums = [float(gathered[r * longest:(r + 1) * longest].double().sum()) for r in range(ctx.world)]
+        agree = all(ctx.max_over_ranks([x])[0] == x and -ctx.max_over_ranks([-x])[0] == x for x in sums) and all(x != 0.0 for x in sums)
+        del unit_outs, slot, gathered
+        _free()
+        return {"ms_per_step": ms, "kernel_ms": kernel_ms, "exchange_ms": x_ms, "slot_checksums_agree_on_all_ranks": bool(agree)}
+
+    def run_pipelined():
+        """NCCL again, one in-place all-gather per unit on a side stream: the exchange of unit u runs under the kernels of
+        unit u + 1, only the last one is exposed.  Buffer laid out unit by unit, [unit][rank][values]."""
+        nu = len(units[0::ctx.world])
+        gathered = torch.zeros(nu * ctx.world * per_unit, device=dev)
+        block = lambda u: gathered[u * ctx.world * per_unit:(u + 1) * ctx.world * per_unit]
+        mine_slot = lambda u: block(u)[ctx.rank * per_unit:(ctx.rank + 1) * per_unit]
+        unit_outs = [[mine_slot(u)[v * NZ * hc:(v + 1) * NZ * hc].view(cshape) for v in range(nout + 1)] for u in range(len(mine))]
+        comm = torch.cuda.Stream(dev)
+        done = [torch.cuda.Event() for _ in range(nu)]
+
+        def step():
+            k_ev[0].record()
+            cur = torch.cuda.current_stream(dev)
+            for u in range(nu):
+                if u < len(mine):
+                    o = unit_outs[u]
+                    ops.pressure_level_average(fields, delp, area, f, outs=o[:nout], delp_coarse_out=o[nout])
+                done[u].record(cur)
+                comm.wait_event(done[u])
+                with torch.cuda.stream(comm):
+                    dist.all_gather_into_tensor(block(u), mine_slot(u))
+            k_ev[1].record()
+            cur.wait_stream(comm)
+            k_ev[2].record()
+
+        ms = ctx.timed(step, steps=min(ctx.steps, 3))
+        torch.cuda.synchronize()
+        kernel_ms, x_ms = ctx.max_over_ranks([k_ev[0].elapsed_time(k_ev[1]), k_ev[1].elapsed_time(k_ev[2])])
+        sums = [float(block(u)[r * per_unit:(r + 1) * per_unit].double().sum()) for u in range(nu) for r in range(ctx.world)]
+        agree = all(ctx.max_over_ranks([x])[0] == x and -ctx.max_over_ranks([-x])[0] == x for x in sums) and all(x != 0.0 for x in sums)
+        del unit_outs, gathered
+        _free()
+        return {"ms_per_step": ms, "kernel_ms": kernel_ms, "exchange_ms": x_ms, "slot_checksums_agree_on_all_ranks": bool(agree),
+                "note": "kernel_ms = the compute stream's kernels with the all-gathers of earlier units running beside them; "
+                        "exchange_ms = what is left of the last unit's all-gather after the last kernel"}
+
+    paths = OrderedDict([("nccl_all_gather_in_place", run(False))])
+    if ctx.world > 1:
+        if len(units) % ctx.world == 0:
+            paths["nccl_all_gather_per_unit_overlapped"] = run_pipelined()
+        paths["fused_multicast_stores"] = run("multicast")
+        if ctx.world == 2 or "ms_per_step" not in paths["fused_multicast_stores"]:
+            paths["fused_peer_stores"] = run("peers")
+    good = {k: v for k, v in paths.items() if "ms_per_step" in v and (ctx.world == 1 or v["slot_checksums_agree_on_all_ranks"])}
+    which = min(good, key=lambda k: good[k]["ms_per_step"])
+    best = good[which]
+    ms, kernel_ms, gather_ms = best["ms_per_step"], best["kernel_ms"], best["exchange_ms"]
     fine3 = NZ * band * n
     cells = len(units) * (nout + 1) * fine3
     per_shard = 4 * ((len(keep) + 1) * fine3 + band * n + (nout + 1) * NZ * hc)
@@ -192,12 +279,25 @@ def config4(ctx, n=3072, n_tile=6, band=768, f=8):
            "scaling": "strong", "ms_per_step": ms, "value": cells / (ms * 1e-3), "unit": "cells/s",
            "shards_per_rank": [len(units[r::ctx.world]) for r in range(ctx.world)],
            "kernel_ms": kernel_ms, "collective": None if ctx.world == 1 else
-           {"op": "ncclAllGather (dist.all_gather_into_tensor)", "bytes_out_per_rank": int(gathered.numel() * 4), "ms": gather_ms},
+           {"op": _EXCHANGE_OPS[which], "bytes_out_per_rank": int(ctx.world * longest * 4), "ms": gather_ms},
+           "exchange_paths": paths,
            "data": "synthetic; each rank keeps ONE shard-sized input set (20 GB) and runs it once per shard it owns",
            "roofline": ctx.roofline(per_shard * len(units[0::ctx.world]), kernel_ms, "cg::pairk::plevel_pair_kernel")}
-    del fields, keep, delp, area, gathered
+    del fields, keep, delp, area
     _free()
     return rec
+
+
+_EXCHANGE_OPS = {
+    "nccl_all_gather_in_place": "ncclAllGather in place (dist.all_gather_into_tensor, one per step; the kernels write into the send slot)",
+    "nccl_all_gather_per_unit_overlapped": "ncclAllGather in place, one per (tile, band) unit on a side stream under the next unit's kernels "
+                                           "(dist.all_gather_into_tensor; the kernels write into the send slots)",
+    "fused_multicast_stores": "fused: the kernel stores every coarse value ONCE to the NVLS multicast mapping of the symmetric output "
+                              "buffer (multimem.st, the NVSwitch writes all GPUs' copies; cg_pressure_level_average_replicated), "
+                              "then one device-side barrier",
+    "fused_peer_stores": "fused: the kernel stores every coarse value into every peer's copy of the symmetric output buffer "
+                         "(one NVLink store per peer; cg_pressure_level_average_replicated), then one device-side barrier",
+}
 
 
 # ------------------------------------------------------------------------------------------- strong scaling
@@ -229,35 +329,66 @@ def strong_config2(ctx, inp, n=384, n_tile=6, f=8):
     k_ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
     result = {}
 
-    def step():
-        k_ev[0].record()
-        local = {k: [] for k in out_names}
-        for fields, delp, area, _, _ in local_in:
-            outs, dc = ops.pressure_level_average(fields, delp, area, f)
-            for k, o in zip(out_names, outs + [dc]):
-                local[k].append(o)
-        k_ev[1].record()
-        result["g"] = S.gather_coarse(local, shards, shapes, dst=None)
-        k_ev[2].record()
+    def make_step(bufs, fused):
+        # the kernels write straight into this rank's slot of the exchange buffer (sharding.CoarseBuffers); fused: they
+        # store every value into every GPU's copy themselves - "multicast": one multimem.st to the NVLS mapping, the
+        # NVSwitch replicates; "peers": one NVLink store per peer - and only a barrier follows
+        shard_outs = [[bufs.local[k][j] for k in out_names] for j in range(len(local_in))]
+        offs = bufs.peer_offsets() if fused == "peers" else None
+        mc = bufs.multicast_offset() if fused == "multicast" else None
+        if fused == "multicast" and mc is None:
+            raise RuntimeError("no multicast mapping (NVLS) for the symmetric buffer")
 
-    step()
-    torch.cuda.synchronize()
-    # bit-for-bit against the unsharded run of the same timestep (every rank holds it)
+        def step():
+            k_ev[0].record()
+            for (fields, delp, area, _, _), o in zip(local_in, shard_outs):
+                ops.pressure_level_average(fields, delp, area, f, outs=o[:-1], delp_coarse_out=o[-1], replica_offsets=offs,
+                                           multicast_offset=mc)
+            k_ev[1].record()
+            result["g"] = bufs.barrier() if fused else bufs.all_gather()
+            k_ev[2].record()
+        return step
+
+    # the unsharded run of the same timestep (every rank holds it): both exchange paths must reproduce it bit for bit
     fields = [inp["middle3d"][k] for k in names3]
     for a, b in B.SECOND_MOMENTS:
         fields.append(ops.product(inp["middle3d"][a], inp["middle3d"][b]))
     for k in B.STORAGE_TERMS:
         fields.append(ops.storage(inp["end"][k], inp["begin"][k], B.DT))
     ref, ref_dc = ops.pressure_level_average(fields, inp["delp"], inp["area"], f)
-    ok = True
-    for k, e in zip(out_names, ref + [ref_dc]):
-        got = S.assemble(result["g"][k], 1, n_tile, (NZ,), n, n, f)[0]
-        ok = ok and bool(torch.equal(torch.nan_to_num(got), torch.nan_to_num(e)))
-    ok = bool(ctx.max_over_ranks([0.0 if ok else 1.0])[0] == 0.0)
-    del ref, ref_dc, fields
-    ms = ctx.timed(step)
-    torch.cuda.synchronize()
-    kernel_ms, gather_ms = ctx.max_over_ranks([k_ev[0].elapsed_time(k_ev[1]), k_ev[1].elapsed_time(k_ev[2])])
+    del fields
+
+    def run(fused):
+        try:
+            bufs = S.CoarseBuffers(shards, shapes, ctx.rank, ctx.world, dev, symmetric=bool(fused))
+            step = make_step(bufs, fused)
+        except Exception as e:                       # no peer-mapped memory on this box: the NCCL path is the product
+            if not fused:
+                raise
+            return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+        step()
+        torch.cuda.synchronize()
+        ok = True
+        for k, e in zip(out_names, ref + [ref_dc]):
+            got = S.assemble(result["g"][k], 1, n_tile, (NZ,), n, n, f)[0]
+            ok = ok and bool(torch.equal(torch.nan_to_num(got), torch.nan_to_num(e)))
+        ok = bool(ctx.max_over_ranks([0.0 if ok else 1.0])[0] == 0.0)
+        ms = ctx.timed(step)
+        torch.cuda.synchronize()
+        kernel_ms, x_ms = ctx.max_over_ranks([k_ev[0].elapsed_time(k_ev[1]), k_ev[1].elapsed_time(k_ev[2])])
+        result.clear()
+        return {"ms_per_step": ms, "kernel_ms": kernel_ms, "exchange_ms": x_ms, "bit_identical_to_unsharded": ok}
+
+    paths = OrderedDict([("nccl_all_gather_in_place", run(False))])
+    if ctx.world > 1:
+        paths["fused_multicast_stores"] = run("multicast")
+        if ctx.world == 2 or "ms_per_step" not in paths["fused_multicast_stores"]:
+            paths["fused_peer_stores"] = run("peers")        # (7 small NVLink stores per value at N = 8: slower than NCCL)
+    del ref, ref_dc
+    good = {k: v for k, v in paths.items() if "ms_per_step" in v and v["bit_identical_to_unsharded"]}
+    which = min(good, key=lambda k: good[k]["ms_per_step"])
+    best = good[which]
+    ms, kernel_ms, gather_ms, ok = best["ms_per_step"], best["kernel_ms"], best["exchange_ms"], best["bit_identical_to_unsharded"]
     fine3 = n_tile * NZ * n * n
     cells = len(out_names) * fine3
     rows = max(sum((s.tile1 - s.tile0) * ((n if s.row1 is None else s.row1) - s.row0) for s in r) for r in shards)    # tile-rows of the busiest rank
@@ -268,8 +399,9 @@ def strong_config2(ctx, inp, n=384, n_tile=6, f=8):
            "scaling": "strong", "ms_per_step": ms, "value": cells / (ms * 1e-3), "unit": "cells/s",
            "bit_identical_to_unsharded": ok, "shards_per_rank": [len(r) for r in shards],
            "kernel_ms": kernel_ms,
-           "collective": {"op": "ncclAllGather (dist.all_gather_into_tensor, one per step)" if ctx.world > 1 else "none (one rank)",
+           "collective": {"op": "none (one rank)" if ctx.world == 1 else _EXCHANGE_OPS[which],
                           "bytes_out_per_rank": int(nbytes), "ms": gather_ms},
+           "exchange_paths": paths,
            "roofline": ctx.roofline(per_rank, kernel_ms, "cg::pairk::plevel_pair_kernel on the busiest rank's shards")}
     del local_in, result
     _free()

@@ -33,7 +33,8 @@ int launch_surface_pressure_seq(const float *delp, float *ps, float toa, long n_
 int pair_supported(int nfields, int nz, int ny, int nx, int f);
 int launch_plevel_pair(const cg_field *fields, float *const *outs, int nfields, const float *delp,
                        const float *area, const float *delp_coarse, const float *psurf, int *flags, long n_outer,
-                       int nz, int ny, int nx, int mask_below, float toa, int nansafe_only, cudaStream_t st);
+                       int nz, int ny, int nx, int mask_below, float toa, int nansafe_only, int nrep, const long long *rep,
+                       int rep_dc, int rep_kind, cudaStream_t st);
 int launch_plevel_stream(const cg_field *fields, float *const *outs, int nfields, const float *delp,
                          const float *area, const float *delp_coarse, const float *psurf, int *flags, long n_outer,
                          int nz, int ny, int nx, int mask_below, float toa, cudaStream_t st);
@@ -356,6 +357,9 @@ static int composed(const cg_field *fields, float *const *outs, int nfields, con
 static bool impl_is(int which) { return options().plevel_impl == which; }
 static bool want_composed() { return impl_is(PLEVEL_COMPOSED); }
 static thread_local const char *g_last_impl = "none";
+// replicas of the coarse outputs requested by cg_pressure_level_average_replicated for the call in progress
+struct Replicas { int n; int dc; int kind; long long off[CG_MAX_REPLICAS]; };
+static thread_local Replicas g_rep = {0, 0, 0, {0}};
 
 static int stream_path(const cg_field *fields, float *const *outs, int nfields, const float *delp,
                        const float *area, float *delp_coarse, long n_outer, int nz, int ny, int nx,
@@ -375,11 +379,13 @@ static int stream_path(const cg_field *fields, float *const *outs, int nfields, 
     if (rc) return rc;
     if (mask_below && (rc = launch_surface_pressure_seq(delp, ps, toa, n_outer, nz, h, st))) return rc;
     // the pair-thread kernel where its shared-memory layout fits (option plevel_impl = stream pins the round-1 kernel)
-    if (!impl_is(PLEVEL_STREAM) && pair_supported(nfields, nz, ny, nx, 8)) {
+    if ((!impl_is(PLEVEL_STREAM) || g_rep.n > 0) && pair_supported(nfields, nz, ny, nx, 8)) {
         rc = launch_plevel_pair(fields, outs, nfields, delp, area, dc, mask_below ? ps : nullptr, flags, n_outer, nz,
-                                ny, nx, mask_below, toa, options().plevel_nansafe, st);
+                                ny, nx, mask_below, toa, options().plevel_nansafe, g_rep.n, g_rep.off,
+                                g_rep.dc && delp_coarse != nullptr, g_rep.kind, st);
         if (rc != CG_ENOTSUP) { g_last_impl = "pair"; return rc; }
     }
+    if (g_rep.n > 0) return CG_ENOTSUP;         // only the pair kernel stores replicas
     if (!stream_supported(nfields, nz, ny, nx, 8)) return CG_ENOTSUP;
     g_last_impl = "stream";
     return launch_plevel_stream(fields, outs, nfields, delp, area, dc, mask_below ? ps : nullptr, flags, n_outer, nz,
@@ -434,8 +440,9 @@ extern "C" int cg_pressure_level_average(const cg_field *fields, float *const *o
         (stream_supported(nfields, nz, ny, nx, f) || pair_supported(nfields, nz, ny, nx, f))) {
         const int rc = stream_path(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz, ny, nx,
                                    mask_below, (float)toa, workspace, workspace_bytes, st);
-        if (rc != CG_ENOTSUP) return rc;        // misaligned pointers / no workspace: next implementation
+        if (rc != CG_ENOTSUP || g_rep.n > 0) return rc;     // misaligned pointers / no workspace: next implementation
     }
+    if (g_rep.n > 0) return CG_ENOTSUP;
     if (!want_composed() && !impl_is(PLEVEL_STREAM) && fused_supported(nz, ny, nx, f)) {
         const int rc = launch_plevel_fused(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz,
                                            ny, nx, f, mask_below, (float)toa, workspace, workspace_bytes, st);
@@ -452,6 +459,46 @@ extern "C" int cg_pressure_level_average(const cg_field *fields, float *const *o
     }
     return composed(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz, ny, nx, f, mask_below,
                     (float)toa, workspace, workspace_bytes, st);
+}
+
+extern "C" int cg_pressure_level_average_replicated(const cg_field *fields, float *const *outs, int nfields,
+                                                    const float *delp, const float *area, float *delp_coarse,
+                                                    long n_outer, int nz, int ny, int nx, int f, int mask_below,
+                                                    double toa, int replica_kind, int n_replicas,
+                                                    const long long *replica_offsets,
+                                                    void *workspace, long workspace_bytes, void *stream)
+{
+    CG_REQUIRE(replica_kind == CG_REPLICA_PEERS || replica_kind == CG_REPLICA_MULTICAST, "bad replica_kind");
+    CG_REQUIRE(n_replicas >= 0 && n_replicas <= CG_MAX_REPLICAS, "n_replicas must be in [0, %d]", CG_MAX_REPLICAS);
+    CG_REQUIRE(replica_kind != CG_REPLICA_MULTICAST || n_replicas <= 1, "a multicast mapping is ONE offset");
+    CG_REQUIRE(n_replicas == 0 || replica_offsets, "null replica_offsets");
+    for (int r = 0; r < n_replicas; ++r)
+        CG_REQUIRE(replica_offsets[r] % 16 == 0, "replica offset %d (%lld bytes) is not a multiple of 16", r, replica_offsets[r]);
+    for (int v = 0; n_replicas > 0 && outs && v < nfields; ++v)
+        CG_REQUIRE(((uintptr_t)outs[v] & 15) == 0, "replicated outputs are stored 16 bytes at a time: outs[%d] is not 16-byte aligned", v);
+    CG_REQUIRE(n_replicas == 0 || ((uintptr_t)delp_coarse & 15) == 0, "delp_coarse is not 16-byte aligned");
+    if (n_replicas == 0)
+        return cg_pressure_level_average(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz, ny, nx, f,
+                                         mask_below, toa, workspace, workspace_bytes, stream);
+    CG_REQUIRE(fields && outs && delp && area, "null pointer");
+    CG_REQUIRE(nfields >= 1 && nfields <= CG_MAX_FIELDS, "nfields must be in [1, %d]", CG_MAX_FIELDS);
+    CG_REQUIRE(n_outer >= 0 && nz >= 4 && ny >= 1 && nx >= 1 && f >= 1, "bad shape (nz >= 4 required)");
+    if (!(f == 8 && ny % 8 == 0 && nx % 8 == 0 && pair_supported(nfields, nz, ny, nx, 8))) {
+        set_error("cg_pressure_level_average_replicated: only the pair-thread kernel stores replicas (f = 8, "
+                  "nx %% 32 == 0, shared-memory layout for %d fields x %d levels)", nfields, nz);
+        return CG_ENOTSUP;
+    }
+    g_rep.n = n_replicas;
+    g_rep.dc = 1;
+    g_rep.kind = replica_kind;
+    for (int r = 0; r < n_replicas; ++r) g_rep.off[r] = replica_offsets[r];
+    int rc = cg_pressure_level_average(fields, outs, nfields, delp, area, delp_coarse, n_outer, nz, ny, nx, f,
+                                       mask_below, toa, workspace, workspace_bytes, stream);
+    g_rep.n = 0;
+    if (rc == CG_ENOTSUP)
+        set_error("cg_pressure_level_average_replicated: the pair-thread kernel does not take these arguments "
+                  "(16-byte aligned field arrays, a workspace of cg_pressure_level_workspace_bytes)");
+    return rc;
 }
 
 extern "C" int cg_area_above_fine_surface(const float *delp, const float *delp_coarse, const float *area,

@@ -74,6 +74,10 @@ struct Params {
     int nfw;                         // field warps = ceil(16 nfields / 32)
     float toa;
     int *flags;                      // per CTA: the fast variant met a non-finite field value (NaN-safe variant reruns the CTA)
+    // cg_pressure_level_average_replicated: every coarse value is also stored at its address + rep[r] bytes (peer
+    // copies of the output buffer over NVLink: the stores are the all-gather); rep_dc: delp_coarse as well
+    int nrep, rep_dc, rep_kind;      // rep_kind CG_REPLICA_MULTICAST: rep[0] leads to a multicast mapping (one multimem.st)
+    long long rep[CG_MAX_REPLICAS];
 };
 
 // ---- shared-memory carve-up --------------------------------------------------------------------
@@ -122,6 +126,16 @@ __device__ __forceinline__ float frcp(float x)
     float r;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
+}
+// NVLS: one store to a multicast address, the NVSwitch writes the value into every GPU's copy of the buffer
+__device__ __forceinline__ void multimem_st(float *mc, float v)
+{
+    asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(mc), "f"(v) : "memory");
+}
+__device__ __forceinline__ void multimem_st4(float *mc, float4 v)
+{
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+                 : "memory");
 }
 __device__ __forceinline__ int ldsu8(uint32_t addr)
 {
@@ -649,6 +663,43 @@ __device__ __forceinline__ void hot_step(Pair &s, uint32_t recp, u64 qn, uint32_
     s.q[S] = qn; s.dq = dqn; s.dc = dcn; s.xp = xn; s.mk = mkn;
 }
 
+// one value of delp_coarse to every GPU's copy (cg_pressure_level_average_replicated); out of line like the outputs
+__device__ __noinline__ void replicate_value(const Params &p, float *dst, float v)
+{
+    if (p.rep_kind == CG_REPLICA_MULTICAST) multimem_st((float *)((char *)dst + p.rep[0]), v);
+    else for (int r = 0; r < p.nrep; ++r) *(float *)((char *)dst + p.rep[r]) = v;
+}
+
+// cg_pressure_level_average_replicated: the CTA's four cells of a (field, level) as one 16-byte store, sent to
+// every GPU's copy of the output buffer - through the multicast mapping (one multimem.st, the NVSwitch
+// replicates) or with one store per peer over NVLink.  Same sums in the same order as the plain output loop.
+// Out of line: the single-GPU kernel's code and registers stay as they are.
+__device__ __noinline__ void replicated_outputs(const Params &p, uint32_t acc0, int acc_stride, uint32_t den0, int cell_bytes,
+                                                int nz, int V, int nfw, int tid, long o, long hc, long cell_off)
+{
+    for (int idx = tid; idx < nz * V; idx += nfw * 32) {
+        const int vv = idx % V, k = idx / V;
+        float r4[NCELL];
+#pragma unroll
+        for (int c = 0; c < NCELL; ++c) {
+            const uint32_t a = acc0 + (k + 1) * acc_stride + 4 * ((NCELL * c) * V + vv);
+            float sum = lds32(a);
+            sum += lds32(a + 4 * V);
+            sum += lds32(a + 8 * V);
+            sum += lds32(a + 12 * V);
+            r4[c] = sum / lds32(den0 + c * cell_bytes + 4 * k);
+        }
+        float *dst = p.outs[vv] + (o * nz + k) * hc + cell_off;
+        const float4 val = make_float4(r4[0], r4[1], r4[2], r4[3]);
+        if (p.rep_kind == CG_REPLICA_MULTICAST) {
+            multimem_st4((float *)((char *)dst + p.rep[0]), val);       // lands in this GPU's copy as well
+        } else {
+            *(float4 *)dst = val;
+            for (int r = 0; r < p.nrep; ++r) *(float4 *)((char *)dst + p.rep[r]) = val;
+        }
+    }
+}
+
 // ---- the kernel ------------------------------------------------------------------------------------
 // (nfw + 4) warps: field warps 0 .. nfw-1, the three geometry warps, the column walker.  120 registers per
 // thread at 544 threads.
@@ -777,8 +828,12 @@ plevel_pair_kernel(const __grid_constant__ Params p)
         }
         for (int c = gw; c < NCELL; c += NGW) {
             const uint32_t cbw = sbase + lay.cell0 + c * lay.cell_bytes;
-            for (int k = lane; k < nz; k += 32)
-                sts32(cbw + lay.rdp2 + 4 * k, p.delp_coarse[(o * nz + k) * hc + (long)by * nxc + NCELL * bx + c]);
+            for (int k = lane; k < nz; k += 32) {
+                const float *src = p.delp_coarse + (o * nz + k) * hc + (long)by * nxc + NCELL * bx + c;
+                const float dcv = *src;
+                sts32(cbw + lay.rdp2 + 4 * k, dcv);
+                if (p.rep_dc) replicate_value(p, const_cast<float *>(src), dcv);
+            }
             __syncwarp();
             if (lane == 0) {
                 float pe = toa;
@@ -1049,16 +1104,21 @@ plevel_pair_kernel(const __grid_constant__ Params p)
     // 0/0 -> NaN like the reference
     asm volatile("bar.sync %0, %1;" ::"n"(BAR_OUT), "r"(nfw * 32) : "memory");
     const uint32_t acc0 = sbase + lay.acc;
-    for (int idx = tid; idx < nz * NCELL * V; idx += nfw * 32) {
-        const int c = idx % NCELL, vv = (idx / NCELL) % V, k = idx / (NCELL * V);
-        const uint32_t a = acc0 + (k + 1) * lay.acc_stride + 4 * ((NCELL * c) * V + vv);
-        float sum = lds32(a);
-        sum += lds32(a + 4 * V);
-        sum += lds32(a + 8 * V);
-        sum += lds32(a + 12 * V);
-        const float den = lds32(sbase + lay.cell0 + c * lay.cell_bytes + lay.den + 4 * k);
-        p.outs[vv][(o * nz + k) * hc + (long)by * nxc + NCELL * bx + c] = sum / den;
+    if (p.nrep == 0) {
+        for (int idx = tid; idx < nz * NCELL * V; idx += nfw * 32) {
+            const int c = idx % NCELL, vv = (idx / NCELL) % V, k = idx / (NCELL * V);
+            const uint32_t a = acc0 + (k + 1) * lay.acc_stride + 4 * ((NCELL * c) * V + vv);
+            float sum = lds32(a);
+            sum += lds32(a + 4 * V);
+            sum += lds32(a + 8 * V);
+            sum += lds32(a + 12 * V);
+            const float den = lds32(sbase + lay.cell0 + c * lay.cell_bytes + lay.den + 4 * k);
+            p.outs[vv][(o * nz + k) * hc + (long)by * nxc + NCELL * bx + c] = sum / den;
+        }
+        return;
     }
+    replicated_outputs(p, acc0, lay.acc_stride, sbase + lay.cell0 + lay.den, lay.cell_bytes, nz, V, nfw, tid, o, hc,
+                       (long)by * nxc + NCELL * bx);
 }
 
 // ---- host side ----------------------------------------------------------------------------------
@@ -1067,7 +1127,8 @@ constexpr int SMEM_LIMIT = 227 * 1024 - 1024;
 // one launch: nfields <= MAXV output fields
 static int launch_group(const cg_field *fields, float *const *outs, int nfields, const float *delp, const float *area,
                         const float *delp_coarse, const float *psurf, int *flags, long n_outer, int nz, int ny, int nx,
-                        int mask_below, float toa, int nansafe_only, cudaStream_t st)
+                        int mask_below, float toa, int nansafe_only, int nrep, const long long *rep, int rep_dc,
+                        int rep_kind, cudaStream_t st)
 {
     static Params p;                       // ~8 KB: keep it off the stack; filled under a lock
     static std::mutex mu;
@@ -1100,6 +1161,11 @@ static int launch_group(const cg_field *fields, float *const *outs, int nfields,
     p.area = area; p.psurf = psurf; p.delp_coarse = delp_coarse; p.delp = delp;
     p.nsrc = nsrc; p.nfields = nfields; p.nz = nz; p.ny = ny; p.nx = nx; p.mask_below = mask_below; p.toa = toa;
     p.nfw = nfw;
+    p.nrep = nrep; p.rep_dc = rep_dc; p.rep_kind = rep_kind;
+    if (nrep > 0)                           // 16-byte stores of the four cells of a CTA
+        for (int v = 0; v < nfields; ++v)
+            if (((uintptr_t)outs[v]) & 15) return CG_ENOTSUP;
+    for (int r = 0; r < CG_MAX_REPLICAS; ++r) p.rep[r] = r < nrep ? rep[r] : 0;
     // per device attributes: cheap, so set on every call (a process may drive several devices)
     for (int v = 0; v < 2; ++v) {
         const void *fn = v ? (const void *)plevel_pair_kernel<true> : (const void *)plevel_pair_kernel<false>;
@@ -1165,7 +1231,8 @@ static int distinct_sources(const cg_field *fields, int n)
 // fields/outs as in cg_pressure_level_average; delp_coarse (and psurf when mask_below) already computed
 int launch_plevel_pair(const cg_field *fields, float *const *outs, int nfields, const float *delp,
                        const float *area, const float *delp_coarse, const float *psurf, int *flags, long n_outer,
-                       int nz, int ny, int nx, int mask_below, float toa, int nansafe_only, cudaStream_t st)
+                       int nz, int ny, int nx, int mask_below, float toa, int nansafe_only, int nrep, const long long *rep,
+                       int rep_dc, int rep_kind, cudaStream_t st)
 {
     if (n_outer > 65535 || n_outer * nz > 0x7fffffffL) return CG_ENOTSUP;
     if (((uintptr_t)delp) & 3) return CG_ENOTSUP;
@@ -1180,8 +1247,9 @@ int launch_plevel_pair(const cg_field *fields, float *const *outs, int nfields, 
     }
     for (int v0 = 0; v0 < nfields; v0 += per) {
         const int n = nfields - v0 < per ? nfields - v0 : per;
+        // (delp_coarse goes to the replicas with the first group only)
         const int rc = pairk::launch_group(fields + v0, outs + v0, n, delp, area, delp_coarse, psurf, flags, n_outer, nz, ny,
-                                           nx, mask_below, toa, nansafe_only, st);
+                                           nx, mask_below, toa, nansafe_only, nrep, rep, rep_dc && v0 == 0, rep_kind, st);
         if (rc) return rc;
     }
     return CG_OK;

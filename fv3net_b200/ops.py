@@ -247,10 +247,17 @@ def _describe(fields):
     return descs, keep
 
 
-def pressure_level_average(fields, delp, area, f, mask_below=False, toa=300.0, want_delp_coarse=True):
+def pressure_level_average(fields, delp, area, f, mask_below=False, toa=300.0, want_delp_coarse=True,
+                           outs=None, delp_coarse_out=None, replica_offsets=None, multicast_offset=None):
     """Fused regrid-to-coarse-pressure + (masked) area-weighted block average.
     fields: list of (n_outer, nz, ny, nx) float32 tensors or descriptors from product() /
     storage(); delp same shape; area (n_outer, ny, nx).
+    outs / delp_coarse_out: arrays the kernels write their results into (contiguous float32 of the coarse shape,
+    e.g. views of a collective's send buffer: sharding.CoarseBuffers) instead of new ones.
+    replica_offsets: byte offsets at which every coarse value is stored once more by the kernel itself
+    (cg_pressure_level_average_replicated: peer copies of the output buffer over NVLink; needs `outs`).
+    multicast_offset: instead, the byte offset from the output buffer to its NVLS multicast mapping - every value is
+    stored once with multimem.st and the NVSwitch writes all copies.
     Returns (list of coarse fields, delp_coarse or None)."""
     fields = list(fields)
     n_outer, nz, ny, nx = delp.shape
@@ -260,9 +267,33 @@ def pressure_level_average(fields, delp, area, f, mask_below=False, toa=300.0, w
         if t.dtype != torch.float32 or not t.is_contiguous():
             raise ValueError("pressure_level_average needs contiguous float32 tensors")
     dev = delp.device
-    dcoarse = torch.empty((n_outer, nz, ny // f, nx // f), dtype=torch.float32, device=dev) \
-        if want_delp_coarse else None
-    outs = [torch.empty((n_outer, nz, ny // f, nx // f), dtype=torch.float32, device=dev) for _ in fields]
+    cshape = (n_outer, nz, ny // f, nx // f)
+
+    def given(t, what):
+        if tuple(t.shape) != cshape or t.dtype != torch.float32 or not t.is_contiguous() or t.device != dev:
+            raise ValueError(f"{what} must be a contiguous float32 array of shape {cshape} on {dev}")
+        return t
+
+    if delp_coarse_out is not None:
+        dcoarse = given(delp_coarse_out, "delp_coarse_out")
+    else:
+        dcoarse = torch.empty(cshape, dtype=torch.float32, device=dev) if want_delp_coarse else None
+    outs_given = outs is not None
+    if outs is not None:
+        outs = [given(t, f"outs[{i}]") for i, t in enumerate(outs)]
+        if len(outs) != len(fields):
+            raise ValueError(f"{len(outs)} output arrays for {len(fields)} fields")
+    else:
+        outs = [torch.empty(cshape, dtype=torch.float32, device=dev) for _ in fields]
+    reps = [int(x) for x in (replica_offsets if replica_offsets is not None else [])]
+    kind = 0
+    if multicast_offset is not None:
+        if reps:
+            raise ValueError("either replica_offsets or multicast_offset")
+        reps, kind = [int(multicast_offset)], 1
+    if reps and outs_given is False:
+        raise ValueError("replica_offsets need the caller's own output arrays (outs=, delp_coarse_out=)")
+    rep_arr = (ctypes.c_longlong * max(len(reps), 1))(*reps)
     step = L.CG_MAX_FIELDS
     first = True
     for i in range(0, max(len(fields), 1), step):
@@ -273,6 +304,10 @@ def pressure_level_average(fields, delp, area, f, mask_below=False, toa=300.0, w
         pout, _k2 = L.ptr_array([t.data_ptr() for t in res])
         args = (ctypes.cast(descs, ctypes.c_void_p), pout, len(chunk), _p(delp), _p(area),
                 _p(dcoarse) if first else None, n_outer, nz, ny, nx, f, int(mask_below), float(toa))
+        if reps:                            # (no fallback: only the pair-thread kernel stores replicas)
+            L.check(L.lib().cg_pressure_level_average_replicated(*args, kind, len(reps), rep_arr, _p(ws), ws.numel(), _stream()))
+            first = False
+            continue
         rc = L.lib().cg_pressure_level_average(*args, _p(ws), ws.numel(), _stream())
         if rc == L.CG_ENOTSUP:
             # arguments the streaming kernels do not take (e.g. views that are not 16-byte aligned): the

@@ -158,6 +158,109 @@ def gather_coarse(local, shards, shapes, dst=0, group=None):
     return out
 
 
+class CoarseBuffers:
+    """The coarse outputs of one step, of every rank, in ONE buffer laid out for an in-place all-gather.
+
+    Slot r = [r * longest, (r + 1) * longest) holds rank r's outputs name by name, shard by shard (the order of
+    `gather_coarse`; slots are padded to the longest rank of a ragged plan).  `local[name]` are views into this
+    rank's own slot: hand them to the kernels as their output arrays (`ops.pressure_level_average(..., outs=...)`),
+    so nothing is packed or copied before the collective, and `all_gather()` is one `ncclAllGather` whose send
+    buffer is the rank's slot of the receive buffer.  The plan is known everywhere, so no sizes are exchanged.
+
+    `symmetric=True`: the buffer lives in peer-mapped (symmetric) memory; the kernels can then store each output
+    into every peer's copy themselves (`peer_offsets()` -> `ops.pressure_level_average(replica_offsets=...)`,
+    NVLink stores from inside the compute kernel) and the collective reduces to `barrier()`."""
+
+    def __init__(self, shards, shapes, rank, world, device, dtype=torch.float32, whole=None, symmetric=False,
+                 group=None):
+        self.shards, self.shapes, self.rank, self.world = shards, shapes, rank, world
+        self.handle, self.group = None, group
+        self.names = list(shapes)
+
+        def numel(shape):
+            n = 1
+            for d in shape:
+                n *= d
+            return n
+
+        self._layout = []                                    # per rank: [(name, shard, offset in the slot, shape)]
+        sizes = []
+        for r in range(world):
+            pos, items = 0, []
+            for name in self.names:
+                lead, ny, nx, f = shapes[name]
+                for s in shards[r]:
+                    shape = coarse_shape(s, lead, ny, nx, f)
+                    items.append((name, s, pos, shape))
+                    pos += numel(shape)
+            self._layout.append(items)
+            sizes.append(pos)
+        # slots start on 16-byte boundaries whatever the dtype (vector stores, NCCL's preferred alignment)
+        q = max(1, 16 // torch.empty((), dtype=dtype).element_size())
+        self.longest = max(1, (max(sizes) + q - 1) // q * q)
+        if symmetric and world > 1:
+            # peer-mapped memory (CUDA VMM handles exchanged over the process group): every rank's buffer has the
+            # same layout and is addressable from every GPU of the box through NVLink
+            import torch.distributed._symmetric_memory as symm
+
+            whole = symm.empty(world * self.longest, dtype=dtype, device=device)
+            whole.zero_()
+            self.handle = symm.rendezvous(whole, (group or dist.group.WORLD).group_name)
+        elif whole is None:
+            whole = torch.zeros(world * self.longest, dtype=dtype, device=device)
+        elif whole.numel() != world * self.longest or whole.dtype != dtype:
+            raise ValueError(f"the buffer must hold {world * self.longest} values of {dtype}")
+        self.whole = whole
+        self.local = OrderedDict((name, []) for name in self.names)
+        for name, s, pos, shape in self._layout[rank]:
+            self.local[name].append(self._view(rank, pos, shape))
+
+    def _view(self, r, pos, shape):
+        n = 1
+        for d in shape:
+            n *= d
+        return self.whole[r * self.longest + pos:r * self.longest + pos + n].view(shape)
+
+    def slot(self, r=None):
+        r = self.rank if r is None else r
+        return self.whole[r * self.longest:(r + 1) * self.longest]
+
+    def peer_offsets(self):
+        """Byte offsets from this rank's buffer to every other rank's copy (symmetric=True), for the kernels that
+        store their outputs into the peers themselves (ops.pressure_level_average(replica_offsets=...))."""
+        if self.handle is None:
+            return []
+        ptrs = list(self.handle.buffer_ptrs)
+        return [int(ptrs[r]) - int(ptrs[self.rank]) for r in range(self.world) if r != self.rank]
+
+    def multicast_offset(self):
+        """Byte offset from this rank's buffer to the NVLS multicast mapping of the symmetric buffer (a store there is
+        written into every rank's copy by the NVSwitch), or None where the box has no multicast support."""
+        mc = int(getattr(self.handle, "multicast_ptr", 0) or 0) if self.handle is not None else 0
+        return mc - int(self.whole.data_ptr()) if mc else None
+
+    def barrier(self):
+        """After kernels that stored into the peers: every rank's stores have landed everywhere when this returns on
+        the stream (a device-side barrier over the symmetric memory's signal pads, no data moves).  Returns the views
+        of `all_gather`.  Call it once more before the buffers are overwritten if a peer may still be reading."""
+        if self.handle is not None:
+            self.handle.barrier()
+        return self.views()
+
+    def all_gather(self, group=None):
+        """In place: afterwards every rank's `whole` holds every slot.  Returns {name: {shard: view}}."""
+        if self.world > 1:
+            dist.all_gather_into_tensor(self.whole, self.slot(), group=group)
+        return self.views()
+
+    def views(self):
+        out = OrderedDict((name, OrderedDict()) for name in self.names)
+        for r in range(self.world):
+            for name, s, pos, shape in self._layout[r]:
+                out[name][s] = self._view(r, pos, shape)
+        return out
+
+
 def assemble(gathered, n_time, n_tile, lead, ny, nx, factor):
     """{shard: tensor} of one output -> the global (time, tile, *lead, ny/f, nx/f) tensor."""
     first = next(iter(gathered.values()))

@@ -182,6 +182,31 @@ int cg_pressure_level_average(const cg_field *fields, float *const *outs, int nf
                               int mask_below, double toa,
                               void *workspace, long workspace_bytes, void *stream);
 
+/* Multi-GPU form of cg_pressure_level_average, the compute step fused with the exchange that follows it (one
+ * timestep sharded by tile / row band over the GPUs of a box, every GPU wanting every coarse value:
+ * coarsen_surface_c3072.py:29-76 gathers the sub-tiles in a later Beam stage).  No counterpart in the
+ * reference's native interface.  Every coarse value the call produces - outs[v][i] and delp_coarse[i] - is stored
+ * at its own address AND at that address + replica_offsets[r] bytes for r < n_replicas: with the outputs placed
+ * in a buffer that is mapped at the same layout on every GPU (symmetric / peer memory over NVLink), the offsets
+ * are peer_base - own_base and the kernel's stores ARE the all-gather; the caller only adds a barrier between
+ * the ranks before the values are read.
+ *   replica_kind CG_REPLICA_PEERS:     one NVLink store per value and offset, n_replicas <= CG_MAX_REPLICAS
+ *   replica_kind CG_REPLICA_MULTICAST: replica_offsets[0] = multicast_base - own_base of an NVLS multicast mapping
+ *                                      of the buffer; every value is stored ONCE (multimem.st) and the NVSwitch
+ *                                      writes it into every GPU's copy, this GPU's included
+ * The four coarse cells a CTA owns in a row go out as one 16-byte store: outs[v], delp_coarse and the offsets must
+ * be multiples of 16 bytes (CG_EINVAL).  Served by the pair-thread kernel only (f = 8, nx % 32 == 0; CG_ENOTSUP
+ * otherwise, nothing is launched). */
+#define CG_MAX_REPLICAS 7
+#define CG_REPLICA_PEERS 0
+#define CG_REPLICA_MULTICAST 1
+int cg_pressure_level_average_replicated(const cg_field *fields, float *const *outs, int nfields,
+                                         const float *delp, const float *area, float *delp_coarse,
+                                         long n_outer, int nz, int ny, int nx, int f,
+                                         int mask_below, double toa,
+                                         int replica_kind, int n_replicas, const long long *replica_offsets,
+                                         void *workspace, long workspace_bytes, void *stream);
+
 /* budgets.py:62-77 area_above_fine_surface: block sum of area where the coarse
  * log-midpoint pressure (upsampled) <= fine surface pressure. */
 int cg_area_above_fine_surface(const float *delp, const float *delp_coarse, const float *area,

@@ -462,6 +462,58 @@ def test_pressure_level_on_a_second_device_of_the_process(ops, monkeypatch, kern
             np.testing.assert_array_equal(a, b)
 
 
+@pytest.mark.parametrize("mask_below", [False, True])
+def test_pressure_level_replicated_outputs(ops, monkeypatch, mask_below):
+    """cg_pressure_level_average_replicated: every coarse value (outputs and delp_coarse) lands at its own address and
+    at address + offset, bit for bit what the plain entry point gives.  The replicas of the multi-GPU path are peer
+    copies of one buffer; here they are a second and third region of the same device buffer."""
+    _pin_impl(monkeypatch, "default")
+    nt, nc, f = 2, 8, 8
+    ny = nx = nc * f
+    delp = syn.delp_from_ps(syn.surface_pressure((nt, ny, nx), seed=51))
+    area = syn.area((nt, ny, nx), seed=52)
+    flds = [syn.field((nt, syn.NZ, ny, nx), 53 + i) for i in range(3)]
+    flds[1][0, :, 3, 5] = np.nan                                        # a CTA that the NaN-safe pass redoes
+    d_f, d_delp, d_area = [dev(x) for x in flds], dev(delp), dev(area)
+    ref, ref_dc = ops.pressure_level_average(d_f, d_delp, d_area, f, mask_below=mask_below)
+    n = ref_dc.numel()
+    per = (len(flds) + 1) * n
+    whole = torch.full((3 * per + 8,), -7.0, dtype=torch.float32, device="cuda")
+    views = [whole[i * n:(i + 1) * n].view(ref_dc.shape) for i in range(len(flds) + 1)]
+    outs, dc = ops.pressure_level_average(d_f, d_delp, d_area, f, mask_below=mask_below, outs=views[:-1],
+                                          delp_coarse_out=views[-1], replica_offsets=[4 * per, 8 * per + 16])
+    from fv3net_b200 import _lib
+    assert _lib.lib().cg_pressure_level_last_impl() == b"pair"
+    w = host(whole)
+    for i, e in enumerate(ref + [ref_dc]):
+        e = host(e).ravel()
+        for base in (0, per, 2 * per + 4):
+            np.testing.assert_array_equal(w[base + i * n:base + (i + 1) * n], e)
+    assert (w[2 * per:2 * per + 4] == -7.0).all() and (w[3 * per + 4:] == -7.0).all()    # nothing else was touched
+    # multicast form: ONE store per value, at address + offset only (on a multi-GPU box that address is the NVLS
+    # mapping and the switch writes every copy, this GPU's included; here it is plain memory)
+    whole.fill_(-7.0)
+    ops.pressure_level_average(d_f, d_delp, d_area, f, mask_below=mask_below, outs=views[:-1], delp_coarse_out=views[-1],
+                               multicast_offset=4 * per)
+    w = host(whole)
+    for i, e in enumerate(ref + [ref_dc]):
+        np.testing.assert_array_equal(w[per + i * n:per + (i + 1) * n], host(e).ravel())
+    assert (w[:len(flds) * n] == -7.0).all() and (w[2 * per:] == -7.0).all()
+    np.testing.assert_array_equal(w[len(flds) * n:per], host(ref_dc).ravel())      # (delp_coarse's own copy is the block average's)
+    with pytest.raises(ValueError):
+        ops.pressure_level_average(d_f, d_delp, d_area, f, outs=views[:-1], delp_coarse_out=views[-1], replica_offsets=[6])
+    with pytest.raises(ValueError):
+        ops.pressure_level_average(d_f, d_delp, d_area, f, outs=views[:-1], delp_coarse_out=views[-1], replica_offsets=[16],
+                                   multicast_offset=32)
+    with pytest.raises(ValueError):
+        ops.pressure_level_average(d_f, d_delp, d_area, f, replica_offsets=[4 * per])          # needs the caller's arrays
+    d2, a2 = dev(delp[:, :, :32, :32]), dev(area[:, :32, :32])
+    small = [torch.empty((nt, syn.NZ, 8, 8), device="cuda")]
+    with pytest.raises(NotImplementedError):                              # f = 4: not the pair kernel's shape
+        ops.pressure_level_average([dev(flds[0][:, :, :32, :32])], d2, a2, 4, outs=small,
+                                   delp_coarse_out=torch.empty_like(small[0]), replica_offsets=[0])
+
+
 def test_pressure_level_golden_restart_T(ops):
     """The reference's golden pressure-level T (test_coarsen_restarts.py) through CUDA."""
     tag = "pressure-level-without-agrid-winds"

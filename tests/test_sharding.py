@@ -64,8 +64,19 @@ def _worker(rank, world, port, n_time, n_tile, case, result_file):
             local["q"].append(torch.from_numpy(oracle.weighted_block_average(q, a[:, None], f)))
             local["area"].append(torch.from_numpy(oracle.block_sum(a, f)))
         shapes = {"q": ((nz,), ny, nx, f), "area": ((), ny, nx, f)}
-        everywhere = case.endswith("(all ranks)")
-        gathered = S.gather_coarse(local, shards, shapes, dst=None if everywhere else 0)
+        everywhere = case.endswith("(all ranks)") or case.endswith("(in place)")
+        if case.endswith("(in place)"):
+            # the producers write into their slot of the receive buffer, the all-gather runs in place
+            bufs = S.CoarseBuffers(shards, shapes, rank, world, "cpu")
+            assert bufs.whole.numel() == world * bufs.longest and bufs.longest % 4 == 0
+            for name, parts in local.items():
+                assert len(parts) == len(bufs.local[name])
+                for t, view in zip(parts, bufs.local[name]):
+                    assert view.shape == t.shape and view.data_ptr() >= bufs.slot().data_ptr()
+                    view.copy_(t)
+            gathered = bufs.all_gather()
+        else:
+            gathered = S.gather_coarse(local, shards, shapes, dst=None if everywhere else 0)
         if everywhere:
             assert gathered is not None                     # one all-gather: every rank holds every shard
         if rank == 0:
@@ -82,7 +93,8 @@ def _worker(rank, world, port, n_time, n_tile, case, result_file):
 
 @pytest.mark.parametrize("n_time,n_tile,case", [(4, 6, "by time"), (3, 6, "ragged by time"),
                                                 (1, 6, "by tile"), (1, 1, "by row band"),
-                                                (1, 6, "by tile (all ranks)"), (1, 5, "by row band across tiles (all ranks)")])
+                                                (1, 6, "by tile (all ranks)"), (1, 5, "by row band across tiles (all ranks)"),
+                                                (1, 5, "by row band across tiles (in place)"), (3, 6, "ragged by time (in place)")])
 def test_world_size_2_gloo_matches_unsharded(tmp_path, n_time, n_tile, case):
     result_file = str(tmp_path / "ok.npy")
     mp.spawn(_worker, args=(2, _free_port(), n_time, n_tile, case, result_file), nprocs=2, join=True)
