@@ -201,12 +201,25 @@ def config4(ctx, n=3072, n_tile=6, band=768, f=8):
         unit_outs = [[slot[u * per_unit + v * NZ * hc:u * per_unit + (v + 1) * NZ * hc].view(cshape) for v in range(nout + 1)]
                      for u in range(len(mine))]
 
+        comm = torch.cuda.Stream(dev) if fused == "broadcast" else None
+        done = [torch.cuda.Event() for _ in unit_outs]
+
         def step():
             k_ev[0].record()
-            for o in unit_outs:
+            cur = torch.cuda.current_stream(dev)
+            if comm is not None:
+                handle.barrier()                    # nobody still reads the previous step's values from my copy
+            for u, o in enumerate(unit_outs):
                 ops.pressure_level_average(fields, delp, area, f, outs=o[:nout], delp_coarse_out=o[nout], replica_offsets=offs,
-                                           multicast_offset=mc)
+                                           multicast_offset=mc if comm is None else None)
+                if comm is not None:                # this unit's values to every GPU, under the next unit's kernels
+                    done[u].record(cur)
+                    comm.wait_event(done[u])
+                    with torch.cuda.stream(comm):
+                        ops.multicast_store(slot[u * per_unit:(u + 1) * per_unit], mc)
             k_ev[1].record()
+            if comm is not None:
+                cur.wait_stream(comm)
             if handle is not None:
                 handle.barrier()
             elif ctx.world > 1:
@@ -264,6 +277,7 @@ def config4(ctx, n=3072, n_tile=6, band=768, f=8):
     if ctx.world > 1:
         if len(units) % ctx.world == 0:
             paths["nccl_all_gather_per_unit_overlapped"] = run_pipelined()
+        paths["nvls_broadcast_kernel_per_unit_overlapped"] = run("broadcast")
         paths["fused_multicast_stores"] = run("multicast")
         if ctx.world == 2 or "ms_per_step" not in paths["fused_multicast_stores"]:
             paths["fused_peer_stores"] = run("peers")
@@ -292,6 +306,12 @@ _EXCHANGE_OPS = {
     "nccl_all_gather_in_place": "ncclAllGather in place (dist.all_gather_into_tensor, one per step; the kernels write into the send slot)",
     "nccl_all_gather_per_unit_overlapped": "ncclAllGather in place, one per (tile, band) unit on a side stream under the next unit's kernels "
                                            "(dist.all_gather_into_tensor; the kernels write into the send slots)",
+    "nvls_broadcast_kernel_per_unit_overlapped": "own NVLS all-gather, one per (tile, band) unit on a side stream under the next unit's kernels: the "
+                                                 "unit's slice of the rank's slot is stored to the multicast mapping of the symmetric output buffer "
+                                                 "(cg_multicast_store: multimem.st, 512 contiguous bytes per warp instruction), barriers at both ends",
+    "nvls_broadcast_kernel": "own NVLS all-gather: after the kernels every rank stores its slot of the symmetric output buffer to the buffer's "
+                             "multicast mapping (cg_multicast_store: multimem.st, 512 contiguous bytes per warp instruction, the NVSwitch "
+                             "writes all GPUs' copies), device-side barriers before and after",
     "fused_multicast_stores": "fused: the kernel stores every coarse value ONCE to the NVLS multicast mapping of the symmetric output "
                               "buffer (multimem.st, the NVSwitch writes all GPUs' copies; cg_pressure_level_average_replicated), "
                               "then one device-side barrier",
@@ -345,7 +365,7 @@ def strong_config2(ctx, inp, n=384, n_tile=6, f=8):
                 ops.pressure_level_average(fields, delp, area, f, outs=o[:-1], delp_coarse_out=o[-1], replica_offsets=offs,
                                            multicast_offset=mc)
             k_ev[1].record()
-            result["g"] = bufs.barrier() if fused else bufs.all_gather()
+            result["g"] = bufs.multicast_gather() if fused == "broadcast" else bufs.barrier() if fused else bufs.all_gather()
             k_ev[2].record()
         return step
 
@@ -381,6 +401,7 @@ def strong_config2(ctx, inp, n=384, n_tile=6, f=8):
 
     paths = OrderedDict([("nccl_all_gather_in_place", run(False))])
     if ctx.world > 1:
+        paths["nvls_broadcast_kernel"] = run("broadcast")
         paths["fused_multicast_stores"] = run("multicast")
         if ctx.world == 2 or "ms_per_step" not in paths["fused_multicast_stores"]:
             paths["fused_peer_stores"] = run("peers")        # (7 small NVLink stores per value at N = 8: slower than NCCL)

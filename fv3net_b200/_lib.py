@@ -46,6 +46,7 @@ SIGNATURES = {
                                        _vp, _l, _vp]),
     "cg_pressure_level_average_replicated": (_i, [_vp, _pp, _i, _vp, _vp, _vp, _l, _i, _i, _i, _i, _i, _d,
                                                   _i, _i, _c.POINTER(_c.c_longlong), _vp, _l, _vp]),
+    "cg_multicast_store": (_i, [_vp, _c.c_longlong, _l, _vp]),
     "cg_area_above_fine_surface": (_i, [_vp, _vp, _vp, _vp, _l, _i, _i, _i, _i, _d, _vp]),
     "cg_static_scratch_bytes": (_l, []),
     "cg_area_above_fine_surface_static": (_i, [_vp, _vp, _vp, _vp, _l, _i, _i, _i, _i, _d, _vp]),

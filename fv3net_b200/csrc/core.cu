@@ -87,3 +87,36 @@ extern "C" int cg_device_info(int *sm, int *cc, long *total_mem_bytes)
     if (total_mem_bytes) *total_mem_bytes = (long)p.totalGlobalMem;
     return CG_OK;
 }
+
+// ---- NVLS broadcast of a buffer region (the exchange step of the sharded pressure-level path) -------------------
+// Every 16 bytes of [src, src + nbytes) are stored once to src + mc_offset, the multicast mapping of the symmetric
+// buffer src lives in: the NVSwitch writes them into every GPU's copy (this GPU's included).  Warps store 512
+// contiguous bytes per instruction, so the fabric sees full-size packets - unlike stores issued from inside the
+// compute kernel, which can only make 16 bytes contiguous.
+namespace cg {
+__global__ void __launch_bounds__(256) multicast_store_kernel(const uint4 *__restrict__ src, long long mc_offset, long n16)
+{
+    const long stride = (long)gridDim.x * blockDim.x;
+    for (long i = blockIdx.x * (long)blockDim.x + threadIdx.x; i < n16; i += stride) {
+        const uint4 v = src[i];
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"((const char *)(src + i) + mc_offset),
+                     "f"(__uint_as_float(v.x)), "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+                     : "memory");
+    }
+}
+}  // namespace cg
+
+extern "C" int cg_multicast_store(const void *src, long long mc_offset, long nbytes, void *stream)
+{
+    CG_REQUIRE(src, "null pointer");
+    CG_REQUIRE(nbytes >= 0 && nbytes % 16 == 0 && ((uintptr_t)src & 15) == 0 && mc_offset % 16 == 0,
+               "cg_multicast_store moves 16-byte pieces: pointer, offset and size must be multiples of 16");
+    if (nbytes == 0) return CG_OK;
+    const long n16 = nbytes / 16;
+    long blocks = (n16 + 255) / 256;
+    const long cap = 8L * cg::sm_count();
+    if (blocks > cap) blocks = cap;
+    cg::multicast_store_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((const uint4 *)src, mc_offset, n16);
+    CG_LAUNCH_CHECK("cg_multicast_store");
+    return CG_OK;
+}

@@ -319,6 +319,14 @@ def pressure_level_average(fields, delp, area, f, mask_below=False, toa=300.0, w
     return outs, dcoarse
 
 
+def multicast_store(t, mc_offset):
+    """Broadcast the contiguous tensor `t` (a region of a symmetric buffer) into every GPU's copy of that buffer:
+    one multimem.st per 16 bytes to `t`'s address + mc_offset (sharding.CoarseBuffers.multicast_offset())."""
+    if not t.is_contiguous():
+        raise ValueError("multicast_store needs a contiguous tensor")
+    L.check(L.lib().cg_multicast_store(_p(t), int(mc_offset), t.numel() * t.element_size(), _stream()))
+
+
 def area_above_fine_surface(delp, delp_coarse, area, f, toa=300.0):
     n_outer, nz, ny, nx = delp.shape
     out = torch.empty((n_outer, nz, ny // f, nx // f), dtype=torch.float32, device=delp.device)

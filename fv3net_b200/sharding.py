@@ -247,6 +247,20 @@ class CoarseBuffers:
             self.handle.barrier()
         return self.views()
 
+    def multicast_gather(self):
+        """The all-gather as ONE small kernel per rank (symmetric=True on a box with NVLS): this rank's slot is stored
+        to the multicast mapping of the buffer (ops.multicast_store: 512 contiguous bytes per warp instruction, the
+        NVSwitch writes every GPU's copy), then the device-side barrier.  Returns the views of `all_gather`."""
+        from . import ops
+
+        mc = self.multicast_offset()
+        if mc is None:
+            raise RuntimeError("no multicast mapping (NVLS) for the symmetric buffer")
+        self.handle.barrier()                  # nobody is still reading the previous step's values from my copy
+        ops.multicast_store(self.slot(), mc)
+        self.handle.barrier()
+        return self.views()
+
     def all_gather(self, group=None):
         """In place: afterwards every rank's `whole` holds every slot.  Returns {name: {shard: view}}."""
         if self.world > 1:

@@ -207,6 +207,13 @@ int cg_pressure_level_average_replicated(const cg_field *fields, float *const *o
                                          int replica_kind, int n_replicas, const long long *replica_offsets,
                                          void *workspace, long workspace_bytes, void *stream);
 
+/* The exchange step of that sharded path as a stand-alone NVLS broadcast, no counterpart in the reference: every 16
+ * bytes of [src, src + nbytes) are stored once (multimem.st) to src + mc_offset, the multicast mapping of the
+ * symmetric buffer that src lies in, and the NVSwitch writes them into every GPU's copy.  With every rank
+ * broadcasting its own slot this is an all-gather in one small kernel per rank plus a barrier; pointer, offset and
+ * size are multiples of 16. */
+int cg_multicast_store(const void *src, long long mc_offset, long nbytes, void *stream);
+
 /* budgets.py:62-77 area_above_fine_surface: block sum of area where the coarse
  * log-midpoint pressure (upsampled) <= fine surface pressure. */
 int cg_area_above_fine_surface(const float *delp, const float *delp_coarse, const float *area,

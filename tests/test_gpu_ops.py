@@ -274,3 +274,20 @@ def test_interp_to_edges(ops, axis, dt):
     c = rng.uniform(3, 5, (6, 3, 8, 8)).astype(dt)
     got = host(ops.interp_to_edges(dev(c), axis))
     np.testing.assert_array_equal(got, recipes.interp_to_edges(c, axis).astype(dt))
+
+
+def test_multicast_store_copies_16_byte_pieces(ops):
+    """cg_multicast_store: every 16 bytes of a region stored once at region + offset.  On a multi-GPU box the offset
+    leads to the NVLS multicast mapping of a symmetric buffer (bench.py's strong-scaling exchange checks that end
+    bit for bit); here it leads to plain memory of the same device."""
+    n = 4 * 100003
+    whole = torch.full((2 * n + 8,), -3.0, dtype=torch.float32, device="cuda")
+    whole[:n] = torch.arange(n, dtype=torch.float32, device="cuda")
+    ops.multicast_store(whole[:n], 4 * (n + 4))
+    w = whole.cpu().numpy()
+    np.testing.assert_array_equal(w[n + 4:2 * n + 4], np.arange(n, dtype=np.float32))
+    assert (w[n:n + 4] == -3.0).all() and (w[2 * n + 4:] == -3.0).all()
+    with pytest.raises(ValueError):
+        ops.multicast_store(whole[:n], 4)                      # not a multiple of 16
+    with pytest.raises(ValueError):
+        ops.multicast_store(whole[1:n + 1], 16)                # misaligned region
