@@ -15,6 +15,7 @@ Every record: `ms_per_step` = CUDA events on the launching stream, barrier + syn
 over ranks; `value` = fine-grid cells of every coarse-grained field per second, all ranks; `roofline` =
 algorithmic bytes of the rank's kernels / their time against the measured copy bandwidth.
 """
+import os
 from collections import OrderedDict
 
 import torch
@@ -193,10 +194,13 @@ def config4(ctx, n=3072, n_tile=6, band=768, f=8):
                     mc -= int(gathered.data_ptr())
             else:
                 gathered = torch.zeros(ctx.world * longest, device=dev)
+            err = None
         except Exception as e:
             if not fused:
                 raise
-            return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+            err = f"{type(e).__name__}: {e}"[:200]
+        if fused and ctx.max_over_ranks([0.0 if err is None else 1.0])[0] != 0.0:        # every rank takes the same way out
+            return {"unavailable": err or "another rank could not map the symmetric buffer"}
         slot = gathered[ctx.rank * longest:(ctx.rank + 1) * longest]
         unit_outs = [[slot[u * per_unit + v * NZ * hc:u * per_unit + (v + 1) * NZ * hc].view(cshape) for v in range(nout + 1)]
                      for u in range(len(mine))]
@@ -277,10 +281,11 @@ def config4(ctx, n=3072, n_tile=6, band=768, f=8):
     if ctx.world > 1:
         if len(units) % ctx.world == 0:
             paths["nccl_all_gather_per_unit_overlapped"] = run_pipelined()
-        paths["nvls_broadcast_kernel_per_unit_overlapped"] = run("broadcast")
-        paths["fused_multicast_stores"] = run("multicast")
-        if ctx.world == 2 or "ms_per_step" not in paths["fused_multicast_stores"]:
-            paths["fused_peer_stores"] = run("peers")
+        if _FUSED_EXCHANGE:
+            paths["nvls_broadcast_kernel_per_unit_overlapped"] = run("broadcast")
+            paths["fused_multicast_stores"] = run("multicast")
+            if ctx.world == 2 or "ms_per_step" not in paths["fused_multicast_stores"]:
+                paths["fused_peer_stores"] = run("peers")
     good = {k: v for k, v in paths.items() if "ms_per_step" in v and (ctx.world == 1 or v["slot_checksums_agree_on_all_ranks"])}
     which = min(good, key=lambda k: good[k]["ms_per_step"])
     best = good[which]
@@ -302,6 +307,8 @@ def config4(ctx, n=3072, n_tile=6, band=768, f=8):
     return rec
 
 
+# CG_BENCH_EXCHANGE=nccl: time the NCCL forms of the exchange only (no symmetric memory, no NVLS stores)
+_FUSED_EXCHANGE = os.environ.get("CG_BENCH_EXCHANGE", "all") != "nccl"
 _EXCHANGE_OPS = {
     "nccl_all_gather_in_place": "ncclAllGather in place (dist.all_gather_into_tensor, one per step; the kernels write into the send slot)",
     "nccl_all_gather_per_unit_overlapped": "ncclAllGather in place, one per (tile, band) unit on a side stream under the next unit's kernels "
@@ -382,10 +389,13 @@ def strong_config2(ctx, inp, n=384, n_tile=6, f=8):
         try:
             bufs = S.CoarseBuffers(shards, shapes, ctx.rank, ctx.world, dev, symmetric=bool(fused))
             step = make_step(bufs, fused)
+            err = None
         except Exception as e:                       # no peer-mapped memory on this box: the NCCL path is the product
             if not fused:
                 raise
-            return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+            err = f"{type(e).__name__}: {e}"[:200]
+        if fused and ctx.max_over_ranks([0.0 if err is None else 1.0])[0] != 0.0:        # every rank takes the same way out
+            return {"unavailable": err or "another rank could not map the symmetric buffer"}
         step()
         torch.cuda.synchronize()
         ok = True
@@ -400,7 +410,7 @@ def strong_config2(ctx, inp, n=384, n_tile=6, f=8):
         return {"ms_per_step": ms, "kernel_ms": kernel_ms, "exchange_ms": x_ms, "bit_identical_to_unsharded": ok}
 
     paths = OrderedDict([("nccl_all_gather_in_place", run(False))])
-    if ctx.world > 1:
+    if ctx.world > 1 and _FUSED_EXCHANGE:
         paths["nvls_broadcast_kernel"] = run("broadcast")
         paths["fused_multicast_stores"] = run("multicast")
         if ctx.world == 2 or "ms_per_step" not in paths["fused_multicast_stores"]:
