@@ -616,10 +616,12 @@ __device__ __forceinline__ void hot_step(Pair &s, uint32_t recp, u64 qn, uint32_
     const u64 df2 = fma2(r.E1, dqn, mul2(r.E2, dq1));                   // layer t-1, mappm.f90:661
     u64 dcn, mkn, xl, yl;
     if (!NS) {
-        float dfa, dfb, d1a, d1b, dna, dnb, saa, sab, sda, sdb;
+        float dfa, dfb, d1a, d1b, dna, dnb, saa, sab;
         upk(df2, dfa, dfb); upk(dq1, d1a, d1b); upk(dqn, dna, dnb);
-        upk(add2(dq1, dqn), saa, sab); upk(sub2(dq1, dqn), sda, sdb);
-        mkn = pk(gt01(fabsf(saa), fabsf(sda)), gt01(fabsf(sab), fabsf(sdb)));      // |a + b| > |a - b|  <=>  a b > 0
+        // a b > 0 from the product's sign (one packed multiply instead of a packed sum and difference; a product that
+        // underflows - both differences below 1e-19 - gives slope 0 where the compare form gives one of that size)
+        upk(mul2(dq1, dqn), saa, sab);
+        mkn = pk(gt01(saa, 0.f), gt01(sab, 0.f));
         dcn = mul2(pk(absmin3_sign(dfa, d1a, dna, d1a), absmin3_sign(dfb, d1b, dnb, d1b)), mkn);
     } else {
         dcn = slope2(df2, dq1, dqn);
