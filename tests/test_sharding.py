@@ -42,6 +42,41 @@ def test_plan_covers_everything_once(n_time, world):
         assert all(len(r) >= 1 for r in shards)
 
 
+@pytest.mark.parametrize("n_time,world,n_tile", [(1, 8, 6), (1, 5, 6), (3, 4, 6), (1, 1, 6), (2, 3, 1)])
+def test_coarse_buffers_layout_is_the_same_on_every_rank(n_time, world, n_tile):
+    """The exchange buffer of sharding.CoarseBuffers: every rank computes the same layout from the plan alone; the slots
+    are 16-byte aligned, padded to the longest rank, and the views of all ranks' shards tile them without overlap."""
+    nz, ny, nx, f = 3, 32, 16, 4
+    shards = S.plan(n_time, world, n_tile=n_tile, ny=ny, factor=f)
+    shapes = {"q": ((nz,), ny, nx, f), "area": ((), ny, nx, f)}
+    layouts = []
+    for rank in range(world):
+        b = S.CoarseBuffers(shards, shapes, rank, world, "cpu")
+        assert b.whole.numel() == world * b.longest and (b.longest * 4) % 16 == 0
+        assert [len(b.local[k]) for k in shapes] == [len(shards[rank])] * 2
+        spans = []
+        for name, per_shard in b.views().items():
+            for s_, v in per_shard.items():
+                start = (v.data_ptr() - b.whole.data_ptr()) // 4
+                spans.append((start, start + v.numel(), name, s_))
+                assert tuple(v.shape) == tuple(S.coarse_shape(s_, shapes[name][0], ny, nx, f))
+        spans.sort()
+        for (a0, a1, *_), (b0, b1, *_) in zip(spans, spans[1:]):
+            assert a1 <= b0                                            # no two views overlap
+        for r in range(world):                                        # every view of rank r lies inside slot r
+            mine = [(a, e) for a, e, name, s_ in spans if s_ in shards[r]]
+            assert all(r * b.longest <= a and e <= (r + 1) * b.longest for a, e in mine)
+        for name in shapes:                                           # this rank's own views are the plan's, in order
+            for v, s_ in zip(b.local[name], shards[rank]):
+                assert v.data_ptr() == b.views()[name][s_].data_ptr()
+        layouts.append([(a, e, name, tuple(s_)) for a, e, name, s_ in spans])
+        assert b.peer_offsets() == [] and b.multicast_offset() is None     # not symmetric memory
+    assert all(l == layouts[0] for l in layouts)
+    total = sum(e - a for a, e, *_ in layouts[0])
+    every = sum(int(np.prod(S.coarse_shape(s_, shapes[k][0], ny, nx, f))) for k in shapes for r in shards for s_ in r)
+    assert total == every
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
